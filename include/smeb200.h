@@ -1,0 +1,215 @@
+/*
+ * smeb200.h — C-ABI of the B200-native Pixel simulator (libsmeb200.so).
+ *
+ * This is the drop-in boundary for ONE path of Spatial Model Editor: the Pixel
+ * (finite-difference, explicit Runge-Kutta) simulator that lives behind
+ * sme::simulate::BaseSim (reference core/simulate/src/basesim.hpp:15-55) and is
+ * implemented there by PixelSim (pixelsim.cpp) and CudaPixelSim
+ * (cudapixelsim.cpp).  An SME-side adapter class (adapter/b200pixelsim.hpp)
+ * fills `smeb200_problem` from sme::model::Model exactly as
+ * cudapixelsim.cpp:857-1150 does and forwards every BaseSim virtual to one of
+ * the entry points below.  Plain pointers and sizes only: no C++ types, no
+ * exceptions, no torch types.  Errors are int codes + smeb200_error().
+ *
+ * All floating point data is fp64.  Concentrations are species-interleaved
+ * ("AoS"): value of species s at voxel i is conc[i * n_species + s], voxels in
+ * the order of geometry::Compartment (z outermost, then x, then y;
+ * geometry.cpp:55-72).
+ */
+#ifndef SMEB200_H
+#define SMEB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SMEB200_ABI_VERSION 1
+
+/* mirrors sme::simulate::PixelIntegratorType (simulate_options.hpp:113-119) */
+enum smeb200_integrator {
+  SMEB200_RK101 = 0,
+  SMEB200_RK212 = 1,
+  SMEB200_RK323 = 2,
+  SMEB200_RK435 = 3
+};
+
+/* membrane face directions, geometry::Membrane::FACE_DIRECTION
+ * (geometry.cpp:18-36): sign of (voxel B - voxel A), x first, then y, then z */
+enum smeb200_face { SMEB200_XP = 0, SMEB200_XM, SMEB200_YP, SMEB200_YM,
+                    SMEB200_ZP, SMEB200_ZM };
+
+/* bits of smeb200_problem.unsupported: features of the CPU PixelSim that the
+ * reference GPU backend rejects in its constructor (cudapixelsim.cpp:789-809,
+ * pixelsim_common.hpp:80-121).  The adapter sets them; smeb200_create then
+ * fails with the same message text as the reference. */
+enum smeb200_unsupported {
+  SMEB200_HAS_CROSS_DIFFUSION = 1,
+  SMEB200_HAS_TIME_OR_SPACE_DEPENDENCE = 2,
+  SMEB200_HAS_NON_SPATIAL_SPECIES = 4,
+  SMEB200_HAS_NON_UNIFORM_DIFFUSION = 8,
+  SMEB200_HAS_NON_UNIT_STORAGE = 16
+};
+
+/* One geometry::Compartment + SimCompartment (pixelsim_impl.hpp:58-322). */
+typedef struct smeb200_compartment {
+  const char *id;          /* compartment id (diagnostics only) */
+  uint64_t n_voxels;       /* Compartment::nVoxels() */
+  uint32_t n_species;      /* simulated species in this compartment */
+  /* Geometry, one of:
+   *  - box: nn == NULL and box_nx*box_ny*box_nz == n_voxels: the compartment
+   *    fills its whole image; neighbours are implicit (zero-flux Neumann at
+   *    the faces, i.e. missing neighbour = own index, geometry.cpp:98-110);
+   *  - voxel list: nn[6*i + k] = index of the +x,-x,+y,-y,+z,-z neighbour of
+   *    voxel i (own index if outside the compartment), as uint32 like the
+   *    reference GPU backend (cudapixelsim.cpp:877-890). */
+  int32_t box_nx, box_ny, box_nz;
+  const uint32_t *nn;
+  /* optional [3*n_voxels] image coordinates (x, y, z) of each voxel, used for
+   * errorImages (pixelsim_impl.cpp:794-824) and for z-slab partitioning;
+   * may be NULL (implied for a box) */
+  const int32_t *voxels;
+  /* [3*n_species] dimensionless diffusion D/dx^2, D/dy^2, D/dz^2 per species
+   * (pixelsim_impl.cpp:236-237) */
+  const double *diffusion;
+  /* [n_voxels*n_species] initial (or restart) concentrations */
+  const double *conc0;
+  /* n_species CUDA-C expressions for d(species)/dt from reactions, written in
+   * terms of sme_var_0 .. sme_var_{n_species-1}: exactly the strings
+   * Symbolic::cudaCode(i) returns after Symbolic::relabel
+   * (cudapixelsim.cpp:108-136) */
+  const char *const *expressions;
+  const char *const *species_names; /* optional, for the adaptive-failure text */
+} smeb200_compartment;
+
+/* One geometry::Membrane + SimMembrane (pixelsim_impl.cpp:929-1047). */
+typedef struct smeb200_membrane {
+  const char *id;
+  int32_t comp_a, comp_b;  /* indices into compartments[], -1 if not simulated */
+  /* per face direction: n_pairs[d] (ixA, ixB) uint32 pairs, in the order of
+   * Membrane::getFaceIndexPairs(d) (geometry.cpp:165-172) */
+  uint64_t n_pairs[6];
+  const uint32_t *pairs[6];
+  /* voxel length in the flux direction per face (pixelsim_common.hpp:39-54) */
+  double flux_length[6];
+  /* (SA + SB) CUDA-C expressions in sme_var_0..sme_var_{SA+SB-1}: variables
+   * are [species of A | species of B], results [0,SA) go to A and [SA,SA+SB)
+   * to B (pixelsim_impl.cpp:960-973, 84-111); already scaled by volOverL3 */
+  const char *const *expressions;
+} smeb200_membrane;
+
+typedef struct smeb200_problem {
+  uint32_t abi_version;    /* SMEB200_ABI_VERSION */
+  uint32_t n_compartments;
+  const smeb200_compartment *compartments;
+  uint32_t n_membranes;
+  const smeb200_membrane *membranes;
+  /* PixelOptions (simulate_options.hpp:160-200) */
+  int32_t integrator;      /* enum smeb200_integrator */
+  double max_err_abs;      /* PixelIntegratorError::abs */
+  double max_err_rel;      /* PixelIntegratorError::rel */
+  double max_timestep;
+  /* geometry image size, for errorImages */
+  int32_t image_nx, image_ny, image_nz;
+  uint32_t unsupported;    /* enum smeb200_unsupported bits */
+  int32_t device;          /* CUDA device ordinal; -1 = current device */
+  /* z-slab decomposition of box compartments over `n_ranks` processes, one
+   * GPU each (0/1 = single GPU).  See smeb200_slab_* below. */
+  int32_t rank, n_ranks;
+  /* kernel variant: 0 = auto, 1 = direct-gather kernels only,
+   * 2 = TMA-staged z-marching kernel for box compartments */
+  int32_t kernel_variant;
+  uint32_t reserved[7];
+} smeb200_problem;
+
+typedef struct smeb200_sim smeb200_sim;
+
+/* number of usable CUDA devices, 0 if none; never fails */
+int smeb200_device_count(void);
+
+/* Constructor (PixelSim::PixelSim / CudaPixelSim::CudaPixelSim).  Like the
+ * reference constructors it never throws: on failure a simulator object is
+ * still returned whose smeb200_error() is non-empty and whose run() returns 0
+ * (cudapixelsim.cpp:1156-1167,1621-1623).  Returns 0 on success, non-zero if
+ * the simulator carries an error. *out is NULL only if p or out is NULL. */
+int smeb200_create(const smeb200_problem *p, smeb200_sim **out);
+void smeb200_destroy(smeb200_sim *sim);
+
+/* BaseSim::run (basesim.hpp:24-27; pixelsim.cpp:423-471): integrate for
+ * `time`, returns the number of accepted steps.  timeout_ms < 0 = none.
+ * stop_cb (may be NULL) is polled once per step; non-zero = stop. */
+size_t smeb200_run(smeb200_sim *sim, double time, double timeout_ms,
+                   int (*stop_cb)(void *user), void *user);
+
+/* BaseSim::getConcentrations (host mirror, valid until the next run/destroy) */
+int smeb200_get_concentrations(smeb200_sim *sim, size_t compartment,
+                               const double **data, size_t *n);
+/* PixelSim::getDcdt (pixelsim.cpp:481-484): last evaluated dc/dt */
+int smeb200_get_dcdt(smeb200_sim *sim, size_t compartment, const double **data,
+                     size_t *n);
+/* PixelSim::getLowerOrderConcentration (pixelsim.cpp:486-490) */
+int smeb200_get_lower_order(smeb200_sim *sim, size_t compartment,
+                            size_t species, size_t pixel, double *value);
+/* BaseSim::getConcentrationPadding — always 0 on this backend */
+size_t smeb200_get_concentration_padding(const smeb200_sim *sim);
+/* restart: overwrite the state of one compartment (SimCompartment::
+ * setConcentrations, used with SimulationData, pixelsim.cpp:399-406) */
+int smeb200_set_concentrations(smeb200_sim *sim, size_t compartment,
+                               const double *data, size_t n);
+
+/* BaseSim::errorMessage / setCurrentErrormessage */
+const char *smeb200_error(const smeb200_sim *sim);
+void smeb200_set_error(smeb200_sim *sim, const char *msg);
+/* BaseSim::errorImages: image_nz RGB32 images of image_nx*image_ny pixels
+ * (0x00RRGGBB, row-major, y = 0 at the top like QImage), empty (n = 0) unless
+ * the adaptive controller failed (pixelsim.cpp:236-253) */
+int smeb200_error_images(const smeb200_sim *sim, const uint32_t **data,
+                         size_t *n);
+/* BaseSim::getStopRequested / setStopRequested (thread-safe) */
+int smeb200_get_stop_requested(const smeb200_sim *sim);
+void smeb200_set_stop_requested(smeb200_sim *sim, int stop);
+
+/* controller state (PixelSimBase, pixelsim_base.hpp:40-49) */
+double smeb200_get_next_timestep(const smeb200_sim *sim);
+void smeb200_set_next_timestep(smeb200_sim *sim, double dt);
+size_t smeb200_get_discarded_steps(const smeb200_sim *sim);
+double smeb200_get_max_stable_timestep(const smeb200_sim *sim);
+
+/* ---- measurement hooks (bench.py; not part of BaseSim) ------------------ */
+/* Take `n_steps` steps of fixed size dt without host-side control: no
+ * download, state stays resident in HBM.  Returns device milliseconds for
+ * the n_steps (CUDA events on the launching stream), <0 on error. */
+double smeb200_bench_steps(smeb200_sim *sim, double dt, size_t n_steps);
+/* kernels launched since construction */
+uint64_t smeb200_launch_count(const smeb200_sim *sim);
+/* device time of the dominant stage kernel over the last bench/run window:
+ * sum of ms and number of launches (CUDA events, only if profiling enabled
+ * with smeb200_set_kernel_timing(sim, 1)) */
+void smeb200_set_kernel_timing(smeb200_sim *sim, int enable);
+int smeb200_get_kernel_timing(const smeb200_sim *sim, double *total_ms,
+                              uint64_t *launches);
+/* generated CUDA source of the model module (for inspection / tests) */
+const char *smeb200_kernel_source(const smeb200_sim *sim);
+
+/* ---- multi-GPU z-slabs (one process per GPU) ---------------------------- */
+/* Each rank owns planes [z0, z1) of every box compartment plus one ghost
+ * plane per side.  The halo planes live in device buffers exported as CUDA
+ * IPC handles; peers map them and the stage kernels store boundary planes
+ * straight into the neighbour's ghost plane over NVLink.  The host passes the
+ * opaque handle blobs between ranks (bench.py uses torch.distributed).    */
+size_t smeb200_slab_handle_bytes(const smeb200_sim *sim);
+int smeb200_slab_export(smeb200_sim *sim, void *blob);
+int smeb200_slab_connect(smeb200_sim *sim, const void *blob_prev,
+                         const void *blob_next);
+/* error-norm exchange for the adaptive controller: the host supplies an
+ * allreduce-max over ranks for 2 doubles (NCCL/gloo in the caller) */
+typedef void (*smeb200_allreduce_max_fn)(double *values, int n, void *user);
+void smeb200_set_allreduce_max(smeb200_sim *sim, smeb200_allreduce_max_fn fn,
+                               void *user);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SMEB200_H */

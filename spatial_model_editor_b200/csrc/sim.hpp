@@ -1,0 +1,163 @@
+// B200PixelSim host side: the controller and device-state owner behind the
+// C-ABI of include/smeb200.h.  Mirrors the member layout and control flow of
+// sme::simulate::PixelSim / PixelSimBase (reference pixelsim.cpp:423-471,
+// 207-270, 122-205; pixelsim_base.hpp:40-49) — the loops are the reference's,
+// the per-stage work is one fused kernel launch per compartment.
+#pragma once
+
+#include "../../include/smeb200.h"
+#include "cuda_api.hpp"
+#include <atomic>
+#include <cstdint>
+#include <limits>
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace smeb200 {
+
+// host mirror of the device-side SmebStageArgs<S> header (device_kernels.cuh);
+// the D[3*S] table follows directly.
+struct StageArgsHost {
+  const double *cin;
+  const double *c0;
+  const double *s2in;
+  double *s2out;
+  double *cout;
+  double *dcdt_out;
+  const uint32_t *nn;
+  unsigned long long *err;
+  uint32_t n;
+  uint32_t nx, ny, nz;
+  uint32_t z_lo_ghost, z_hi_ghost;
+  uint32_t flags;
+  uint32_t pad_;
+  double g1, g2, g3, bdt, delta;
+  double cF, s2F, s3F, eps;
+  double D[3 * 64];
+};
+
+struct MembEntryHost {
+  uint32_t partner;
+  uint32_t info;
+};
+
+// one Runge-Kutta stage in terms of buffer roles
+enum Role : int { CUR = 0, RA = 1, RB = 2, RS = 3 };
+struct StageDesc {
+  int cin{CUR}, cout{RA};
+  bool useC0{false};
+  int s2mode{0}; // 0 none, 1 starts at zero, 2 read from CUR, 3 read from RS
+  bool writeS2{false};
+  double g1{1}, g2{0}, g3{0}, beta{1}, delta{0};
+  bool final{false}, lowerIsCin{false}, clampOut{false};
+  double cF{0}, s2F{0}, s3F{0};
+};
+
+struct CompartmentState {
+  std::string id;
+  uint64_t n{0};
+  uint32_t S{0};
+  bool box{false};
+  uint32_t nx{0}, ny{0}, nz{0};
+  std::vector<std::string> speciesNames;
+  std::vector<double> D;
+  std::vector<int32_t> voxels;
+  int nbuf{0};
+  double *buf[4]{nullptr, nullptr, nullptr, nullptr};
+  int role[4]{0, 1, 2, 3};
+  bool curNeedsClamp{false};
+  uint32_t *dNn{nullptr};
+  uint32_t nMvox{0};
+  uint32_t *dMvox{nullptr};
+  uint32_t *dMstart{nullptr};
+  MembEntryHost *dEnt{nullptr};
+  CUfunction kStage{nullptr};
+  CUfunction kMemb{nullptr};
+  // host mirrors
+  double *hostConc{nullptr}; // pinned
+  bool hostStale{true};
+  std::vector<double> hostDcdt;
+  std::vector<double> hostLower;
+  bool dcdtStale{true}, lowerStale{true};
+  double *scratch{nullptr};
+  // record of the last attempted step's final stage (getDcdt / lower order)
+  bool haveLast{false};
+  StageArgsHost last{};
+  uint32_t lastClampMask{0};
+  const double *lastCin{nullptr};
+};
+
+class Sim {
+public:
+  explicit Sim(const smeb200_problem &p);
+  ~Sim();
+  Sim(const Sim &) = delete;
+  Sim &operator=(const Sim &) = delete;
+
+  std::size_t run(double time, double timeoutMs, int (*stopCb)(void *),
+                  void *user);
+  const double *getConcentrations(std::size_t comp, std::size_t *n);
+  const double *getDcdt(std::size_t comp, std::size_t *n);
+  double getLowerOrder(std::size_t comp, std::size_t species, std::size_t pixel);
+  void setConcentrations(std::size_t comp, const double *data, std::size_t n);
+  double benchSteps(double dt, std::size_t nSteps);
+
+  std::string errorMessage;
+  bool ctorFailed{false};
+  std::vector<uint32_t> errorImages;
+  std::atomic<bool> stopRequested{false};
+  // PixelSimBase state (pixelsim_base.hpp:40-49)
+  double maxStableTimestep{std::numeric_limits<double>::max()};
+  std::size_t discardedSteps{0};
+  int integrator{SMEB200_RK212};
+  double errMaxAbs{std::numeric_limits<double>::max()};
+  double errMaxRel{0.005};
+  double maxTimestep{std::numeric_limits<double>::max()};
+  double nextTimestep{1e-7};
+  double epsilon{1e-14};
+
+  uint64_t launchCount{0};
+  bool kernelTiming{false};
+  double kernelMs{0};
+  uint64_t kernelLaunchesTimed{0};
+  std::string kernelSource;
+  std::size_t nCompartments() const { return comps.size(); }
+  smeb200_allreduce_max_fn allreduceMax{nullptr};
+  void *allreduceUser{nullptr};
+
+private:
+  void build(const smeb200_problem &p);
+  void generateSource(const smeb200_problem &p);
+  void compileModule();
+  void setupMembranes(const smeb200_problem &p);
+  void makePlan();
+  void bindDevice() const;
+  void doStep(double dt);           // all stages of one RK step
+  void launchStage(const StageDesc &sd, double dt, bool dcdtOnly);
+  void rotateAfterAccept();
+  void readError(double &eabs, double &erel);
+  double doRK101(double dt);
+  double doRKAdaptive(double dtMax);
+  void plotRKError(double relMax, std::string &problemSpecies);
+  void evaluateLastDcdt();
+  void flushTimers();
+
+  int device{0};
+  cudaStream_t stream{nullptr};
+  CUmodule module{nullptr};
+  CUfunction kLower{nullptr}, kClampCopy{nullptr};
+  std::vector<CompartmentState> comps;
+  std::vector<StageDesc> plan;
+  std::vector<double> fluxLen;
+  double *dFluxLen{nullptr};
+  uint32_t nMembranes{0};
+  unsigned long long *dErr{nullptr};
+  unsigned long long *hErr{nullptr}; // pinned
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timerEvents;
+  std::size_t timerUsed{0};
+  int imageNx{0}, imageNy{0}, imageNz{0};
+  std::vector<std::string> stageNames, membNames;
+};
+
+} // namespace smeb200
