@@ -1,0 +1,866 @@
+#include "sim.hpp"
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <sstream>
+
+namespace smeb200 {
+
+// the kernel template text (device_kernels.cuh), generated at build time
+extern const char *const kDeviceKernelSource;
+
+namespace {
+
+constexpr uint32_t F_CLAMP_CIN = 1u, F_CLAMP_C0 = 2u, F_CLAMP_OUT = 4u,
+                   F_USE_C0 = 8u, F_USE_S2 = 16u, F_USE_S2IN = 32u,
+                   F_WRITE_S2 = 64u, F_FINAL = 128u, F_LOWER_IS_CIN = 256u,
+                   F_DCDT_ONLY = 512u, F_CLAMP_S2IN = 1024u;
+constexpr uint32_t MEMB_FLAG = 0x80000000u;
+constexpr unsigned BLOCK = 256;
+
+// RK tableaux: pixelsim_common.hpp:138-171
+namespace rk323 {
+constexpr double g1[3]{1.0, 0.25, 0.666666666666666666666};
+constexpr double g2[3]{0.0, 0.0, 0.0};
+constexpr double g3[3]{0.0, 0.75, 0.333333333333333333333};
+constexpr double beta[3]{1.0, 0.25, 0.6666666666666666666};
+constexpr double delta[3]{0.0, 0.0, 1.0};
+constexpr double finaliseFactors[3]{0.0, 2.0, -1.0};
+} // namespace rk323
+namespace rk435 {
+constexpr double g1[5]{0.0, -0.497531095840104, 1.010070514199942,
+                       -3.196559004608766, 1.717835630267259};
+constexpr double g2[5]{1.0, 1.384996869124138, 3.878155713328178,
+                       -2.324512951813145, -0.514633322274467};
+constexpr double g3[5]{0.0, 0.0, 0.0, 1.642598936063715, 0.188295940828347};
+constexpr double beta[5]{0.075152045700771, 0.211361016946069,
+                         1.100713347634329, 0.728537814675568,
+                         0.393172889823198};
+constexpr double delta[7]{1.0,
+                          0.081252332929194,
+                          -1.083849060586449,
+                          -1.096110881845602,
+                          2.859440022030827,
+                          -0.655568367959557,
+                          -0.194421504490852};
+constexpr double deltaSumReciprocal =
+    1.0 / (delta[0] + delta[1] + delta[2] + delta[3] + delta[4] + delta[5] +
+           delta[6]);
+} // namespace rk435
+
+template <typename T> T *devAlloc(std::size_t count, const char *what) {
+  void *p = nullptr;
+  check(cudaMalloc(&p, std::max<std::size_t>(count, 1) * sizeof(T)), what);
+  return static_cast<T *>(p);
+}
+
+template <typename T>
+T *devUpload(const std::vector<T> &v, cudaStream_t s, const char *what) {
+  T *p = devAlloc<T>(v.size(), what);
+  if (!v.empty()) {
+    check(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T),
+                          cudaMemcpyHostToDevice, s),
+          what);
+  }
+  return p;
+}
+
+std::string functorSource(const std::string &header, uint32_t nVars,
+                          const char *const *expressions, uint32_t nExpr) {
+  std::ostringstream s;
+  s << header;
+  s << "  static __device__ __forceinline__ void eval(double* sme_out, const "
+       "double* sme_values) {\n";
+  for (uint32_t i = 0; i < nVars; ++i) {
+    s << "    const double sme_var_" << i << " = sme_values[" << i << "];\n";
+  }
+  for (uint32_t i = 0; i < nExpr; ++i) {
+    s << "    sme_out[" << i << "] = " << expressions[i] << ";\n";
+  }
+  s << "  }\n};\n\n";
+  return s.str();
+}
+
+} // namespace
+
+void Sim::bindDevice() const { check(cudaSetDevice(device), "cudaSetDevice"); }
+
+// ---- model module: generated functors + kernel template -> NVRTC -> cubin ---
+void Sim::generateSource(const smeb200_problem &p) {
+  std::ostringstream src;
+  src << "#define SMEB_NCOMP " << std::max<uint32_t>(p.n_compartments, 1)
+      << "\n";
+  src << kDeviceKernelSource << "\n";
+  for (uint32_t c = 0; c < p.n_compartments; ++c) {
+    const auto &comp = p.compartments[c];
+    if (comp.n_species == 0) {
+      continue;
+    }
+    std::ostringstream h;
+    h << "// compartment " << c << ": " << (comp.id ? comp.id : "") << "\n";
+    h << "struct Reac" << c << " {\n  static constexpr int S = "
+      << comp.n_species << ";\n";
+    src << functorSource(h.str(), comp.n_species, comp.expressions,
+                         comp.n_species);
+  }
+  for (uint32_t m = 0; m < p.n_membranes; ++m) {
+    const auto &mb = p.membranes[m];
+    const uint32_t SA =
+        mb.comp_a >= 0 ? p.compartments[mb.comp_a].n_species : 0;
+    const uint32_t SB =
+        mb.comp_b >= 0 ? p.compartments[mb.comp_b].n_species : 0;
+    std::ostringstream h;
+    h << "// membrane " << m << ": " << (mb.id ? mb.id : "") << "\n";
+    h << "struct Memb" << m << " {\n  static constexpr int SA = " << SA
+      << ", SB = " << SB << ", CA = " << std::max(mb.comp_a, 0)
+      << ", CB = " << std::max(mb.comp_b, 0) << ";\n";
+    src << functorSource(h.str(), SA + SB, mb.expressions, SA + SB);
+  }
+  src << "template <int S_OWN>\n__device__ __forceinline__ void\n"
+         "smeb_memb_dispatch(smeb_u32 info, smeb_u32 partner, const double "
+         "*cown,\n                   const SmebMembArgs &m, double *f) {\n"
+         "  switch (info & 0xffffu) {\n";
+  for (uint32_t m = 0; m < p.n_membranes; ++m) {
+    src << "  case " << m << ":\n    smeb_memb_term<Memb" << m
+        << ", S_OWN>(info, partner, cown, m, f);\n    break;\n";
+  }
+  src << "  default:\n    break;\n  }\n}\n";
+  kernelSource = src.str();
+}
+
+void Sim::compileModule() {
+  nvrtcProgram prog{};
+  check(nvrtcCreateProgram(&prog, kernelSource.c_str(), "smeb200_model.cu", 0,
+                           nullptr, nullptr),
+        "nvrtcCreateProgram");
+  stageNames.assign(comps.size(), {});
+  membNames.assign(comps.size(), {});
+  for (std::size_t c = 0; c < comps.size(); ++c) {
+    if (comps[c].S == 0) {
+      continue;
+    }
+    std::ostringstream a, b;
+    a << "smeb_stage<Reac" << c << ", " << (comps[c].box ? 1 : 0) << ">";
+    stageNames[c] = a.str();
+    nvrtcAddNameExpression(prog, stageNames[c].c_str());
+    if (comps[c].nMvox > 0) {
+      b << "smeb_stage_memb<Reac" << c << ">";
+      membNames[c] = b.str();
+      nvrtcAddNameExpression(prog, membNames[c].c_str());
+    }
+  }
+  nvrtcAddNameExpression(prog, "smeb_lower_order");
+  nvrtcAddNameExpression(prog, "smeb_clamp_copy");
+  // sm_100a only; --fmad=false keeps every a*b+c as two IEEE operations so the
+  // result matches the CPU solver's evaluation order bit for bit.
+  const char *opts[] = {"--gpu-architecture=sm_100a", "--std=c++17",
+                        "--fmad=false", "-lineinfo", "-default-device"};
+  nvrtcResult r = nvrtcCompileProgram(prog, 5, opts);
+  if (r != NVRTC_SUCCESS) {
+    std::size_t n = 0;
+    nvrtcGetProgramLogSize(prog, &n);
+    std::string log(n, '\0');
+    nvrtcGetProgramLog(prog, log.data());
+    nvrtcDestroyProgram(&prog);
+    throw Error("Failed to compile CUDA pixel kernels with NVRTC: " + log);
+  }
+  std::size_t n = 0;
+  check(nvrtcGetCUBINSize(prog, &n), "nvrtcGetCUBINSize");
+  std::vector<char> cubin(n);
+  check(nvrtcGetCUBIN(prog, cubin.data()), "nvrtcGetCUBIN");
+  const auto &drv = DriverApi::get();
+  check(drv.ModuleLoadData(&module, cubin.data()), "cuModuleLoadData");
+  auto getFn = [&](const std::string &expr) {
+    const char *lowered = nullptr;
+    check(nvrtcGetLoweredName(prog, expr.c_str(), &lowered),
+          "nvrtcGetLoweredName");
+    CUfunction f{};
+    check(drv.ModuleGetFunction(&f, module, lowered), "cuModuleGetFunction");
+    return f;
+  };
+  for (std::size_t c = 0; c < comps.size(); ++c) {
+    if (!stageNames[c].empty()) {
+      comps[c].kStage = getFn(stageNames[c]);
+    }
+    if (!membNames[c].empty()) {
+      comps[c].kMemb = getFn(membNames[c]);
+    }
+  }
+  kLower = getFn("smeb_lower_order");
+  kClampCopy = getFn("smeb_clamp_copy");
+  nvrtcDestroyProgram(&prog);
+}
+
+// ---- membranes: per-voxel face lists in the reference accumulation order ----
+// (membranes in model order; within one membrane XP,XM,YP,YM,ZP,ZM; within one
+// direction the pair order — pixelsim.cpp:105-111, pixelsim_impl.cpp:1012-1025)
+void Sim::setupMembranes(const smeb200_problem &p,
+                         std::vector<std::vector<uint32_t>> &nnHost) {
+  nMembranes = p.n_membranes;
+  fluxLen.assign(std::size_t{6} * std::max<uint32_t>(nMembranes, 1), 1.0);
+  struct Face {
+    uint32_t voxel;
+    MembEntryHost e;
+  };
+  std::vector<std::vector<Face>> faces(comps.size());
+  for (uint32_t m = 0; m < p.n_membranes; ++m) {
+    const auto &mb = p.membranes[m];
+    if (mb.comp_a >= static_cast<int32_t>(comps.size()) ||
+        mb.comp_b >= static_cast<int32_t>(comps.size())) {
+      throw Error("membrane refers to a compartment that does not exist");
+    }
+    for (uint32_t d = 0; d < 6; ++d) {
+      fluxLen[6 * m + d] = mb.flux_length[d];
+      for (uint64_t k = 0; k < mb.n_pairs[d]; ++k) {
+        const uint32_t ixA = mb.pairs[d][2 * k];
+        const uint32_t ixB = mb.pairs[d][2 * k + 1];
+        if (mb.comp_a >= 0 && comps[mb.comp_a].S > 0) {
+          faces[mb.comp_a].push_back({ixA, {ixB, m | (0u << 16) | (d << 17)}});
+        }
+        if (mb.comp_b >= 0 && comps[mb.comp_b].S > 0) {
+          faces[mb.comp_b].push_back({ixB, {ixA, m | (1u << 16) | (d << 17)}});
+        }
+      }
+    }
+  }
+  for (std::size_t c = 0; c < comps.size(); ++c) {
+    auto &f = faces[c];
+    if (f.empty()) {
+      continue;
+    }
+    if (comps[c].box) {
+      throw Error("a box compartment (implicit neighbours) cannot have "
+                  "membrane faces: supply its neighbour list");
+    }
+    std::stable_sort(f.begin(), f.end(), [](const Face &a, const Face &b) {
+      return a.voxel < b.voxel;
+    });
+    std::vector<uint32_t> mvox, mstart;
+    std::vector<MembEntryHost> ent;
+    ent.reserve(f.size());
+    for (std::size_t k = 0; k < f.size(); ++k) {
+      if (f[k].voxel >= comps[c].n) {
+        throw Error("membrane voxel index out of range");
+      }
+      if (k == 0 || f[k].voxel != f[k - 1].voxel) {
+        mvox.push_back(f[k].voxel);
+        mstart.push_back(static_cast<uint32_t>(k));
+      }
+      ent.push_back(f[k].e);
+    }
+    mstart.push_back(static_cast<uint32_t>(f.size()));
+    comps[c].nMvox = static_cast<uint32_t>(mvox.size());
+    for (uint32_t v : mvox) {
+      nnHost[c][std::size_t{6} * v] |= MEMB_FLAG;
+    }
+    comps[c].dMvox = devUpload(mvox, stream, "upload membrane voxels");
+    comps[c].dMstart = devUpload(mstart, stream, "upload membrane offsets");
+    comps[c].dEnt = devUpload(ent, stream, "upload membrane faces");
+    check(cudaStreamSynchronize(stream), "upload membrane tables");
+  }
+  dFluxLen = devUpload(fluxLen, stream, "upload flux lengths");
+  check(cudaStreamSynchronize(stream), "upload flux lengths");
+}
+
+// ---- the integrator as a list of fused stages over rotating buffers ---------
+void Sim::makePlan() {
+  plan.clear();
+  int nbuf = 2;
+  if (integrator == SMEB200_RK101) {
+    // pixelsim.cpp:122-140
+    StageDesc s;
+    s.cin = CUR;
+    s.cout = RA;
+    s.clampOut = true;
+    plan.push_back(s);
+    nbuf = 2;
+  } else if (integrator == SMEB200_RK212) {
+    // pixelsim.cpp:142-164, pixelsim_impl.cpp:672-701
+    StageDesc s1;
+    s1.cin = CUR;
+    s1.cout = RA;
+    plan.push_back(s1);
+    StageDesc s2;
+    s2.cin = RA;
+    s2.cout = RB;
+    s2.useC0 = true;
+    s2.g1 = 0.5;
+    s2.g3 = 0.5;
+    s2.beta = 0.5;
+    s2.final = true;
+    s2.lowerIsCin = true;
+    plan.push_back(s2);
+    nbuf = 3;
+  } else if (integrator == SMEB200_RK323) {
+    // pixelsim.cpp:166-178; s2 only ever holds delta[2]*c2, so it stays in
+    // registers and the lower-order solution 2*c2 - c0 is formed in the
+    // final stage (pixelsim_impl.cpp:737-743)
+    const int cin[3] = {CUR, RA, RB};
+    const int cout[3] = {RA, RB, RA};
+    for (int i = 0; i < 3; ++i) {
+      StageDesc s;
+      s.cin = cin[i];
+      s.cout = cout[i];
+      s.useC0 = rk323::g3[i] != 0.0;
+      s.s2mode = rk323::delta[i] != 0.0 ? 1 : 0;
+      s.g1 = rk323::g1[i];
+      s.g2 = rk323::g2[i];
+      s.g3 = rk323::g3[i];
+      s.beta = rk323::beta[i];
+      s.delta = rk323::delta[i];
+      if (i == 2) {
+        s.final = true;
+        s.useC0 = true;
+        s.cF = rk323::finaliseFactors[0];
+        s.s2F = rk323::finaliseFactors[1];
+        s.s3F = rk323::finaliseFactors[2];
+      }
+      plan.push_back(s);
+    }
+    nbuf = 3;
+  } else {
+    // RK435, pixelsim.cpp:180-192: s2 is a true running sum.  After stage 0
+    // it equals c0 exactly (0 + 1*c0), so stage 1 reads it from the c0 buffer.
+    const int cin[5] = {CUR, RA, RB, RA, RB};
+    const int cout[5] = {RA, RB, RA, RB, RA};
+    for (int i = 0; i < 5; ++i) {
+      StageDesc s;
+      s.cin = cin[i];
+      s.cout = cout[i];
+      s.useC0 = rk435::g3[i] != 0.0;
+      s.s2mode = i == 0 ? 1 : (i == 1 ? 2 : 3);
+      s.writeS2 = i >= 1 && i <= 3;
+      s.g1 = rk435::g1[i];
+      s.g2 = rk435::g2[i];
+      s.g3 = rk435::g3[i];
+      s.beta = rk435::beta[i];
+      s.delta = rk435::delta[i];
+      if (i == 4) {
+        s.final = true;
+        s.useC0 = true;
+        s.cF = rk435::deltaSumReciprocal * rk435::delta[5];
+        s.s2F = rk435::deltaSumReciprocal;
+        s.s3F = rk435::deltaSumReciprocal * rk435::delta[6];
+      }
+      plan.push_back(s);
+    }
+    nbuf = 4;
+  }
+  for (auto &c : comps) {
+    c.nbuf = nbuf;
+  }
+}
+
+// ---- constructor: mirrors PixelSim::PixelSim / CudaPixelSim::CudaPixelSim ---
+Sim::Sim(const smeb200_problem &p) {
+  try {
+    build(p);
+  } catch (const std::exception &e) {
+    // like the reference constructors: never throw, keep the message
+    // (pixelsim.cpp:415-418, cudapixelsim.cpp:1156-1167)
+    errorMessage = e.what();
+    ctorFailed = true;
+  }
+}
+
+void Sim::build(const smeb200_problem &p) {
+  if (p.abi_version != SMEB200_ABI_VERSION) {
+    throw Error("smeb200: ABI version mismatch");
+  }
+  integrator = p.integrator;
+  errMaxAbs = p.max_err_abs;
+  errMaxRel = p.max_err_rel;
+  maxTimestep = p.max_timestep;
+  imageNx = p.image_nx;
+  imageNy = p.image_ny;
+  imageNz = p.image_nz;
+  if (integrator < SMEB200_RK101 || integrator > SMEB200_RK435) {
+    throw Error("smeb200: unknown integrator");
+  }
+  // feature gates of the reference GPU backend, same texts
+  // (cudapixelsim.cpp:789-809, pixelsim_common.hpp:80-121)
+  if (p.unsupported & SMEB200_HAS_CROSS_DIFFUSION) {
+    throw Error("CUDA pixel backend does not yet support cross-diffusion");
+  }
+  if (p.unsupported & SMEB200_HAS_TIME_OR_SPACE_DEPENDENCE) {
+    throw Error("CUDA pixel backend does not yet support time- or "
+                "space-dependent reaction terms");
+  }
+  if (p.unsupported & SMEB200_HAS_NON_SPATIAL_SPECIES) {
+    throw Error("CUDA pixel backend PoC does not yet support non-spatial "
+                "species");
+  }
+  if (p.unsupported & SMEB200_HAS_NON_UNIFORM_DIFFUSION) {
+    throw Error("CUDA pixel backend PoC does not yet support non-uniform "
+                "diffusion constants");
+  }
+  if (p.unsupported & SMEB200_HAS_NON_UNIT_STORAGE) {
+    throw Error("CUDA pixel backend PoC currently requires unit storage for "
+                "all species");
+  }
+  if (p.n_compartments > 32) {
+    throw Error("smeb200: at most 32 compartments are supported");
+  }
+  // no CPU fallback: without a device the simulator carries an error
+  if (auto reason = unavailableReason(); !reason.empty()) {
+    throw Error(reason);
+  }
+  if (p.device >= 0) {
+    device = p.device;
+  } else {
+    check(cudaGetDevice(&device), "Failed to get the primary CUDA device");
+  }
+  bindDevice();
+  check(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking),
+        "Failed to create the CUDA stream");
+  DriverApi::get();
+
+  comps.resize(p.n_compartments);
+  std::vector<std::vector<uint32_t>> nnHost(p.n_compartments);
+  for (uint32_t ci = 0; ci < p.n_compartments; ++ci) {
+    const auto &pc = p.compartments[ci];
+    auto &c = comps[ci];
+    c.id = pc.id != nullptr ? pc.id : "";
+    c.n = pc.n_voxels;
+    c.S = pc.n_species;
+    if (c.S > 64) {
+      throw Error("smeb200: at most 64 species per compartment");
+    }
+    if (c.n >= (uint64_t{1} << 31)) {
+      throw Error("smeb200: at most 2^31 voxels per compartment");
+    }
+    c.box = pc.nn == nullptr;
+    if (c.box) {
+      if (pc.box_nx <= 0 || pc.box_ny <= 0 || pc.box_nz <= 0 ||
+          static_cast<uint64_t>(pc.box_nx) * pc.box_ny * pc.box_nz != c.n) {
+        throw Error("smeb200: compartment '" + c.id +
+                    "' has neither a neighbour list nor valid box dimensions");
+      }
+      c.nx = pc.box_nx;
+      c.ny = pc.box_ny;
+      c.nz = pc.box_nz;
+    } else {
+      nnHost[ci].assign(pc.nn, pc.nn + 6 * c.n);
+      for (uint32_t v : nnHost[ci]) {
+        if (v >= c.n) {
+          throw Error("smeb200: neighbour index out of range in '" + c.id +
+                      "'");
+        }
+      }
+    }
+    if (pc.voxels != nullptr) {
+      c.voxels.assign(pc.voxels, pc.voxels + 3 * c.n);
+    }
+    c.D.assign(pc.diffusion, pc.diffusion + 3 * c.S);
+    for (uint32_t s = 0; s < c.S; ++s) {
+      c.speciesNames.emplace_back(
+          pc.species_names != nullptr && pc.species_names[s] != nullptr
+              ? pc.species_names[s]
+              : "");
+      // forwards-Euler stability bound, pixelsim_common.hpp:33-37 and
+      // pixelsim_impl.cpp:249-255 (unit storage)
+      const double sum = c.D[3 * s] + c.D[3 * s + 1] + c.D[3 * s + 2];
+      maxStableTimestep = std::min(maxStableTimestep, 1.0 / (2.0 * sum));
+    }
+  }
+  makePlan();
+  setupMembranes(p, nnHost);
+  for (uint32_t ci = 0; ci < p.n_compartments; ++ci) {
+    auto &c = comps[ci];
+    if (c.S == 0) {
+      continue;
+    }
+    const std::size_t nv = c.n * c.S;
+    for (int b = 0; b < c.nbuf; ++b) {
+      c.buf[b] = devAlloc<double>(nv, "allocate concentration buffers");
+      c.role[b] = b;
+    }
+    check(cudaMemcpyAsync(c.buf[0], p.compartments[ci].conc0,
+                          nv * sizeof(double), cudaMemcpyHostToDevice, stream),
+          "upload initial concentrations");
+    if (!c.box) {
+      c.dNn = devUpload(nnHost[ci], stream, "upload neighbour list");
+    }
+    check(cudaMallocHost(reinterpret_cast<void **>(&c.hostConc),
+                         std::max<std::size_t>(nv, 1) * sizeof(double)),
+          "allocate pinned host mirror");
+    // before the first run() the mirror is the initial state
+    std::memcpy(c.hostConc, p.compartments[ci].conc0, nv * sizeof(double));
+    c.hostStale = false;
+    c.hostDcdt.assign(nv, 0.0);
+    c.dcdtStale = false;
+  }
+  dErr = devAlloc<unsigned long long>(2, "allocate error accumulators");
+  check(cudaMemsetAsync(dErr, 0, 16, stream), "clear error accumulators");
+  check(cudaMallocHost(reinterpret_cast<void **>(&hErr), 16),
+        "allocate pinned error mirror");
+  generateSource(p);
+  compileModule();
+  check(cudaStreamSynchronize(stream), "initial upload");
+}
+
+Sim::~Sim() {
+  if (stream == nullptr) {
+    return;
+  }
+  cudaSetDevice(device);
+  cudaStreamSynchronize(stream);
+  for (auto &c : comps) {
+    for (double *b : c.buf) {
+      cudaFree(b);
+    }
+    cudaFree(c.dNn);
+    cudaFree(c.dMvox);
+    cudaFree(c.dMstart);
+    cudaFree(c.dEnt);
+    cudaFree(c.scratch);
+    cudaFreeHost(c.hostConc);
+  }
+  cudaFree(dFluxLen);
+  cudaFree(dErr);
+  cudaFreeHost(hErr);
+  for (auto &[a, b] : timerEvents) {
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+  }
+  if (module != nullptr) {
+    try {
+      DriverApi::get().ModuleUnload(module);
+    } catch (...) {
+    }
+  }
+  cudaStreamDestroy(stream);
+}
+
+// ---- one fused stage over all compartments ----------------------------------
+// replaces calculateDcdt() + the RK substep (+ error norm) of
+// pixelsim.cpp:92-120,194-205
+void Sim::launchStage(const StageDesc &sd, double dt, bool /*unused*/) {
+  const auto &drv = DriverApi::get();
+  uint32_t clampMask = 0;
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    if (sd.cin == CUR && comps[ci].curNeedsClamp) {
+      clampMask |= 1u << ci;
+    }
+  }
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    auto &c = comps[ci];
+    if (c.S == 0 || c.n == 0) {
+      continue;
+    }
+    StageArgsHost a{};
+    a.cin = c.buf[c.role[sd.cin]];
+    a.cout = c.buf[c.role[sd.cout]];
+    a.c0 = c.buf[c.role[CUR]];
+    a.nn = c.dNn;
+    a.err = dErr;
+    a.n = static_cast<uint32_t>(c.n);
+    a.nx = c.nx;
+    a.ny = c.ny;
+    a.nz = c.nz;
+    a.z_lo_ghost = 0;
+    a.z_hi_ghost = 0;
+    uint32_t flags = 0;
+    if (sd.cin == CUR && c.curNeedsClamp) {
+      flags |= F_CLAMP_CIN;
+    }
+    if (sd.useC0) {
+      flags |= F_USE_C0;
+      if (c.curNeedsClamp) {
+        flags |= F_CLAMP_C0;
+      }
+    }
+    if (sd.s2mode != 0) {
+      flags |= F_USE_S2;
+      if (sd.s2mode == 2) {
+        flags |= F_USE_S2IN;
+        a.s2in = c.buf[c.role[CUR]];
+        if (c.curNeedsClamp) {
+          flags |= F_CLAMP_S2IN;
+        }
+      } else if (sd.s2mode == 3) {
+        flags |= F_USE_S2IN;
+        a.s2in = c.buf[c.role[RS]];
+      }
+      if (sd.writeS2) {
+        flags |= F_WRITE_S2;
+        a.s2out = c.buf[c.role[RS]];
+      }
+    }
+    if (sd.final) {
+      flags |= F_FINAL;
+    }
+    if (sd.lowerIsCin) {
+      flags |= F_LOWER_IS_CIN;
+    }
+    if (sd.clampOut) {
+      flags |= F_CLAMP_OUT;
+    }
+    a.flags = flags;
+    a.g1 = sd.g1;
+    a.g2 = sd.g2;
+    a.g3 = sd.g3;
+    a.bdt = sd.beta * dt;
+    a.delta = sd.delta;
+    a.cF = sd.cF;
+    a.s2F = sd.s2F;
+    a.s3F = sd.s3F;
+    a.eps = epsilon;
+    std::copy(c.D.begin(), c.D.end(), a.D);
+    launchCompartment(ci, a, clampMask, sd.cin);
+    if (&sd == &plan.back()) {
+      c.last = a;
+      c.lastClampMask = clampMask;
+      c.lastCinRole = sd.cin;
+      c.haveLast = true;
+    }
+  }
+  if (&sd == &plan.back()) {
+    lastCin.resize(comps.size());
+    for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+      lastCin[ci] = comps[ci].S > 0 ? comps[ci].buf[comps[ci].role[sd.cin]]
+                                    : nullptr;
+    }
+  }
+  (void)drv;
+}
+
+void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
+                            uint32_t clampMask, int cinRole) {
+  const auto &drv = DriverApi::get();
+  auto &c = comps[ci];
+  const unsigned grid = static_cast<unsigned>((c.n + BLOCK - 1) / BLOCK);
+  void *params[] = {&a};
+  const bool timed = kernelTiming && ci == dominantComp;
+  if (timed) {
+    if (timerUsed == timerEvents.size()) {
+      cudaEvent_t e0{}, e1{};
+      check(cudaEventCreate(&e0), "cudaEventCreate");
+      check(cudaEventCreate(&e1), "cudaEventCreate");
+      timerEvents.emplace_back(e0, e1);
+    }
+    check(cudaEventRecord(timerEvents[timerUsed].first, stream),
+          "cudaEventRecord");
+  }
+  check(drv.LaunchKernel(c.kStage, grid, 1, 1, BLOCK, 1, 1, 0, stream, params,
+                         nullptr),
+        "launch stage kernel");
+  ++launchCount;
+  if (timed) {
+    check(cudaEventRecord(timerEvents[timerUsed].second, stream),
+          "cudaEventRecord");
+    ++timerUsed;
+    if (timerUsed >= 4096) {
+      flushTimers();
+    }
+  }
+  if (c.nMvox > 0) {
+    // SmebMembArgs: 4 pointers, SMEB_NCOMP pointers, 2 x u32
+    std::vector<unsigned long long> blob(4 + comps.size() + 1);
+    blob[0] = reinterpret_cast<unsigned long long>(c.dMvox);
+    blob[1] = reinterpret_cast<unsigned long long>(c.dMstart);
+    blob[2] = reinterpret_cast<unsigned long long>(c.dEnt);
+    blob[3] = reinterpret_cast<unsigned long long>(dFluxLen);
+    for (std::size_t k = 0; k < comps.size(); ++k) {
+      const double *pc = nullptr;
+      if (comps[k].S > 0) {
+        pc = cinRole >= 0 ? comps[k].buf[comps[k].role[cinRole]] : lastCin[k];
+      }
+      blob[4 + k] = reinterpret_cast<unsigned long long>(pc);
+    }
+    blob[4 + comps.size()] = static_cast<unsigned long long>(c.nMvox) |
+                             (static_cast<unsigned long long>(clampMask) << 32);
+    void *mparams[] = {&a, blob.data()};
+    const unsigned mgrid = (c.nMvox + BLOCK - 1) / BLOCK;
+    check(drv.LaunchKernel(c.kMemb, mgrid, 1, 1, BLOCK, 1, 1, 0, stream,
+                           mparams, nullptr),
+          "launch membrane stage kernel");
+    ++launchCount;
+  }
+}
+
+void Sim::flushTimers() {
+  if (timerUsed == 0) {
+    return;
+  }
+  check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+  for (std::size_t i = 0; i < timerUsed; ++i) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, timerEvents[i].first,
+                             timerEvents[i].second) == cudaSuccess) {
+      kernelMs += ms;
+      ++kernelLaunchesTimed;
+    }
+  }
+  timerUsed = 0;
+}
+
+void Sim::doStep(double dt) {
+  for (const auto &sd : plan) {
+    launchStage(sd, dt, false);
+  }
+  for (auto &c : comps) {
+    c.dcdtStale = true;
+    c.lowerStale = true;
+    c.hostStale = true;
+  }
+}
+
+// accepted step: the final stage's output buffer becomes the state; the old
+// state buffer takes its place in the rotation (no copy — the reference's
+// undoRKStep / D2D restore, pixelsim_impl.cpp:759-763, cudapixelsim.cpp:
+// 1476-1484, is simply "do not rotate")
+void Sim::rotateAfterAccept() {
+  const int outRole = plan.back().cout;
+  for (auto &c : comps) {
+    std::swap(c.role[CUR], c.role[outRole]);
+    c.curNeedsClamp = integrator != SMEB200_RK101;
+  }
+}
+
+void Sim::readError(double &eabs, double &erel) {
+  check(cudaMemcpyAsync(hErr, dErr, 16, cudaMemcpyDeviceToHost, stream),
+        "download error norms");
+  check(cudaMemsetAsync(dErr, 0, 16, stream), "clear error accumulators");
+  check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+  double v[2];
+  std::memcpy(v, hErr, 16);
+  if (allreduceMax != nullptr) {
+    allreduceMax(v, 2, allreduceUser);
+  }
+  eabs = v[0];
+  erel = v[1];
+}
+
+// ---- controller: pixelsim.cpp:122-140, 207-270, 423-471 ----------------------
+double Sim::doRK101(double dt) {
+  dt = std::min(dt, maxStableTimestep);
+  doStep(dt);
+  rotateAfterAccept();
+  return dt;
+}
+
+double Sim::doRKAdaptive(double dtMax) {
+  double eabs = 0.0, erel = 0.0;
+  double dt = 0.0;
+  const double errPower = integrator == SMEB200_RK323   ? 1.0 / 3.0
+                          : integrator == SMEB200_RK435 ? 1.0 / 4.0
+                                                        : 1.0 / 2.0;
+  do {
+    dt = std::min(nextTimestep, dtMax);
+    doStep(dt);
+    readError(eabs, erel);
+    double errFactor = std::min(errMaxAbs / eabs, errMaxRel / erel);
+    errFactor = std::pow(errFactor, errPower);
+    nextTimestep = std::min(0.95 * dt * errFactor, dtMax);
+    if (nextTimestep / dtMax < 1e-20) {
+      std::string problemSpecies{"unknown"};
+      plotRKError(erel, problemSpecies);
+      errorMessage =
+          "Failed to solve model to required accuracy. The largest "
+          "relative integration error comes from species '" +
+          problemSpecies +
+          "'. The location "
+          "of the pixels with the largest relative integration error are shown "
+          "below in red:";
+      return nextTimestep;
+    }
+    if (eabs > errMaxAbs || erel > errMaxRel) {
+      ++discardedSteps;
+    }
+  } while (eabs > errMaxAbs || erel > errMaxRel);
+  rotateAfterAccept();
+  return dt;
+}
+
+std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
+                     void *user) {
+  if (ctorFailed) {
+    return 0; // cudapixelsim.cpp:1621-1623
+  }
+  errorMessage.clear();
+  errorImages.clear();
+  std::size_t steps = 0;
+  try {
+    bindDevice();
+    const auto t0 = std::chrono::steady_clock::now();
+    double tNow = 0;
+    discardedSteps = 0;
+    constexpr double relativeTolerance = 1e-12;
+    while (tNow + time * relativeTolerance < time) {
+      const double maxDt = std::min(maxTimestep, time - tNow);
+      if (integrator == SMEB200_RK101) {
+        double timestep = std::min(maxDt, maxStableTimestep);
+        tNow += doRK101(timestep);
+      } else {
+        tNow += doRKAdaptive(maxDt);
+        if (!errorMessage.empty()) {
+          flushTimers();
+          return steps;
+        }
+      }
+      ++steps;
+      if (timeoutMs >= 0.0) {
+        // the reference compares wall time after each step; with asynchronous
+        // RK101 launches the queue is drained first so the clock means the
+        // same thing
+        if (integrator == SMEB200_RK101) {
+          check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+        }
+        const double elapsed =
+            std::chrono::duration<double, std::milli>(
+                std::chrono::steady_clock::now() - t0)
+                .count();
+        if (elapsed >= timeoutMs) {
+          stopRequested.store(true);
+        }
+      }
+      if (stopCb != nullptr && stopCb(user) != 0) {
+        stopRequested.store(true);
+      }
+      if (stopRequested.load()) {
+        errorMessage = "Simulation stopped early";
+        break;
+      }
+    }
+    flushTimers();
+    check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+  } catch (const std::exception &e) {
+    errorMessage = e.what();
+  }
+  return steps;
+}
+
+double Sim::benchSteps(double dt, std::size_t nSteps) {
+  if (ctorFailed) {
+    return -1.0;
+  }
+  try {
+    bindDevice();
+    cudaEvent_t e0{}, e1{};
+    check(cudaEventCreate(&e0), "cudaEventCreate");
+    check(cudaEventCreate(&e1), "cudaEventCreate");
+    check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+    check(cudaEventRecord(e0, stream), "cudaEventRecord");
+    for (std::size_t i = 0; i < nSteps; ++i) {
+      doStep(integrator == SMEB200_RK101 ? std::min(dt, maxStableTimestep)
+                                         : dt);
+      if (integrator != SMEB200_RK101) {
+        check(cudaMemsetAsync(dErr, 0, 16, stream), "clear error accumulators");
+      }
+      rotateAfterAccept();
+    }
+    check(cudaEventRecord(e1, stream), "cudaEventRecord");
+    check(cudaEventSynchronize(e1), "cudaEventSynchronize");
+    float ms = 0;
+    check(cudaEventElapsedTime(&ms, e0, e1), "cudaEventElapsedTime");
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    flushTimers();
+    return ms;
+  } catch (const std::exception &e) {
+    errorMessage = e.what();
+    return -1.0;
+  }
+}

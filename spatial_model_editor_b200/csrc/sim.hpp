@@ -130,7 +130,8 @@ private:
   void build(const smeb200_problem &p);
   void generateSource(const smeb200_problem &p);
   void compileModule();
-  void setupMembranes(const smeb200_problem &p);
+  void setupMembranes(const smeb200_problem &p,
+                      std::vector<std::vector<uint32_t>> &nnHost);
   void makePlan();
   void bindDevice() const;
   void doStep(double dt);           // all stages of one RK step
