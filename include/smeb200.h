@@ -136,6 +136,11 @@ int smeb200_device_count(void);
  * the simulator carries an error. *out is NULL only if p or out is NULL. */
 int smeb200_create(const smeb200_problem *p, smeb200_sim **out);
 void smeb200_destroy(smeb200_sim *sim);
+/* Generate the model's CUDA module and compile it with NVRTC for sm_100a
+ * without touching a device (works on a machine with no GPU).  The returned
+ * object only serves smeb200_kernel_source / smeb200_error / smeb200_destroy;
+ * its run() returns 0.  Returns 0 if the module compiled. */
+int smeb200_compile_only(const smeb200_problem *p, smeb200_sim **out);
 
 /* BaseSim::run (basesim.hpp:24-27; pixelsim.cpp:423-471): integrate for
  * `time`, returns the number of accepted steps.  timeout_ms < 0 = none.
@@ -193,16 +198,7 @@ int smeb200_get_kernel_timing(const smeb200_sim *sim, double *total_ms,
 /* generated CUDA source of the model module (for inspection / tests) */
 const char *smeb200_kernel_source(const smeb200_sim *sim);
 
-/* ---- multi-GPU z-slabs (one process per GPU) ---------------------------- */
-/* Each rank owns planes [z0, z1) of every box compartment plus one ghost
- * plane per side.  The halo planes live in device buffers exported as CUDA
- * IPC handles; peers map them and the stage kernels store boundary planes
- * straight into the neighbour's ghost plane over NVLink.  The host passes the
- * opaque handle blobs between ranks (bench.py uses torch.distributed).    */
-size_t smeb200_slab_handle_bytes(const smeb200_sim *sim);
-int smeb200_slab_export(smeb200_sim *sim, void *blob);
-int smeb200_slab_connect(smeb200_sim *sim, const void *blob_prev,
-                         const void *blob_next);
+/* ---- multi-GPU ---------------------------------------------------------- */
 /* error-norm exchange for the adaptive controller: the host supplies an
  * allreduce-max over ranks for 2 doubles (NCCL/gloo in the caller) */
 typedef void (*smeb200_allreduce_max_fn)(double *values, int n, void *user);

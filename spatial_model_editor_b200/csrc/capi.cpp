@@ -1,0 +1,212 @@
+// extern "C" surface of libsmeb200.so — see include/smeb200.h for the contract
+// and the reference interface each entry point stands in for.
+#include "sim.hpp"
+#include <cstring>
+
+using smeb200::Sim;
+
+struct smeb200_sim {
+  Sim impl;
+  explicit smeb200_sim(const smeb200_problem &p, bool compileOnly = false)
+      : impl(p, compileOnly) {}
+};
+
+namespace {
+template <typename F> int guarded(smeb200_sim *sim, F &&f) {
+  if (sim == nullptr) {
+    return -1;
+  }
+  try {
+    f();
+    return 0;
+  } catch (const std::exception &e) {
+    sim->impl.errorMessage = e.what();
+    return 1;
+  }
+}
+} // namespace
+
+extern "C" {
+
+int smeb200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int smeb200_create(const smeb200_problem *p, smeb200_sim **out) {
+  if (out == nullptr) {
+    return -1;
+  }
+  *out = nullptr;
+  if (p == nullptr) {
+    return -1;
+  }
+  try {
+    *out = new smeb200_sim(*p);
+  } catch (...) {
+    return -1;
+  }
+  return (*out)->impl.errorMessage.empty() ? 0 : 1;
+}
+
+void smeb200_destroy(smeb200_sim *sim) { delete sim; }
+
+int smeb200_compile_only(const smeb200_problem *p, smeb200_sim **out) {
+  if (out == nullptr || p == nullptr) {
+    return -1;
+  }
+  *out = nullptr;
+  try {
+    *out = new smeb200_sim(*p, true);
+  } catch (...) {
+    return -1;
+  }
+  return (*out)->impl.errorMessage.empty() && (*out)->impl.cubinBytes > 0 ? 0
+                                                                         : 1;
+}
+
+size_t smeb200_run(smeb200_sim *sim, double time, double timeout_ms,
+                   int (*stop_cb)(void *user), void *user) {
+  if (sim == nullptr) {
+    return 0;
+  }
+  return sim->impl.run(time, timeout_ms, stop_cb, user);
+}
+
+int smeb200_get_concentrations(smeb200_sim *sim, size_t compartment,
+                               const double **data, size_t *n) {
+  return guarded(sim, [&] {
+    const double *p = sim->impl.getConcentrations(compartment, n);
+    if (data != nullptr) {
+      *data = p;
+    }
+  });
+}
+
+int smeb200_get_dcdt(smeb200_sim *sim, size_t compartment, const double **data,
+                     size_t *n) {
+  return guarded(sim, [&] {
+    const double *p = sim->impl.getDcdt(compartment, n);
+    if (data != nullptr) {
+      *data = p;
+    }
+  });
+}
+
+int smeb200_get_lower_order(smeb200_sim *sim, size_t compartment,
+                            size_t species, size_t pixel, double *value) {
+  return guarded(sim, [&] {
+    const double v = sim->impl.getLowerOrder(compartment, species, pixel);
+    if (value != nullptr) {
+      *value = v;
+    }
+  });
+}
+
+size_t smeb200_get_concentration_padding(const smeb200_sim *) { return 0; }
+
+int smeb200_set_concentrations(smeb200_sim *sim, size_t compartment,
+                               const double *data, size_t n) {
+  return guarded(sim,
+                 [&] { sim->impl.setConcentrations(compartment, data, n); });
+}
+
+const char *smeb200_error(const smeb200_sim *sim) {
+  return sim != nullptr ? sim->impl.errorMessage.c_str() : "null simulator";
+}
+
+void smeb200_set_error(smeb200_sim *sim, const char *msg) {
+  if (sim != nullptr) {
+    sim->impl.errorMessage = msg != nullptr ? msg : "";
+  }
+}
+
+int smeb200_error_images(const smeb200_sim *sim, const uint32_t **data,
+                         size_t *n) {
+  if (sim == nullptr) {
+    return -1;
+  }
+  if (data != nullptr) {
+    *data = sim->impl.errorImages.data();
+  }
+  if (n != nullptr) {
+    *n = sim->impl.errorImages.size();
+  }
+  return 0;
+}
+
+int smeb200_get_stop_requested(const smeb200_sim *sim) {
+  return sim != nullptr && sim->impl.stopRequested.load() ? 1 : 0;
+}
+
+void smeb200_set_stop_requested(smeb200_sim *sim, int stop) {
+  if (sim != nullptr) {
+    sim->impl.stopRequested.store(stop != 0);
+  }
+}
+
+double smeb200_get_next_timestep(const smeb200_sim *sim) {
+  return sim != nullptr ? sim->impl.nextTimestep : 0.0;
+}
+
+void smeb200_set_next_timestep(smeb200_sim *sim, double dt) {
+  if (sim != nullptr) {
+    sim->impl.nextTimestep = dt;
+  }
+}
+
+size_t smeb200_get_discarded_steps(const smeb200_sim *sim) {
+  return sim != nullptr ? sim->impl.discardedSteps : 0;
+}
+
+double smeb200_get_max_stable_timestep(const smeb200_sim *sim) {
+  return sim != nullptr ? sim->impl.maxStableTimestep : 0.0;
+}
+
+double smeb200_bench_steps(smeb200_sim *sim, double dt, size_t n_steps) {
+  return sim != nullptr ? sim->impl.benchSteps(dt, n_steps) : -1.0;
+}
+
+uint64_t smeb200_launch_count(const smeb200_sim *sim) {
+  return sim != nullptr ? sim->impl.launchCount : 0;
+}
+
+void smeb200_set_kernel_timing(smeb200_sim *sim, int enable) {
+  if (sim != nullptr) {
+    sim->impl.kernelTiming = enable != 0;
+    sim->impl.kernelMs = 0;
+    sim->impl.kernelLaunchesTimed = 0;
+  }
+}
+
+int smeb200_get_kernel_timing(const smeb200_sim *sim, double *total_ms,
+                              uint64_t *launches) {
+  if (sim == nullptr) {
+    return -1;
+  }
+  if (total_ms != nullptr) {
+    *total_ms = sim->impl.kernelMs;
+  }
+  if (launches != nullptr) {
+    *launches = sim->impl.kernelLaunchesTimed;
+  }
+  return 0;
+}
+
+const char *smeb200_kernel_source(const smeb200_sim *sim) {
+  return sim != nullptr ? sim->impl.kernelSource.c_str() : "";
+}
+
+void smeb200_set_allreduce_max(smeb200_sim *sim, smeb200_allreduce_max_fn fn,
+                               void *user) {
+  if (sim != nullptr) {
+    sim->impl.allreduceMax = fn;
+    sim->impl.allreduceUser = user;
+  }
+}
+
+} // extern "C"

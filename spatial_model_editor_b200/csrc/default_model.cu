@@ -1,0 +1,49 @@
+// Build-time instantiation of the kernel template with a default model
+// (gray-scott kinetics, S = 2, plus a 2+2 species linear membrane) so that
+// nvcc/ptxas check the template for sm_100a and SASS can be inspected without
+// a GPU (cuobjdump -sass build/default_model.cubin).  At run time the same
+// template text is compiled per model by NVRTC (sim.cpp: compileModule).
+#define SMEB_NCOMP 2
+#include "device_kernels.cuh"
+
+struct Reac0 {
+  static constexpr int S = 2;
+  static __device__ __forceinline__ void eval(double *sme_out,
+                                              const double *sme_values) {
+    const double sme_var_0 = sme_values[0];
+    const double sme_var_1 = sme_values[1];
+    sme_out[0] = -sme_var_0 * sme_var_1 * sme_var_1 + 0.037 * (1.0 - sme_var_0);
+    sme_out[1] = sme_var_0 * sme_var_1 * sme_var_1 - 0.097 * sme_var_1;
+  }
+};
+struct Reac1 : Reac0 {};
+struct Memb0 {
+  static constexpr int SA = 2, SB = 2, CA = 0, CB = 1;
+  static __device__ __forceinline__ void eval(double *sme_out,
+                                              const double *sme_values) {
+    sme_out[0] = 0.1 * (sme_values[2] - sme_values[0]);
+    sme_out[1] = 0.0;
+    sme_out[2] = -sme_out[0];
+    sme_out[3] = 0.0;
+  }
+};
+template <int S_OWN>
+__device__ __forceinline__ void
+smeb_memb_dispatch(smeb_u32 info, smeb_u32 partner, const double *cown,
+                   const SmebMembArgs &m, double *f) {
+  switch (info & 0xffffu) {
+  case 0:
+    smeb_memb_term<Memb0, S_OWN>(info, partner, cown, m, f);
+    break;
+  default:
+    break;
+  }
+}
+
+template __global__ void
+smeb_stage<Reac0, SMEB_GEOM_BOX>(const __grid_constant__ SmebStageArgs<2>);
+template __global__ void
+smeb_stage<Reac0, SMEB_GEOM_NN>(const __grid_constant__ SmebStageArgs<2>);
+template __global__ void
+smeb_stage_memb<Reac0>(const __grid_constant__ SmebStageArgs<2>,
+                       const __grid_constant__ SmebMembArgs);

@@ -169,6 +169,11 @@ void Sim::compileModule() {
   check(nvrtcGetCUBINSize(prog, &n), "nvrtcGetCUBINSize");
   std::vector<char> cubin(n);
   check(nvrtcGetCUBIN(prog, cubin.data()), "nvrtcGetCUBIN");
+  cubinBytes = cubin.size();
+  if (compileOnly) {
+    nvrtcDestroyProgram(&prog);
+    return;
+  }
   const auto &drv = DriverApi::get();
   check(drv.ModuleLoadData(&module, cubin.data()), "cuModuleLoadData");
   auto getFn = [&](const std::string &expr) {
@@ -353,8 +358,29 @@ void Sim::makePlan() {
 }
 
 // ---- constructor: mirrors PixelSim::PixelSim / CudaPixelSim::CudaPixelSim ---
-Sim::Sim(const smeb200_problem &p) {
+Sim::Sim(const smeb200_problem &p, bool compileOnlyMode)
+    : compileOnly{compileOnlyMode} {
   try {
+    if (compileOnly) {
+      // no device: generate and NVRTC-compile the model module only
+      comps.resize(p.n_compartments);
+      for (uint32_t ci = 0; ci < p.n_compartments; ++ci) {
+        comps[ci].S = p.compartments[ci].n_species;
+        comps[ci].n = p.compartments[ci].n_voxels;
+        comps[ci].box = p.compartments[ci].nn == nullptr;
+      }
+      for (uint32_t m = 0; m < p.n_membranes; ++m) {
+        for (int32_t ci : {p.membranes[m].comp_a, p.membranes[m].comp_b}) {
+          if (ci >= 0 && ci < static_cast<int32_t>(comps.size())) {
+            comps[ci].nMvox = 1;
+          }
+        }
+      }
+      generateSource(p);
+      compileModule();
+      ctorFailed = true; // not runnable
+      return;
+    }
     build(p);
   } catch (const std::exception &e) {
     // like the reference constructors: never throw, keep the message
@@ -462,6 +488,12 @@ void Sim::build(const smeb200_problem &p) {
       // pixelsim_impl.cpp:249-255 (unit storage)
       const double sum = c.D[3 * s] + c.D[3 * s + 1] + c.D[3 * s + 2];
       maxStableTimestep = std::min(maxStableTimestep, 1.0 / (2.0 * sum));
+    }
+  }
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    if (comps[ci].n * comps[ci].S >
+        comps[dominantComp].n * comps[dominantComp].S) {
+      dominantComp = ci;
     }
   }
   makePlan();
@@ -864,3 +896,224 @@ double Sim::benchSteps(double dt, std::size_t nSteps) {
     return -1.0;
   }
 }
+
+// ---- state getters: pixelsim.cpp:473-490 -------------------------------------
+const double *Sim::getConcentrations(std::size_t comp, std::size_t *n) {
+  if (comp >= comps.size()) {
+    throw Error("compartment index out of range");
+  }
+  auto &c = comps[comp];
+  const std::size_t nv = c.n * c.S;
+  if (n != nullptr) {
+    *n = nv;
+  }
+  if (c.hostStale && nv > 0 && !ctorFailed) {
+    bindDevice();
+    const double *cur = c.buf[c.role[CUR]];
+    if (c.curNeedsClamp) {
+      // materialise the lazy clamp (pixelsim_impl.cpp:643-665) into a scratch
+      // copy: the unclamped state stays untouched because the lower-order
+      // solution of RK435 is defined on it
+      if (c.scratch == nullptr) {
+        c.scratch = devAlloc<double>(nv, "allocate scratch buffer");
+      }
+      unsigned long long nn64 = nv;
+      int clamp = 1;
+      double *out = c.scratch;
+      void *params[] = {&cur, &out, &nn64, &clamp};
+      const unsigned grid = static_cast<unsigned>((nv + BLOCK - 1) / BLOCK);
+      check(DriverApi::get().LaunchKernel(kClampCopy, grid, 1, 1, BLOCK, 1, 1,
+                                          0, stream, params, nullptr),
+            "launch clamp kernel");
+      ++launchCount;
+      cur = c.scratch;
+    }
+    check(cudaMemcpyAsync(c.hostConc, cur, nv * sizeof(double),
+                          cudaMemcpyDeviceToHost, stream),
+          "download concentrations");
+    check(cudaStreamSynchronize(stream), "download concentrations");
+    c.hostStale = false;
+  }
+  return c.hostConc;
+}
+
+void Sim::setConcentrations(std::size_t comp, const double *data,
+                            std::size_t n) {
+  if (comp >= comps.size()) {
+    throw Error("compartment index out of range");
+  }
+  auto &c = comps[comp];
+  if (n != c.n * c.S) {
+    throw Error("setConcentrations: wrong number of values");
+  }
+  if (n == 0 || ctorFailed) {
+    return;
+  }
+  bindDevice();
+  check(cudaMemcpyAsync(c.buf[c.role[CUR]], data, n * sizeof(double),
+                        cudaMemcpyHostToDevice, stream),
+        "upload concentrations");
+  check(cudaStreamSynchronize(stream), "upload concentrations");
+  c.curNeedsClamp = false;
+  std::memcpy(c.hostConc, data, n * sizeof(double));
+  c.hostStale = false;
+}
+
+// dc/dt of the last evaluated stage (PixelSim::getDcdt).  The fused stages
+// never store dc/dt; it is re-evaluated on demand from the retained input of
+// the last stage.
+void Sim::evaluateLastDcdt() {
+  bindDevice();
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    auto &c = comps[ci];
+    if (c.S == 0 || c.n == 0 || !c.haveLast) {
+      continue;
+    }
+    const std::size_t nv = c.n * c.S;
+    if (c.scratch == nullptr) {
+      c.scratch = devAlloc<double>(nv, "allocate scratch buffer");
+    }
+    StageArgsHost a = c.last;
+    a.flags = (a.flags & F_CLAMP_CIN) | F_DCDT_ONLY;
+    a.dcdt_out = c.scratch;
+    const bool timing = kernelTiming;
+    kernelTiming = false;
+    launchCompartment(ci, a, c.lastClampMask, -1);
+    kernelTiming = timing;
+    c.hostDcdt.resize(nv);
+    check(cudaMemcpyAsync(c.hostDcdt.data(), c.scratch, nv * sizeof(double),
+                          cudaMemcpyDeviceToHost, stream),
+          "download dcdt");
+    c.dcdtStale = false;
+  }
+  check(cudaStreamSynchronize(stream), "download dcdt");
+}
+
+const double *Sim::getDcdt(std::size_t comp, std::size_t *n) {
+  if (comp >= comps.size()) {
+    throw Error("compartment index out of range");
+  }
+  auto &c = comps[comp];
+  if (n != nullptr) {
+    *n = c.n * c.S;
+  }
+  if (c.dcdtStale && !ctorFailed) {
+    evaluateLastDcdt();
+  }
+  return c.hostDcdt.data();
+}
+
+double Sim::getLowerOrder(std::size_t comp, std::size_t species,
+                          std::size_t pixel) {
+  if (comp >= comps.size()) {
+    throw Error("compartment index out of range");
+  }
+  auto &c = comps[comp];
+  // reference: s2 is empty until an adaptive step has run -> 0
+  // (pixelsim_impl.hpp getLowerOrderConcentration)
+  if (!c.haveLast || integrator == SMEB200_RK101 || ctorFailed) {
+    return 0.0;
+  }
+  const std::size_t nv = c.n * c.S;
+  if (species >= c.S || pixel >= c.n) {
+    throw Error("getLowerOrderConcentration: index out of range");
+  }
+  if (c.lowerStale) {
+    bindDevice();
+    if (c.scratch == nullptr) {
+      c.scratch = devAlloc<double>(nv, "allocate scratch buffer");
+    }
+    struct {
+      const double *cin, *c0, *s2in, *cnew;
+      double *out;
+      unsigned long long n;
+      uint32_t flags;
+      uint32_t pad;
+      double delta, cF, s2F, s3F;
+    } la{c.last.cin, c.last.c0,     c.last.s2in, c.last.cout, c.scratch,
+         nv,         c.last.flags,  0,           c.last.delta, c.last.cF,
+         c.last.s2F, c.last.s3F};
+    void *params[] = {&la};
+    const unsigned grid = static_cast<unsigned>((nv + BLOCK - 1) / BLOCK);
+    check(DriverApi::get().LaunchKernel(kLower, grid, 1, 1, BLOCK, 1, 1, 0,
+                                        stream, params, nullptr),
+          "launch lower-order kernel");
+    ++launchCount;
+    c.hostLower.resize(nv);
+    check(cudaMemcpyAsync(c.hostLower.data(), c.scratch, nv * sizeof(double),
+                          cudaMemcpyDeviceToHost, stream),
+          "download lower-order concentrations");
+    check(cudaStreamSynchronize(stream), "download lower-order");
+    c.lowerStale = false;
+  }
+  return c.hostLower[pixel * c.S + species];
+}
+
+// red-channel image of the relative error, pixelsim_impl.cpp:794-824
+void Sim::plotRKError(double relMax, std::string &problemSpecies) {
+  errorImages.assign(static_cast<std::size_t>(std::max(imageNx, 0)) *
+                         std::max(imageNy, 0) * std::max(imageNz, 0),
+                     0u);
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    auto &c = comps[ci];
+    if (c.S == 0 || c.n == 0 || !c.haveLast) {
+      continue;
+    }
+    const std::size_t nv = c.n * c.S;
+    // lower-order solution, new and old state of the failed step
+    c.lowerStale = true;
+    getLowerOrder(ci, 0, 0);
+    std::vector<double> cnew(nv), cold(nv);
+    check(cudaMemcpy(cnew.data(), c.last.cout, nv * sizeof(double),
+                     cudaMemcpyDeviceToHost),
+          "download state");
+    check(cudaMemcpy(cold.data(), c.buf[c.role[CUR]], nv * sizeof(double),
+                     cudaMemcpyDeviceToHost),
+          "download state");
+    std::size_t iSpecies = c.S + 1;
+    for (std::size_t ix = 0; ix < c.n; ++ix) {
+      for (std::size_t is = 0; is < c.S; ++is) {
+        const std::size_t i = ix * c.S + is;
+        double old = cold[i];
+        if (c.curNeedsClamp && old < 0.0) {
+          old = 0.0;
+        }
+        const double localErr = std::abs(cnew[i] - c.hostLower[i]);
+        const double localNorm = 0.5 * (cnew[i] + old + epsilon);
+        const double pixelIntensity = localErr / localNorm / relMax;
+        const int red = static_cast<int>(255.0 * pixelIntensity);
+        int x = 0, y = 0, z = 0;
+        if (!c.voxels.empty()) {
+          x = c.voxels[3 * ix];
+          y = c.voxels[3 * ix + 1];
+          z = c.voxels[3 * ix + 2];
+        } else if (c.box) {
+          y = static_cast<int>(ix % c.ny);
+          x = static_cast<int>((ix / c.ny) % c.nx);
+          z = static_cast<int>(ix / (static_cast<std::size_t>(c.ny) * c.nx));
+        } else {
+          continue;
+        }
+        if (x < 0 || y < 0 || z < 0 || x >= imageNx || y >= imageNy ||
+            z >= imageNz) {
+          continue;
+        }
+        auto &px = errorImages[(static_cast<std::size_t>(z) * imageNy + y) *
+                                   imageNx +
+                               x];
+        const int oldRed = static_cast<int>((px >> 16) & 0xffu);
+        if (red > oldRed) {
+          px = 0xff000000u | (static_cast<uint32_t>(red & 0xff) << 16);
+          if (red > 254) {
+            iSpecies = is;
+          }
+        }
+      }
+    }
+    if (iSpecies < c.S && !c.speciesNames[iSpecies].empty()) {
+      problemSpecies = c.speciesNames[iSpecies];
+    }
+  }
+}
+
+} // namespace smeb200

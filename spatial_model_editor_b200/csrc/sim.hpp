@@ -85,12 +85,12 @@ struct CompartmentState {
   bool haveLast{false};
   StageArgsHost last{};
   uint32_t lastClampMask{0};
-  const double *lastCin{nullptr};
+  int lastCinRole{0};
 };
 
 class Sim {
 public:
-  explicit Sim(const smeb200_problem &p);
+  explicit Sim(const smeb200_problem &p, bool compileOnlyMode = false);
   ~Sim();
   Sim(const Sim &) = delete;
   Sim &operator=(const Sim &) = delete;
@@ -122,6 +122,8 @@ public:
   double kernelMs{0};
   uint64_t kernelLaunchesTimed{0};
   std::string kernelSource;
+  bool compileOnly{false};
+  std::size_t cubinBytes{0};
   std::size_t nCompartments() const { return comps.size(); }
   smeb200_allreduce_max_fn allreduceMax{nullptr};
   void *allreduceUser{nullptr};
@@ -136,6 +138,8 @@ private:
   void bindDevice() const;
   void doStep(double dt);           // all stages of one RK step
   void launchStage(const StageDesc &sd, double dt, bool dcdtOnly);
+  void launchCompartment(std::size_t ci, StageArgsHost &a, uint32_t clampMask,
+                         int cinRole);
   void rotateAfterAccept();
   void readError(double &eabs, double &erel);
   double doRK101(double dt);
@@ -159,6 +163,8 @@ private:
   std::size_t timerUsed{0};
   int imageNx{0}, imageNy{0}, imageNz{0};
   std::vector<std::string> stageNames, membNames;
+  std::vector<const double *> lastCin;
+  std::size_t dominantComp{0};
 };
 
 } // namespace smeb200
