@@ -1,0 +1,65 @@
+"""Per-species reaction right-hand sides from reactions x stoichiometry.
+
+Restates ``sme::simulate::Pde`` / ``Reaction`` / ``ReacExpr``
+(core/simulate/src/pde.cpp:19-108,171-207; pixelsim_impl.cpp:115-148):
+
+    rhs_i = 0.0 + sum_j ((M_ji * (rate_j)) * (scale))
+
+with global constants and reaction-local parameters inlined as numbers.  The
+reference lets SymEngine simplify the sum; here zero-stoichiometry terms and
+multiplications by one are dropped, which is the part of that simplification
+that matters for cost.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence
+
+from . import expr as E
+
+
+@dataclass
+class ReactionDef:
+    id: str
+    rate: str                              # kinetic law, infix
+    stoich: Dict[str, float]               # species id -> net stoichiometry (products +, reactants -)
+    parameters: Dict[str, float] = field(default_factory=dict)  # local parameters
+
+
+def _scaled(node, factor: float):
+    if factor == 1.0:
+        return node
+    if factor == -1.0:
+        return ("neg", node)
+    return ("mul", float(factor), node)
+
+
+def build_rhs(species: Sequence[str], reactions: Sequence[ReactionDef],
+              constants: Optional[Dict[str, float]] = None, scale: float = 1.0,
+              functions=None, substitutions: Optional[Dict[str, float]] = None
+              ) -> List[str]:
+    """C expressions (in sme_var_k, k = index into ``species``) of the reaction
+    term of every species: what ``ReacExpr.expressions`` holds after the
+    reference's Pde step, printed for the C-ABI."""
+    constants = dict(constants or {})
+    substitutions = substitutions or {}
+    names = {v: f"sme_var_{k}" for k, v in enumerate(species)}
+    out = []
+    for sp in species:
+        total = None
+        for r in reactions:
+            m = float(r.stoich.get(sp, 0.0))
+            if m == 0.0:
+                continue
+            env = dict(constants)
+            env.update(r.parameters)
+            for k, v in substitutions.items():  # pde.cpp:65-77
+                if k in env:
+                    env[k] = v
+            for v in species:
+                env.pop(v, None)
+            rate = E.substitute(E.parse(r.rate), env, functions)
+            term = _scaled(_scaled(rate, m), scale)
+            total = term if total is None else ("add", total, term)
+        out.append(E.to_c(total if total is not None else 0.0, names))
+    return out

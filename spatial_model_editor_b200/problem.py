@@ -1,0 +1,202 @@
+"""Flat problem description: the contract between the "model world" (SME's
+``sme::model::Model``) and the kernel world (``include/smeb200.h``).
+
+Everything the reference's two Pixel backends pull out of ``Model`` in their
+constructors (pixelsim.cpp:272-406, cudapixelsim.cpp:857-1150) ends up in these
+plain arrays and strings.  ``Problem.to_c()`` produces the ``smeb200_problem``
+POD that crosses the C-ABI.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+RK101, RK212, RK323, RK435 = 0, 1, 2, 3
+INTEGRATOR_NAMES = {"rk101": RK101, "rk212": RK212, "rk323": RK323, "rk435": RK435}
+STAGES = {RK101: 1, RK212: 2, RK323: 3, RK435: 5}
+DBL_MAX = float(np.finfo(np.float64).max)
+
+HAS_CROSS_DIFFUSION = 1
+HAS_TIME_OR_SPACE_DEPENDENCE = 2
+HAS_NON_SPATIAL_SPECIES = 4
+HAS_NON_UNIFORM_DIFFUSION = 8
+HAS_NON_UNIT_STORAGE = 16
+
+ABI_VERSION = 1
+
+
+class CCompartment(C.Structure):
+    _fields_ = [
+        ("id", C.c_char_p),
+        ("n_voxels", C.c_uint64),
+        ("n_species", C.c_uint32),
+        ("box_nx", C.c_int32),
+        ("box_ny", C.c_int32),
+        ("box_nz", C.c_int32),
+        ("nn", C.POINTER(C.c_uint32)),
+        ("voxels", C.POINTER(C.c_int32)),
+        ("diffusion", C.POINTER(C.c_double)),
+        ("conc0", C.POINTER(C.c_double)),
+        ("expressions", C.POINTER(C.c_char_p)),
+        ("species_names", C.POINTER(C.c_char_p)),
+    ]
+
+
+class CMembrane(C.Structure):
+    _fields_ = [
+        ("id", C.c_char_p),
+        ("comp_a", C.c_int32),
+        ("comp_b", C.c_int32),
+        ("n_pairs", C.c_uint64 * 6),
+        ("pairs", C.POINTER(C.c_uint32) * 6),
+        ("flux_length", C.c_double * 6),
+        ("expressions", C.POINTER(C.c_char_p)),
+    ]
+
+
+class CProblem(C.Structure):
+    _fields_ = [
+        ("abi_version", C.c_uint32),
+        ("n_compartments", C.c_uint32),
+        ("compartments", C.POINTER(CCompartment)),
+        ("n_membranes", C.c_uint32),
+        ("membranes", C.POINTER(CMembrane)),
+        ("integrator", C.c_int32),
+        ("max_err_abs", C.c_double),
+        ("max_err_rel", C.c_double),
+        ("max_timestep", C.c_double),
+        ("image_nx", C.c_int32),
+        ("image_ny", C.c_int32),
+        ("image_nz", C.c_int32),
+        ("unsupported", C.c_uint32),
+        ("device", C.c_int32),
+        ("rank", C.c_int32),
+        ("n_ranks", C.c_int32),
+        ("kernel_variant", C.c_int32),
+        ("reserved", C.c_uint32 * 7),
+    ]
+
+
+@dataclass
+class Compartment:
+    """geometry::Compartment + the SimCompartment inputs."""
+
+    id: str
+    species: List[str]                    # simulated species ids
+    expressions: List[str]                # C expressions in sme_var_k, one per species
+    diffusion: np.ndarray                 # [S, 3]  D/dx^2, D/dy^2, D/dz^2
+    conc0: np.ndarray                     # [N, S]
+    nn: Optional[np.ndarray] = None       # [N, 6] uint32 or None for a box
+    box: Optional[Tuple[int, int, int]] = None  # (nx, ny, nz) when nn is None
+    voxels: Optional[np.ndarray] = None   # [N, 3] int32 (x, y, z) image coordinates
+
+    @property
+    def n_voxels(self) -> int:
+        return int(self.conc0.shape[0])
+
+    @property
+    def n_species(self) -> int:
+        return len(self.species)
+
+
+@dataclass
+class Membrane:
+    """geometry::Membrane + the SimMembrane inputs."""
+
+    id: str
+    comp_a: int
+    comp_b: int
+    pairs: List[np.ndarray]               # 6 x [n_d, 2] uint32 (ixA, ixB)
+    flux_length: Sequence[float]          # 6 values
+    expressions: List[str]                # SA + SB expressions
+
+
+@dataclass
+class Problem:
+    compartments: List[Compartment]
+    membranes: List[Membrane] = field(default_factory=list)
+    integrator: int = RK212
+    max_err_abs: float = DBL_MAX          # PixelOptions defaults,
+    max_err_rel: float = 0.005            # simulate_options.hpp:132-136
+    max_timestep: float = DBL_MAX
+    image_size: Tuple[int, int, int] = (0, 0, 0)
+    unsupported: int = 0
+    device: int = -1
+    kernel_variant: int = 0
+
+    def evals_per_step(self) -> int:
+        """voxel*species RHS evaluations in one RK step (the bench metric)."""
+        return STAGES[self.integrator] * sum(
+            c.n_voxels * c.n_species for c in self.compartments)
+
+    def to_c(self):
+        """Returns (CProblem, keepalive).  keepalive owns every buffer the POD
+        points into and must outlive the create call."""
+        keep = []
+
+        def strs(items):
+            arr = (C.c_char_p * max(len(items), 1))()
+            for i, s in enumerate(items):
+                arr[i] = s.encode()
+            keep.append(arr)
+            return C.cast(arr, C.POINTER(C.c_char_p))
+
+        def arr(a, dtype, ctype):
+            a = np.ascontiguousarray(a, dtype=dtype)
+            keep.append(a)
+            return a.ctypes.data_as(C.POINTER(ctype))
+
+        comps = (CCompartment * max(len(self.compartments), 1))()
+        for i, c in enumerate(self.compartments):
+            cc = comps[i]
+            cc.id = c.id.encode()
+            cc.n_voxels = c.n_voxels
+            cc.n_species = c.n_species
+            if c.nn is None:
+                assert c.box is not None
+                cc.box_nx, cc.box_ny, cc.box_nz = c.box
+                cc.nn = None
+            else:
+                assert c.nn.shape == (c.n_voxels, 6)
+                cc.nn = arr(c.nn, np.uint32, C.c_uint32)
+            cc.voxels = arr(c.voxels, np.int32, C.c_int32) if c.voxels is not None else None
+            d = np.asarray(c.diffusion, dtype=np.float64).reshape(c.n_species, 3)
+            cc.diffusion = arr(d, np.float64, C.c_double)
+            assert c.conc0.shape == (c.n_voxels, c.n_species)
+            cc.conc0 = arr(c.conc0, np.float64, C.c_double)
+            assert len(c.expressions) == c.n_species
+            cc.expressions = strs(c.expressions)
+            cc.species_names = strs(c.species)
+        membs = (CMembrane * max(len(self.membranes), 1))()
+        for i, m in enumerate(self.membranes):
+            cm = membs[i]
+            cm.id = m.id.encode()
+            cm.comp_a = m.comp_a
+            cm.comp_b = m.comp_b
+            for d in range(6):
+                p = np.ascontiguousarray(m.pairs[d], dtype=np.uint32).reshape(-1, 2)
+                cm.n_pairs[d] = p.shape[0]
+                cm.pairs[d] = arr(p, np.uint32, C.c_uint32)
+                cm.flux_length[d] = float(m.flux_length[d])
+            cm.expressions = strs(m.expressions)
+        keep += [comps, membs]
+        p = CProblem()
+        p.abi_version = ABI_VERSION
+        p.n_compartments = len(self.compartments)
+        p.compartments = C.cast(comps, C.POINTER(CCompartment))
+        p.n_membranes = len(self.membranes)
+        p.membranes = C.cast(membs, C.POINTER(CMembrane))
+        p.integrator = self.integrator
+        p.max_err_abs = self.max_err_abs
+        p.max_err_rel = self.max_err_rel
+        p.max_timestep = self.max_timestep
+        p.image_nx, p.image_ny, p.image_nz = self.image_size
+        p.unsupported = self.unsupported
+        p.device = self.device
+        p.rank = 0
+        p.n_ranks = 1
+        p.kernel_variant = self.kernel_variant
+        return p, keep
