@@ -1,0 +1,313 @@
+#!/usr/bin/env python
+"""Benchmark of the Pixel-simulator hot path (see DESIGN.md "Measurement").
+
+A "step" is one RK212 step (2 fused RHS+RK stages) of the gray-scott-3d model
+over a full-box compartment, driven through the product's public call
+(``PixelSim.run`` -> C-ABI ``smeb200_run``) in the reference benchmark's
+fixed-step configuration (benchmark/benchmark.cpp:214-216: maxErr = DBL_MAX,
+maxTimestep = dt): the controller still reads the fused error norm every step.
+
+  python bench.py --gpus N --steps K --warmup W            (own arm)
+  python bench.py --impl reference --gpus N --steps K ...  (CPU reference arm)
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "pixel_voxel_species_rhs_evals_per_sec"
+UNIT = "evals/s"
+DT = 0.25  # below the forward-Euler bound 1/(2*3*D/dx^2) = 3.18 for voxel size 2
+
+
+def gray_scott_3d_state(nx, ny, nz, z0=0):
+    """U = 1, V = separable Gaussian spots with period 100 voxels; [N, 2] in
+    voxel-list order (z, x, y)"""
+    def axis(n, c, off=0):
+        p = ((np.arange(n) + off) % 100).astype(np.float64)
+        return np.exp(-((p - c) ** 2) / 50.0)
+    v = (axis(nz, 25.0, z0)[:, None, None] * axis(nx, 33.0)[None, :, None]
+         * axis(ny, 40.0)[None, None, :]
+         + axis(nz, 60.0, z0)[:, None, None] * axis(nx, 70.0)[None, :, None]
+         * axis(ny, 66.0)[None, None, :])
+    out = np.empty((nx * ny * nz, 2), dtype=np.float64)
+    out[:, 0] = 1.0
+    out[:, 1] = v.reshape(-1)
+    return out
+
+
+def make_problem(nx, ny, nz, integrator, device=-1, z0=0):
+    import spatial_model_editor_b200 as smeb
+    from spatial_model_editor_b200 import models as M
+    p = M.box_problem(M.GRAY_SCOTT, nx, ny, nz, conc0=gray_scott_3d_state(nx, ny, nz, z0),
+                      voxel_size=(2.0, 2.0, 2.0), integrator=integrator,
+                      max_err_rel=smeb.DBL_MAX, max_err_abs=smeb.DBL_MAX, max_timestep=DT)
+    p.device = device
+    return p
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                smax.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for k, n in enumerate(names):
+                if len(r) > 3 + k and r[3 + k].lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_baseline(args, integrator, threads, budget_s=20.0):
+    """the CPU restatement of the reference TBB Pixel path on a bounded sample of
+    the same workload: a slab of the same model, sized for ~10-30 s"""
+    from oracle.oracle_sim import OraclePixelSim
+    nx = ny = min(args.size, 256)
+    nz = 16
+    p = make_problem(nx, ny, nz, integrator)
+    sim = OraclePixelSim(p, threads=threads)
+    sim.nextTimestep = DT  # skip the controller's 1e-7 start-up step
+    sim.run(DT)    # warm-up
+    evals_per_step = p.evals_per_step()
+    t0 = time.perf_counter()
+    steps = 0
+    while True:
+        steps += sim.run(2 * DT)
+        el = time.perf_counter() - t0
+        if el > budget_s or steps >= 40:
+            break
+    ncores = OraclePixelSim.maxThreads() if threads == 0 else threads
+    return {"value": evals_per_step * steps / el, "unit": UNIT, "cores": ncores,
+            "kind": "port",
+            "sample": f"gray-scott-3d RK212 fixed step, {nx}x{ny}x{nz} slab "
+                      f"({nx * ny * nz} voxels x 2 species), {steps} steps, {el:.1f} s, "
+                      f"OpenMP threads={ncores}"}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path — here the
+    oracle port (the reference cannot be built: see DESIGN.md), all host threads"""
+    if rank != 0:
+        return
+    import spatial_model_editor_b200 as smeb
+    from oracle.oracle_sim import OraclePixelSim
+    nx = ny = min(args.size, 256)
+    nz = 32
+    p = make_problem(nx, ny, nz, smeb.RK212)
+    sim = OraclePixelSim(p, threads=0)
+    sim.nextTimestep = DT
+    for _ in range(args.warmup):
+        sim.run(DT)
+    t0 = time.perf_counter()
+    steps = 0
+    for _ in range(args.steps):
+        steps += sim.run(DT)
+    el = time.perf_counter() - t0
+    value = p.evals_per_step() * steps / el
+    cores = OraclePixelSim.maxThreads()
+    sample = (f"{nx}x{ny}x{nz} slab of the gray-scott-3d workload per step "
+              f"({nx * ny * nz} voxels x 2 species), OpenMP threads={cores}")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+        "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * el / max(steps, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"gray-scott-3d RK212 fixed-step, {sample}"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--size", type=int, default=512, help="box edge (voxels)")
+    ap.add_argument("--nz", type=int, default=0, help="planes per GPU (default: size)")
+    ap.add_argument("--integrator", default="rk212")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--variant", type=int, default=0)
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import spatial_model_editor_b200 as smeb
+    from spatial_model_editor_b200.problem import INTEGRATOR_NAMES, STAGES
+    import torch.distributed as dist
+
+    integrator = INTEGRATOR_NAMES[args.integrator]
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    nx = ny = args.size
+    nz = args.nz or args.size
+    W, K = max(args.warmup, 3), args.steps
+    if world > 1:
+        from spatial_model_editor_b200.multigpu import SlabPixelSim
+        p = make_problem(nx, ny, nz * world, integrator, device=local_rank)
+        sim = SlabPixelSim(p, rank, world, make_slab=lambda z0, z1: gray_scott_3d_state(
+            nx, ny, z1 - z0, z0), variant=args.variant)
+        evals_per_step = STAGES[integrator] * nx * ny * nz * world * 2
+    else:
+        p = make_problem(nx, ny, nz, integrator, device=local_rank)
+        p.kernel_variant = args.variant
+        sim = smeb.PixelSim(p)
+        evals_per_step = p.evals_per_step()
+    if sim.errorMessage():
+        raise SystemExit("bench: " + sim.errorMessage())
+    values_per_rank = nx * ny * nz * 2
+
+    # warm-up: W steps of DT (the controller's 1e-7 start-up step is skipped by
+    # seeding nextTimestep, which run() otherwise raises to DT after one step)
+    sim.nextTimestep = DT
+    assert sim.run(W * DT) == W
+    launches0 = sim.launchCount()
+    sim.setKernelTiming(True)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    steps = sim.run(K * DT)
+    barrier()
+    ms = sim.lastRunMs()
+    clocks = sampler.stop() if rank == 0 else None
+    kms, klaunches = sim.kernelTiming()
+    sim.setKernelTiming(False)
+    launches = sim.launchCount() - launches0
+    assert steps == K, (steps, K, sim.errorMessage())
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        tl = torch.tensor([launches], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tl, op=dist.ReduceOp.SUM)
+        launches = int(tl.item())
+    value = evals_per_step * K / (ms * 1e-3)
+
+    # end to end through the public call with HOST buffers: one image interval =
+    # upload of the state from pinned host memory, K steps, download of the result
+    host = sim.getConcentrations(0)  # pinned mirror
+    h2d = d2h = host.nbytes
+    barrier()
+    t0 = time.perf_counter()
+    sim.setConcentrations(0, host)
+    steps2 = sim.run(K * DT)
+    out = sim.getConcentrations(0)
+    checksum = float(out[::4097, 1].sum())
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e = evals_per_step * steps2 / e2e_s
+
+    # roofline of the dominant kernel (the fused stage kernel): algorithmic bytes
+    # per launch = 8 B x values x (reads + writes of whole arrays) averaged over
+    # the stages of one step: RK212 16 + 24 = 40 B per value per step
+    bytes_per_value_step = {0: 16, 1: 40, 2: 64, 3: 152}[integrator]
+    alg_bytes_per_launch = bytes_per_value_step * values_per_rank / STAGES[integrator]
+    peak, peak_src = measured_peak()
+    roofline = None
+    if klaunches:
+        achieved = alg_bytes_per_launch / (kms / klaunches * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "kernel": "smeb_stage<Reac0, BOX>", "launches_timed": klaunches,
+                    "avg_launch_ms": kms / klaunches,
+                    "algorithmic_bytes_per_launch": alg_bytes_per_launch}
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(args, integrator, threads=0)
+    if rank == 0:
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {
+                "workload": f"gray-scott-3d kinetics, {nx}x{ny}x{nz * world} full-box "
+                            f"compartment ({nz} planes per GPU), S=2, {args.integrator.upper()} "
+                            f"fixed step dt={DT} (maxErr=DBL_MAX like benchmark.cpp:214-216)",
+                "l2": "inputs larger than L2 (state array %.2f GiB per GPU)" % (
+                    values_per_rank * 8 / 2 ** 30),
+                "parallelism": f"z-slabs x{world}" if world > 1 else "single GPU",
+                "kernel_variant": args.variant},
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d / max(steps2, 1),
+                    "d2h_bytes_per_step": d2h / max(steps2, 1),
+                    "note": "one image interval: pinned H2D of the state, K steps, D2H "
+                            "of the result; bytes are per interval / K",
+                    "checksum": checksum},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
+            "cpu_baseline": cpu}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -187,6 +187,9 @@ double smeb200_get_max_stable_timestep(const smeb200_sim *sim);
  * download, state stays resident in HBM.  Returns device milliseconds for
  * the n_steps (CUDA events on the launching stream), <0 on error. */
 double smeb200_bench_steps(smeb200_sim *sim, double dt, size_t n_steps);
+/* device time (ms, CUDA events on the launching stream) of the last
+ * smeb200_run call */
+double smeb200_last_run_ms(const smeb200_sim *sim);
 /* kernels launched since construction */
 uint64_t smeb200_launch_count(const smeb200_sim *sim);
 /* device time of the dominant stage kernel over the last bench/run window:

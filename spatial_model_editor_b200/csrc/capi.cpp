@@ -171,6 +171,10 @@ double smeb200_bench_steps(smeb200_sim *sim, double dt, size_t n_steps) {
   return sim != nullptr ? sim->impl.benchSteps(dt, n_steps) : -1.0;
 }
 
+double smeb200_last_run_ms(const smeb200_sim *sim) {
+  return sim != nullptr ? sim->impl.lastRunMs : 0.0;
+}
+
 uint64_t smeb200_launch_count(const smeb200_sim *sim) {
   return sim != nullptr ? sim->impl.launchCount : 0;
 }

@@ -552,6 +552,10 @@ Sim::~Sim() {
   cudaFree(dFluxLen);
   cudaFree(dErr);
   cudaFreeHost(hErr);
+  if (runEv0 != nullptr) {
+    cudaEventDestroy(runEv0);
+    cudaEventDestroy(runEv1);
+  }
   for (auto &[a, b] : timerEvents) {
     cudaEventDestroy(a);
     cudaEventDestroy(b);
@@ -816,6 +820,11 @@ std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
   std::size_t steps = 0;
   try {
     bindDevice();
+    if (runEv0 == nullptr) {
+      check(cudaEventCreate(&runEv0), "cudaEventCreate");
+      check(cudaEventCreate(&runEv1), "cudaEventCreate");
+    }
+    check(cudaEventRecord(runEv0, stream), "cudaEventRecord");
     const auto t0 = std::chrono::steady_clock::now();
     double tNow = 0;
     discardedSteps = 0;
@@ -856,8 +865,12 @@ std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
         break;
       }
     }
+    check(cudaEventRecord(runEv1, stream), "cudaEventRecord");
     flushTimers();
     check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+    float ms = 0;
+    check(cudaEventElapsedTime(&ms, runEv0, runEv1), "cudaEventElapsedTime");
+    lastRunMs = ms;
   } catch (const std::exception &e) {
     errorMessage = e.what();
   }
@@ -950,12 +963,16 @@ void Sim::setConcentrations(std::size_t comp, const double *data,
     return;
   }
   bindDevice();
-  check(cudaMemcpyAsync(c.buf[c.role[CUR]], data, n * sizeof(double),
+  // data may be the pinned mirror itself (filled in place by the caller):
+  // then the upload is a single pinned H2D copy
+  if (data != c.hostConc) {
+    std::memcpy(c.hostConc, data, n * sizeof(double));
+  }
+  check(cudaMemcpyAsync(c.buf[c.role[CUR]], c.hostConc, n * sizeof(double),
                         cudaMemcpyHostToDevice, stream),
         "upload concentrations");
   check(cudaStreamSynchronize(stream), "upload concentrations");
   c.curNeedsClamp = false;
-  std::memcpy(c.hostConc, data, n * sizeof(double));
   c.hostStale = false;
 }
 

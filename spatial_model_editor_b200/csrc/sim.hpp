@@ -118,6 +118,8 @@ public:
   double epsilon{1e-14};
 
   uint64_t launchCount{0};
+  double lastRunMs{0}; // device time of the last run() (CUDA events)
+  cudaEvent_t runEv0{nullptr}, runEv1{nullptr};
   bool kernelTiming{false};
   double kernelMs{0};
   uint64_t kernelLaunchesTimed{0};

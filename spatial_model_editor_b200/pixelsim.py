@@ -63,6 +63,7 @@ def _bind(lib, prefix: str):
     fn("set_error", None, [vp, C.c_char_p], optional=True)
     fn("bench_steps", C.c_double, [vp, C.c_double, C.c_size_t], optional=True)
     fn("launch_count", C.c_uint64, [vp], optional=True)
+    fn("last_run_ms", C.c_double, [vp], optional=True)
     fn("set_kernel_timing", None, [vp, C.c_int], optional=True)
     fn("get_kernel_timing", C.c_int,
        [vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)], optional=True)
@@ -222,6 +223,9 @@ class PixelSim(CSim):
         if ms < 0:
             raise RuntimeError(self.errorMessage())
         return ms
+
+    def lastRunMs(self) -> float:
+        return float(self._f("last_run_ms")(self._h))
 
     def launchCount(self) -> int:
         return int(self._f("launch_count")(self._h))
