@@ -279,7 +279,7 @@ def main():
         achieved = alg_bytes_per_launch / (kms / klaunches * 1e-3) / 1e9
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                    "kernel": "smeb_stage<Reac0, BOX>", "launches_timed": klaunches,
+                    "kernel": sim.dominantKernel() if hasattr(sim, "dominantKernel") else "stage kernel", "launches_timed": klaunches,
                     "avg_launch_ms": kms / klaunches,
                     "algorithmic_bytes_per_launch": alg_bytes_per_launch}
     cpu = None

@@ -40,10 +40,31 @@ smeb_memb_dispatch(smeb_u32 info, smeb_u32 partner, const double *cown,
   }
 }
 
+// RK212: stage 1 (Euler) and stage 2 (final, fused error norm, clamp)
+#define F1 0u
+#define F2 (SMEB_F_USE_C0 | SMEB_F_FINAL | SMEB_F_LOWER_IS_CIN | SMEB_F_CLAMP_OUT)
+// RK435 stage 3: generic low-storage update with the running sum in memory
+#define F3 (SMEB_F_GENERIC | SMEB_F_USE_S2 | SMEB_F_USE_S2IN | SMEB_F_WRITE_S2)
 template __global__ void
-smeb_stage<Reac0, SMEB_GEOM_BOX>(const __grid_constant__ SmebStageArgs<2>);
+smeb_stage_tile<Reac0, F1, 16, 64, 5, true>(const __grid_constant__ SmebStageArgs<2>,
+                                            const __grid_constant__ SmebTensorMap,
+                                            const smeb_u32);
 template __global__ void
-smeb_stage<Reac0, SMEB_GEOM_NN>(const __grid_constant__ SmebStageArgs<2>);
+smeb_stage_tile<Reac0, F2, 16, 64, 5, true>(const __grid_constant__ SmebStageArgs<2>,
+                                            const __grid_constant__ SmebTensorMap,
+                                            const smeb_u32);
 template __global__ void
-smeb_stage_memb<Reac0>(const __grid_constant__ SmebStageArgs<2>,
-                       const __grid_constant__ SmebMembArgs);
+smeb_stage_tile<Reac0, F3, 16, 64, 5, true>(const __grid_constant__ SmebStageArgs<2>,
+                                            const __grid_constant__ SmebTensorMap,
+                                            const smeb_u32);
+template __global__ void
+smeb_stage_tile<Reac0, F2, 16, 64, 3, false>(const __grid_constant__ SmebStageArgs<2>,
+                                             const __grid_constant__ SmebTensorMap,
+                                             const smeb_u32);
+template __global__ void
+smeb_stage_box<Reac0, F2>(const __grid_constant__ SmebStageArgs<2>);
+template __global__ void
+smeb_stage_nn<Reac0, F2>(const __grid_constant__ SmebStageArgs<2>);
+template __global__ void
+smeb_stage_memb<Reac0, F2>(const __grid_constant__ SmebStageArgs<2>,
+                           const __grid_constant__ SmebMembArgs);

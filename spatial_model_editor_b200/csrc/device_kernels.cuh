@@ -16,44 +16,47 @@
 //                                                  pixelsim_impl.cpp:625-721
 //   err   = max|c'-lower| , max|c'-lower|/(0.5(c'+s3+eps))
 //                                                  pixelsim_impl.cpp:774-792
-//   clamp = max(c,0) applied lazily on the next load
-//                                                  pixelsim_impl.cpp:643-665
+//   clamp = max(c',0) at the store of the last stage (the state is only used
+//           if the step is accepted)               pixelsim_impl.cpp:643-665
 // The floating point association order of every expression follows the cited
 // reference lines so that fixed-step results agree to the last bits.
+//
+// Stage flags are a compile-time template argument: the host instantiates one
+// kernel per distinct stage of the chosen integrator (2 for RK212).
 
 typedef unsigned long long smeb_u64;
 typedef unsigned int smeb_u32;
 
-#define SMEB_F_CLAMP_CIN 1u      // clamp stage input to >= 0 on load
-#define SMEB_F_CLAMP_C0 2u       // clamp pre-step state to >= 0 on load
-#define SMEB_F_CLAMP_OUT 4u      // clamp output (RK101: no accept/reject)
-#define SMEB_F_USE_C0 8u         // load c0 (s3)
-#define SMEB_F_USE_S2 16u        // running sum s2 is live (RK323/RK435)
-#define SMEB_F_USE_S2IN 32u      // s2 read from memory (else starts at 0)
-#define SMEB_F_WRITE_S2 64u      // s2 written back
-#define SMEB_F_FINAL 128u        // last stage: fused error norm
-#define SMEB_F_LOWER_IS_CIN 256u // RK212: lower order solution = stage input
-#define SMEB_F_DCDT_ONLY 512u    // only evaluate dc/dt into dcdt_out
-#define SMEB_F_CLAMP_S2IN 1024u  // s2 is read from the (lazily clamped) c0
+#define SMEB_F_USE_C0 1u         // update reads the pre-step state c0 (s3)
+#define SMEB_F_USE_S2 2u         // running sum s2 is live (RK323/RK435)
+#define SMEB_F_USE_S2IN 4u       // s2 read from memory (else starts at 0)
+#define SMEB_F_WRITE_S2 8u       // s2 written back
+#define SMEB_F_FINAL 16u         // last stage: fused error norm
+#define SMEB_F_LOWER_IS_CIN 32u  // RK212: lower order solution = stage input
+#define SMEB_F_CLAMP_OUT 64u     // clamp output to >= 0 at the store
+#define SMEB_F_GENERIC 128u      // update = g1 c + g2 s2 + g3 c0 + bdt f
+                                 // (else the two-term forms of RK101/RK212)
+#define SMEB_F_OUT_DCDT 256u     // on demand: store dc/dt, nothing else
+#define SMEB_F_OUT_LOWER 512u    // on demand: store the lower-order solution
+#define SMEB_F_OUT_CNEW 1024u    // on demand: store the unclamped new state
 
-#define SMEB_GEOM_NN 0
-#define SMEB_GEOM_BOX 1
 #define SMEB_MEMB_FLAG 0x80000000u
 #define SMEB_BLOCK 256
+#ifndef SMEB_TILE_MIN_CTAS
+#define SMEB_TILE_MIN_CTAS 2 // resident CTAs per SM the tile kernel is built for
+#endif
 
 template <int S> struct SmebStageArgs {
   const double *cin;   // stage input: RHS is evaluated on this state
   const double *c0;    // pre-step state (reference: s3)
   const double *s2in;  // low-storage running sum in (reference: s2)
   double *s2out;       // running sum out (may alias s2in)
-  double *cout;        // stage output
-  double *dcdt_out;    // SMEB_F_DCDT_ONLY target
-  const smeb_u32 *nn;  // [6 n] neighbour list (SMEB_GEOM_NN)
+  double *cout;        // stage output (or the on-demand output)
+  const smeb_u32 *nn;  // [6 n] neighbour list (voxel-list geometry)
   smeb_u64 *err;       // [2] bit patterns of max abs / max rel error
   smeb_u32 n;          // voxels in this launch's index space
-  smeb_u32 nx, ny, nz; // box dims (SMEB_GEOM_BOX); voxel = (z*nx + x)*ny + y
-  smeb_u32 z_lo_ghost, z_hi_ghost; // 1 if plane 0 / nz-1 is a ghost plane
-  smeb_u32 flags;
+  smeb_u32 nx, ny, nz; // box dims; voxel = (z*nx + x)*ny + y
+  smeb_u32 z_begin, z_end; // planes updated by this launch (ghosts excluded)
   double g1, g2, g3, bdt, delta; // stage coefficients (bdt = beta*dt)
   double cF, s2F, s3F, eps;      // finalise factors, error epsilon
   double D[3 * S];               // D/dx^2, D/dy^2, D/dz^2 per species
@@ -75,15 +78,14 @@ struct SmebMembArgs {
   const double *flux_len;     // [n_membranes*6]
   const double *comp_cin[SMEB_NCOMP]; // stage input of every compartment
   smeb_u32 n_mvox;
-  smeb_u32 clamp_mask;        // bit c: clamp comp_cin[c] on load
+  smeb_u32 pad_;
 };
 
 template <int S>
 __device__ __forceinline__ void smeb_load_voxel(const double *__restrict__ p,
-                                                smeb_u32 i, bool clamp,
-                                                double *v) {
+                                                size_t i, double *v) {
   if constexpr (S % 2 == 0) {
-    const double2 *q = reinterpret_cast<const double2 *>(p) + (size_t)i * (S / 2);
+    const double2 *q = reinterpret_cast<const double2 *>(p) + i * (S / 2);
 #pragma unroll
     for (int k = 0; k < S / 2; ++k) {
       double2 t = q[k];
@@ -91,31 +93,25 @@ __device__ __forceinline__ void smeb_load_voxel(const double *__restrict__ p,
       v[2 * k + 1] = t.y;
     }
   } else {
-    const double *q = p + (size_t)i * S;
+    const double *q = p + i * S;
 #pragma unroll
     for (int k = 0; k < S; ++k) {
       v[k] = q[k];
-    }
-  }
-  if (clamp) {
-#pragma unroll
-    for (int k = 0; k < S; ++k) {
-      v[k] = v[k] < 0.0 ? 0.0 : v[k];
     }
   }
 }
 
 template <int S>
 __device__ __forceinline__ void smeb_store_voxel(double *__restrict__ p,
-                                                 smeb_u32 i, const double *v) {
+                                                 size_t i, const double *v) {
   if constexpr (S % 2 == 0) {
-    double2 *q = reinterpret_cast<double2 *>(p) + (size_t)i * (S / 2);
+    double2 *q = reinterpret_cast<double2 *>(p) + i * (S / 2);
 #pragma unroll
     for (int k = 0; k < S / 2; ++k) {
       q[k] = make_double2(v[2 * k], v[2 * k + 1]);
     }
   } else {
-    double *q = p + (size_t)i * S;
+    double *q = p + i * S;
 #pragma unroll
     for (int k = 0; k < S; ++k) {
       q[k] = v[k];
@@ -126,7 +122,7 @@ __device__ __forceinline__ void smeb_store_voxel(double *__restrict__ p,
 // max-reduction of the two error norms over the block, then one atomicMax per
 // block on the ordered bit patterns (values are >= 0 and never NaN, because
 // like std::max in pixelsim_impl.cpp:783-788 a NaN or negative candidate is
-// never taken).
+// never taken).  Called once per thread at the end of a kernel.
 __device__ __forceinline__ void smeb_block_max2(double eabs, double erel,
                                                 smeb_u64 *err) {
 #pragma unroll
@@ -165,79 +161,113 @@ __device__ __forceinline__ void smeb_block_max2(double eabs, double erel,
   }
 }
 
-// RK stage update + error norm for one voxel, given c (stage input) and the
-// complete dc/dt in f.  Association order: pixelsim_impl.cpp:627,675,699,
-// 718-719,741,783-788.
-template <int S>
+// RK stage update + error norm for one voxel, all in registers.
+//   c    stage input, f complete dc/dt, c0v pre-step state (if USE_C0),
+//   s2v  in: running sum from memory or 0; out: updated running sum,
+//   out  the value the caller stores to a.cout.
+// Association order: pixelsim_impl.cpp:627,675,699,718-719,741,783-788.
+template <int S, unsigned F>
 __device__ __forceinline__ void
-smeb_stage_update(const SmebStageArgs<S> &a, smeb_u32 i, const double *c,
-                  const double *f, double &eabs, double &erel) {
-  const smeb_u32 flags = a.flags;
-  if (flags & SMEB_F_DCDT_ONLY) {
-    smeb_store_voxel<S>(a.dcdt_out, i, f);
+smeb_update(const SmebStageArgs<S> &a, const double *c, const double *f,
+            const double *c0v, double *s2v, double *out, double &eabs,
+            double &erel) {
+  if constexpr ((F & SMEB_F_OUT_DCDT) != 0) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      out[s] = f[s];
+    }
     return;
   }
-  double c0v[S], s2v[S], cn[S];
+  double cn[S];
+#pragma unroll
+  for (int s = 0; s < S; ++s) {
+    if constexpr ((F & SMEB_F_USE_S2) != 0) {
+      s2v[s] = s2v[s] + a.delta * c[s];
+    }
+    if constexpr ((F & SMEB_F_GENERIC) != 0) {
+      cn[s] = a.g1 * c[s] + a.g2 * s2v[s] + a.g3 * c0v[s] + a.bdt * f[s];
+    } else if constexpr ((F & SMEB_F_USE_C0) != 0) {
+      cn[s] = a.g3 * c0v[s] + a.g1 * c[s] + a.bdt * f[s];
+    } else {
+      cn[s] = c[s] + a.bdt * f[s];
+    }
+  }
+  if constexpr ((F & SMEB_F_FINAL) != 0) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      double lower;
+      if constexpr ((F & SMEB_F_LOWER_IS_CIN) != 0) {
+        lower = c[s];
+      } else {
+        lower = a.cF * cn[s] + a.s2F * s2v[s] + a.s3F * c0v[s];
+      }
+      if constexpr ((F & SMEB_F_OUT_LOWER) != 0) {
+        out[s] = lower;
+      } else {
+        const double e = fabs(cn[s] - lower);
+        eabs = eabs < e ? e : eabs;
+        const double norm = 0.5 * (cn[s] + c0v[s] + a.eps);
+        // e / norm can only raise the running maximum if it exceeds erel;
+        // the exact division is done only for candidates within 0.1% of
+        // that (or with a non-positive / NaN norm), so the result is the
+        // same value std::max over all quotients gives
+        if (!(e < 0.999 * erel * norm)) {
+          const double r = e / norm;
+          erel = erel < r ? r : erel;
+        }
+      }
+    }
+  }
+  if constexpr ((F & SMEB_F_OUT_LOWER) == 0) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      double v = cn[s];
+      if constexpr ((F & SMEB_F_CLAMP_OUT) != 0 && (F & SMEB_F_OUT_CNEW) == 0) {
+        v = v < 0.0 ? 0.0 : v;
+      }
+      out[s] = v;
+    }
+  }
+}
+
+// complete per-voxel epilogue for the direct kernels: loads of c0 / s2,
+// update, stores
+template <int S, unsigned F>
+__device__ __forceinline__ void
+smeb_finish_voxel(const SmebStageArgs<S> &a, size_t i, const double *c,
+                  const double *f, double &eabs, double &erel) {
+  double c0v[S], s2v[S], out[S];
 #pragma unroll
   for (int s = 0; s < S; ++s) {
     c0v[s] = 0.0;
     s2v[s] = 0.0;
   }
-  if (flags & SMEB_F_USE_C0) {
-    smeb_load_voxel<S>(a.c0, i, flags & SMEB_F_CLAMP_C0, c0v);
-  }
-  if (flags & SMEB_F_USE_S2) {
-    if (flags & SMEB_F_USE_S2IN) {
-      smeb_load_voxel<S>(a.s2in, i, flags & SMEB_F_CLAMP_S2IN, s2v);
+  if constexpr ((F & SMEB_F_OUT_DCDT) == 0) {
+    if constexpr ((F & SMEB_F_USE_C0) != 0) {
+      smeb_load_voxel<S>(a.c0, i, c0v);
     }
-#pragma unroll
-    for (int s = 0; s < S; ++s) {
-      s2v[s] = s2v[s] + a.delta * c[s];
-    }
-    if (flags & SMEB_F_WRITE_S2) {
-      smeb_store_voxel<S>(a.s2out, i, s2v);
+    if constexpr ((F & SMEB_F_USE_S2IN) != 0) {
+      smeb_load_voxel<S>(a.s2in, i, s2v);
     }
   }
-#pragma unroll
-  for (int s = 0; s < S; ++s) {
-    double v = a.g1 * c[s] + a.g2 * s2v[s] + a.g3 * c0v[s] + a.bdt * f[s];
-    if (flags & SMEB_F_CLAMP_OUT) {
-      v = v < 0.0 ? 0.0 : v;
-    }
-    cn[s] = v;
+  smeb_update<S, F>(a, c, f, c0v, s2v, out, eabs, erel);
+  constexpr bool onDemand =
+      (F & (SMEB_F_OUT_DCDT | SMEB_F_OUT_LOWER | SMEB_F_OUT_CNEW)) != 0;
+  if constexpr ((F & SMEB_F_WRITE_S2) != 0 && !onDemand) {
+    smeb_store_voxel<S>(a.s2out, i, s2v);
   }
-  smeb_store_voxel<S>(a.cout, i, cn);
-  if (flags & SMEB_F_FINAL) {
-#pragma unroll
-    for (int s = 0; s < S; ++s) {
-      const double lower = (flags & SMEB_F_LOWER_IS_CIN)
-                               ? c[s]
-                               : a.cF * cn[s] + a.s2F * s2v[s] + a.s3F * c0v[s];
-      const double e = fabs(cn[s] - lower);
-      eabs = e > eabs ? e : eabs;
-      const double norm = 0.5 * (cn[s] + c0v[s] + a.eps);
-      const double r = e / norm;
-      erel = r > erel ? r : erel;
-    }
-  }
+  smeb_store_voxel<S>(a.cout, i, out);
 }
 
-// reaction + uniform diffusion for one voxel whose six neighbour indices are
-// known; cin values of the voxel itself are returned in c.
+// reaction + uniform diffusion given the voxel and its six neighbours
+// (pixelsim_impl.cpp:444-450: x, y, z terms summed left to right)
 template <class R>
 __device__ __forceinline__ void
-smeb_rhs(const SmebStageArgs<R::S> &a, smeb_u32 i, const smeb_u32 *nb,
-         double *c, double *f) {
+smeb_rhs_values(const SmebStageArgs<R::S> &a, const double *c,
+                const double *xp, const double *xm, const double *yp,
+                const double *ym, const double *zp, const double *zm,
+                double *f) {
   constexpr int S = R::S;
-  const bool clamp = a.flags & SMEB_F_CLAMP_CIN;
-  double xp[S], xm[S], yp[S], ym[S], zp[S], zm[S];
-  smeb_load_voxel<S>(a.cin, i, clamp, c);
-  smeb_load_voxel<S>(a.cin, nb[0], clamp, xp);
-  smeb_load_voxel<S>(a.cin, nb[1], clamp, xm);
-  smeb_load_voxel<S>(a.cin, nb[2], clamp, yp);
-  smeb_load_voxel<S>(a.cin, nb[3], clamp, ym);
-  smeb_load_voxel<S>(a.cin, nb[4], clamp, zp);
-  smeb_load_voxel<S>(a.cin, nb[5], clamp, zm);
   R::eval(f, c);
 #pragma unroll
   for (int s = 0; s < S; ++s) {
@@ -247,51 +277,76 @@ smeb_rhs(const SmebStageArgs<R::S> &a, smeb_u32 i, const smeb_u32 *nb,
   }
 }
 
-// ---- direct-gather stage kernel: one thread per voxel -----------------------
-// GEOM_NN: neighbour indices from the uint32 list (24 B per voxel); voxels
-// flagged SMEB_MEMB_FLAG are left to smeb_stage_memb.
-// GEOM_BOX: neighbours implicit; planes marked as ghost are read but not
-// updated (z-slab decomposition).
-template <class R, int GEOM>
-__global__ void __launch_bounds__(SMEB_BLOCK)
-    smeb_stage(const __grid_constant__ SmebStageArgs<R::S> a) {
+template <class R>
+__device__ __forceinline__ void
+smeb_rhs_gather(const SmebStageArgs<R::S> &a, smeb_u32 i, const smeb_u32 *nb,
+                double *c, double *f) {
   constexpr int S = R::S;
-  const smeb_u32 i = blockIdx.x * SMEB_BLOCK + threadIdx.x;
+  double xp[S], xm[S], yp[S], ym[S], zp[S], zm[S];
+  smeb_load_voxel<S>(a.cin, i, c);
+  smeb_load_voxel<S>(a.cin, nb[0], xp);
+  smeb_load_voxel<S>(a.cin, nb[1], xm);
+  smeb_load_voxel<S>(a.cin, nb[2], yp);
+  smeb_load_voxel<S>(a.cin, nb[3], ym);
+  smeb_load_voxel<S>(a.cin, nb[4], zp);
+  smeb_load_voxel<S>(a.cin, nb[5], zm);
+  smeb_rhs_values<R>(a, c, xp, xm, yp, ym, zp, zm, f);
+}
+
+// ---- direct-gather stage kernels: grid-stride loop, one voxel at a time -----
+// voxel-list geometry: neighbour indices from the uint32 list (24 B per
+// voxel); voxels flagged SMEB_MEMB_FLAG are left to smeb_stage_memb.
+template <class R, unsigned F>
+__global__ void __launch_bounds__(SMEB_BLOCK)
+    smeb_stage_nn(const __grid_constant__ SmebStageArgs<R::S> a) {
+  constexpr int S = R::S;
   double eabs = 0.0, erel = 0.0;
-  if (i < a.n) {
-    smeb_u32 nb[6];
-    bool active = true;
-    if constexpr (GEOM == SMEB_GEOM_BOX) {
-      const smeb_u32 y = i % a.ny;
-      const smeb_u32 t = i / a.ny;
-      const smeb_u32 x = t % a.nx;
-      const smeb_u32 z = t / a.nx;
-      const smeb_u32 sx = a.ny, sz = a.nx * a.ny;
-      nb[0] = x + 1 < a.nx ? i + sx : i;
-      nb[1] = x > 0 ? i - sx : i;
-      nb[2] = y + 1 < a.ny ? i + 1 : i;
-      nb[3] = y > 0 ? i - 1 : i;
-      nb[4] = z + 1 < a.nz ? i + sz : i;
-      nb[5] = z > 0 ? i - sz : i;
-      active = !((z == 0 && a.z_lo_ghost) || (z + 1 == a.nz && a.z_hi_ghost));
-    } else {
-      const uint2 *q = reinterpret_cast<const uint2 *>(a.nn) + (size_t)i * 3;
-      const uint2 n0 = q[0], n1 = q[1], n2 = q[2];
-      active = !(n0.x & SMEB_MEMB_FLAG);
-      nb[0] = n0.x & ~SMEB_MEMB_FLAG;
-      nb[1] = n0.y;
-      nb[2] = n1.x;
-      nb[3] = n1.y;
-      nb[4] = n2.x;
-      nb[5] = n2.y;
+  for (smeb_u32 i = blockIdx.x * SMEB_BLOCK + threadIdx.x; i < a.n;
+       i += gridDim.x * SMEB_BLOCK) {
+    const uint2 *q = reinterpret_cast<const uint2 *>(a.nn) + (size_t)i * 3;
+    const uint2 n0 = q[0], n1 = q[1], n2 = q[2];
+    if (n0.x & SMEB_MEMB_FLAG) {
+      continue;
     }
-    if (active) {
-      double c[S], f[S];
-      smeb_rhs<R>(a, i, nb, c, f);
-      smeb_stage_update<S>(a, i, c, f, eabs, erel);
-    }
+    const smeb_u32 nb[6] = {n0.x, n0.y, n1.x, n1.y, n2.x, n2.y};
+    double c[S], f[S];
+    smeb_rhs_gather<R>(a, i, nb, c, f);
+    smeb_finish_voxel<S, F>(a, i, c, f, eabs, erel);
   }
-  if (a.flags & SMEB_F_FINAL) {
+  if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
+    smeb_block_max2(eabs, erel, a.err);
+  }
+}
+
+// box geometry without tiling (fallback for shapes the TMA kernel does not
+// take): neighbours implicit, zero-flux Neumann at the faces (missing
+// neighbour = own index, geometry.cpp:98-110); only planes
+// [z_begin, z_end) are updated (the others are z-slab ghost planes).
+template <class R, unsigned F>
+__global__ void __launch_bounds__(SMEB_BLOCK)
+    smeb_stage_box(const __grid_constant__ SmebStageArgs<R::S> a) {
+  constexpr int S = R::S;
+  double eabs = 0.0, erel = 0.0;
+  const smeb_u32 sx = a.ny, sz = a.nx * a.ny;
+  const smeb_u32 iEnd = a.z_end * sz;
+  for (smeb_u32 i = a.z_begin * sz + blockIdx.x * SMEB_BLOCK + threadIdx.x;
+       i < iEnd; i += gridDim.x * SMEB_BLOCK) {
+    const smeb_u32 y = i % a.ny;
+    const smeb_u32 t = i / a.ny;
+    const smeb_u32 x = t % a.nx;
+    const smeb_u32 z = t / a.nx;
+    smeb_u32 nb[6];
+    nb[0] = x + 1 < a.nx ? i + sx : i;
+    nb[1] = x > 0 ? i - sx : i;
+    nb[2] = y + 1 < a.ny ? i + 1 : i;
+    nb[3] = y > 0 ? i - 1 : i;
+    nb[4] = z + 1 < a.nz ? i + sz : i;
+    nb[5] = z > 0 ? i - sz : i;
+    double c[S], f[S];
+    smeb_rhs_gather<R>(a, i, nb, c, f);
+    smeb_finish_voxel<S, F>(a, i, c, f, eabs, erel);
+  }
+  if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
     smeb_block_max2(eabs, erel, a.err);
   }
 }
@@ -318,8 +373,7 @@ smeb_memb_term(smeb_u32 info, smeb_u32 partner, const double *cown,
         in[s] = cown[s];
       }
       if constexpr (SB > 0) {
-        smeb_load_voxel<SB>(m.comp_cin[M::CB], partner,
-                            (m.clamp_mask >> M::CB) & 1u, in + SA);
+        smeb_load_voxel<SB>(m.comp_cin[M::CB], partner, in + SA);
       }
       M::eval(out, in);
 #pragma unroll
@@ -334,8 +388,7 @@ smeb_memb_term(smeb_u32 info, smeb_u32 partner, const double *cown,
         in[SA + s] = cown[s];
       }
       if constexpr (SA > 0) {
-        smeb_load_voxel<SA>(m.comp_cin[M::CA], partner,
-                            (m.clamp_mask >> M::CA) & 1u, in);
+        smeb_load_voxel<SA>(m.comp_cin[M::CA], partner, in);
       }
       M::eval(out, in);
 #pragma unroll
@@ -352,75 +405,351 @@ __device__ __forceinline__ void
 smeb_memb_dispatch(smeb_u32 info, smeb_u32 partner, const double *cown,
                    const SmebMembArgs &m, double *f);
 
-template <class R>
+template <class R, unsigned F>
 __global__ void __launch_bounds__(SMEB_BLOCK)
     smeb_stage_memb(const __grid_constant__ SmebStageArgs<R::S> a,
                     const __grid_constant__ SmebMembArgs m) {
   constexpr int S = R::S;
-  const smeb_u32 k = blockIdx.x * SMEB_BLOCK + threadIdx.x;
   double eabs = 0.0, erel = 0.0;
-  if (k < m.n_mvox) {
+  for (smeb_u32 k = blockIdx.x * SMEB_BLOCK + threadIdx.x; k < m.n_mvox;
+       k += gridDim.x * SMEB_BLOCK) {
     const smeb_u32 i = m.mvox[k];
     const uint2 *q = reinterpret_cast<const uint2 *>(a.nn) + (size_t)i * 3;
     const uint2 n0 = q[0], n1 = q[1], n2 = q[2];
-    smeb_u32 nb[6] = {n0.x & ~SMEB_MEMB_FLAG, n0.y, n1.x, n1.y, n2.x, n2.y};
+    const smeb_u32 nb[6] = {n0.x & ~SMEB_MEMB_FLAG, n0.y, n1.x, n1.y, n2.x, n2.y};
     double c[S], f[S];
-    smeb_rhs<R>(a, i, nb, c, f);
+    smeb_rhs_gather<R>(a, i, nb, c, f);
     const smeb_u32 e1 = m.mstart[k + 1];
     for (smeb_u32 e = m.mstart[k]; e < e1; ++e) {
       const SmebMembEntry ent = m.ent[e];
       smeb_memb_dispatch<S>(ent.info, ent.partner, c, m, f);
     }
-    smeb_stage_update<S>(a, i, c, f, eabs, erel);
+    smeb_finish_voxel<S, F>(a, i, c, f, eabs, erel);
   }
-  if (a.flags & SMEB_F_FINAL) {
+  if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
     smeb_block_max2(eabs, erel, a.err);
   }
 }
 
-// ---- on-demand elementwise kernels ------------------------------------------
-// lower-order solution (pixelsim_impl.cpp:737-743; RK212: s2 = stage-2 input)
-struct SmebLowerArgs {
-  const double *cin, *c0, *s2in, *cnew;
-  double *out;
-  smeb_u64 n; // values
-  smeb_u32 flags;
-  double delta, cF, s2F, s3F;
+// ---- TMA-staged tile-marching stage kernel for box compartments -------------
+// The compartment fills its image, so the voxel list is a dense
+// [nz][nx][ny*S] fp64 array (y contiguous).  A CTA owns a TX x TY tile of the
+// (x, y) plane and marches along z (M3) — or, for 2-D images (nz == 1), owns a
+// TY-wide strip and marches along x in bricks of TX rows.  Every plane/brick of
+// the stage input is fetched ONCE by TMA (cp.async.bulk.tensor, halo of one
+// voxel in x and y, out-of-image cells zero-filled and never used) into a ring
+// of NST shared-memory slots, NST-3 (M3) or NST-1 loads ahead of the compute;
+// the seven stencil operands are then read from shared memory, the pre-step
+// state / running sum are register-prefetched one plane ahead with coalesced
+// 16-byte loads, and the result is written with coalesced 16-byte stores.
+// Zero-flux Neumann faces (missing neighbour = own voxel) are address selects
+// computed once per thread, not per voxel.  Host guarantees nx % RPT == 0.
+struct alignas(64) SmebTensorMap {
+  smeb_u64 opaque[16];
 };
 
-__global__ void __launch_bounds__(SMEB_BLOCK)
-    smeb_lower_order(const __grid_constant__ SmebLowerArgs a) {
-  const smeb_u64 i = (smeb_u64)blockIdx.x * SMEB_BLOCK + threadIdx.x;
-  if (i >= a.n) {
-    return;
-  }
-  const double c = a.cin[i];
-  if (a.flags & SMEB_F_LOWER_IS_CIN) {
-    a.out[i] = c;
-    return;
-  }
-  double c0 = a.c0[i];
-  if (a.flags & SMEB_F_CLAMP_C0) {
-    c0 = c0 < 0.0 ? 0.0 : c0;
-  }
-  double s2 = (a.flags & SMEB_F_USE_S2IN) ? a.s2in[i] : 0.0;
-  if (a.flags & SMEB_F_CLAMP_S2IN) {
-    s2 = s2 < 0.0 ? 0.0 : s2;
-  }
-  s2 = s2 + a.delta * c;
-  a.out[i] = a.cF * a.cnew[i] + a.s2F * s2 + a.s3F * c0;
+__device__ __forceinline__ smeb_u32 smeb_smem_addr(const void *p) {
+  smeb_u64 a;
+  asm volatile("cvta.to.shared.u64 %0, %1;" : "=l"(a) : "l"(p));
+  return (smeb_u32)a;
 }
 
-// materialise the lazy clamp into a contiguous copy (download path)
-__global__ void __launch_bounds__(SMEB_BLOCK)
-    smeb_clamp_copy(const double *__restrict__ in, double *__restrict__ out,
-                    smeb_u64 n, int clamp) {
-  const smeb_u64 i = (smeb_u64)blockIdx.x * SMEB_BLOCK + threadIdx.x;
-  if (i < n) {
-    double v = in[i];
-    if (clamp) {
-      v = v < 0.0 ? 0.0 : v;
+__device__ __forceinline__ void smeb_mbar_init(smeb_u32 bar, smeb_u32 count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count)
+               : "memory");
+}
+
+__device__ __forceinline__ void smeb_mbar_expect_tx(smeb_u32 bar,
+                                                    smeb_u32 bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(
+                   bar),
+               "r"(bytes)
+               : "memory");
+}
+
+__device__ __forceinline__ void smeb_mbar_wait(smeb_u32 bar, smeb_u32 parity) {
+  asm volatile("{\n"
+               ".reg .pred P1;\n"
+               "SMEB_WAIT:\n"
+               "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+               "@P1 bra SMEB_DONE;\n"
+               "bra SMEB_WAIT;\n"
+               "SMEB_DONE:\n"
+               "}" ::"r"(bar),
+               "r"(parity)
+               : "memory");
+}
+
+__device__ __forceinline__ void smeb_tma_load_3d(smeb_u32 dst,
+                                                 const SmebTensorMap *tmap,
+                                                 int c0, int c1, int c2,
+                                                 smeb_u32 bar) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::"
+               "complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(dst),
+               "l"((smeb_u64)tmap), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+               : "memory");
+}
+
+template <int S>
+__device__ __forceinline__ void smeb_lds(const double *p, double *v) {
+  if constexpr (S % 2 == 0) {
+    const double2 *q = reinterpret_cast<const double2 *>(p);
+#pragma unroll
+    for (int k = 0; k < S / 2; ++k) {
+      double2 t = q[k];
+      v[2 * k] = t.x;
+      v[2 * k + 1] = t.y;
     }
-    out[i] = v;
+  } else {
+#pragma unroll
+    for (int k = 0; k < S; ++k) {
+      v[k] = p[k];
+    }
+  }
+}
+
+extern __shared__ __align__(128) unsigned char smeb_dyn_smem[];
+
+template <class R, unsigned F, int TX, int TY, int NST, bool M3>
+__global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
+    smeb_stage_tile(const __grid_constant__ SmebStageArgs<R::S> a,
+                    const __grid_constant__ SmebTensorMap tmap,
+                    const smeb_u32 chunk) {
+  constexpr int S = R::S;
+  constexpr int G = SMEB_BLOCK / TY;   // thread groups along x
+  constexpr int RPT = TX / G;          // consecutive rows per thread
+  // TMA needs the box start to be 16-byte aligned in the row: for an odd
+  // number of species the box starts one double early (and ends one late)
+  constexpr int PAD = S % 2;
+  constexpr int PITCH = (TY + 2) * S + 2 * PAD; // doubles per smem row
+  constexpr smeb_u32 BOX_BYTES = (TX + 2) * PITCH * 8;
+  constexpr smeb_u32 SLOT_BYTES = (BOX_BYTES + 127u) & ~127u;
+  constexpr int LOOK = M3 ? 2 : 0;     // planes needed beyond the current one
+  constexpr bool USE_C0 =
+      (F & SMEB_F_USE_C0) != 0 && (F & SMEB_F_OUT_DCDT) == 0;
+  constexpr bool USE_S2IN =
+      (F & SMEB_F_USE_S2IN) != 0 && (F & SMEB_F_OUT_DCDT) == 0;
+  constexpr bool ON_DEMAND =
+      (F & (SMEB_F_OUT_DCDT | SMEB_F_OUT_LOWER | SMEB_F_OUT_CNEW)) != 0;
+  static_assert(SMEB_BLOCK % TY == 0 && TX % G == 0, "tile shape");
+  static_assert(NST >= LOOK + 2, "ring too short");
+
+  __shared__ smeb_u64 fullBar[NST];
+  unsigned char *ring = smeb_dyn_smem;
+  {
+    const smeb_u32 mis = smeb_smem_addr(ring) & 127u;
+    ring += (128u - mis) & 127u;
+  }
+  const smeb_u32 ringAddr = smeb_smem_addr(ring);
+  const smeb_u32 barAddr = smeb_smem_addr(fullBar);
+
+  const int tid = threadIdx.x;
+  const int ty = tid % TY, tg = tid / TY;
+  const int r0 = tg * RPT; // first tile row of this thread
+  const int y0 = blockIdx.x * TY;
+  const int gy = y0 + ty;
+  // march range [m0, m1): planes (M3) or bricks of TX rows (2-D)
+  int m0, m1, x0;
+  if constexpr (M3) {
+    x0 = blockIdx.y * TX;
+    m0 = a.z_begin + blockIdx.z * chunk;
+    m1 = min(m0 + (int)chunk, (int)a.z_end);
+  } else {
+    x0 = 0;
+    m0 = blockIdx.y * chunk;
+    m1 = min(m0 + (int)chunk, (int)((a.nx + TX - 1) / TX));
+  }
+  const int nIter = m1 - m0;
+  if (nIter <= 0) {
+    return;
+  }
+  const int nLoads = nIter + LOOK;
+  // load j fetches plane m0 - 1 + j (M3) / brick m0 + j (2-D)
+  auto issue = [&](int j, int slot) {
+    const smeb_u32 bar = barAddr + 8u * slot;
+    smeb_mbar_expect_tx(bar, BOX_BYTES);
+    if constexpr (M3) {
+      // planes outside the array are never read (Neumann select below);
+      // the coordinate is clamped so that every box overlaps the tensor
+      const int plane = max(0, min((int)a.nz - 1, m0 - 1 + j));
+      smeb_tma_load_3d(ringAddr + slot * SLOT_BYTES, &tmap,
+                       (y0 - 1) * S - PAD, x0 - 1, plane, bar);
+    } else {
+      smeb_tma_load_3d(ringAddr + slot * SLOT_BYTES, &tmap,
+                       (y0 - 1) * S - PAD, (m0 + j) * TX - 1, 0, bar);
+    }
+  };
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NST; ++s) {
+      smeb_mbar_init(barAddr + 8u * s, 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    for (int j = 0; j < NST && j < nLoads; ++j) {
+      issue(j, j);
+    }
+  }
+  __syncthreads();
+
+  // per-thread geometry: Neumann faces as address selects
+  const int offYm = gy == 0 ? 0 : -S;
+  const int offYp = gy + 1 >= (int)a.ny ? 0 : S;
+  const int ownOff = (r0 + 1) * PITCH + (ty + 1) * S + PAD; // row r0, own col
+  int gx0 = x0 + r0;
+  bool active = gy < (int)a.ny && (M3 ? gx0 < (int)a.nx : true);
+  int offLo = (M3 && gx0 == 0) ? 0 : -PITCH;               // row r0 - 1
+  int offHi = (M3 && gx0 + RPT >= (int)a.nx) ? (RPT - 1) * PITCH
+                                              : RPT * PITCH; // row r0 + RPT
+  const size_t rowStride = (size_t)a.ny;               // voxels per x row
+  const size_t marchStride =
+      M3 ? (size_t)a.nx * a.ny : (size_t)TX * a.ny;    // voxels per iteration
+  size_t g = M3 ? ((size_t)m0 * a.nx + gx0) * a.ny + gy
+                : ((size_t)m0 * TX + r0) * a.ny + gy;
+
+  double c0cur[RPT][S], s2cur[RPT][S];
+#pragma unroll
+  for (int k = 0; k < RPT; ++k) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      c0cur[k][s] = 0.0;
+      s2cur[k][s] = 0.0;
+    }
+  }
+  if constexpr (!M3) {
+    active = gy < (int)a.ny && m0 * TX + r0 < (int)a.nx;
+  }
+  if (active) {
+#pragma unroll
+    for (int k = 0; k < RPT; ++k) {
+      if constexpr (USE_C0) {
+        smeb_load_voxel<S>(a.c0, g + k * rowStride, c0cur[k]);
+      }
+      if constexpr (USE_S2IN) {
+        smeb_load_voxel<S>(a.s2in, g + k * rowStride, s2cur[k]);
+      }
+    }
+  }
+
+  double eabs = 0.0, erel = 0.0;
+  // ring bookkeeping: slot / parity of load j = it + LOOK (the newest plane
+  // this iteration needs), and slots of the current and previous plane
+  int slotW = LOOK % NST, parW = (LOOK / NST) & 1;
+  int slotC = M3 ? 1 % NST : 0, slotM = 0;
+  if constexpr (M3) {
+    smeb_mbar_wait(barAddr, 0);
+    smeb_mbar_wait(barAddr + 8u * (1 % NST), 0);
+  }
+  for (int it = 0; it < nIter; ++it) {
+    const int m = m0 + it;
+    // 2-D: the brick's x range changes every iteration
+    bool activeNext = active;
+    if constexpr (!M3) {
+      gx0 = m * TX + r0;
+      active = gy < (int)a.ny && gx0 < (int)a.nx;
+      activeNext = gy < (int)a.ny && gx0 + TX < (int)a.nx;
+      offLo = gx0 == 0 ? 0 : -PITCH;
+      offHi = gx0 + RPT >= (int)a.nx ? (RPT - 1) * PITCH : RPT * PITCH;
+    }
+    // register prefetch of the next plane's c0 / s2
+    double c0nxt[RPT][S], s2nxt[RPT][S];
+#pragma unroll
+    for (int k = 0; k < RPT; ++k) {
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        c0nxt[k][s] = 0.0;
+        s2nxt[k][s] = 0.0;
+      }
+    }
+    if (it + 1 < nIter && activeNext) {
+#pragma unroll
+      for (int k = 0; k < RPT; ++k) {
+        if constexpr (USE_C0) {
+          smeb_load_voxel<S>(a.c0, g + marchStride + k * rowStride, c0nxt[k]);
+        }
+        if constexpr (USE_S2IN) {
+          smeb_load_voxel<S>(a.s2in, g + marchStride + k * rowStride,
+                             s2nxt[k]);
+        }
+      }
+    }
+    smeb_mbar_wait(barAddr + 8u * slotW, parW);
+    if (active) {
+      const double *sc =
+          reinterpret_cast<const double *>(ring + slotC * SLOT_BYTES) + ownOff;
+      const double *sm = sc, *sp = sc;
+      if constexpr (M3) {
+        if (m > 0) {
+          sm = reinterpret_cast<const double *>(ring + slotM * SLOT_BYTES) +
+               ownOff;
+        }
+        if (m + 1 < (int)a.nz) {
+          sp = reinterpret_cast<const double *>(ring + slotW * SLOT_BYTES) +
+               ownOff;
+        }
+      }
+      double col[RPT + 2][S];
+      smeb_lds<S>(sc + offLo, col[0]);
+#pragma unroll
+      for (int k = 0; k < RPT; ++k) {
+        smeb_lds<S>(sc + k * PITCH, col[k + 1]);
+      }
+      smeb_lds<S>(sc + offHi, col[RPT + 1]);
+#pragma unroll
+      for (int k = 0; k < RPT; ++k) {
+        double yp[S], ym[S], zp[S], zm[S], f[S], out[S];
+        smeb_lds<S>(sc + k * PITCH + offYp, yp);
+        smeb_lds<S>(sc + k * PITCH + offYm, ym);
+        smeb_lds<S>(sp + k * PITCH, zp);
+        smeb_lds<S>(sm + k * PITCH, zm);
+        smeb_rhs_values<R>(a, col[k + 1], col[k + 2], col[k], yp, ym, zp, zm,
+                           f);
+        smeb_update<S, F>(a, col[k + 1], f, c0cur[k], s2cur[k], out, eabs,
+                          erel);
+        if constexpr ((F & SMEB_F_WRITE_S2) != 0 && !ON_DEMAND) {
+          smeb_store_voxel<S>(a.s2out, g + k * rowStride, s2cur[k]);
+        }
+        smeb_store_voxel<S>(a.cout, g + k * rowStride, out);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < RPT; ++k) {
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        c0cur[k][s] = c0nxt[k][s];
+        s2cur[k][s] = s2nxt[k][s];
+      }
+    }
+    g += marchStride;
+    __syncthreads(); // every thread is done with the oldest slot
+    const int slotFree = M3 ? slotM : slotC;
+    if (tid == 0 && it + NST < nLoads) {
+      issue(it + NST, slotFree);
+    }
+    slotM = slotC;
+    slotC = (slotC + 1 == NST) ? 0 : slotC + 1;
+    slotW = slotW + 1;
+    if (slotW == NST) {
+      slotW = 0;
+      parW ^= 1;
+    }
+  }
+  if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
+    smeb_block_max2(eabs, erel, a.err);
+  }
+}
+
+// ---- elementwise helper -------------------------------------------------------
+// c = max(c, 0) in place: SimCompartment::clampNegativeConcentrations for a
+// state injected from the host (pixelsim_impl.cpp:643-665); the stage kernels
+// clamp at their own store
+__global__ void __launch_bounds__(SMEB_BLOCK)
+    smeb_clamp(double *__restrict__ c, smeb_u64 n) {
+  for (smeb_u64 i = (smeb_u64)blockIdx.x * SMEB_BLOCK + threadIdx.x; i < n;
+       i += (smeb_u64)gridDim.x * SMEB_BLOCK) {
+    const double v = c[i];
+    if (v < 0.0) {
+      c[i] = 0.0;
+    }
   }
 }

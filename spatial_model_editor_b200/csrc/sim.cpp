@@ -12,10 +12,6 @@ extern const char *const kDeviceKernelSource;
 
 namespace {
 
-constexpr uint32_t F_CLAMP_CIN = 1u, F_CLAMP_C0 = 2u, F_CLAMP_OUT = 4u,
-                   F_USE_C0 = 8u, F_USE_S2 = 16u, F_USE_S2IN = 32u,
-                   F_WRITE_S2 = 64u, F_FINAL = 128u, F_LOWER_IS_CIN = 256u,
-                   F_DCDT_ONLY = 512u, F_CLAMP_S2IN = 1024u;
 constexpr uint32_t MEMB_FLAG = 0x80000000u;
 constexpr unsigned BLOCK = 256;
 
@@ -84,7 +80,37 @@ std::string functorSource(const std::string &header, uint32_t nVars,
 
 } // namespace
 
+
 void Sim::bindDevice() const { check(cudaSetDevice(device), "cudaSetDevice"); }
+
+uint32_t StageDesc::flags() const {
+  uint32_t f = 0;
+  if (useC0) {
+    f |= F_USE_C0;
+  }
+  if (s2mode != 0) {
+    f |= F_USE_S2;
+    if (s2mode >= 2) {
+      f |= F_USE_S2IN;
+    }
+    if (writeS2) {
+      f |= F_WRITE_S2;
+    }
+  }
+  if (final) {
+    f |= F_FINAL;
+  }
+  if (lowerIsCin) {
+    f |= F_LOWER_IS_CIN;
+  }
+  if (clampOut) {
+    f |= F_CLAMP_OUT;
+  }
+  if (generic) {
+    f |= F_GENERIC;
+  }
+  return f;
+}
 
 // ---- model module: generated functors + kernel template -> NVRTC -> cubin ---
 void Sim::generateSource(const smeb200_problem &p) {
@@ -129,29 +155,33 @@ void Sim::generateSource(const smeb200_problem &p) {
   kernelSource = src.str();
 }
 
-void Sim::compileModule() {
+// name expression of the stage kernel of compartment ci for one flag set
+std::string Sim::kernelName(std::size_t ci, uint32_t flags, bool memb) const {
+  const auto &c = comps[ci];
+  std::ostringstream s;
+  if (memb) {
+    s << "smeb_stage_memb<Reac" << ci << ", " << flags << "u>";
+  } else if (c.geom == Geom::TILE) {
+    s << "smeb_stage_tile<Reac" << ci << ", " << flags << "u, " << c.tile.tx
+      << ", " << c.tile.ty << ", " << c.tile.nst << ", "
+      << (c.tile.m3 ? "true" : "false") << ">";
+  } else if (c.geom == Geom::BOX) {
+    s << "smeb_stage_box<Reac" << ci << ", " << flags << "u>";
+  } else {
+    s << "smeb_stage_nn<Reac" << ci << ", " << flags << "u>";
+  }
+  return s.str();
+}
+
+Sim::Module Sim::compile(const std::vector<std::string> &names) {
+  Module m;
   nvrtcProgram prog{};
   check(nvrtcCreateProgram(&prog, kernelSource.c_str(), "smeb200_model.cu", 0,
                            nullptr, nullptr),
         "nvrtcCreateProgram");
-  stageNames.assign(comps.size(), {});
-  membNames.assign(comps.size(), {});
-  for (std::size_t c = 0; c < comps.size(); ++c) {
-    if (comps[c].S == 0) {
-      continue;
-    }
-    std::ostringstream a, b;
-    a << "smeb_stage<Reac" << c << ", " << (comps[c].box ? 1 : 0) << ">";
-    stageNames[c] = a.str();
-    nvrtcAddNameExpression(prog, stageNames[c].c_str());
-    if (comps[c].nMvox > 0) {
-      b << "smeb_stage_memb<Reac" << c << ">";
-      membNames[c] = b.str();
-      nvrtcAddNameExpression(prog, membNames[c].c_str());
-    }
+  for (const auto &n : names) {
+    nvrtcAddNameExpression(prog, n.c_str());
   }
-  nvrtcAddNameExpression(prog, "smeb_lower_order");
-  nvrtcAddNameExpression(prog, "smeb_clamp_copy");
   // sm_100a only; --fmad=false keeps every a*b+c as two IEEE operations so the
   // result matches the CPU solver's evaluation order bit for bit.
   const char *opts[] = {"--gpu-architecture=sm_100a", "--std=c++17",
@@ -169,32 +199,187 @@ void Sim::compileModule() {
   check(nvrtcGetCUBINSize(prog, &n), "nvrtcGetCUBINSize");
   std::vector<char> cubin(n);
   check(nvrtcGetCUBIN(prog, cubin.data()), "nvrtcGetCUBIN");
-  cubinBytes = cubin.size();
+  cubinBytes += cubin.size();
   if (compileOnly) {
     nvrtcDestroyProgram(&prog);
-    return;
+    return m;
   }
   const auto &drv = DriverApi::get();
-  check(drv.ModuleLoadData(&module, cubin.data()), "cuModuleLoadData");
-  auto getFn = [&](const std::string &expr) {
+  check(drv.ModuleLoadData(&m.mod, cubin.data()), "cuModuleLoadData");
+  for (const auto &name : names) {
     const char *lowered = nullptr;
-    check(nvrtcGetLoweredName(prog, expr.c_str(), &lowered),
+    check(nvrtcGetLoweredName(prog, name.c_str(), &lowered),
           "nvrtcGetLoweredName");
     CUfunction f{};
-    check(drv.ModuleGetFunction(&f, module, lowered), "cuModuleGetFunction");
-    return f;
-  };
-  for (std::size_t c = 0; c < comps.size(); ++c) {
-    if (!stageNames[c].empty()) {
-      comps[c].kStage = getFn(stageNames[c]);
-    }
-    if (!membNames[c].empty()) {
-      comps[c].kMemb = getFn(membNames[c]);
+    check(drv.ModuleGetFunction(&f, m.mod, lowered), "cuModuleGetFunction");
+    m.fn[name] = f;
+  }
+  nvrtcDestroyProgram(&prog);
+  return m;
+}
+
+StageKernels Sim::lookup(const Module &m, std::size_t ci,
+                         uint32_t flags) const {
+  StageKernels k;
+  const auto &drv = DriverApi::get();
+  auto it = m.fn.find(kernelName(ci, flags, false));
+  if (it != m.fn.end()) {
+    k.main = it->second;
+    if (comps[ci].geom == Geom::TILE) {
+      check(drv.FuncSetAttribute(
+                k.main, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES,
+                static_cast<int>(comps[ci].tile.dynSmem)),
+            "cuFuncSetAttribute(max dynamic shared memory)");
     }
   }
-  kLower = getFn("smeb_lower_order");
-  kClampCopy = getFn("smeb_clamp_copy");
-  nvrtcDestroyProgram(&prog);
+  if (comps[ci].nMvox > 0) {
+    it = m.fn.find(kernelName(ci, flags, true));
+    if (it != m.fn.end()) {
+      k.memb = it->second;
+    }
+  }
+  return k;
+}
+
+// kernels that are only needed on demand (getDcdt, lower-order solution,
+// error images) are compiled into an extra module at first use
+StageKernels Sim::onDemandKernels(std::size_t ci, uint32_t flags) {
+  const std::string name = kernelName(ci, flags, false);
+  if (auxFn.find(name) == auxFn.end()) {
+    std::vector<std::string> names{name};
+    if (comps[ci].nMvox > 0) {
+      names.push_back(kernelName(ci, flags, true));
+    }
+    auxModules.push_back(compile(names));
+    for (const auto &[k, f] : auxModules.back().fn) {
+      auxFn[k] = f;
+    }
+  }
+  Module view;
+  view.fn = auxFn;
+  return lookup(view, ci, flags);
+}
+
+// ---- geometry path per compartment -------------------------------------------
+// Box compartments (implicit neighbours) use the TMA tile-marching kernel when
+// the array can be described by a tensor map (16-byte row pitch) and the tile
+// fits; otherwise the direct box kernel.  variant: 0 auto, 1 direct kernels
+// only, 2 tile kernel required.
+void Sim::chooseGeometry(int variant) {
+  for (auto &c : comps) {
+    if (!c.box) {
+      c.geom = Geom::NN;
+      continue;
+    }
+    c.geom = Geom::BOX;
+    if (variant == 1 || c.S == 0 || c.n == 0) {
+      continue;
+    }
+    const bool pitchOk = (static_cast<uint64_t>(c.ny) * c.S) % 2 == 0;
+    // TY: 64 voxels of y per tile, less for narrow images; the TMA box is
+    // limited to 256 elements per dimension
+    int ty = 64;
+    while (ty > 8 && ty / 2 >= static_cast<int>(c.ny)) {
+      ty /= 2;
+    }
+    // row of the TMA box in doubles; an odd species count is padded by one
+    // double on each side so that the box starts 16-byte aligned
+    auto boxRow = [&c](int t) {
+      return (t + 2) * static_cast<int>(c.S) + 2 * static_cast<int>(c.S % 2);
+    };
+    while (ty > 8 && boxRow(ty) > 256) {
+      ty /= 2;
+    }
+    const bool boxOk = boxRow(ty) <= 256;
+    if (!pitchOk || !boxOk) {
+      if (variant == 2) {
+        throw Error("smeb200: the TMA tile kernel cannot take compartment '" +
+                    c.id + "' (row pitch not a multiple of 16 bytes or too "
+                           "many species)");
+      }
+      continue;
+    }
+    const int groups = static_cast<int>(BLOCK) / ty;
+    int rpt = c.S <= 2 ? 4 : (c.S <= 4 ? 2 : 1);
+    while (rpt > 1 && c.nx % rpt != 0) {
+      rpt /= 2;
+    }
+    TileConfig t;
+    t.ty = ty;
+    t.tx = groups * rpt;
+    t.m3 = c.nz > 1;
+    const unsigned boxBytes = (t.tx + 2) * boxRow(t.ty) * 8;
+    const unsigned slotBytes = (boxBytes + 127u) & ~127u;
+    t.nst = t.m3 ? 5 : 3;
+    const int nstMin = t.m3 ? 4 : 2;
+    while (t.nst > nstMin && t.nst * slotBytes + 128u > 110u * 1024u) {
+      --t.nst;
+    }
+    t.dynSmem = t.nst * slotBytes + 128u;
+    if (t.dynSmem > 220u * 1024u) {
+      if (variant == 2) {
+        throw Error("smeb200: tile does not fit shared memory");
+      }
+      continue;
+    }
+    const unsigned tilesY = (c.ny + t.ty - 1) / t.ty;
+    const unsigned target = static_cast<unsigned>(smCount) * 2u * 4u;
+    if (t.m3) {
+      const unsigned tilesX = (c.nx + t.tx - 1) / t.tx;
+      const unsigned owned = c.nz - c.zLoGhost - c.zHiGhost;
+      const unsigned tiles = tilesX * tilesY;
+      unsigned chunks = std::max(1u, std::min(owned, (target + tiles - 1) / tiles));
+      unsigned chunk = (owned + chunks - 1) / chunks;
+      chunk = std::max(chunk, std::min(owned, 32u));
+      chunks = (owned + chunk - 1) / chunk;
+      t.chunk = chunk;
+      t.grid[0] = tilesY;
+      t.grid[1] = tilesX;
+      t.grid[2] = chunks;
+    } else {
+      const unsigned bricks = (c.nx + t.tx - 1) / t.tx;
+      unsigned chunks =
+          std::max(1u, std::min(bricks, (target + tilesY - 1) / tilesY));
+      unsigned chunk = (bricks + chunks - 1) / chunks;
+      chunk = std::max(chunk, std::min(bricks, 8u));
+      chunks = (bricks + chunk - 1) / chunk;
+      t.chunk = chunk;
+      t.grid[0] = tilesY;
+      t.grid[1] = chunks;
+      t.grid[2] = 1;
+    }
+    if (t.grid[1] > 65535u || t.grid[2] > 65535u) {
+      if (variant == 2) {
+        throw Error("smeb200: tile grid too large");
+      }
+      continue;
+    }
+    c.tile = t;
+    c.geom = Geom::TILE;
+  }
+}
+
+// one tensor map per concentration buffer: fp64 [nz][nx][ny*S], box
+// [(TY+2)*S, TX+2, 1], no swizzle, out-of-bounds cells read as zero
+void Sim::encodeTensorMaps(CompartmentState &c) {
+  const auto &drv = DriverApi::get();
+  for (int b = 0; b < c.nbuf; ++b) {
+    const cuuint64_t dims[3] = {static_cast<cuuint64_t>(c.ny) * c.S, c.nx,
+                                c.nz};
+    const cuuint64_t strides[2] = {
+        static_cast<cuuint64_t>(c.ny) * c.S * 8,
+        static_cast<cuuint64_t>(c.nx) * c.ny * c.S * 8};
+    const cuuint32_t box[3] = {static_cast<cuuint32_t>((c.tile.ty + 2) * c.S +
+                                                       2 * (c.S % 2)),
+                               static_cast<cuuint32_t>(c.tile.tx + 2), 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    check(drv.TensorMapEncodeTiled(
+              &c.tmap[b], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, c.buf[b], dims,
+              strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE),
+          "cuTensorMapEncodeTiled");
+  }
 }
 
 // ---- membranes: per-voxel face lists in the reference accumulation order ----
@@ -295,6 +480,7 @@ void Sim::makePlan() {
     s2.beta = 0.5;
     s2.final = true;
     s2.lowerIsCin = true;
+    s2.clampOut = true;
     plan.push_back(s2);
     nbuf = 3;
   } else if (integrator == SMEB200_RK323) {
@@ -305,6 +491,7 @@ void Sim::makePlan() {
     const int cout[3] = {RA, RB, RA};
     for (int i = 0; i < 3; ++i) {
       StageDesc s;
+      s.generic = true;
       s.cin = cin[i];
       s.cout = cout[i];
       s.useC0 = rk323::g3[i] != 0.0;
@@ -316,6 +503,7 @@ void Sim::makePlan() {
       s.delta = rk323::delta[i];
       if (i == 2) {
         s.final = true;
+        s.clampOut = true;
         s.useC0 = true;
         s.cF = rk323::finaliseFactors[0];
         s.s2F = rk323::finaliseFactors[1];
@@ -331,6 +519,7 @@ void Sim::makePlan() {
     const int cout[5] = {RA, RB, RA, RB, RA};
     for (int i = 0; i < 5; ++i) {
       StageDesc s;
+      s.generic = true;
       s.cin = cin[i];
       s.cout = cout[i];
       s.useC0 = rk435::g3[i] != 0.0;
@@ -343,6 +532,7 @@ void Sim::makePlan() {
       s.delta = rk435::delta[i];
       if (i == 4) {
         s.final = true;
+        s.clampOut = true;
         s.useC0 = true;
         s.cF = rk435::deltaSumReciprocal * rk435::delta[5];
         s.s2F = rk435::deltaSumReciprocal;
@@ -357,31 +547,15 @@ void Sim::makePlan() {
   }
 }
 
+
 // ---- constructor: mirrors PixelSim::PixelSim / CudaPixelSim::CudaPixelSim ---
 Sim::Sim(const smeb200_problem &p, bool compileOnlyMode)
     : compileOnly{compileOnlyMode} {
   try {
-    if (compileOnly) {
-      // no device: generate and NVRTC-compile the model module only
-      comps.resize(p.n_compartments);
-      for (uint32_t ci = 0; ci < p.n_compartments; ++ci) {
-        comps[ci].S = p.compartments[ci].n_species;
-        comps[ci].n = p.compartments[ci].n_voxels;
-        comps[ci].box = p.compartments[ci].nn == nullptr;
-      }
-      for (uint32_t m = 0; m < p.n_membranes; ++m) {
-        for (int32_t ci : {p.membranes[m].comp_a, p.membranes[m].comp_b}) {
-          if (ci >= 0 && ci < static_cast<int32_t>(comps.size())) {
-            comps[ci].nMvox = 1;
-          }
-        }
-      }
-      generateSource(p);
-      compileModule();
-      ctorFailed = true; // not runnable
-      return;
-    }
     build(p);
+    if (compileOnly) {
+      ctorFailed = true; // not runnable
+    }
   } catch (const std::exception &e) {
     // like the reference constructors: never throw, keep the message
     // (pixelsim.cpp:415-418, cudapixelsim.cpp:1156-1167)
@@ -428,19 +602,27 @@ void Sim::build(const smeb200_problem &p) {
   if (p.n_compartments > 32) {
     throw Error("smeb200: at most 32 compartments are supported");
   }
-  // no CPU fallback: without a device the simulator carries an error
-  if (auto reason = unavailableReason(); !reason.empty()) {
-    throw Error(reason);
+  if (!compileOnly) {
+    // no CPU fallback: without a device the simulator carries an error
+    if (auto reason = unavailableReason(); !reason.empty()) {
+      throw Error(reason);
+    }
+    if (p.device >= 0) {
+      device = p.device;
+    } else {
+      check(cudaGetDevice(&device), "Failed to get the primary CUDA device");
+    }
+    bindDevice();
+    check(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking),
+          "Failed to create the CUDA stream");
+    DriverApi::get();
+    int sms = 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) ==
+            cudaSuccess &&
+        sms > 0) {
+      smCount = sms;
+    }
   }
-  if (p.device >= 0) {
-    device = p.device;
-  } else {
-    check(cudaGetDevice(&device), "Failed to get the primary CUDA device");
-  }
-  bindDevice();
-  check(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking),
-        "Failed to create the CUDA stream");
-  DriverApi::get();
 
   comps.resize(p.n_compartments);
   std::vector<std::vector<uint32_t>> nnHost(p.n_compartments);
@@ -466,7 +648,7 @@ void Sim::build(const smeb200_problem &p) {
       c.nx = pc.box_nx;
       c.ny = pc.box_ny;
       c.nz = pc.box_nz;
-    } else {
+    } else if (!compileOnly) {
       nnHost[ci].assign(pc.nn, pc.nn + 6 * c.n);
       for (uint32_t v : nnHost[ci]) {
         if (v >= c.n) {
@@ -475,7 +657,7 @@ void Sim::build(const smeb200_problem &p) {
         }
       }
     }
-    if (pc.voxels != nullptr) {
+    if (pc.voxels != nullptr && !compileOnly) {
       c.voxels.assign(pc.voxels, pc.voxels + 3 * c.n);
     }
     c.D.assign(pc.diffusion, pc.diffusion + 3 * c.S);
@@ -497,7 +679,47 @@ void Sim::build(const smeb200_problem &p) {
     }
   }
   makePlan();
-  setupMembranes(p, nnHost);
+  if (compileOnly) {
+    // no device: only mark which compartments need a membrane kernel
+    for (uint32_t m = 0; m < p.n_membranes; ++m) {
+      for (int32_t ci : {p.membranes[m].comp_a, p.membranes[m].comp_b}) {
+        if (ci >= 0 && ci < static_cast<int32_t>(comps.size())) {
+          comps[ci].nMvox = 1;
+        }
+      }
+    }
+  } else {
+    setupMembranes(p, nnHost);
+  }
+  chooseGeometry(p.kernel_variant);
+
+  // the model module: one kernel per compartment and distinct stage
+  generateSource(p);
+  std::vector<std::string> names;
+  auto addName = [&names](const std::string &n) {
+    if (std::find(names.begin(), names.end(), n) == names.end()) {
+      names.push_back(n);
+    }
+  };
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    if (comps[ci].S == 0) {
+      continue;
+    }
+    for (const auto &sd : plan) {
+      addName(kernelName(ci, sd.flags(), false));
+      if (comps[ci].nMvox > 0) {
+        addName(kernelName(ci, sd.flags(), true));
+      }
+    }
+  }
+  mainModule = compile(names);
+  if (compileOnly) {
+    return;
+  }
+  dominantKernelName = comps.empty() || comps[dominantComp].S == 0
+                           ? std::string{}
+                           : kernelName(dominantComp, plan.back().flags(), false);
+
   for (uint32_t ci = 0; ci < p.n_compartments; ++ci) {
     auto &c = comps[ci];
     if (c.S == 0) {
@@ -514,6 +736,12 @@ void Sim::build(const smeb200_problem &p) {
     if (!c.box) {
       c.dNn = devUpload(nnHost[ci], stream, "upload neighbour list");
     }
+    if (c.geom == Geom::TILE) {
+      encodeTensorMaps(c);
+    }
+    for (const auto &sd : plan) {
+      c.kStage.push_back(lookup(mainModule, ci, sd.flags()));
+    }
     check(cudaMallocHost(reinterpret_cast<void **>(&c.hostConc),
                          std::max<std::size_t>(nv, 1) * sizeof(double)),
           "allocate pinned host mirror");
@@ -523,12 +751,11 @@ void Sim::build(const smeb200_problem &p) {
     c.hostDcdt.assign(nv, 0.0);
     c.dcdtStale = false;
   }
-  dErr = devAlloc<unsigned long long>(2, "allocate error accumulators");
-  check(cudaMemsetAsync(dErr, 0, 16, stream), "clear error accumulators");
+  dErr = devAlloc<unsigned long long>(4, "allocate error accumulators");
+  dErrScratch = dErr + 2;
+  check(cudaMemsetAsync(dErr, 0, 32, stream), "clear error accumulators");
   check(cudaMallocHost(reinterpret_cast<void **>(&hErr), 16),
         "allocate pinned error mirror");
-  generateSource(p);
-  compileModule();
   check(cudaStreamSynchronize(stream), "initial upload");
 }
 
@@ -560,26 +787,27 @@ Sim::~Sim() {
     cudaEventDestroy(a);
     cudaEventDestroy(b);
   }
-  if (module != nullptr) {
-    try {
-      DriverApi::get().ModuleUnload(module);
-    } catch (...) {
+  try {
+    const auto &drv = DriverApi::get();
+    if (mainModule.mod != nullptr) {
+      drv.ModuleUnload(mainModule.mod);
     }
+    for (auto &m : auxModules) {
+      if (m.mod != nullptr) {
+        drv.ModuleUnload(m.mod);
+      }
+    }
+  } catch (...) {
   }
   cudaStreamDestroy(stream);
 }
 
 // ---- one fused stage over all compartments ----------------------------------
-// replaces calculateDcdt() + the RK substep (+ error norm) of
+// replaces calculateDcdt() + the RK substep (+ error norm, + clamp) of
 // pixelsim.cpp:92-120,194-205
-void Sim::launchStage(const StageDesc &sd, double dt, bool /*unused*/) {
-  const auto &drv = DriverApi::get();
-  uint32_t clampMask = 0;
-  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
-    if (sd.cin == CUR && comps[ci].curNeedsClamp) {
-      clampMask |= 1u << ci;
-    }
-  }
+void Sim::launchStage(std::size_t stageIndex, double dt) {
+  const StageDesc &sd = plan[stageIndex];
+  const bool last = stageIndex + 1 == plan.size();
   for (std::size_t ci = 0; ci < comps.size(); ++ci) {
     auto &c = comps[ci];
     if (c.S == 0 || c.n == 0) {
@@ -595,45 +823,16 @@ void Sim::launchStage(const StageDesc &sd, double dt, bool /*unused*/) {
     a.nx = c.nx;
     a.ny = c.ny;
     a.nz = c.nz;
-    a.z_lo_ghost = 0;
-    a.z_hi_ghost = 0;
-    uint32_t flags = 0;
-    if (sd.cin == CUR && c.curNeedsClamp) {
-      flags |= F_CLAMP_CIN;
+    a.z_begin = c.zLoGhost;
+    a.z_end = c.nz - c.zHiGhost;
+    if (sd.s2mode == 2) {
+      a.s2in = c.buf[c.role[CUR]];
+    } else if (sd.s2mode == 3) {
+      a.s2in = c.buf[c.role[RS]];
     }
-    if (sd.useC0) {
-      flags |= F_USE_C0;
-      if (c.curNeedsClamp) {
-        flags |= F_CLAMP_C0;
-      }
+    if (sd.writeS2) {
+      a.s2out = c.buf[c.role[RS]];
     }
-    if (sd.s2mode != 0) {
-      flags |= F_USE_S2;
-      if (sd.s2mode == 2) {
-        flags |= F_USE_S2IN;
-        a.s2in = c.buf[c.role[CUR]];
-        if (c.curNeedsClamp) {
-          flags |= F_CLAMP_S2IN;
-        }
-      } else if (sd.s2mode == 3) {
-        flags |= F_USE_S2IN;
-        a.s2in = c.buf[c.role[RS]];
-      }
-      if (sd.writeS2) {
-        flags |= F_WRITE_S2;
-        a.s2out = c.buf[c.role[RS]];
-      }
-    }
-    if (sd.final) {
-      flags |= F_FINAL;
-    }
-    if (sd.lowerIsCin) {
-      flags |= F_LOWER_IS_CIN;
-    }
-    if (sd.clampOut) {
-      flags |= F_CLAMP_OUT;
-    }
-    a.flags = flags;
     a.g1 = sd.g1;
     a.g2 = sd.g2;
     a.g3 = sd.g3;
@@ -644,30 +843,22 @@ void Sim::launchStage(const StageDesc &sd, double dt, bool /*unused*/) {
     a.s3F = sd.s3F;
     a.eps = epsilon;
     std::copy(c.D.begin(), c.D.end(), a.D);
-    launchCompartment(ci, a, clampMask, sd.cin);
-    if (&sd == &plan.back()) {
+    launchCompartment(ci, a, c.kStage[stageIndex], c.role[sd.cin]);
+    if (last) {
       c.last = a;
-      c.lastClampMask = clampMask;
-      c.lastCinRole = sd.cin;
+      c.lastCinBuf = c.role[sd.cin];
+      c.lastFlags = sd.flags();
       c.haveLast = true;
     }
   }
-  if (&sd == &plan.back()) {
-    lastCin.resize(comps.size());
-    for (std::size_t ci = 0; ci < comps.size(); ++ci) {
-      lastCin[ci] = comps[ci].S > 0 ? comps[ci].buf[comps[ci].role[sd.cin]]
-                                    : nullptr;
-    }
-  }
-  (void)drv;
 }
 
+// cinBuf: index of the buffer every compartment's stage input lives in (the
+// roles rotate in lock step, so one index serves all compartments)
 void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
-                            uint32_t clampMask, int cinRole) {
+                            const StageKernels &k, int cinBuf) {
   const auto &drv = DriverApi::get();
   auto &c = comps[ci];
-  const unsigned grid = static_cast<unsigned>((c.n + BLOCK - 1) / BLOCK);
-  void *params[] = {&a};
   const bool timed = kernelTiming && ci == dominantComp;
   if (timed) {
     if (timerUsed == timerEvents.size()) {
@@ -679,9 +870,26 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     check(cudaEventRecord(timerEvents[timerUsed].first, stream),
           "cudaEventRecord");
   }
-  check(drv.LaunchKernel(c.kStage, grid, 1, 1, BLOCK, 1, 1, 0, stream, params,
-                         nullptr),
-        "launch stage kernel");
+  const unsigned persistent = static_cast<unsigned>(smCount) * 8u;
+  if (c.geom == Geom::TILE) {
+    uint32_t chunk = c.tile.chunk;
+    void *params[] = {&a, &c.tmap[cinBuf], &chunk};
+    check(drv.LaunchKernel(k.main, c.tile.grid[0], c.tile.grid[1],
+                           c.tile.grid[2], BLOCK, 1, 1, c.tile.dynSmem, stream,
+                           params, nullptr),
+          "launch tile stage kernel");
+  } else {
+    uint64_t work = c.n;
+    if (c.geom == Geom::BOX) {
+      work = static_cast<uint64_t>(a.z_end - a.z_begin) * c.nx * c.ny;
+    }
+    const unsigned grid = static_cast<unsigned>(std::max<uint64_t>(
+        1, std::min<uint64_t>((work + BLOCK - 1) / BLOCK, persistent)));
+    void *params[] = {&a};
+    check(drv.LaunchKernel(k.main, grid, 1, 1, BLOCK, 1, 1, 0, stream, params,
+                           nullptr),
+          "launch stage kernel");
+  }
   ++launchCount;
   if (timed) {
     check(cudaEventRecord(timerEvents[timerUsed].second, stream),
@@ -698,18 +906,15 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     blob[1] = reinterpret_cast<unsigned long long>(c.dMstart);
     blob[2] = reinterpret_cast<unsigned long long>(c.dEnt);
     blob[3] = reinterpret_cast<unsigned long long>(dFluxLen);
-    for (std::size_t k = 0; k < comps.size(); ++k) {
-      const double *pc = nullptr;
-      if (comps[k].S > 0) {
-        pc = cinRole >= 0 ? comps[k].buf[comps[k].role[cinRole]] : lastCin[k];
-      }
-      blob[4 + k] = reinterpret_cast<unsigned long long>(pc);
+    for (std::size_t j = 0; j < comps.size(); ++j) {
+      blob[4 + j] = reinterpret_cast<unsigned long long>(
+          comps[j].S > 0 ? comps[j].buf[cinBuf] : nullptr);
     }
-    blob[4 + comps.size()] = static_cast<unsigned long long>(c.nMvox) |
-                             (static_cast<unsigned long long>(clampMask) << 32);
+    blob[4 + comps.size()] = static_cast<unsigned long long>(c.nMvox);
     void *mparams[] = {&a, blob.data()};
-    const unsigned mgrid = (c.nMvox + BLOCK - 1) / BLOCK;
-    check(drv.LaunchKernel(c.kMemb, mgrid, 1, 1, BLOCK, 1, 1, 0, stream,
+    const unsigned mgrid =
+        std::min((c.nMvox + BLOCK - 1) / BLOCK, persistent);
+    check(drv.LaunchKernel(k.memb, mgrid, 1, 1, BLOCK, 1, 1, 0, stream,
                            mparams, nullptr),
           "launch membrane stage kernel");
     ++launchCount;
@@ -733,8 +938,8 @@ void Sim::flushTimers() {
 }
 
 void Sim::doStep(double dt) {
-  for (const auto &sd : plan) {
-    launchStage(sd, dt, false);
+  for (std::size_t i = 0; i < plan.size(); ++i) {
+    launchStage(i, dt);
   }
   for (auto &c : comps) {
     c.dcdtStale = true;
@@ -746,12 +951,12 @@ void Sim::doStep(double dt) {
 // accepted step: the final stage's output buffer becomes the state; the old
 // state buffer takes its place in the rotation (no copy — the reference's
 // undoRKStep / D2D restore, pixelsim_impl.cpp:759-763, cudapixelsim.cpp:
-// 1476-1484, is simply "do not rotate")
+// 1476-1484, is simply "do not rotate").  The final stage already clamped its
+// output (clampNegativeConcentrations, pixelsim.cpp:268).
 void Sim::rotateAfterAccept() {
   const int outRole = plan.back().cout;
   for (auto &c : comps) {
     std::swap(c.role[CUR], c.role[outRole]);
-    c.curNeedsClamp = integrator != SMEB200_RK101;
   }
 }
 
@@ -922,26 +1127,7 @@ const double *Sim::getConcentrations(std::size_t comp, std::size_t *n) {
   }
   if (c.hostStale && nv > 0 && !ctorFailed) {
     bindDevice();
-    const double *cur = c.buf[c.role[CUR]];
-    if (c.curNeedsClamp) {
-      // materialise the lazy clamp (pixelsim_impl.cpp:643-665) into a scratch
-      // copy: the unclamped state stays untouched because the lower-order
-      // solution of RK435 is defined on it
-      if (c.scratch == nullptr) {
-        c.scratch = devAlloc<double>(nv, "allocate scratch buffer");
-      }
-      unsigned long long nn64 = nv;
-      int clamp = 1;
-      double *out = c.scratch;
-      void *params[] = {&cur, &out, &nn64, &clamp};
-      const unsigned grid = static_cast<unsigned>((nv + BLOCK - 1) / BLOCK);
-      check(DriverApi::get().LaunchKernel(kClampCopy, grid, 1, 1, BLOCK, 1, 1,
-                                          0, stream, params, nullptr),
-            "launch clamp kernel");
-      ++launchCount;
-      cur = c.scratch;
-    }
-    check(cudaMemcpyAsync(c.hostConc, cur, nv * sizeof(double),
+    check(cudaMemcpyAsync(c.hostConc, c.buf[c.role[CUR]], nv * sizeof(double),
                           cudaMemcpyDeviceToHost, stream),
           "download concentrations");
     check(cudaStreamSynchronize(stream), "download concentrations");
@@ -972,8 +1158,23 @@ void Sim::setConcentrations(std::size_t comp, const double *data,
                         cudaMemcpyHostToDevice, stream),
         "upload concentrations");
   check(cudaStreamSynchronize(stream), "upload concentrations");
-  c.curNeedsClamp = false;
   c.hostStale = false;
+}
+
+// re-run the last attempted step's final stage of compartment ci with an
+// on-demand output (dc/dt, lower-order solution or unclamped new state)
+// written to `out`; the stage's inputs are still intact in the rotation
+void Sim::runOnDemand(std::size_t ci, uint32_t flags, double *out) {
+  auto &c = comps[ci];
+  const StageKernels k = onDemandKernels(ci, flags);
+  StageArgsHost a = c.last;
+  a.cout = out;
+  a.s2out = nullptr;
+  a.err = dErrScratch;
+  const bool timing = kernelTiming;
+  kernelTiming = false;
+  launchCompartment(ci, a, k, c.lastCinBuf);
+  kernelTiming = timing;
 }
 
 // dc/dt of the last evaluated stage (PixelSim::getDcdt).  The fused stages
@@ -990,13 +1191,7 @@ void Sim::evaluateLastDcdt() {
     if (c.scratch == nullptr) {
       c.scratch = devAlloc<double>(nv, "allocate scratch buffer");
     }
-    StageArgsHost a = c.last;
-    a.flags = (a.flags & F_CLAMP_CIN) | F_DCDT_ONLY;
-    a.dcdt_out = c.scratch;
-    const bool timing = kernelTiming;
-    kernelTiming = false;
-    launchCompartment(ci, a, c.lastClampMask, -1);
-    kernelTiming = timing;
+    runOnDemand(ci, F_OUT_DCDT, c.scratch);
     c.hostDcdt.resize(nv);
     check(cudaMemcpyAsync(c.hostDcdt.data(), c.scratch, nv * sizeof(double),
                           cudaMemcpyDeviceToHost, stream),
@@ -1040,22 +1235,7 @@ double Sim::getLowerOrder(std::size_t comp, std::size_t species,
     if (c.scratch == nullptr) {
       c.scratch = devAlloc<double>(nv, "allocate scratch buffer");
     }
-    struct {
-      const double *cin, *c0, *s2in, *cnew;
-      double *out;
-      unsigned long long n;
-      uint32_t flags;
-      uint32_t pad;
-      double delta, cF, s2F, s3F;
-    } la{c.last.cin, c.last.c0,     c.last.s2in, c.last.cout, c.scratch,
-         nv,         c.last.flags,  0,           c.last.delta, c.last.cF,
-         c.last.s2F, c.last.s3F};
-    void *params[] = {&la};
-    const unsigned grid = static_cast<unsigned>((nv + BLOCK - 1) / BLOCK);
-    check(DriverApi::get().LaunchKernel(kLower, grid, 1, 1, BLOCK, 1, 1, 0,
-                                        stream, params, nullptr),
-          "launch lower-order kernel");
-    ++launchCount;
+    runOnDemand(comp, c.lastFlags | F_OUT_LOWER, c.scratch);
     c.hostLower.resize(nv);
     check(cudaMemcpyAsync(c.hostLower.data(), c.scratch, nv * sizeof(double),
                           cudaMemcpyDeviceToHost, stream),
@@ -1077,26 +1257,25 @@ void Sim::plotRKError(double relMax, std::string &problemSpecies) {
       continue;
     }
     const std::size_t nv = c.n * c.S;
-    // lower-order solution, new and old state of the failed step
+    // lower-order solution, unclamped new state and old state of the failed
+    // step
     c.lowerStale = true;
     getLowerOrder(ci, 0, 0);
     std::vector<double> cnew(nv), cold(nv);
-    check(cudaMemcpy(cnew.data(), c.last.cout, nv * sizeof(double),
-                     cudaMemcpyDeviceToHost),
+    runOnDemand(ci, (c.lastFlags & ~F_FINAL) | F_OUT_CNEW, c.scratch);
+    check(cudaMemcpyAsync(cnew.data(), c.scratch, nv * sizeof(double),
+                          cudaMemcpyDeviceToHost, stream),
           "download state");
-    check(cudaMemcpy(cold.data(), c.buf[c.role[CUR]], nv * sizeof(double),
-                     cudaMemcpyDeviceToHost),
+    check(cudaMemcpyAsync(cold.data(), c.buf[c.role[CUR]], nv * sizeof(double),
+                          cudaMemcpyDeviceToHost, stream),
           "download state");
+    check(cudaStreamSynchronize(stream), "download state");
     std::size_t iSpecies = c.S + 1;
     for (std::size_t ix = 0; ix < c.n; ++ix) {
       for (std::size_t is = 0; is < c.S; ++is) {
         const std::size_t i = ix * c.S + is;
-        double old = cold[i];
-        if (c.curNeedsClamp && old < 0.0) {
-          old = 0.0;
-        }
         const double localErr = std::abs(cnew[i] - c.hostLower[i]);
-        const double localNorm = 0.5 * (cnew[i] + old + epsilon);
+        const double localNorm = 0.5 * (cnew[i] + cold[i] + epsilon);
         const double pixelIntensity = localErr / localNorm / relMax;
         const int red = static_cast<int>(255.0 * pixelIntensity);
         int x = 0, y = 0, z = 0;

@@ -10,28 +10,33 @@
 #include <atomic>
 #include <cstdint>
 #include <limits>
+#include <map>
 #include <memory>
 #include <string>
 #include <vector>
 
 namespace smeb200 {
 
-// host mirror of the device-side SmebStageArgs<S> header (device_kernels.cuh);
-// the D[3*S] table follows directly.
+// stage flags: compile-time template argument of the stage kernels
+// (device_kernels.cuh SMEB_F_*)
+constexpr uint32_t F_USE_C0 = 1u, F_USE_S2 = 2u, F_USE_S2IN = 4u,
+                   F_WRITE_S2 = 8u, F_FINAL = 16u, F_LOWER_IS_CIN = 32u,
+                   F_CLAMP_OUT = 64u, F_GENERIC = 128u, F_OUT_DCDT = 256u,
+                   F_OUT_LOWER = 512u, F_OUT_CNEW = 1024u;
+
+// host mirror of the device-side SmebStageArgs<S> (device_kernels.cuh); the
+// D[3*S] table is the tail.
 struct StageArgsHost {
   const double *cin;
   const double *c0;
   const double *s2in;
   double *s2out;
   double *cout;
-  double *dcdt_out;
   const uint32_t *nn;
   unsigned long long *err;
   uint32_t n;
   uint32_t nx, ny, nz;
-  uint32_t z_lo_ghost, z_hi_ghost;
-  uint32_t flags;
-  uint32_t pad_;
+  uint32_t z_begin, z_end;
   double g1, g2, g3, bdt, delta;
   double cF, s2F, s3F, eps;
   double D[3 * 64];
@@ -49,9 +54,27 @@ struct StageDesc {
   bool useC0{false};
   int s2mode{0}; // 0 none, 1 starts at zero, 2 read from CUR, 3 read from RS
   bool writeS2{false};
+  bool generic{false};
   double g1{1}, g2{0}, g3{0}, beta{1}, delta{0};
   bool final{false}, lowerIsCin{false}, clampOut{false};
   double cF{0}, s2F{0}, s3F{0};
+  uint32_t flags() const;
+};
+
+enum class Geom { NN, BOX, TILE };
+
+// kernel pair for one compartment and one set of stage flags
+struct StageKernels {
+  CUfunction main{nullptr};
+  CUfunction memb{nullptr};
+};
+
+struct TileConfig {
+  int tx{0}, ty{0}, nst{0};
+  bool m3{true};
+  uint32_t chunk{1};
+  unsigned grid[3]{1, 1, 1};
+  unsigned dynSmem{0};
 };
 
 struct CompartmentState {
@@ -59,21 +82,23 @@ struct CompartmentState {
   uint64_t n{0};
   uint32_t S{0};
   bool box{false};
+  Geom geom{Geom::NN};
   uint32_t nx{0}, ny{0}, nz{0};
+  uint32_t zLoGhost{0}, zHiGhost{0}; // z-slab ghost planes (read, not updated)
+  TileConfig tile;
   std::vector<std::string> speciesNames;
   std::vector<double> D;
   std::vector<int32_t> voxels;
   int nbuf{0};
   double *buf[4]{nullptr, nullptr, nullptr, nullptr};
+  CUtensorMap tmap[4]{};
   int role[4]{0, 1, 2, 3};
-  bool curNeedsClamp{false};
   uint32_t *dNn{nullptr};
   uint32_t nMvox{0};
   uint32_t *dMvox{nullptr};
   uint32_t *dMstart{nullptr};
   MembEntryHost *dEnt{nullptr};
-  CUfunction kStage{nullptr};
-  CUfunction kMemb{nullptr};
+  std::vector<StageKernels> kStage; // per plan stage
   // host mirrors
   double *hostConc{nullptr}; // pinned
   bool hostStale{true};
@@ -84,8 +109,8 @@ struct CompartmentState {
   // record of the last attempted step's final stage (getDcdt / lower order)
   bool haveLast{false};
   StageArgsHost last{};
-  uint32_t lastClampMask{0};
-  int lastCinRole{0};
+  int lastCinBuf{0};
+  uint32_t lastFlags{0};
 };
 
 class Sim {
@@ -124,6 +149,7 @@ public:
   double kernelMs{0};
   uint64_t kernelLaunchesTimed{0};
   std::string kernelSource;
+  std::string dominantKernelName;
   bool compileOnly{false};
   std::size_t cubinBytes{0};
   std::size_t nCompartments() const { return comps.size(); }
@@ -131,41 +157,52 @@ public:
   void *allreduceUser{nullptr};
 
 private:
+  struct Module {
+    CUmodule mod{nullptr};
+    std::map<std::string, CUfunction> fn;
+  };
   void build(const smeb200_problem &p);
   void generateSource(const smeb200_problem &p);
-  void compileModule();
+  Module compile(const std::vector<std::string> &names);
+  std::string kernelName(std::size_t ci, uint32_t flags, bool memb) const;
+  StageKernels lookup(const Module &m, std::size_t ci, uint32_t flags) const;
+  StageKernels onDemandKernels(std::size_t ci, uint32_t flags);
+  void chooseGeometry(int variant);
+  void encodeTensorMaps(CompartmentState &c);
   void setupMembranes(const smeb200_problem &p,
                       std::vector<std::vector<uint32_t>> &nnHost);
   void makePlan();
   void bindDevice() const;
-  void doStep(double dt);           // all stages of one RK step
-  void launchStage(const StageDesc &sd, double dt, bool dcdtOnly);
-  void launchCompartment(std::size_t ci, StageArgsHost &a, uint32_t clampMask,
-                         int cinRole);
+  void doStep(double dt); // all stages of one RK step
+  void launchStage(std::size_t stageIndex, double dt);
+  void launchCompartment(std::size_t ci, StageArgsHost &a,
+                         const StageKernels &k, int cinBuf);
   void rotateAfterAccept();
   void readError(double &eabs, double &erel);
   double doRK101(double dt);
   double doRKAdaptive(double dtMax);
   void plotRKError(double relMax, std::string &problemSpecies);
+  void runOnDemand(std::size_t ci, uint32_t flags, double *out);
   void evaluateLastDcdt();
   void flushTimers();
 
   int device{0};
   cudaStream_t stream{nullptr};
-  CUmodule module{nullptr};
-  CUfunction kLower{nullptr}, kClampCopy{nullptr};
+  Module mainModule;
+  std::vector<Module> auxModules;
+  std::map<std::string, CUfunction> auxFn;
   std::vector<CompartmentState> comps;
   std::vector<StageDesc> plan;
   std::vector<double> fluxLen;
   double *dFluxLen{nullptr};
   uint32_t nMembranes{0};
   unsigned long long *dErr{nullptr};
+  unsigned long long *dErrScratch{nullptr};
   unsigned long long *hErr{nullptr}; // pinned
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timerEvents;
   std::size_t timerUsed{0};
   int imageNx{0}, imageNy{0}, imageNz{0};
-  std::vector<std::string> stageNames, membNames;
-  std::vector<const double *> lastCin;
+  int smCount{148};
   std::size_t dominantComp{0};
 };
 

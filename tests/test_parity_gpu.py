@@ -52,10 +52,25 @@ def fixed_step(problem, dt):
     return problem
 
 
+def _variant(problem, v):
+    problem.kernel_variant = v
+    return problem
+
+
 GEOMETRIES = {
     "box3d": lambda integ: M.box_problem(M.GRAY_SCOTT, 19, 23, 7, integrator=integ,
                                          voxel_size=(2.0, 2.0, 2.0)),
     "box2d": lambda integ: M.box_problem(M.GRAY_SCOTT, 64, 48, 1, integrator=integ),
+    "box3d_direct": lambda integ: _variant(M.box_problem(
+        M.GRAY_SCOTT, 19, 23, 7, integrator=integ, voxel_size=(2.0, 2.0, 2.0)), 1),
+    "box2d_direct": lambda integ: _variant(M.box_problem(
+        M.GRAY_SCOTT, 64, 48, 1, integrator=integ), 1),
+    # several tiles in x and y, several z chunks, ragged tile edges
+    "box3d_tiles": lambda integ: _variant(M.box_problem(
+        M.GRAY_SCOTT, 44, 150, 70, integrator=integ, voxel_size=(1.0, 2.0, 1.5)), 2),
+    # 2-D: several y strips, several x chunks of bricks, ragged edges
+    "box2d_tiles": lambda integ: _variant(M.box_problem(
+        M.BRUSSELATOR, 300, 200, 1, integrator=integ), 2),
     "box_as_list": lambda integ: M.box_problem(M.BRUSSELATOR, 17, 9, 4, integrator=integ,
                                                as_voxel_list=True),
     "abtoc_disc": lambda integ: M.labelled_problem(
@@ -89,7 +104,7 @@ def test_fixed_step_run(geom, integ):
     assert gpu.discardedSteps == cpu.discardedSteps == 0
 
 
-@pytest.mark.parametrize("geom", ["box3d", "abtoc_disc", "membranes2d"])
+@pytest.mark.parametrize("geom", ["box3d", "box3d_direct", "box2d_tiles", "abtoc_disc", "membranes2d"])
 @pytest.mark.parametrize("integ", [smeb.RK212, smeb.RK323, smeb.RK435])
 def test_adaptive_run(geom, integ):
     """adaptive runs: same accepted/discarded step counts and a final state well
