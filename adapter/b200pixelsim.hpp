@@ -1,0 +1,385 @@
+// B200PixelSim — SME-side adapter for libsmeb200.so (include/smeb200.h).
+//
+// Drop this header into core/simulate/src/ of Spatial Model Editor and link
+// libsmeb200.so.  The class has the constructor contract of PixelSim /
+// CudaPixelSim (pixelsim.hpp:52-56, cudapixelsim.hpp:59-63), derives from
+// PixelSimBase (pixelsim_base.hpp:17-50) and forwards every BaseSim virtual
+// (basesim.hpp:24-54) to one C-ABI entry point.  It fills smeb200_problem from
+// sme::model::Model exactly as CudaPixelSim's constructor does
+// (cudapixelsim.cpp:770-1168): nn table as uint32, D/dx^2 table, AoS initial
+// concentrations, ReacExpr -> Symbolic -> relabel -> cudaCode strings, per-face
+// membrane pair lists, restart concentrations.
+//
+// It is written against the reference headers and is NOT compiled in this
+// repository (Qt6 / SymEngine / libSBML are not installed here); INTEGRATION.md
+// shows the patch to simulate.cpp that selects it.
+#pragma once
+
+#include "pixelsim_base.hpp"
+#include "pixelsim_common.hpp"
+#include "pixelsim_impl.hpp" // ReacExpr
+#include "sme/geometry.hpp"
+#include "sme/model.hpp"
+#include "sme/symbolic.hpp"
+#include "sme/utils.hpp"
+#include "smeb200.h"
+#include <QImage>
+#include <array>
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace sme::simulate {
+
+class B200PixelSim : public PixelSimBase {
+private:
+  struct SimDeleter {
+    void operator()(smeb200_sim *s) const { smeb200_destroy(s); }
+  };
+  std::unique_ptr<smeb200_sim, SimDeleter> sim;
+  const model::Model &doc;
+  std::size_t nCompartments{0};
+  // BaseSim returns references: host mirrors owned here
+  mutable std::vector<std::vector<double>> conc;
+  mutable std::vector<std::vector<double>> dcdt;
+
+  static std::vector<std::string>
+  cudaExpressions(const std::vector<std::string> &variables,
+                  const std::vector<std::string> &expressions) {
+    // cudapixelsim.cpp:108-136
+    std::vector<std::string> safe;
+    for (std::size_t i = 0; i < variables.size(); ++i) {
+      safe.push_back("sme_var_" + std::to_string(i));
+    }
+    common::Symbolic symbolic{expressions, variables};
+    if (!symbolic.isValid()) {
+      throw std::runtime_error("Failed to convert reaction expression to CUDA "
+                               "code: " +
+                               symbolic.getErrorMessage());
+    }
+    symbolic.relabel(safe);
+    std::vector<std::string> out;
+    for (std::size_t i = 0; i < expressions.size(); ++i) {
+      out.push_back(symbolic.cudaCode(i, false));
+    }
+    return out;
+  }
+
+  void syncErrorState() {
+    currentErrorMessage = smeb200_error(sim.get());
+    const std::uint32_t *px{nullptr};
+    std::size_t n{0};
+    smeb200_error_images(sim.get(), &px, &n);
+    if (n > 0) {
+      const auto size{doc.getGeometry().getImages().volume()};
+      currentErrorImages = common::ImageStack(size, QImage::Format_ARGB32);
+      std::size_t i{0};
+      for (std::size_t z = 0; z < size.depth(); ++z) {
+        for (int y = 0; y < size.height(); ++y) {
+          for (int x = 0; x < size.width(); ++x) {
+            currentErrorImages[z].setPixel(x, y, px[i++]);
+          }
+        }
+      }
+    }
+  }
+
+public:
+  explicit B200PixelSim(
+      const model::Model &sbmlDoc,
+      const std::vector<std::string> &compartmentIds,
+      const std::vector<std::vector<std::string>> &compartmentSpeciesIds,
+      const std::map<std::string, double, std::less<>> &substitutions = {})
+      : PixelSimBase{sbmlDoc.getSimulationSettings().options.pixel.integrator,
+                     sbmlDoc.getSimulationSettings().options.pixel.maxErr,
+                     sbmlDoc.getSimulationSettings().options.pixel.maxTimestep},
+        doc{sbmlDoc} {
+    try {
+      smeb200_problem p{};
+      p.abi_version = SMEB200_ABI_VERSION;
+      p.integrator = static_cast<int32_t>(integrator);
+      p.max_err_abs = errMax.abs;
+      p.max_err_rel = errMax.rel;
+      p.max_timestep = maxTimestep;
+      p.device = -1;
+      const auto imageSize{doc.getGeometry().getImages().volume()};
+      p.image_nx = imageSize.width();
+      p.image_ny = imageSize.height();
+      p.image_nz = static_cast<int32_t>(imageSize.depth());
+      // feature gates, same as cudapixelsim.cpp:789-809
+      if (hasAnyCrossDiffusion(doc, compartmentSpeciesIds)) {
+        p.unsupported |= SMEB200_HAS_CROSS_DIFFUSION;
+      }
+      const auto &coords{doc.getParameters().getSpatialCoordinates()};
+      if (doc.getReactions().dependOnVariable("time")) {
+        p.unsupported |= SMEB200_HAS_TIME_DEPENDENCE;
+      }
+      if (doc.getReactions().dependOnVariable(coords.x.id.c_str()) ||
+          doc.getReactions().dependOnVariable(coords.y.id.c_str()) ||
+          doc.getReactions().dependOnVariable(coords.z.id.c_str())) {
+        p.unsupported |= SMEB200_HAS_SPACE_DEPENDENCE;
+      }
+      const auto voxelSize{doc.getGeometry().getVoxelSize()};
+      const double dx2 = voxelSize.width() * voxelSize.width();
+      const double dy2 = voxelSize.height() * voxelSize.height();
+      const double dz2 = voxelSize.depth() * voxelSize.depth();
+
+      nCompartments = compartmentIds.size();
+      std::vector<smeb200_compartment> comps(nCompartments);
+      std::vector<std::vector<std::uint32_t>> nn(nCompartments);
+      std::vector<std::vector<std::int32_t>> voxels(nCompartments);
+      std::vector<std::vector<double>> diffusion(nCompartments);
+      std::vector<std::vector<std::string>> exprs(nCompartments);
+      std::vector<std::vector<const char *>> exprPtrs(nCompartments);
+      std::vector<std::vector<const char *>> namePtrs(nCompartments);
+      std::map<std::string, std::size_t, std::less<>> compIndexById;
+      conc.resize(nCompartments);
+      dcdt.resize(nCompartments);
+      for (std::size_t ci = 0; ci < nCompartments; ++ci) {
+        const auto &speciesIds{compartmentSpeciesIds[ci]};
+        const auto *comp{doc.getCompartments().getCompartment(
+            compartmentIds[ci].c_str())};
+        compIndexById[comp->getId()] = ci;
+        const std::size_t n{comp->nVoxels()};
+        const std::size_t S{speciesIds.size()};
+        auto &c{comps[ci]};
+        c.id = comp->getId().c_str();
+        c.n_voxels = n;
+        c.n_species = static_cast<std::uint32_t>(S);
+        // a compartment that fills the whole image needs no neighbour table:
+        // the library then uses the TMA tile kernel with implicit neighbours
+        const bool fillsImage{n == static_cast<std::size_t>(p.image_nx) *
+                                       p.image_ny * p.image_nz};
+        voxels[ci].reserve(3 * n);
+        for (std::size_t i = 0; i < n; ++i) {
+          const auto &v{comp->getVoxel(i)};
+          voxels[ci].push_back(v.p.x());
+          voxels[ci].push_back(v.p.y());
+          voxels[ci].push_back(static_cast<std::int32_t>(v.z));
+        }
+        c.voxels = voxels[ci].data();
+        if (fillsImage) {
+          c.box_nx = p.image_nx;
+          c.box_ny = p.image_ny;
+          c.box_nz = p.image_nz;
+          c.nn = nullptr;
+        } else {
+          nn[ci].reserve(6 * n); // cudapixelsim.cpp:877-890
+          for (std::size_t i = 0; i < n; ++i) {
+            nn[ci].push_back(static_cast<std::uint32_t>(comp->up_x(i)));
+            nn[ci].push_back(static_cast<std::uint32_t>(comp->dn_x(i)));
+            nn[ci].push_back(static_cast<std::uint32_t>(comp->up_y(i)));
+            nn[ci].push_back(static_cast<std::uint32_t>(comp->dn_y(i)));
+            nn[ci].push_back(static_cast<std::uint32_t>(comp->up_z(i)));
+            nn[ci].push_back(static_cast<std::uint32_t>(comp->dn_z(i)));
+          }
+          c.nn = nn[ci].data();
+        }
+        std::vector<const geometry::Field *> fields;
+        for (const auto &speciesId : speciesIds) {
+          const auto *field{doc.getSpecies().getField(speciesId.c_str())};
+          if (field == nullptr) {
+            throw std::runtime_error("could not find field for species '" +
+                                     speciesId + "'");
+          }
+          if (!field->getIsSpatial()) {
+            p.unsupported |= SMEB200_HAS_NON_SPATIAL_SPECIES;
+          }
+          if (!field->getIsUniformDiffusionConstant()) {
+            p.unsupported |= SMEB200_HAS_NON_UNIFORM_DIFFUSION;
+          }
+          if (doc.getSpecies().getStorage(speciesId.c_str()) != 1.0) {
+            p.unsupported |= SMEB200_HAS_NON_UNIT_STORAGE;
+          }
+          fields.push_back(field);
+          const auto &d{field->getDiffusionConstant()};
+          const double dc{d.empty() ? 0.0 : d.front()};
+          diffusion[ci].push_back(dc / dx2);
+          diffusion[ci].push_back(dc / dy2);
+          diffusion[ci].push_back(dc / dz2);
+          namePtrs[ci].push_back(speciesId.c_str());
+        }
+        c.diffusion = diffusion[ci].data();
+        c.species_names = namePtrs[ci].data();
+        conc[ci].resize(n * S);
+        auto it{conc[ci].begin()};
+        for (std::size_t ix = 0; ix < n; ++ix) {
+          for (const auto *field : fields) {
+            *it++ = field->getConcentration()[ix];
+          }
+        }
+        c.conc0 = conc[ci].data();
+        dcdt[ci].assign(n * S, 0.0);
+        std::vector<std::string> reactionIDs;
+        if (auto r{doc.getReactions().getIds(comp->getId().c_str())};
+            !r.isEmpty()) {
+          reactionIDs = common::toStdString(r);
+        }
+        const ReacExpr reacExpr(doc, speciesIds, reactionIDs, 1.0, false, false,
+                                substitutions);
+        exprs[ci] = cudaExpressions(reacExpr.variables, reacExpr.expressions);
+        for (const auto &e : exprs[ci]) {
+          exprPtrs[ci].push_back(e.c_str());
+        }
+        c.expressions = exprPtrs[ci].data();
+      }
+      // restart concentrations (pixelsim.cpp:399-406)
+      const auto &data{doc.getSimulationData()};
+      if (data.concentration.size() > 1 && !data.concentration.back().empty() &&
+          data.concentration.back().size() == nCompartments) {
+        for (std::size_t ci = 0; ci < nCompartments; ++ci) {
+          if (data.concentration.back()[ci].size() == conc[ci].size()) {
+            conc[ci] = data.concentration.back()[ci];
+            comps[ci].conc0 = conc[ci].data();
+          }
+        }
+      }
+      // membranes with reactions (cudapixelsim.cpp:1020-1096)
+      const auto &lengthUnit{doc.getUnits().getLength()};
+      const auto &volumeUnit{doc.getUnits().getVolume()};
+      const double volOverL3{model::getVolOverL3(lengthUnit, volumeUnit)};
+      std::vector<smeb200_membrane> membs;
+      std::vector<std::array<std::vector<std::uint32_t>, 6>> pairs;
+      std::vector<std::vector<std::string>> mExprs;
+      std::vector<std::vector<const char *>> mExprPtrs;
+      const auto &membranes{doc.getMembranes().getMembranes()};
+      pairs.reserve(membranes.size());
+      mExprs.reserve(membranes.size());
+      mExprPtrs.reserve(membranes.size());
+      for (const auto &membrane : membranes) {
+        auto reacs{doc.getReactions().getIds(membrane.getId().c_str())};
+        if (reacs.isEmpty()) {
+          continue;
+        }
+        smeb200_membrane m{};
+        m.id = membrane.getId().c_str();
+        m.comp_a = m.comp_b = -1;
+        std::vector<std::string> speciesIds;
+        if (auto it{compIndexById.find(membrane.getCompartmentA()->getId())};
+            it != compIndexById.end()) {
+          m.comp_a = static_cast<int32_t>(it->second);
+          const auto &s{compartmentSpeciesIds[it->second]};
+          speciesIds.insert(speciesIds.end(), s.begin(), s.end());
+        }
+        if (auto it{compIndexById.find(membrane.getCompartmentB()->getId())};
+            it != compIndexById.end()) {
+          m.comp_b = static_cast<int32_t>(it->second);
+          const auto &s{compartmentSpeciesIds[it->second]};
+          speciesIds.insert(speciesIds.end(), s.begin(), s.end());
+        }
+        if (speciesIds.empty()) {
+          continue;
+        }
+        const ReacExpr reacExpr(doc, speciesIds, common::toStdString(reacs),
+                                volOverL3, false, false, substitutions);
+        mExprs.push_back(
+            cudaExpressions(reacExpr.variables, reacExpr.expressions));
+        mExprPtrs.emplace_back();
+        for (const auto &e : mExprs.back()) {
+          mExprPtrs.back().push_back(e.c_str());
+        }
+        m.expressions = mExprPtrs.back().data();
+        pairs.emplace_back();
+        for (std::size_t d = 0; d < 6; ++d) {
+          const auto dir{static_cast<geometry::Membrane::FACE_DIRECTION>(d)};
+          const auto &facePairs{membrane.getFaceIndexPairs(dir)};
+          auto &flat{pairs.back()[d]};
+          for (const auto &[ixA, ixB] : facePairs) {
+            flat.push_back(static_cast<std::uint32_t>(ixA));
+            flat.push_back(static_cast<std::uint32_t>(ixB));
+          }
+          m.n_pairs[d] = facePairs.size();
+          m.pairs[d] = flat.data();
+          m.flux_length[d] = getFaceFluxLength(dir, voxelSize);
+        }
+        membs.push_back(m);
+      }
+      p.n_compartments = static_cast<std::uint32_t>(comps.size());
+      p.compartments = comps.data();
+      p.n_membranes = static_cast<std::uint32_t>(membs.size());
+      p.membranes = membs.data();
+      smeb200_sim *raw{nullptr};
+      smeb200_create(&p, &raw);
+      sim.reset(raw);
+      if (!sim) {
+        throw std::runtime_error("smeb200_create failed");
+      }
+      currentErrorMessage = smeb200_error(sim.get());
+      maxStableTimestep = smeb200_get_max_stable_timestep(sim.get());
+    } catch (const std::exception &e) {
+      // like the reference constructors: never throw (pixelsim.cpp:415-418)
+      currentErrorMessage = e.what();
+    }
+  }
+
+  std::size_t run(double time, double timeout_ms,
+                  const std::function<bool()> &stopRunningCallback) override {
+    if (!sim || !currentErrorMessage.empty()) {
+      return 0; // cudapixelsim.cpp:1621-1623
+    }
+    smeb200_set_stop_requested(sim.get(), stopRequested.load() ? 1 : 0);
+    auto trampoline = [](void *user) -> int {
+      const auto &cb{*static_cast<const std::function<bool()> *>(user)};
+      return cb && cb() ? 1 : 0;
+    };
+    const std::size_t steps{smeb200_run(
+        sim.get(), time, timeout_ms, trampoline,
+        const_cast<void *>(static_cast<const void *>(&stopRunningCallback)))};
+    stopRequested.store(smeb200_get_stop_requested(sim.get()) != 0);
+    discardedSteps = smeb200_get_discarded_steps(sim.get());
+    nextTimestep = smeb200_get_next_timestep(sim.get());
+    syncErrorState();
+    return steps;
+  }
+
+  void setStopRequested(bool stop) override {
+    stopRequested.store(stop);
+    if (sim) {
+      smeb200_set_stop_requested(sim.get(), stop ? 1 : 0); // thread-safe
+    }
+  }
+
+  [[nodiscard]] const std::vector<double> &
+  getConcentrations(std::size_t compartmentIndex) const override {
+    if (sim) {
+      const double *data{nullptr};
+      std::size_t n{0};
+      if (smeb200_get_concentrations(sim.get(), compartmentIndex, &data, &n) ==
+          0) {
+        conc[compartmentIndex].assign(data, data + n);
+      }
+    }
+    return conc[compartmentIndex];
+  }
+
+  [[nodiscard]] std::size_t getConcentrationPadding() const override {
+    return 0;
+  }
+
+  [[nodiscard]] const std::vector<double> &
+  getDcdt(std::size_t compartmentIndex) const {
+    if (sim) {
+      const double *data{nullptr};
+      std::size_t n{0};
+      if (smeb200_get_dcdt(sim.get(), compartmentIndex, &data, &n) == 0) {
+        dcdt[compartmentIndex].assign(data, data + n);
+      }
+    }
+    return dcdt[compartmentIndex];
+  }
+
+  [[nodiscard]] double getLowerOrderConcentration(std::size_t compartmentIndex,
+                                                  std::size_t speciesIndex,
+                                                  std::size_t pixelIndex) const {
+    double v{0.0};
+    if (sim) {
+      smeb200_get_lower_order(sim.get(), compartmentIndex, speciesIndex,
+                              pixelIndex, &v);
+    }
+    return v;
+  }
+};
+
+} // namespace sme::simulate

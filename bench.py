@@ -108,50 +108,65 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def cpu_baseline(args, integrator, threads, budget_s=20.0):
-    """the CPU restatement of the reference TBB Pixel path on a bounded sample of
-    the same workload: a slab of the same model, sized for ~10-30 s"""
-    from oracle.oracle_sim import OraclePixelSim
-    nx = ny = min(args.size, 256)
-    nz = 16
-    p = make_problem(nx, ny, nz, integrator)
-    sim = OraclePixelSim(p, threads=threads)
-    sim.nextTimestep = DT  # skip the controller's 1e-7 start-up step
-    sim.run(DT)    # warm-up
-    evals_per_step = p.evals_per_step()
+def cpu_sample_problem(args, integrator, nz):
+    """a slab of the bench workload for the CPU arm: same kinetics, same x-y
+    extent (capped at 512), nz planes"""
+    nx = ny = min(args.size, 512)
+    nz = 1 if (args.nz == 1) else nz
+    return make_problem(nx, ny, nz, integrator), (nx, ny, nz)
+
+
+def time_oracle(sim, evals_per_step, budget_s, max_steps):
+    """run fixed steps of DT until the time budget or the step cap is reached"""
     t0 = time.perf_counter()
     steps = 0
     while True:
-        steps += sim.run(2 * DT)
+        steps += sim.run(DT)
         el = time.perf_counter() - t0
-        if el > budget_s or steps >= 40:
+        if el > budget_s or steps >= max_steps:
             break
+    return evals_per_step * steps / el, steps, el
+
+
+def cpu_baseline(args, integrator, threads, budget_s=12.0):
+    """the CPU restatement of the reference TBB Pixel path on a bounded sample of
+    the same workload (a 32-plane slab of the same x-y extent, about 10-20 s of
+    CPU work), all host threads"""
+    from oracle.oracle_sim import OraclePixelSim
+    p, (nx, ny, nz) = cpu_sample_problem(args, integrator, 32)
+    sim = OraclePixelSim(p, threads=threads)
+    sim.nextTimestep = DT  # skip the controller's 1e-7 start-up step
+    sim.run(DT)    # warm-up
+    value, steps, el = time_oracle(sim, p.evals_per_step(), budget_s, 100000)
     ncores = OraclePixelSim.maxThreads() if threads == 0 else threads
-    return {"value": evals_per_step * steps / el, "unit": UNIT, "cores": ncores,
+    return {"value": value, "unit": UNIT, "cores": ncores,
             "kind": "port",
-            "sample": f"gray-scott-3d RK212 fixed step, {nx}x{ny}x{nz} slab "
-                      f"({nx * ny * nz} voxels x 2 species), {steps} steps, {el:.1f} s, "
+            "sample": f"gray-scott-3d {args.integrator.upper()} fixed step, {nx}x{ny}x{nz} "
+                      f"slab ({nx * ny * nz} voxels x 2 species), {steps} steps, {el:.1f} s, "
                       f"OpenMP threads={ncores}"}
 
 
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU implementation of the path — here the
-    oracle port (the reference cannot be built: see DESIGN.md), all host threads"""
+    oracle port (the reference cannot be built: see DESIGN.md), all host threads.
+    Each step is one RK step over a bounded sample (a 32-plane slab) of the
+    workload."""
     if rank != 0:
         return
-    import spatial_model_editor_b200 as smeb
+    from spatial_model_editor_b200.problem import INTEGRATOR_NAMES
     from oracle.oracle_sim import OraclePixelSim
-    nx = ny = min(args.size, 256)
-    nz = 32
-    p = make_problem(nx, ny, nz, smeb.RK212)
+    integrator = INTEGRATOR_NAMES[args.integrator]
+    p, (nx, ny, nz) = cpu_sample_problem(args, integrator, 32)
     sim = OraclePixelSim(p, threads=0)
     sim.nextTimestep = DT
-    for _ in range(args.warmup):
+    for _ in range(max(args.warmup, 1)):
         sim.run(DT)
     t0 = time.perf_counter()
     steps = 0
     for _ in range(args.steps):
         steps += sim.run(DT)
+        if time.perf_counter() - t0 > 120.0:
+            break
     el = time.perf_counter() - t0
     value = p.evals_per_step() * steps / el
     cores = OraclePixelSim.maxThreads()
@@ -162,7 +177,8 @@ def run_reference(args, rank, world):
         "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * el / max(steps, 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"gray-scott-3d RK212 fixed-step, {sample}"},
+        "config": {"workload": f"gray-scott-3d {args.integrator.upper()} fixed-step dt={DT}, "
+                               f"{sample}"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0,
@@ -274,12 +290,20 @@ def main():
     bytes_per_value_step = {0: 16, 1: 40, 2: 64, 3: 152}[integrator]
     alg_bytes_per_launch = bytes_per_value_step * values_per_rank / STAGES[integrator]
     peak, peak_src = measured_peak()
+    traffic = None
+    try:  # ncu dram__bytes of the same kernel on the headline config (profiles/)
+        with open(os.path.join(ROOT, "profiles", "r1_v2_traffic.json")) as f:
+            tj = json.load(f)
+        if (nx, ny, nz, args.integrator) == (512, 512, 512, "rk212"):
+            traffic = tj["dram_bytes_per_launch"]["mean"]
+    except Exception:
+        traffic = None
     roofline = None
     if klaunches:
         achieved = alg_bytes_per_launch / (kms / klaunches * 1e-3) / 1e9
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                    "kernel": sim.dominantKernel() if hasattr(sim, "dominantKernel") else "stage kernel", "launches_timed": klaunches,
+                    "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                    "kernel": sim.dominantKernel(), "launches_timed": klaunches,
                     "avg_launch_ms": kms / klaunches,
                     "algorithmic_bytes_per_launch": alg_bytes_per_launch}
     cpu = None

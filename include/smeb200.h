@@ -47,10 +47,11 @@ enum smeb200_face { SMEB200_XP = 0, SMEB200_XM, SMEB200_YP, SMEB200_YM,
  * fails with the same message text as the reference. */
 enum smeb200_unsupported {
   SMEB200_HAS_CROSS_DIFFUSION = 1,
-  SMEB200_HAS_TIME_OR_SPACE_DEPENDENCE = 2,
+  SMEB200_HAS_TIME_DEPENDENCE = 2,
   SMEB200_HAS_NON_SPATIAL_SPECIES = 4,
   SMEB200_HAS_NON_UNIFORM_DIFFUSION = 8,
-  SMEB200_HAS_NON_UNIT_STORAGE = 16
+  SMEB200_HAS_NON_UNIT_STORAGE = 16,
+  SMEB200_HAS_SPACE_DEPENDENCE = 32
 };
 
 /* One geometry::Compartment + SimCompartment (pixelsim_impl.hpp:58-322). */
@@ -118,8 +119,9 @@ typedef struct smeb200_problem {
   /* z-slab decomposition of box compartments over `n_ranks` processes, one
    * GPU each (0/1 = single GPU).  See smeb200_slab_* below. */
   int32_t rank, n_ranks;
-  /* kernel variant: 0 = auto, 1 = direct-gather kernels only,
-   * 2 = TMA-staged z-marching kernel for box compartments */
+  /* kernel variant: 0 = auto (TMA tile-marching kernel for box compartments
+   * where the shape allows it), 1 = direct-gather kernels only, 2 = require
+   * the TMA tile kernel for box compartments (error if it cannot be used) */
   int32_t kernel_variant;
   uint32_t reserved[7];
 } smeb200_problem;
@@ -200,6 +202,10 @@ int smeb200_get_kernel_timing(const smeb200_sim *sim, double *total_ms,
                               uint64_t *launches);
 /* generated CUDA source of the model module (for inspection / tests) */
 const char *smeb200_kernel_source(const smeb200_sim *sim);
+/* name expression of the stage kernel that set_kernel_timing times: the final
+ * stage of the largest compartment, e.g.
+ * "smeb_stage_tile<Reac0, 113u, 16, 64, 5, true>" */
+const char *smeb200_dominant_kernel(const smeb200_sim *sim);
 
 /* ---- multi-GPU ---------------------------------------------------------- */
 /* error-norm exchange for the adaptive controller: the host supplies an

@@ -205,6 +205,10 @@ const char *smeb200_kernel_source(const smeb200_sim *sim) {
   return sim != nullptr ? sim->impl.kernelSource.c_str() : "";
 }
 
+const char *smeb200_dominant_kernel(const smeb200_sim *sim) {
+  return sim != nullptr ? sim->impl.dominantKernelName.c_str() : "";
+}
+
 void smeb200_set_allreduce_max(smeb200_sim *sim, smeb200_allreduce_max_fn fn,
                                void *user) {
   if (sim != nullptr) {

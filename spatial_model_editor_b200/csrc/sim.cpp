@@ -581,11 +581,15 @@ void Sim::build(const smeb200_problem &p) {
   // feature gates of the reference GPU backend, same texts
   // (cudapixelsim.cpp:789-809, pixelsim_common.hpp:80-121)
   if (p.unsupported & SMEB200_HAS_CROSS_DIFFUSION) {
-    throw Error("CUDA pixel backend does not yet support cross-diffusion");
+    throw Error("CUDA pixel backend PoC does not yet support cross-diffusion");
   }
-  if (p.unsupported & SMEB200_HAS_TIME_OR_SPACE_DEPENDENCE) {
-    throw Error("CUDA pixel backend does not yet support time- or "
-                "space-dependent reaction terms");
+  if (p.unsupported & SMEB200_HAS_TIME_DEPENDENCE) {
+    throw Error("CUDA pixel backend PoC does not yet support time-dependent "
+                "reaction terms");
+  }
+  if (p.unsupported & SMEB200_HAS_SPACE_DEPENDENCE) {
+    throw Error("CUDA pixel backend PoC does not yet support spatially "
+                "dependent reaction terms");
   }
   if (p.unsupported & SMEB200_HAS_NON_SPATIAL_SPECIES) {
     throw Error("CUDA pixel backend PoC does not yet support non-spatial "

@@ -68,6 +68,7 @@ def _bind(lib, prefix: str):
     fn("get_kernel_timing", C.c_int,
        [vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)], optional=True)
     fn("kernel_source", C.c_char_p, [vp], optional=True)
+    fn("dominant_kernel", C.c_char_p, [vp], optional=True)
     fn("set_allreduce_max", None, [vp, _ALLREDUCE_CB, vp], optional=True)
     # oracle-only
     fn("set_threads", None, [vp, C.c_int], optional=True)
@@ -238,6 +239,9 @@ class PixelSim(CSim):
         n = C.c_uint64()
         self._f("get_kernel_timing")(self._h, C.byref(ms), C.byref(n))
         return ms.value, int(n.value)
+
+    def dominantKernel(self) -> str:
+        return self._f("dominant_kernel")(self._h).decode()
 
     def kernelSource(self) -> str:
         return self._f("kernel_source")(self._h).decode()

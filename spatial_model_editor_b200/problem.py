@@ -20,7 +20,8 @@ STAGES = {RK101: 1, RK212: 2, RK323: 3, RK435: 5}
 DBL_MAX = float(np.finfo(np.float64).max)
 
 HAS_CROSS_DIFFUSION = 1
-HAS_TIME_OR_SPACE_DEPENDENCE = 2
+HAS_TIME_DEPENDENCE = 2
+HAS_SPACE_DEPENDENCE = 32
 HAS_NON_SPATIAL_SPECIES = 4
 HAS_NON_UNIFORM_DIFFUSION = 8
 HAS_NON_UNIT_STORAGE = 16
