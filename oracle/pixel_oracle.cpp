@@ -15,9 +15,10 @@
 // gcc -O2 -ffp-contract=off and dlopen'ed.  Threading: OpenMP static chunks
 // stand in for TBB static_partitioner (pixelsim_impl.cpp:26-33).
 //
-// Parity pin: tests/test_oracle_kat.py checks this oracle against the
-// reference's own known-answer tests (simulate_t.cpp:99-275, 882-994,
-// pixelsim_t.cpp) restated in Python.
+// Parity pin: PINNED.  tests/test_golden_cpu.py checks this oracle against the
+// reference's own known-answer tests (simulate_t.cpp:18-275, 301-324, 367-380,
+// 882-994, 1596-1647; pixelsim_t.cpp:12-20) on fixtures extracted from the
+// reference's SBML example models (tests/golden/, README.md there).
 #include "../include/smeb200.h"
 #include <algorithm>
 #include <array>

@@ -1,0 +1,87 @@
+"""Generates the golden fixtures under tests/golden/ from the reference's own
+SBML example models (run HERE, where /root/reference exists; the fixtures are
+what travels to the GPU box).
+
+    python tests/golden/make_golden.py
+
+Each fixture ``<name>.npz`` holds the inputs the reference's Pixel backends
+read from ``sme::model::Model`` for that model — label image, compartment ids
+and labels, simulated species, diffusion constants, initial concentrations,
+reaction expressions (C strings in sme_var_k), membrane ids/orientation and
+expressions, voxel size, pixel options — extracted by
+``spatial_model_editor_b200.sbml``.  The known answers the tests compare
+against are the reference's own (simulate_t.cpp; cited in
+tests/test_golden_cpu.py), not outputs of this repository.
+"""
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+from spatial_model_editor_b200 import sbml  # noqa: E402
+
+REF = "/root/reference"
+MODELS = {
+    "very-simple-model": "core/resources/models/very-simple-model.xml",
+    "ABtoC": "core/resources/models/ABtoC.xml",
+    "gray-scott": "core/resources/models/gray-scott.xml",
+    "gray-scott-3d": "core/resources/models/gray-scott-3d.xml",
+    "brusselator-model": "core/resources/models/brusselator-model.xml",
+    "liver-simplified": "core/resources/models/liver-simplified.xml",
+    "single-compartment-diffusion": "core/resources/models/single-compartment-diffusion.xml",
+    "single-compartment-diffusion-3d":
+        "core/resources/models/single-compartment-diffusion-3d.xml",
+}
+
+
+def dump(name, m, problem):
+    meta = dict(
+        name=name, source=os.path.relpath(m.path, REF), voxel_size=list(m.voxel_size),
+        origin=list(m.origin), vol_over_l3=m.vol_over_l3, label_of=m.label_of,
+        integrator=problem.integrator, max_err_abs=problem.max_err_abs,
+        max_err_rel=problem.max_err_rel, max_timestep=problem.max_timestep,
+        unsupported=problem.unsupported,
+        compartments=[dict(id=c.id, species=c.species, expressions=c.expressions,
+                           diffusion_constants=[s.diffusion for s in m.species
+                                                if s.id in c.species])
+                      for c in problem.compartments],
+        membranes=[dict(id=mb.id, comp_a=mb.comp_a, comp_b=mb.comp_b,
+                        a=[a for i, a, b in m.membranes if i == mb.id][0],
+                        b=[b for i, a, b in m.membranes if i == mb.id][0],
+                        expressions=mb.expressions,
+                        n_pairs=[int(len(p)) for p in mb.pairs])
+                   for mb in problem.membranes])
+    arrays = {"labels": m.labels.astype(np.uint8)}
+    for i, c in enumerate(problem.compartments):
+        conc = c.conc0
+        # uniform initial states are stored as one row
+        if np.all(conc == conc[0]):
+            conc = conc[:1]
+        arrays[f"conc0_{i}"] = conc
+    np.savez_compressed(os.path.join(HERE, name + ".npz"),
+                        meta=np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8), **arrays)
+    print(f"{name}: {[c.conc0.shape for c in problem.compartments]}, "
+          f"{os.path.getsize(os.path.join(HERE, name + '.npz'))} bytes")
+
+
+def main():
+    for name, rel in MODELS.items():
+        m = sbml.load_sbml(os.path.join(REF, rel))
+        dump(name, m, sbml.to_problem(m))
+    # K1: the 1 x 3 voxel membrane chain of simulate_t.cpp:18-88 — the non-spatial
+    # model with a 3-pixel image imported and four reactions moved to membranes
+    lab = np.array([[[1], [2], [3]]])
+    m = sbml.load_sbml(
+        os.path.join(REF, "test/resources/models/very-simple-model-non-spatial.xml"),
+        geometry=dict(labels=lab, label_of={"c1": 1, "c2": 2, "c3": 3}),
+        reaction_locations={"A_uptake": "c1_c2_membrane", "A_transport": "c2_c3_membrane",
+                            "B_transport": "c2_c3_membrane", "B_excretion": "c1_c2_membrane"})
+    dump("single-pixel-chain", m, sbml.to_problem(m, integrator=0))
+
+
+if __name__ == "__main__":
+    main()
