@@ -226,7 +226,10 @@ def main():
     W, K = max(args.warmup, 3), args.steps
     if world > 1:
         from spatial_model_editor_b200.multigpu import SlabPixelSim
-        p = make_problem(nx, ny, nz * world, integrator, device=local_rank)
+        # the global box is only described (no global array is ever built);
+        # every rank generates its own planes, ghosts included
+        p = make_problem(nx, ny, 1, integrator, device=local_rank)
+        p.compartments[0].box = (nx, ny, nz * world)
         sim = SlabPixelSim(p, rank, world, make_slab=lambda z0, z1: gray_scott_3d_state(
             nx, ny, z1 - z0, z0), variant=args.variant)
         evals_per_step = STAGES[integrator] * nx * ny * nz * world * 2
@@ -268,7 +271,8 @@ def main():
 
     # end to end through the public call with HOST buffers: one image interval =
     # upload of the state from pinned host memory, K steps, download of the result
-    host = sim.getConcentrations(0)  # pinned mirror
+    # pinned mirror (the local slab incl. ghost planes when decomposed)
+    host = sim.getConcentrationsWithGhosts(0) if world > 1 else sim.getConcentrations(0)
     h2d = d2h = host.nbytes
     barrier()
     t0 = time.perf_counter()

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define SMEB200_ABI_VERSION 1
+#define SMEB200_ABI_VERSION 2
 
 /* mirrors sme::simulate::PixelIntegratorType (simulate_options.hpp:113-119) */
 enum smeb200_integrator {
@@ -116,14 +116,21 @@ typedef struct smeb200_problem {
   int32_t image_nx, image_ny, image_nz;
   uint32_t unsupported;    /* enum smeb200_unsupported bits */
   int32_t device;          /* CUDA device ordinal; -1 = current device */
-  /* z-slab decomposition of box compartments over `n_ranks` processes, one
-   * GPU each (0/1 = single GPU).  See smeb200_slab_* below. */
+  /* z-slab decomposition of box compartments over `n_ranks` processes on one
+   * node, one GPU each (0/1 = single GPU).  Rank r then describes only ITS
+   * slab: box_nz = owned planes + one ghost plane below (r > 0) + one above
+   * (r < n_ranks-1), conc0 including the ghost planes.  See "multi-GPU". */
   int32_t rank, n_ranks;
   /* kernel variant: 0 = auto (TMA tile-marching kernel for box compartments
    * where the shape allows it), 1 = direct-gather kernels only, 2 = require
    * the TMA tile kernel for box compartments (error if it cannot be used) */
   int32_t kernel_variant;
-  uint32_t reserved[7];
+  uint32_t reserved0;
+  /* name of the node-local communicator (POSIX shared memory segment) the
+   * n_ranks processes of one decomposed simulation rendezvous on; must be the
+   * same string on all ranks and unique per simulation; NULL if n_ranks <= 1 */
+  const char *comm_name;
+  uint32_t reserved[4];
 } smeb200_problem;
 
 typedef struct smeb200_sim smeb200_sim;
@@ -208,8 +215,30 @@ const char *smeb200_kernel_source(const smeb200_sim *sim);
 const char *smeb200_dominant_kernel(const smeb200_sim *sim);
 
 /* ---- multi-GPU ---------------------------------------------------------- */
-/* error-norm exchange for the adaptive controller: the host supplies an
- * allreduce-max over ranks for 2 doubles (NCCL/gloo in the caller) */
+/* z-slab decomposition (no counterpart in the reference, which has no
+ * distributed layer): with n_ranks > 1 every rank's simulator
+ *  - updates only its owned planes; after every Runge-Kutta stage it copies its
+ *    two boundary planes into the neighbours' ghost planes over NVLink
+ *    (CUDA IPC peer memory) and hand-shakes with stream-ordered 32-bit flags
+ *    (cuStreamWriteValue32 / cuStreamWaitValue32) — no host involvement;
+ *  - max-reduces the two error norms over ranks once per adaptive step through
+ *    the shared-memory communicator, so that all ranks take identical
+ *    step-size decisions.
+ * smeb200_get_concentrations returns the local slab including ghost planes.
+ *
+ * The communicator on its own (usable without a GPU; CPU tests): */
+typedef struct smeb200_comm smeb200_comm;
+int smeb200_comm_create(const char *name, int rank, int n_ranks,
+                        smeb200_comm **out);
+int smeb200_comm_allreduce_max(smeb200_comm *comm, double *values, int n);
+int smeb200_comm_barrier(smeb200_comm *comm);
+void smeb200_comm_destroy(smeb200_comm *comm);
+/* halo exchanges performed since construction (0 on a single GPU) */
+uint64_t smeb200_halo_exchanges(const smeb200_sim *sim);
+
+/* alternative error-norm exchange for the adaptive controller: the host
+ * supplies an allreduce-max over ranks for 2 doubles (NCCL/gloo in the caller);
+ * used instead of the communicator's when set */
 typedef void (*smeb200_allreduce_max_fn)(double *values, int n, void *user);
 void smeb200_set_allreduce_max(smeb200_sim *sim, smeb200_allreduce_max_fn fn,
                                void *user);

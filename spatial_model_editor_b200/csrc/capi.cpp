@@ -1,5 +1,6 @@
 // extern "C" surface of libsmeb200.so — see include/smeb200.h for the contract
 // and the reference interface each entry point stands in for.
+#include "comm.hpp"
 #include "sim.hpp"
 #include <cstring>
 
@@ -207,6 +208,58 @@ const char *smeb200_kernel_source(const smeb200_sim *sim) {
 
 const char *smeb200_dominant_kernel(const smeb200_sim *sim) {
   return sim != nullptr ? sim->impl.dominantKernelName.c_str() : "";
+}
+
+struct smeb200_comm {
+  smeb200::ShmComm impl;
+  std::string error;
+  smeb200_comm(const char *name, int rank, int n) : impl(name, rank, n) {}
+};
+
+int smeb200_comm_create(const char *name, int rank, int n_ranks,
+                        smeb200_comm **out) {
+  if (out == nullptr || name == nullptr) {
+    return -1;
+  }
+  *out = nullptr;
+  try {
+    *out = new smeb200_comm(name, rank, n_ranks);
+  } catch (...) {
+    return 1;
+  }
+  return 0;
+}
+
+int smeb200_comm_allreduce_max(smeb200_comm *comm, double *values, int n) {
+  if (comm == nullptr || values == nullptr) {
+    return -1;
+  }
+  try {
+    comm->impl.allreduceMax(values, n);
+  } catch (const std::exception &e) {
+    comm->error = e.what();
+    return 1;
+  }
+  return 0;
+}
+
+int smeb200_comm_barrier(smeb200_comm *comm) {
+  if (comm == nullptr) {
+    return -1;
+  }
+  try {
+    comm->impl.barrier();
+  } catch (const std::exception &e) {
+    comm->error = e.what();
+    return 1;
+  }
+  return 0;
+}
+
+void smeb200_comm_destroy(smeb200_comm *comm) { delete comm; }
+
+uint64_t smeb200_halo_exchanges(const smeb200_sim *sim) {
+  return sim != nullptr ? sim->impl.haloExchanges : 0;
 }
 
 void smeb200_set_allreduce_max(smeb200_sim *sim, smeb200_allreduce_max_fn fn,

@@ -53,6 +53,8 @@ const DriverApi &DriverApi::get() {
       resolve("cuLaunchKernel", api.LaunchKernel);
       resolve("cuFuncSetAttribute", api.FuncSetAttribute);
       resolve("cuTensorMapEncodeTiled", api.TensorMapEncodeTiled);
+      resolve("cuStreamWriteValue32", api.StreamWriteValue32);
+      resolve("cuStreamWaitValue32", api.StreamWaitValue32);
     } catch (const Error &e) {
       failure = e.what();
     }

@@ -31,6 +31,10 @@ struct DriverApi {
       const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
       const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
       CUtensorMapL2promotion, CUtensorMapFloatOOBfill) = nullptr;
+  CUresult (*StreamWriteValue32)(CUstream, CUdeviceptr, cuuint32_t,
+                                 unsigned int) = nullptr;
+  CUresult (*StreamWaitValue32)(CUstream, CUdeviceptr, cuuint32_t,
+                                unsigned int) = nullptr;
   // throws Error if the driver is not available
   static const DriverApi &get();
 };

@@ -682,6 +682,9 @@ void Sim::build(const smeb200_problem &p) {
       dominantComp = ci;
     }
   }
+  if (p.n_ranks > 1) {
+    setupSlabs(p);
+  }
   makePlan();
   if (compileOnly) {
     // no device: only mark which compartments need a membrane kernel
@@ -761,6 +764,150 @@ void Sim::build(const smeb200_problem &p) {
   check(cudaMallocHost(reinterpret_cast<void **>(&hErr), 16),
         "allocate pinned error mirror");
   check(cudaStreamSynchronize(stream), "initial upload");
+  if (comm) {
+    connectSlabs();
+  }
+}
+
+// ---- z-slab decomposition -----------------------------------------------------
+// rank r owns a contiguous range of z planes of every (box) compartment; the
+// local arrays carry one ghost plane towards each neighbour
+void Sim::setupSlabs(const smeb200_problem &p) {
+  rank = p.rank;
+  nRanks = p.n_ranks;
+  if (rank < 0 || rank >= nRanks || nRanks > kCommMaxRanks) {
+    throw Error("smeb200: invalid rank / n_ranks");
+  }
+  if (p.n_membranes > 0) {
+    throw Error("smeb200: z-slab decomposition does not support membranes yet");
+  }
+  if (comps.size() > static_cast<std::size_t>(kCommMaxCompartments)) {
+    throw Error("smeb200: too many compartments for z-slab decomposition");
+  }
+  for (auto &c : comps) {
+    if (!c.box) {
+      throw Error("smeb200: z-slab decomposition needs box compartments "
+                  "(implicit neighbours)");
+    }
+    c.zLoGhost = rank > 0 ? 1u : 0u;
+    c.zHiGhost = rank + 1 < nRanks ? 1u : 0u;
+    if (c.nz < c.zLoGhost + c.zHiGhost + 1u) {
+      throw Error("smeb200: slab of compartment '" + c.id +
+                  "' has no owned plane");
+    }
+  }
+  if (!compileOnly) {
+    if (p.comm_name == nullptr) {
+      throw Error("smeb200: n_ranks > 1 needs comm_name");
+    }
+    comm = std::make_unique<ShmComm>(p.comm_name, rank, nRanks);
+  }
+}
+
+// exchange CUDA IPC handles of all concentration buffers with the neighbours
+// and register the handshake flags with this process's CUDA context
+void Sim::connectSlabs() {
+  auto *seg = comm->segment();
+  auto &mine = seg->slot[rank];
+  mine.device = device;
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    auto &c = comps[ci];
+    mine.nz[ci] = c.nz;
+    for (int b = 0; b < c.nbuf; ++b) {
+      cudaIpcMemHandle_t h{};
+      check(cudaIpcGetMemHandle(&h, c.buf[b]), "cudaIpcGetMemHandle");
+      static_assert(sizeof(h) == 64, "CUDA IPC handle size");
+      std::memcpy(mine.memHandle[ci][b], &h, sizeof(h));
+    }
+  }
+  mine.published.store(1, std::memory_order_release);
+  comm->barrier();
+  for (int side = 0; side < 2; ++side) {
+    const int nb = side == 0 ? rank - 1 : rank + 1;
+    if (nb < 0 || nb >= nRanks) {
+      continue;
+    }
+    for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+      for (int b = 0; b < comps[ci].nbuf; ++b) {
+        cudaIpcMemHandle_t h{};
+        std::memcpy(&h, seg->slot[nb].memHandle[ci][b], sizeof(h));
+        void *ptr = nullptr;
+        check(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess),
+              "cudaIpcOpenMemHandle (is peer access between the GPUs of this "
+              "node available?)");
+        peerBuf[side][ci][b] = static_cast<double *>(ptr);
+      }
+    }
+  }
+  check(cudaHostRegister(comm->flagPages(), comm->flagBytes(),
+                         cudaHostRegisterPortable | cudaHostRegisterMapped),
+        "cudaHostRegister(halo flags)");
+  flagsRegistered = true;
+  void *dev = nullptr;
+  check(cudaHostGetDevicePointer(&dev, comm->flagPages(), 0),
+        "cudaHostGetDevicePointer(halo flags)");
+  flagBaseDev = reinterpret_cast<CUdeviceptr>(dev);
+  comm->barrier();
+}
+
+// after a stage wrote buffer `coutBuf`: push the two owned boundary planes into
+// the neighbours' ghost planes of the same buffer, signal, and make the stream
+// wait for the neighbours' pushes.  Everything is stream-ordered; the host does
+// not wait.  (A neighbour can only overwrite a ghost plane of buffer B after
+// this rank's earlier readers of B finished: it pushes stage k only after it
+// saw this rank's flag of stage k-1, which this rank writes after its own
+// stage k-1 kernel.)
+void Sim::haloExchange(int coutBuf) {
+  const auto &drv = DriverApi::get();
+  auto *seg = comm->segment();
+  ++haloSeq;
+  auto flagDev = [&](int r, int side) {
+    return flagBaseDev +
+           static_cast<CUdeviceptr>(
+               reinterpret_cast<unsigned char *>(comm->haloFlag(r, side)) -
+               static_cast<unsigned char *>(comm->flagPages()));
+  };
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    auto &c = comps[ci];
+    if (c.S == 0 || c.n == 0) {
+      continue;
+    }
+    const std::size_t plane = static_cast<std::size_t>(c.nx) * c.ny * c.S;
+    if (rank > 0) { // my first owned plane -> HIGH ghost of rank-1
+      const std::size_t peerNz = seg->slot[rank - 1].nz[ci];
+      check(cudaMemcpyAsync(peerBuf[0][ci][coutBuf] + (peerNz - 1) * plane,
+                            c.buf[coutBuf] + c.zLoGhost * plane,
+                            plane * sizeof(double), cudaMemcpyDefault, stream),
+            "halo push (low neighbour)");
+    }
+    if (rank + 1 < nRanks) { // my last owned plane -> LOW ghost of rank+1
+      check(cudaMemcpyAsync(peerBuf[1][ci][coutBuf],
+                            c.buf[coutBuf] + (c.nz - 1 - c.zHiGhost) * plane,
+                            plane * sizeof(double), cudaMemcpyDefault, stream),
+            "halo push (high neighbour)");
+    }
+  }
+  if (rank > 0) {
+    check(drv.StreamWriteValue32(stream, flagDev(rank - 1, 1), haloSeq,
+                                 CU_STREAM_WRITE_VALUE_DEFAULT),
+          "cuStreamWriteValue32");
+  }
+  if (rank + 1 < nRanks) {
+    check(drv.StreamWriteValue32(stream, flagDev(rank + 1, 0), haloSeq,
+                                 CU_STREAM_WRITE_VALUE_DEFAULT),
+          "cuStreamWriteValue32");
+  }
+  if (rank > 0) {
+    check(drv.StreamWaitValue32(stream, flagDev(rank, 0), haloSeq,
+                                CU_STREAM_WAIT_VALUE_GEQ),
+          "cuStreamWaitValue32");
+  }
+  if (rank + 1 < nRanks) {
+    check(drv.StreamWaitValue32(stream, flagDev(rank, 1), haloSeq,
+                                CU_STREAM_WAIT_VALUE_GEQ),
+          "cuStreamWaitValue32");
+  }
+  ++haloExchanges;
 }
 
 Sim::~Sim() {
@@ -769,6 +916,25 @@ Sim::~Sim() {
   }
   cudaSetDevice(device);
   cudaStreamSynchronize(stream);
+  if (comm) {
+    // nobody may still be pushing halos into this rank's buffers
+    try {
+      comm->barrier();
+    } catch (...) {
+    }
+    for (auto &side : peerBuf) {
+      for (auto &cb : side) {
+        for (double *ptr : cb) {
+          if (ptr != nullptr) {
+            cudaIpcCloseMemHandle(ptr);
+          }
+        }
+      }
+    }
+    if (flagsRegistered) {
+      cudaHostUnregister(comm->flagPages());
+    }
+  }
   for (auto &c : comps) {
     for (double *b : c.buf) {
       cudaFree(b);
@@ -854,6 +1020,9 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
       c.lastFlags = sd.flags();
       c.haveLast = true;
     }
+  }
+  if (comm && !comps.empty()) {
+    haloExchange(comps[0].role[sd.cout]);
   }
 }
 
@@ -973,6 +1142,8 @@ void Sim::readError(double &eabs, double &erel) {
   std::memcpy(v, hErr, 16);
   if (allreduceMax != nullptr) {
     allreduceMax(v, 2, allreduceUser);
+  } else if (comm) {
+    comm->allreduceMax(v, 2);
   }
   eabs = v[0];
   erel = v[1];

@@ -6,6 +6,7 @@
 #pragma once
 
 #include "../../include/smeb200.h"
+#include "comm.hpp"
 #include "cuda_api.hpp"
 #include <atomic>
 #include <cstdint>
@@ -155,6 +156,7 @@ public:
   std::size_t nCompartments() const { return comps.size(); }
   smeb200_allreduce_max_fn allreduceMax{nullptr};
   void *allreduceUser{nullptr};
+  uint64_t haloExchanges{0};
 
 private:
   struct Module {
@@ -185,6 +187,18 @@ private:
   void runOnDemand(std::size_t ci, uint32_t flags, double *out);
   void evaluateLastDcdt();
   void flushTimers();
+  void setupSlabs(const smeb200_problem &p);
+  void connectSlabs();
+  void haloExchange(int coutBuf);
+
+  // z-slab decomposition (n_ranks > 1): communicator, neighbours' buffers
+  // (CUDA IPC), device addresses of the stream-ordered handshake flags
+  int rank{0}, nRanks{1};
+  std::unique_ptr<ShmComm> comm;
+  double *peerBuf[2][kCommMaxCompartments][kCommMaxBuffers]{};
+  bool flagsRegistered{false};
+  CUdeviceptr flagBaseDev{0};
+  uint32_t haloSeq{0};
 
   int device{0};
   cudaStream_t stream{nullptr};

@@ -70,6 +70,11 @@ def _bind(lib, prefix: str):
     fn("kernel_source", C.c_char_p, [vp], optional=True)
     fn("dominant_kernel", C.c_char_p, [vp], optional=True)
     fn("set_allreduce_max", None, [vp, _ALLREDUCE_CB, vp], optional=True)
+    fn("halo_exchanges", C.c_uint64, [vp], optional=True)
+    fn("comm_create", C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(vp)], optional=True)
+    fn("comm_allreduce_max", C.c_int, [vp, C.POINTER(C.c_double), C.c_int], optional=True)
+    fn("comm_barrier", C.c_int, [vp], optional=True)
+    fn("comm_destroy", None, [vp], optional=True)
     # oracle-only
     fn("set_threads", None, [vp, C.c_int], optional=True)
     fn("max_threads", C.c_int, [], optional=True)

@@ -26,7 +26,7 @@ HAS_NON_SPATIAL_SPECIES = 4
 HAS_NON_UNIFORM_DIFFUSION = 8
 HAS_NON_UNIT_STORAGE = 16
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 class CCompartment(C.Structure):
@@ -77,7 +77,9 @@ class CProblem(C.Structure):
         ("rank", C.c_int32),
         ("n_ranks", C.c_int32),
         ("kernel_variant", C.c_int32),
-        ("reserved", C.c_uint32 * 7),
+        ("reserved0", C.c_uint32),
+        ("comm_name", C.c_char_p),
+        ("reserved", C.c_uint32 * 4),
     ]
 
 
@@ -127,6 +129,9 @@ class Problem:
     unsupported: int = 0
     device: int = -1
     kernel_variant: int = 0
+    rank: int = 0                         # z-slab decomposition (multigpu.py)
+    n_ranks: int = 1
+    comm_name: Optional[str] = None
 
     def evals_per_step(self) -> int:
         """voxel*species RHS evaluations in one RK step (the bench metric)."""
@@ -197,7 +202,8 @@ class Problem:
         p.image_nx, p.image_ny, p.image_nz = self.image_size
         p.unsupported = self.unsupported
         p.device = self.device
-        p.rank = 0
-        p.n_ranks = 1
+        p.rank = self.rank
+        p.n_ranks = self.n_ranks
+        p.comm_name = self.comm_name.encode() if self.comm_name else None
         p.kernel_variant = self.kernel_variant
         return p, keep
