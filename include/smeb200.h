@@ -125,12 +125,19 @@ typedef struct smeb200_problem {
    * where the shape allows it), 1 = direct-gather kernels only, 2 = require
    * the TMA tile kernel for box compartments (error if it cannot be used) */
   int32_t kernel_variant;
-  uint32_t reserved0;
+  /* runtime model parameters: expressions may refer to sme_param_0 ..
+   * sme_param_{n_params-1}; their values are kernel arguments, so simulators
+   * that differ only in these values (parameter scans, optimizer candidates)
+   * share one compiled module, and smeb200_set_params changes them between
+   * runs.  The reference inlines parameter values into the expression text
+   * and re-JITs per member (pde.cpp:65-77). */
+  uint32_t n_params;
   /* name of the node-local communicator (POSIX shared memory segment) the
    * n_ranks processes of one decomposed simulation rendezvous on; must be the
    * same string on all ranks and unique per simulation; NULL if n_ranks <= 1 */
   const char *comm_name;
-  uint32_t reserved[4];
+  const double *params;    /* [n_params] */
+  uint32_t reserved[2];
 } smeb200_problem;
 
 typedef struct smeb200_sim smeb200_sim;
@@ -172,6 +179,9 @@ size_t smeb200_get_concentration_padding(const smeb200_sim *sim);
  * setConcentrations, used with SimulationData, pixelsim.cpp:399-406) */
 int smeb200_set_concentrations(smeb200_sim *sim, size_t compartment,
                                const double *data, size_t n);
+
+/* new values for the runtime model parameters (takes effect at the next run) */
+int smeb200_set_params(smeb200_sim *sim, const double *values, size_t n);
 
 /* BaseSim::errorMessage / setCurrentErrormessage */
 const char *smeb200_error(const smeb200_sim *sim);

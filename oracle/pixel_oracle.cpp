@@ -459,6 +459,14 @@ struct Oracle {
         src << "  const double sme_var_" << i << " = sme_values[" << i
             << "]; (void)sme_var_" << i << ";\n";
       }
+      // runtime parameters of the product are numeric constants here, as in
+      // the reference (pde.cpp:65-77 inlines parameter values)
+      for (uint32_t i = 0; i < p.n_params; ++i) {
+        char buf[64];
+        std::snprintf(buf, sizeof(buf), "%a", p.params[i]);
+        src << "  const double sme_param_" << i << " = " << buf
+            << "; (void)sme_param_" << i << ";\n";
+      }
       for (uint32_t i = 0; i < nVars; ++i) {
         src << "  sme_out[" << i << "] = " << expr[i] << ";\n";
       }

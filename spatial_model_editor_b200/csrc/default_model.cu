@@ -9,7 +9,8 @@
 struct Reac0 {
   static constexpr int S = 2;
   static __device__ __forceinline__ void eval(double *sme_out,
-                                              const double *sme_values) {
+                                              const double *sme_values,
+                                              const double *) {
     const double sme_var_0 = sme_values[0];
     const double sme_var_1 = sme_values[1];
     sme_out[0] = -sme_var_0 * sme_var_1 * sme_var_1 + 0.037 * (1.0 - sme_var_0);
@@ -20,7 +21,8 @@ struct Reac1 : Reac0 {};
 struct Memb0 {
   static constexpr int SA = 2, SB = 2, CA = 0, CB = 1;
   static __device__ __forceinline__ void eval(double *sme_out,
-                                              const double *sme_values) {
+                                              const double *sme_values,
+                                              const double *) {
     sme_out[0] = 0.1 * (sme_values[2] - sme_values[0]);
     sme_out[1] = 0.0;
     sme_out[2] = -sme_out[0];
@@ -30,10 +32,10 @@ struct Memb0 {
 template <int S_OWN>
 __device__ __forceinline__ void
 smeb_memb_dispatch(smeb_u32 info, smeb_u32 partner, const double *cown,
-                   const SmebMembArgs &m, double *f) {
+                   const SmebMembArgs &m, const double *params, double *f) {
   switch (info & 0xffffu) {
   case 0:
-    smeb_memb_term<Memb0, S_OWN>(info, partner, cown, m, f);
+    smeb_memb_term<Memb0, S_OWN>(info, partner, cown, m, params, f);
     break;
   default:
     break;

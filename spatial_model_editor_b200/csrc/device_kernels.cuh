@@ -42,6 +42,9 @@ typedef unsigned int smeb_u32;
 
 #define SMEB_MEMB_FLAG 0x80000000u
 #define SMEB_BLOCK 256
+#ifndef SMEB_NPARAMS
+#define SMEB_NPARAMS 0 // runtime model parameters (sme_param_k), per module
+#endif
 #ifndef SMEB_TILE_MIN_CTAS
 #define SMEB_TILE_MIN_CTAS 2 // resident CTAs per SM the tile kernel is built for
 #endif
@@ -59,7 +62,10 @@ template <int S> struct SmebStageArgs {
   smeb_u32 z_begin, z_end; // planes updated by this launch (ghosts excluded)
   double g1, g2, g3, bdt, delta; // stage coefficients (bdt = beta*dt)
   double cF, s2F, s3F, eps;      // finalise factors, error epsilon
-  double D[3 * S];               // D/dx^2, D/dy^2, D/dz^2 per species
+  // D/dx^2, D/dy^2, D/dz^2 per species, then the runtime model parameters
+  // (values of sme_param_k: scanned parameters of an ensemble stay symbolic so
+  // that one compiled module serves every member)
+  double D[3 * S + SMEB_NPARAMS];
 };
 
 struct SmebMembEntry {
@@ -268,7 +274,7 @@ smeb_rhs_values(const SmebStageArgs<R::S> &a, const double *c,
                 const double *ym, const double *zp, const double *zm,
                 double *f) {
   constexpr int S = R::S;
-  R::eval(f, c);
+  R::eval(f, c, a.D + 3 * S);
 #pragma unroll
   for (int s = 0; s < S; ++s) {
     f[s] += a.D[3 * s] * (xp[s] + xm[s] - 2.0 * c[s]) +
@@ -360,7 +366,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
 template <class M, int S_OWN>
 __device__ __forceinline__ void
 smeb_memb_term(smeb_u32 info, smeb_u32 partner, const double *cown,
-               const SmebMembArgs &m, double *f) {
+               const SmebMembArgs &m, const double *params, double *f) {
   constexpr int SA = M::SA, SB = M::SB;
   double in[SA + SB + 1], out[SA + SB + 1];
   const bool ownIsB = (info >> 16) & 1u;
@@ -375,7 +381,7 @@ smeb_memb_term(smeb_u32 info, smeb_u32 partner, const double *cown,
       if constexpr (SB > 0) {
         smeb_load_voxel<SB>(m.comp_cin[M::CB], partner, in + SA);
       }
-      M::eval(out, in);
+      M::eval(out, in, params);
 #pragma unroll
       for (int s = 0; s < SA; ++s) {
         f[s] += out[s] / L;
@@ -390,7 +396,7 @@ smeb_memb_term(smeb_u32 info, smeb_u32 partner, const double *cown,
       if constexpr (SA > 0) {
         smeb_load_voxel<SA>(m.comp_cin[M::CA], partner, in);
       }
-      M::eval(out, in);
+      M::eval(out, in, params);
 #pragma unroll
       for (int s = 0; s < SB; ++s) {
         f[s] += out[SA + s] / L;
@@ -403,7 +409,7 @@ smeb_memb_term(smeb_u32 info, smeb_u32 partner, const double *cown,
 template <int S_OWN>
 __device__ __forceinline__ void
 smeb_memb_dispatch(smeb_u32 info, smeb_u32 partner, const double *cown,
-                   const SmebMembArgs &m, double *f);
+                   const SmebMembArgs &m, const double *params, double *f);
 
 template <class R, unsigned F>
 __global__ void __launch_bounds__(SMEB_BLOCK)
@@ -422,7 +428,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
     const smeb_u32 e1 = m.mstart[k + 1];
     for (smeb_u32 e = m.mstart[k]; e < e1; ++e) {
       const SmebMembEntry ent = m.ent[e];
-      smeb_memb_dispatch<S>(ent.info, ent.partner, c, m, f);
+      smeb_memb_dispatch<S>(ent.info, ent.partner, c, m, a.D + 3 * S, f);
     }
     smeb_finish_voxel<S, F>(a, i, c, f, eabs, erel);
   }

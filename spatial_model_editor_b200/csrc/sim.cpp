@@ -3,6 +3,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstring>
+#include <mutex>
 #include <sstream>
 
 namespace smeb200 {
@@ -63,13 +64,18 @@ T *devUpload(const std::vector<T> &v, cudaStream_t s, const char *what) {
 }
 
 std::string functorSource(const std::string &header, uint32_t nVars,
-                          const char *const *expressions, uint32_t nExpr) {
+                          const char *const *expressions, uint32_t nExpr,
+                          uint32_t nParams) {
   std::ostringstream s;
   s << header;
   s << "  static __device__ __forceinline__ void eval(double* sme_out, const "
-       "double* sme_values) {\n";
+       "double* sme_values, const double* sme_params) {\n";
   for (uint32_t i = 0; i < nVars; ++i) {
     s << "    const double sme_var_" << i << " = sme_values[" << i << "];\n";
+  }
+  for (uint32_t i = 0; i < nParams; ++i) {
+    s << "    const double sme_param_" << i << " = sme_params[" << i
+      << "]; (void)sme_param_" << i << ";\n";
   }
   for (uint32_t i = 0; i < nExpr; ++i) {
     s << "    sme_out[" << i << "] = " << expressions[i] << ";\n";
@@ -117,6 +123,7 @@ void Sim::generateSource(const smeb200_problem &p) {
   std::ostringstream src;
   src << "#define SMEB_NCOMP " << std::max<uint32_t>(p.n_compartments, 1)
       << "\n";
+  src << "#define SMEB_NPARAMS " << p.n_params << "\n";
   src << kDeviceKernelSource << "\n";
   for (uint32_t c = 0; c < p.n_compartments; ++c) {
     const auto &comp = p.compartments[c];
@@ -128,7 +135,7 @@ void Sim::generateSource(const smeb200_problem &p) {
     h << "struct Reac" << c << " {\n  static constexpr int S = "
       << comp.n_species << ";\n";
     src << functorSource(h.str(), comp.n_species, comp.expressions,
-                         comp.n_species);
+                         comp.n_species, p.n_params);
   }
   for (uint32_t m = 0; m < p.n_membranes; ++m) {
     const auto &mb = p.membranes[m];
@@ -141,15 +148,17 @@ void Sim::generateSource(const smeb200_problem &p) {
     h << "struct Memb" << m << " {\n  static constexpr int SA = " << SA
       << ", SB = " << SB << ", CA = " << std::max(mb.comp_a, 0)
       << ", CB = " << std::max(mb.comp_b, 0) << ";\n";
-    src << functorSource(h.str(), SA + SB, mb.expressions, SA + SB);
+    src << functorSource(h.str(), SA + SB, mb.expressions, SA + SB,
+                         p.n_params);
   }
   src << "template <int S_OWN>\n__device__ __forceinline__ void\n"
          "smeb_memb_dispatch(smeb_u32 info, smeb_u32 partner, const double "
-         "*cown,\n                   const SmebMembArgs &m, double *f) {\n"
+         "*cown,\n                   const SmebMembArgs &m, const double "
+         "*params, double *f) {\n"
          "  switch (info & 0xffffu) {\n";
   for (uint32_t m = 0; m < p.n_membranes; ++m) {
     src << "  case " << m << ":\n    smeb_memb_term<Memb" << m
-        << ", S_OWN>(info, partner, cown, m, f);\n    break;\n";
+        << ", S_OWN>(info, partner, cown, m, params, f);\n    break;\n";
   }
   src << "  default:\n    break;\n  }\n}\n";
   kernelSource = src.str();
@@ -173,48 +182,86 @@ std::string Sim::kernelName(std::size_t ci, uint32_t flags, bool memb) const {
   return s.str();
 }
 
+// Process-wide cache of compiled modules: simulators with the same generated
+// source and kernel list (ensemble members, optimizer candidates, the
+// simulator Simulation re-creates after every event — simulate.cpp:265-267)
+// reuse the cubin instead of running NVRTC again.
+namespace {
+struct CompiledModule {
+  std::vector<char> cubin;
+  std::map<std::string, std::string> lowered;
+};
+std::mutex gModuleCacheMutex;
+std::map<std::string, std::shared_ptr<const CompiledModule>> gModuleCache;
+} // namespace
+
 Sim::Module Sim::compile(const std::vector<std::string> &names) {
   Module m;
-  nvrtcProgram prog{};
-  check(nvrtcCreateProgram(&prog, kernelSource.c_str(), "smeb200_model.cu", 0,
-                           nullptr, nullptr),
-        "nvrtcCreateProgram");
+  std::string key = kernelSource;
   for (const auto &n : names) {
-    nvrtcAddNameExpression(prog, n.c_str());
+    key += "\n//";
+    key += n;
   }
-  // sm_100a only; --fmad=false keeps every a*b+c as two IEEE operations so the
-  // result matches the CPU solver's evaluation order bit for bit.
-  const char *opts[] = {"--gpu-architecture=sm_100a", "--std=c++17",
-                        "--fmad=false", "-lineinfo", "-default-device"};
-  nvrtcResult r = nvrtcCompileProgram(prog, 5, opts);
-  if (r != NVRTC_SUCCESS) {
+  std::shared_ptr<const CompiledModule> compiled;
+  {
+    std::lock_guard<std::mutex> lock(gModuleCacheMutex);
+    if (auto it = gModuleCache.find(key); it != gModuleCache.end()) {
+      compiled = it->second;
+      ++moduleCacheHits;
+    }
+  }
+  if (!compiled) {
+    nvrtcProgram prog{};
+    check(nvrtcCreateProgram(&prog, kernelSource.c_str(), "smeb200_model.cu", 0,
+                             nullptr, nullptr),
+          "nvrtcCreateProgram");
+    for (const auto &n : names) {
+      nvrtcAddNameExpression(prog, n.c_str());
+    }
+    // sm_100a only; --fmad=false keeps every a*b+c as two IEEE operations so
+    // the result matches the CPU solver's evaluation order bit for bit.
+    const char *opts[] = {"--gpu-architecture=sm_100a", "--std=c++17",
+                          "--fmad=false", "-lineinfo", "-default-device"};
+    nvrtcResult r = nvrtcCompileProgram(prog, 5, opts);
+    if (r != NVRTC_SUCCESS) {
+      std::size_t n = 0;
+      nvrtcGetProgramLogSize(prog, &n);
+      std::string log(n, '\0');
+      nvrtcGetProgramLog(prog, log.data());
+      nvrtcDestroyProgram(&prog);
+      throw Error("Failed to compile CUDA pixel kernels with NVRTC: " + log);
+    }
+    auto fresh = std::make_shared<CompiledModule>();
     std::size_t n = 0;
-    nvrtcGetProgramLogSize(prog, &n);
-    std::string log(n, '\0');
-    nvrtcGetProgramLog(prog, log.data());
+    check(nvrtcGetCUBINSize(prog, &n), "nvrtcGetCUBINSize");
+    fresh->cubin.resize(n);
+    check(nvrtcGetCUBIN(prog, fresh->cubin.data()), "nvrtcGetCUBIN");
+    for (const auto &name : names) {
+      const char *lowered = nullptr;
+      check(nvrtcGetLoweredName(prog, name.c_str(), &lowered),
+            "nvrtcGetLoweredName");
+      fresh->lowered[name] = lowered;
+    }
     nvrtcDestroyProgram(&prog);
-    throw Error("Failed to compile CUDA pixel kernels with NVRTC: " + log);
+    compiled = fresh;
+    std::lock_guard<std::mutex> lock(gModuleCacheMutex);
+    if (gModuleCache.size() >= 64) {
+      gModuleCache.clear();
+    }
+    gModuleCache[key] = compiled;
   }
-  std::size_t n = 0;
-  check(nvrtcGetCUBINSize(prog, &n), "nvrtcGetCUBINSize");
-  std::vector<char> cubin(n);
-  check(nvrtcGetCUBIN(prog, cubin.data()), "nvrtcGetCUBIN");
-  cubinBytes += cubin.size();
+  cubinBytes += compiled->cubin.size();
   if (compileOnly) {
-    nvrtcDestroyProgram(&prog);
     return m;
   }
   const auto &drv = DriverApi::get();
-  check(drv.ModuleLoadData(&m.mod, cubin.data()), "cuModuleLoadData");
+  check(drv.ModuleLoadData(&m.mod, compiled->cubin.data()), "cuModuleLoadData");
   for (const auto &name : names) {
-    const char *lowered = nullptr;
-    check(nvrtcGetLoweredName(prog, name.c_str(), &lowered),
-          "nvrtcGetLoweredName");
     CUfunction f{};
-    check(drv.ModuleGetFunction(&f, m.mod, lowered), "cuModuleGetFunction");
+    check(drv.ModuleGetFunction(&f, m.mod, compiled->lowered.at(name).c_str()),
+          "cuModuleGetFunction");
     m.fn[name] = f;
   }
-  nvrtcDestroyProgram(&prog);
   return m;
 }
 
@@ -605,6 +652,12 @@ void Sim::build(const smeb200_problem &p) {
   }
   if (p.n_compartments > 32) {
     throw Error("smeb200: at most 32 compartments are supported");
+  }
+  if (p.n_params > 64) {
+    throw Error("smeb200: at most 64 runtime parameters are supported");
+  }
+  if (p.n_params > 0) {
+    params.assign(p.params, p.params + p.n_params);
   }
   if (!compileOnly) {
     // no CPU fallback: without a device the simulator carries an error
@@ -1013,6 +1066,7 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     a.s3F = sd.s3F;
     a.eps = epsilon;
     std::copy(c.D.begin(), c.D.end(), a.D);
+    std::copy(params.begin(), params.end(), a.D + 3 * c.S);
     launchCompartment(ci, a, c.kStage[stageIndex], c.role[sd.cin]);
     if (last) {
       c.last = a;

@@ -40,7 +40,7 @@ struct StageArgsHost {
   uint32_t z_begin, z_end;
   double g1, g2, g3, bdt, delta;
   double cF, s2F, s3F, eps;
-  double D[3 * 64];
+  double D[3 * 64 + 64]; // + runtime parameters
 };
 
 struct MembEntryHost {
@@ -157,6 +157,8 @@ public:
   smeb200_allreduce_max_fn allreduceMax{nullptr};
   void *allreduceUser{nullptr};
   uint64_t haloExchanges{0};
+  std::vector<double> params; // runtime model parameters (sme_param_k)
+  uint64_t moduleCacheHits{0};
 
 private:
   struct Module {

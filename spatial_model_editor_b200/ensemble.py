@@ -1,0 +1,99 @@
+"""Parameter-scan ensembles (BASELINE config 5): independent simulations that
+differ only in the values of runtime model parameters, sharded one simulation
+per GPU slot — "replicas only": no data-path collective.
+
+The reference has no scan feature: a scan is a Python loop that sets a
+parameter and calls ``simulate()`` again, re-JIT-compiling the reactions every
+time because parameter values are inlined into the expression text
+(sme_model.cpp:541-617, pde.cpp:65-77; docs/sme/notebooks/simulating.ipynb).
+Here the scanned parameters stay symbolic (``sme_param_k`` kernel arguments), so
+every member reuses one NVRTC-compiled module, and the members of one GPU run
+concurrently on their own CUDA streams, driven by a small pool of host threads
+(the ctypes calls release the GIL).
+"""
+from __future__ import annotations
+
+import copy
+from concurrent.futures import ThreadPoolExecutor
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from .pixelsim import PixelSim
+from .problem import Problem
+
+
+def scan_values(centre: float, n_members: int, factor: float = 10.0,
+                seed: int = 5000) -> np.ndarray:
+    """log-uniform samples in [centre / factor, centre * factor] (SURVEY.md
+    section 8(d), config C5: seed 5000)"""
+    rng = np.random.default_rng(seed)
+    return centre * factor ** rng.uniform(-1.0, 1.0, size=n_members)
+
+
+def members_of_rank(n_members: int, rank: int, world: int) -> List[int]:
+    """member m runs on rank m mod world"""
+    return list(range(rank, n_members, world))
+
+
+@dataclass
+class MemberResult:
+    member: int
+    params: np.ndarray
+    steps: int
+    discarded: int
+    error: str
+    concentrations: List[np.ndarray]
+    device_ms: float
+
+
+class Ensemble:
+    """``problem.params`` holds the base values of the runtime parameters;
+    ``values[m]`` are member m's."""
+
+    def __init__(self, problem: Problem, values: Sequence[Sequence[float]],
+                 rank: int = 0, world: int = 1, device: int = 0, concurrency: int = 8,
+                 sim_factory=None):
+        self.problem = problem
+        self.values = np.atleast_2d(np.asarray(values, dtype=np.float64))
+        if self.values.shape[0] == 1 and len(problem.params) == 1 and \
+                np.asarray(values).ndim == 1:
+            self.values = self.values.T
+        assert self.values.shape[1] == len(problem.params)
+        self.rank, self.world, self.device = rank, world, device
+        self.concurrency = max(1, concurrency)
+        self.members = members_of_rank(self.values.shape[0], rank, world)
+        self._factory = sim_factory or PixelSim
+
+    def _make(self, m: int):
+        p = copy.copy(self.problem)
+        p.params = list(self.values[m])
+        p.device = self.device
+        return self._factory(p)
+
+    def _run_member(self, m: int, time: float, sim=None) -> MemberResult:
+        sim = sim or self._make(m)
+        err = sim.errorMessage()
+        steps = sim.run(time) if not err else 0
+        res = MemberResult(
+            member=m, params=self.values[m].copy(), steps=steps,
+            discarded=sim.discardedSteps, error=err or sim.errorMessage(),
+            concentrations=[sim.getConcentrations(ci).copy()
+                            for ci in range(len(self.problem.compartments))],
+            device_ms=sim.lastRunMs() if hasattr(sim, "lastRunMs") else 0.0)
+        sim.close()
+        return res
+
+    def run(self, time: float) -> List[MemberResult]:
+        """simulate this rank's members for ``time``; results in member order"""
+        if not self.members:
+            return []
+        # the first member compiles the module; the others hit the cache
+        first = self._run_member(self.members[0], time)
+        rest = self.members[1:]
+        if not rest:
+            return [first]
+        with ThreadPoolExecutor(max_workers=min(self.concurrency, len(rest))) as pool:
+            others = list(pool.map(lambda m: self._run_member(m, time), rest))
+        return [first] + others

@@ -36,14 +36,21 @@ def _scaled(node, factor: float):
 
 def build_rhs(species: Sequence[str], reactions: Sequence[ReactionDef],
               constants: Optional[Dict[str, float]] = None, scale: float = 1.0,
-              functions=None, substitutions: Optional[Dict[str, float]] = None
-              ) -> List[str]:
+              functions=None, substitutions: Optional[Dict[str, float]] = None,
+              runtime_params: Sequence[str] = ()) -> List[str]:
     """C expressions (in sme_var_k, k = index into ``species``) of the reaction
     term of every species: what ``ReacExpr.expressions`` holds after the
-    reference's Pde step, printed for the C-ABI."""
+    reference's Pde step, printed for the C-ABI.
+
+    ``runtime_params``: ids of global or reaction-local parameters that stay
+    symbolic (printed as ``sme_param_<k>``, k = position in this list) instead
+    of being inlined as numbers; a local parameter of one reaction can be named
+    ``"<reaction id>.<parameter id>"``."""
     constants = dict(constants or {})
     substitutions = substitutions or {}
     names = {v: f"sme_var_{k}" for k, v in enumerate(species)}
+    for k, pid in enumerate(runtime_params):
+        names[pid] = f"sme_param_{k}"
     out = []
     for sp in species:
         total = None
@@ -58,6 +65,11 @@ def build_rhs(species: Sequence[str], reactions: Sequence[ReactionDef],
                     env[k] = v
             for v in species:
                 env.pop(v, None)
+            for pid in runtime_params:
+                if pid.startswith(r.id + ".") and pid[len(r.id) + 1:] in env:
+                    env[pid[len(r.id) + 1:]] = pid  # local parameter -> symbol
+                else:
+                    env.pop(pid, None)
             rate = E.substitute(E.parse(r.rate), env, functions)
             term = _scaled(_scaled(rate, m), scale)
             total = term if total is None else ("add", total, term)

@@ -71,6 +71,7 @@ def _bind(lib, prefix: str):
     fn("dominant_kernel", C.c_char_p, [vp], optional=True)
     fn("set_allreduce_max", None, [vp, _ALLREDUCE_CB, vp], optional=True)
     fn("halo_exchanges", C.c_uint64, [vp], optional=True)
+    fn("set_params", C.c_int, [vp, C.POINTER(C.c_double), C.c_size_t], optional=True)
     fn("comm_create", C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(vp)], optional=True)
     fn("comm_allreduce_max", C.c_int, [vp, C.POINTER(C.c_double), C.c_int], optional=True)
     fn("comm_barrier", C.c_int, [vp], optional=True)
@@ -244,6 +245,13 @@ class PixelSim(CSim):
         n = C.c_uint64()
         self._f("get_kernel_timing")(self._h, C.byref(ms), C.byref(n))
         return ms.value, int(n.value)
+
+    def setParams(self, values) -> None:
+        """new values of the runtime model parameters (sme_param_k)"""
+        a = np.ascontiguousarray(values, dtype=np.float64)
+        rc = self._f("set_params")(self._h, a.ctypes.data_as(C.POINTER(C.c_double)), a.size)
+        if rc != 0:
+            raise RuntimeError(self.errorMessage())
 
     def dominantKernel(self) -> str:
         return self._f("dominant_kernel")(self._h).decode()

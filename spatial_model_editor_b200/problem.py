@@ -77,9 +77,10 @@ class CProblem(C.Structure):
         ("rank", C.c_int32),
         ("n_ranks", C.c_int32),
         ("kernel_variant", C.c_int32),
-        ("reserved0", C.c_uint32),
+        ("n_params", C.c_uint32),
         ("comm_name", C.c_char_p),
-        ("reserved", C.c_uint32 * 4),
+        ("params", C.POINTER(C.c_double)),
+        ("reserved", C.c_uint32 * 2),
     ]
 
 
@@ -132,6 +133,7 @@ class Problem:
     rank: int = 0                         # z-slab decomposition (multigpu.py)
     n_ranks: int = 1
     comm_name: Optional[str] = None
+    params: Sequence[float] = ()          # values of sme_param_k (runtime parameters)
 
     def evals_per_step(self) -> int:
         """voxel*species RHS evaluations in one RK step (the bench metric)."""
@@ -206,4 +208,7 @@ class Problem:
         p.n_ranks = self.n_ranks
         p.comm_name = self.comm_name.encode() if self.comm_name else None
         p.kernel_variant = self.kernel_variant
+        p.n_params = len(self.params)
+        p.params = arr(np.asarray(self.params, dtype=np.float64), np.float64, C.c_double) \
+            if len(self.params) else None
         return p, keep

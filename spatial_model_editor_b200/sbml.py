@@ -548,9 +548,22 @@ def initial_concentration(m: SbmlModel, s: SbmlSpecies, voxels: np.ndarray,
     return np.broadcast_to(np.asarray(out, dtype=np.float64), (n,)).copy()
 
 
+def parameter_value(m: SbmlModel, pid: str) -> float:
+    """current value of a global parameter or of ``"<reaction>.<local parameter>"``"""
+    if "." in pid:
+        rid, lid = pid.split(".", 1)
+        for r in m.reactions:
+            if r.id == rid and lid in r.local:
+                return r.local[lid]
+    return global_constants(m)[pid]
+
+
 def to_problem(m: SbmlModel, integrator: Optional[int] = None,
-               substitutions: Optional[Dict[str, float]] = None) -> P.Problem:
-    """what PixelSim / CudaPixelSim build from the Model, as a flat Problem"""
+               substitutions: Optional[Dict[str, float]] = None,
+               runtime_params: Tuple[str, ...] = ()) -> P.Problem:
+    """what PixelSim / CudaPixelSim build from the Model, as a flat Problem.
+    ``runtime_params`` stay symbolic (see pde.build_rhs); their current values
+    become ``Problem.params``."""
     constants = global_constants(m)
     rules = _resolved_rules(m)
     env_rules = {k: v for k, v in rules.items()}
@@ -595,7 +608,7 @@ def to_problem(m: SbmlModel, integrator: Optional[int] = None,
         conc0 = np.stack([initial_concentration(m, s, voxels, constants)
                           for s in sim_species], axis=1)
         exprs = build_rhs(ids, reaction_defs(cid), constants, functions=m.functions,
-                          substitutions=substitutions)
+                          substitutions=substitutions, runtime_params=runtime_params)
         comp_index[cid] = len(comps)
         comps.append(P.Compartment(
             id=cid, species=ids, expressions=exprs, diffusion=diffusion,
@@ -638,7 +651,8 @@ def to_problem(m: SbmlModel, integrator: Optional[int] = None,
         vb = G.compartment_voxels(m.labels, lb)
         face_pairs = G.membrane_face_pairs(m.labels.shape, va, vb, vp)
         exprs = build_rhs(names, defs, constants, scale=m.vol_over_l3,
-                          functions=m.functions, substitutions=substitutions)
+                          functions=m.functions, substitutions=substitutions,
+                          runtime_params=runtime_params)
         membranes.append(P.Membrane(id=mid, comp_a=ia, comp_b=ib, pairs=face_pairs,
                                     flux_length=G.flux_lengths(m.voxel_size),
                                     expressions=exprs))
@@ -648,4 +662,5 @@ def to_problem(m: SbmlModel, integrator: Optional[int] = None,
         integrator=int(opts.get("integrator", P.RK212)) if integrator is None else integrator,
         max_err_abs=opts.get("maxErrAbs", P.DBL_MAX), max_err_rel=opts.get("maxErrRel", 0.005),
         max_timestep=opts.get("maxTimestep", P.DBL_MAX), image_size=(nx, ny, nz),
-        unsupported=unsupported)
+        unsupported=unsupported,
+        params=[parameter_value(m, pid) for pid in runtime_params])

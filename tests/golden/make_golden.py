@@ -44,7 +44,7 @@ def dump(name, m, problem):
         origin=list(m.origin), vol_over_l3=m.vol_over_l3, label_of=m.label_of,
         integrator=problem.integrator, max_err_abs=problem.max_err_abs,
         max_err_rel=problem.max_err_rel, max_timestep=problem.max_timestep,
-        unsupported=problem.unsupported,
+        unsupported=problem.unsupported, params=list(problem.params),
         compartments=[dict(id=c.id, species=c.species, expressions=c.expressions,
                            diffusion_constants=[s.diffusion for s in m.species
                                                 if s.id in c.species])
@@ -72,6 +72,13 @@ def main():
     for name, rel in MODELS.items():
         m = sbml.load_sbml(os.path.join(REF, rel))
         dump(name, m, sbml.to_problem(m))
+    # BASELINE config 5: liver-simplified with the scanned rate constant (IkBa mRNA degradation;
+    # TNFa is zero in the stored state, so its degradation rate has no effect) kept as
+    # a runtime parameter (sme_param_0), so that all ensemble members share one
+    # compiled module
+    m = sbml.load_sbml(os.path.join(REF, MODELS["liver-simplified"]))
+    dump("liver-simplified-scan", m,
+         sbml.to_problem(m, runtime_params=("IkBa_mRNA_degradation_c_k1",)))
     # K1: the 1 x 3 voxel membrane chain of simulate_t.cpp:18-88 — the non-spatial
     # model with a 3-pixel image imported and four reactions moved to membranes
     lab = np.array([[[1], [2], [3]]])

@@ -80,5 +80,5 @@ def load_golden(name, integrator=None):
         comps, membs, integrator=meta["integrator"] if integrator is None else integrator,
         max_err_abs=meta["max_err_abs"], max_err_rel=meta["max_err_rel"],
         max_timestep=meta["max_timestep"], image_size=(nx, ny, nz),
-        unsupported=meta["unsupported"])
+        unsupported=meta["unsupported"], params=list(meta.get("params", [])))
     return problem, meta, labels
