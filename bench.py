@@ -54,6 +54,36 @@ def make_problem(nx, ny, nz, integrator, device=-1, z0=0):
     return p
 
 
+def make_listed_problem(args, integrator, device):
+    """--workload c2disc / c3: voxel-list geometries (index-list kernels).
+    c2disc: gray-scott on the disc of the 100x100 example upscaled to size^2
+    (N ~ 0.315 size^2); c3: two brusselator compartments (outer frame / inner
+    square) coupled by a membrane flux, size^2 voxels in total."""
+    import spatial_model_editor_b200 as smeb
+    from spatial_model_editor_b200 import models as M
+    n = args.size
+    tol = dict(max_err_rel=0.005) if args.adaptive else dict(
+        max_err_rel=smeb.DBL_MAX, max_err_abs=smeb.DBL_MAX, max_timestep=args.dt)
+    if args.workload == "c2disc":
+        lab = M.disc_labels(n, n)
+        from spatial_model_editor_b200 import geometry as G
+        vox = G.compartment_voxels(lab, 1)
+        px, py = (vox[:, 0] % 100).astype(np.float64), (vox[:, 1] % 100).astype(np.float64)
+        conc0 = np.ones((len(vox), 2))
+        conc0[:, 1] = (np.exp(-((px - 33.0) ** 2 + (py - 40.0) ** 2) / 50.0)
+                       + np.exp(-((px - 70.0) ** 2 + (py - 66.0) ** 2) / 50.0))
+        p = M.labelled_problem(lab, [dict(label=1, id="disc", kin=M.GRAY_SCOTT, conc0=conc0)],
+                               integrator=integrator, **tol)
+        text = f"gray-scott kinetics on the example disc upscaled to {n}x{n}"
+    else:
+        p = M.two_compartment_brusselator(n, n, integrator=integrator, **tol)
+        text = (f"brusselator kinetics in two compartments (outer frame / inner square) + "
+                f"membrane flux km*(X_a-X_b), {n}x{n} pixels")
+    p.device = device
+    sizes = ", ".join(f"{c.id}: N={c.n_voxels} S={c.n_species}" for c in p.compartments)
+    return p, f"{text}; voxel-list geometry ({sizes})"
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region"""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -133,6 +163,22 @@ def cpu_baseline(args, integrator, threads, budget_s=12.0):
     the same workload (a 32-plane slab of the same x-y extent, about 10-20 s of
     CPU work), all host threads"""
     from oracle.oracle_sim import OraclePixelSim
+    if args.workload in ("c2disc", "c3"):
+        import copy
+        a2 = copy.copy(args)
+        a2.size, a2.adaptive = min(args.size, 2048), False
+        p, text = make_listed_problem(a2, integrator, -1)
+        sim = OraclePixelSim(p, threads=threads)
+        sim.nextTimestep = args.dt
+        sim.run(args.dt)
+        t0, steps = time.perf_counter(), 0
+        while time.perf_counter() - t0 < budget_s:
+            steps += sim.run(args.dt)
+        el = time.perf_counter() - t0
+        ncores = OraclePixelSim.maxThreads() if threads == 0 else threads
+        return {"value": p.evals_per_step() * steps / el, "unit": UNIT, "cores": ncores,
+                "kind": "port", "sample": f"{text}, {args.integrator.upper()} fixed step, "
+                                          f"{steps} steps, {el:.1f} s, OpenMP threads={ncores}"}
     p, (nx, ny, nz) = cpu_sample_problem(args, integrator, 32)
     sim = OraclePixelSim(p, threads=threads)
     sim.nextTimestep = DT  # skip the controller's 1e-7 start-up step
@@ -244,7 +290,11 @@ def main():
     ap.add_argument("--integrator", default="rk212")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--variant", type=int, default=0)
-    ap.add_argument("--workload", default="c4", help="c4 (headline) | ensemble")
+    ap.add_argument("--workload", default="c4",
+                    help="c4 (headline) | c2disc | c3 | ensemble")
+    ap.add_argument("--adaptive", action="store_true",
+                    help="c2disc / c3: adaptive steps at relTol 0.005 instead of fixed dt")
+    ap.add_argument("--dt", type=float, default=DT)
     ap.add_argument("--members", type=int, default=64)
     ap.add_argument("--concurrency", type=int, default=8)
     ap.add_argument("--sim-time", type=float, default=1.0)
@@ -278,7 +328,18 @@ def main():
     nx = ny = args.size
     nz = args.nz or args.size
     W, K = max(args.warmup, 3), args.steps
-    if world > 1:
+    listed = args.workload in ("c2disc", "c3")
+    DTs = args.dt
+    if listed:
+        if world > 1:
+            raise SystemExit("bench: voxel-list workloads run on one GPU")
+        p, workload_text = make_listed_problem(args, integrator, local_rank)
+        sim = smeb.PixelSim(p)
+        evals_per_step = p.evals_per_step()
+        dom = max(p.compartments, key=lambda c: c.n_voxels * c.n_species)
+        values_per_rank = dom.n_voxels * dom.n_species
+        nn_bytes = 24 * dom.n_voxels
+    elif world > 1:
         from spatial_model_editor_b200.multigpu import SlabPixelSim
         # the global box is only described (no global array is ever built);
         # every rank generates its own planes, ghosts included
@@ -294,26 +355,38 @@ def main():
         evals_per_step = p.evals_per_step()
     if sim.errorMessage():
         raise SystemExit("bench: " + sim.errorMessage())
-    values_per_rank = nx * ny * nz * 2
+    if not listed:
+        values_per_rank = nx * ny * nz * 2
+        nn_bytes = 0
+        workload_text = (f"gray-scott-3d kinetics, {nx}x{ny}x{nz * world} full-box "
+                         f"compartment ({nz} planes per GPU), S=2")
 
     # warm-up: W steps of DT (the controller's 1e-7 start-up step is skipped by
     # seeding nextTimestep, which run() otherwise raises to DT after one step)
-    sim.nextTimestep = DT
-    assert sim.run(W * DT) == W
+    adaptive = listed and args.adaptive
+    if adaptive:
+        sim.run(W * DTs)  # start-up transient of the step-size controller
+    else:
+        sim.nextTimestep = DTs
+        assert sim.run(W * DTs) == W
     launches0 = sim.launchCount()
+    disc0 = sim.discardedSteps
     sim.setKernelTiming(True)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     barrier()
-    steps = sim.run(K * DT)
+    steps = sim.run(K * DTs)
     barrier()
     ms = sim.lastRunMs()
     clocks = sampler.stop() if rank == 0 else None
     kms, klaunches = sim.kernelTiming()
     sim.setKernelTiming(False)
     launches = sim.launchCount() - launches0
-    assert steps == K, (steps, K, sim.errorMessage())
+    if adaptive:  # a step = one attempted RK step (accepted or discarded)
+        K = steps + (sim.discardedSteps - disc0)
+    else:
+        assert steps == K, (steps, K, sim.errorMessage())
     if world > 1:
         t = torch.tensor([ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -326,14 +399,22 @@ def main():
     # end to end through the public call with HOST buffers: one image interval =
     # upload of the state from pinned host memory, K steps, download of the result
     # pinned mirror (the local slab incl. ghost planes when decomposed)
-    host = sim.getConcentrationsWithGhosts(0) if world > 1 else sim.getConcentrations(0)
-    h2d = d2h = host.nbytes
+    ncomp = len(p.compartments)
+    hosts = [sim.getConcentrationsWithGhosts(0)] if world > 1 else [
+        np.array(sim.getConcentrations(i)) if ncomp > 1 else sim.getConcentrations(i)
+        for i in range(ncomp)]
+    h2d = d2h = sum(h.nbytes for h in hosts)
     barrier()
     t0 = time.perf_counter()
-    sim.setConcentrations(0, host)
-    steps2 = sim.run(K * DT)
-    out = sim.getConcentrations(0)
-    checksum = float(out[::4097, 1].sum())
+    for i, h in enumerate(hosts):
+        sim.setConcentrations(i, h)
+    steps2 = sim.run(args.steps * DTs)
+    if adaptive:
+        steps2 = K
+    checksum = 0.0
+    for i in range(ncomp):
+        out = sim.getConcentrations(i)
+        checksum += float(out[::4097, -1].sum())
     barrier()
     e2e_s = time.perf_counter() - t0
     if world > 1:
@@ -346,13 +427,14 @@ def main():
     # per launch = 8 B x values x (reads + writes of whole arrays) averaged over
     # the stages of one step: RK212 16 + 24 = 40 B per value per step
     bytes_per_value_step = {0: 16, 1: 40, 2: 64, 3: 152}[integrator]
-    alg_bytes_per_launch = bytes_per_value_step * values_per_rank / STAGES[integrator]
+    alg_bytes_per_launch = (bytes_per_value_step * values_per_rank / STAGES[integrator]
+                            + nn_bytes)
     peak, peak_src = measured_peak()
     traffic = None
     try:  # ncu dram__bytes of the same kernel on the headline config (profiles/)
         with open(os.path.join(ROOT, "profiles", "r1_v2_traffic.json")) as f:
             tj = json.load(f)
-        if (nx, ny, nz, args.integrator) == (512, 512, 512, "rk212"):
+        if (nx, ny, nz, args.integrator) == (512, 512, 512, "rk212") and not listed:
             traffic = tj["dram_bytes_per_launch"]["mean"]
     except Exception:
         traffic = None
@@ -373,9 +455,9 @@ def main():
             "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {
-                "workload": f"gray-scott-3d kinetics, {nx}x{ny}x{nz * world} full-box "
-                            f"compartment ({nz} planes per GPU), S=2, {args.integrator.upper()} "
-                            f"fixed step dt={DT} (maxErr=DBL_MAX like benchmark.cpp:214-216)",
+                "workload": workload_text + f", {args.integrator.upper()} " + (
+                    "adaptive relTol=0.005 (a step = one attempted step)" if adaptive else
+                    f"fixed step dt={DTs} (maxErr=DBL_MAX like benchmark.cpp:214-216)"),
                 "l2": "inputs larger than L2 (state array %.2f GiB per GPU)" % (
                     values_per_rank * 8 / 2 ** 30),
                 "parallelism": f"z-slabs x{world}" if world > 1 else "single GPU",

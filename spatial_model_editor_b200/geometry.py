@@ -63,8 +63,13 @@ def membrane_voxel_pairs(labels: np.ndarray, colour_index: Dict[int, int]
     y ascending), then z-neighbours (per x, per y, z ascending).  Each pair is
     (voxel in the lower-index colour, voxel in the higher-index colour)."""
     nz, ny, nx = labels.shape
-    ci = np.vectorize(lambda v: colour_index.get(int(v), -1))(labels) \
-        if labels.size else labels
+    # label -> colour index through a lookup table (labels are small ints)
+    lo, hi = (int(labels.min()), int(labels.max())) if labels.size else (0, 0)
+    lut = np.full(hi - lo + 1, -1, dtype=np.int64)
+    for lab, c in colour_index.items():
+        if lo <= int(lab) <= hi:
+            lut[int(lab) - lo] = c
+    ci = lut[labels.astype(np.int64) - lo] if labels.size else labels
     out: Dict[Tuple[int, int], List[Tuple[tuple, tuple]]] = {}
 
     def add(prev_vox, cur_vox, prev_c, cur_c, prev_l, cur_l):
