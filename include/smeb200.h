@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define SMEB200_ABI_VERSION 2
+#define SMEB200_ABI_VERSION 3
 
 /* mirrors sme::simulate::PixelIntegratorType (simulate_options.hpp:113-119) */
 enum smeb200_integrator {
@@ -41,10 +41,13 @@ enum smeb200_integrator {
 enum smeb200_face { SMEB200_XP = 0, SMEB200_XM, SMEB200_YP, SMEB200_YM,
                     SMEB200_ZP, SMEB200_ZM };
 
-/* bits of smeb200_problem.unsupported: features of the CPU PixelSim that the
- * reference GPU backend rejects in its constructor (cudapixelsim.cpp:789-809,
- * pixelsim_common.hpp:80-121).  The adapter sets them; smeb200_create then
- * fails with the same message text as the reference. */
+/* bits of smeb200_problem.unsupported: features of the CPU PixelSim that this
+ * library does not compute.  The adapter sets them; smeb200_create then fails
+ * with the message text of the reference GPU backend (cudapixelsim.cpp:789-809,
+ * pixelsim_common.hpp:80-121).  Time / space dependent reactions, non-spatial
+ * species and non-unit storage ARE computed (describe them through
+ * smeb200_compartment::n_primary_species / non_spatial / inv_storage); their
+ * bits remain for adapters that prefer to refuse such models. */
 enum smeb200_unsupported {
   SMEB200_HAS_CROSS_DIFFUSION = 1,
   SMEB200_HAS_TIME_DEPENDENCE = 2,
@@ -83,6 +86,24 @@ typedef struct smeb200_compartment {
    * (cudapixelsim.cpp:108-136) */
   const char *const *expressions;
   const char *const *species_names; /* optional, for the adaptive-failure text */
+  /* --- features of the CPU PixelSim beyond the reference GPU backend --------
+   * n_primary_species: the first n_primary_species of the n_species state
+   * components are model species; the remaining ones are the "time, x, y, z"
+   * padding the CPU solver appends when reactions depend on time / space
+   * (pixelsim_impl.cpp:312-349,405-423): ordinary state components with zero
+   * diffusion whose expressions are "1" (time) and "0" (x, y, z), initialised
+   * by the adapter to 0 and to the voxel-centre coordinates.  They are not
+   * clamped (pixelsim_impl.cpp:643-654) and are what getConcentrationPadding
+   * reports (pixelsim.cpp:478).  0 means n_species (no padding). */
+  uint32_t n_primary_species;
+  /* species whose dc/dt is replaced by its spatial average before the update
+   * (SimCompartment::spatiallyAverageDcdt, pixelsim_impl.cpp:150-163) */
+  uint32_t n_non_spatial;
+  const uint32_t *non_spatial;  /* [n_non_spatial] species indices */
+  /* [n_species] 1/storage per state component (pixelsim_impl.cpp:165-189,
+   * 214-232); NULL = unit storage.  A zero entry (zero-storage species,
+   * algebraic constraint) is rejected. */
+  const double *inv_storage;
 } smeb200_compartment;
 
 /* One geometry::Membrane + SimMembrane (pixelsim_impl.cpp:929-1047). */
@@ -95,9 +116,11 @@ typedef struct smeb200_membrane {
   const uint32_t *pairs[6];
   /* voxel length in the flux direction per face (pixelsim_common.hpp:39-54) */
   double flux_length[6];
-  /* (SA + SB) CUDA-C expressions in sme_var_0..sme_var_{SA+SB-1}: variables
-   * are [species of A | species of B], results [0,SA) go to A and [SA,SA+SB)
-   * to B (pixelsim_impl.cpp:960-973, 84-111); already scaled by volOverL3 */
+  /* (SA + SB) CUDA-C expressions in sme_var_0..sme_var_{SA+SB+E-1}: variables
+   * are [primary species of A | primary species of B | the E padding
+   * components (time, x, y, z) of B's voxel, or of A's if B is not simulated],
+   * results [0,SA) go to A and [SA,SA+SB) to B (pixelsim_impl.cpp:960-973,
+   * 84-111); already scaled by volOverL3.  SA, SB = n_primary_species. */
   const char *const *expressions;
 } smeb200_membrane;
 

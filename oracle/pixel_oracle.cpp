@@ -51,6 +51,10 @@ struct OCompartment {
   std::size_t nSpecies{0};
   std::vector<std::size_t> nn; // [6*nPixels]: +x,-x,+y,-y,+z,-z
   std::vector<std::array<double, 3>> diff; // diffConstantsUniform
+  std::size_t nPrimarySpecies{0};          // pixelsim_impl.cpp:205
+  std::vector<std::size_t> nonSpatialSpeciesIndices;
+  std::vector<double> invStorage;
+  bool hasNonUnitStorage{false};
   std::vector<double> conc, dcdt, s2, s3;
   std::vector<int32_t> voxels;
   std::vector<std::string> speciesNames;
@@ -82,6 +86,30 @@ struct OCompartment {
     }
   }
 };
+
+// pixelsim_impl.cpp:150-163 (serial in the reference)
+inline void spatiallyAverageDcdt(OCompartment &c) {
+  for (std::size_t is : c.nonSpatialSpeciesIndices) {
+    double av = 0;
+    for (std::size_t ix = 0; ix < c.nPixels; ++ix) {
+      av += c.dcdt[ix * c.nSpecies + is];
+    }
+    av /= static_cast<double>(c.nPixels);
+    for (std::size_t ix = 0; ix < c.nPixels; ++ix) {
+      c.dcdt[ix * c.nSpecies + is] = av;
+    }
+  }
+}
+
+// pixelsim_impl.cpp:165-189
+inline void applyStorage(OCompartment &c, std::size_t begin, std::size_t end) {
+  for (std::size_t i = begin; i < end; ++i) {
+    const std::size_t ix{i * c.nSpecies};
+    for (std::size_t is = 0; is < c.nSpecies; ++is) {
+      c.dcdt[ix + is] *= c.invStorage[is];
+    }
+  }
+}
 
 template <typename Body>
 void parallelFor(bool threads, std::size_t n, const Body &body) {
@@ -147,24 +175,32 @@ struct Oracle {
                                  std::size_t end) {
     OCompartment *A = m.compA >= 0 ? &comps[m.compA] : nullptr;
     OCompartment *B = m.compB >= 0 ? &comps[m.compB] : nullptr;
-    const std::size_t nA = A != nullptr ? A->nSpecies : 0;
-    const std::size_t nB = B != nullptr ? B->nSpecies : 0;
-    std::vector<double> species(nA + nB, 0.0), result(nA + nB, 0.0);
+    // strides include the time/space padding, nA / nB are the model species
+    const std::size_t strideA = A != nullptr ? A->nSpecies : 0;
+    const std::size_t strideB = B != nullptr ? B->nSpecies : 0;
+    const std::size_t nA = A != nullptr ? A->nPrimarySpecies : 0;
+    const std::size_t nB = B != nullptr ? B->nPrimarySpecies : 0;
+    const std::size_t nExtraVars =
+        B != nullptr ? strideB - nB : (A != nullptr ? strideA - nA : 0);
+    std::vector<double> species(nA + nB + nExtraVars, 0.0),
+        result(nA + nB + nExtraVars, 0.0);
     const double fluxLength = m.fluxLength[dir];
     for (std::size_t i = begin; i < end; ++i) {
       const auto [ixA, ixB] = m.pairs[dir][i];
       if (A != nullptr) {
-        std::copy_n(&A->conc[ixA * nA], nA, &species[0]);
+        std::copy_n(&A->conc[ixA * strideA], nA, &species[0]);
       }
       if (B != nullptr) {
-        std::copy_n(&B->conc[ixB * nB], nB, &species[nA]);
+        std::copy_n(&B->conc[ixB * strideB], strideB, &species[nA]);
+      } else if (A != nullptr) {
+        std::copy_n(&A->conc[ixA * strideA + nA], nExtraVars, &species[nA]);
       }
       m.reac(result.data(), species.data());
       for (std::size_t is = 0; is < nA; ++is) {
-        A->dcdt[ixA * nA + is] += result[is] / fluxLength;
+        A->dcdt[ixA * strideA + is] += result[is] / fluxLength;
       }
       for (std::size_t is = 0; is < nB; ++is) {
-        B->dcdt[ixB * nB + is] += result[is + nA] / fluxLength;
+        B->dcdt[ixB * strideB + is] += result[is + nA] / fluxLength;
       }
     }
   }
@@ -191,6 +227,14 @@ struct Oracle {
                     });
       }
     }
+    for (auto &c : comps) {
+      spatiallyAverageDcdt(c);
+      if (c.hasNonUnitStorage) {
+        parallelFor(useThreads, c.nPixels, [&](std::size_t b, std::size_t e) {
+          applyStorage(c, b, e);
+        });
+      }
+    }
   }
 
   template <typename F> void forValues(OCompartment &c, const F &f) {
@@ -203,9 +247,14 @@ struct Oracle {
 
   // pixelsim_impl.cpp:643-665
   void clampNegative(OCompartment &c) {
-    forValues(c, [&](std::size_t i) {
-      if (c.conc[i] < 0.0) {
-        c.conc[i] = 0.0;
+    parallelFor(useThreads, c.nPixels, [&](std::size_t b, std::size_t e) {
+      for (std::size_t ix = b; ix < e; ++ix) {
+        for (std::size_t is = 0; is < c.nPrimarySpecies; ++is) {
+          double &v = c.conc[ix * c.nSpecies + is];
+          if (v < 0.0) {
+            v = 0.0;
+          }
+        }
       }
     });
   }
@@ -307,11 +356,17 @@ struct Oracle {
 
   // pixelsim_impl.cpp:774-792 — serial in the reference too
   void calculateRKError(const OCompartment &c, double &eabs, double &erel) const {
-    for (std::size_t i = 0; i < c.conc.size(); ++i) {
-      const double localErr = std::abs(c.conc[i] - c.s2[i]);
-      eabs = std::max(eabs, localErr);
-      const double localNorm = 0.5 * (c.conc[i] + c.s3[i] + epsilon);
-      erel = std::max(erel, localErr / localNorm);
+    for (std::size_t ix = 0; ix < c.nPixels; ++ix) {
+      for (std::size_t is = 0; is < c.nSpecies; ++is) {
+        if (c.invStorage[is] == 0.0) {
+          continue;
+        }
+        const std::size_t i = ix * c.nSpecies + is;
+        const double localErr = std::abs(c.conc[i] - c.s2[i]);
+        eabs = std::max(eabs, localErr);
+        const double localNorm = 0.5 * (c.conc[i] + c.s3[i] + epsilon);
+        erel = std::max(erel, localErr / localNorm);
+      }
     }
   }
 
@@ -451,7 +506,7 @@ struct Oracle {
   void compileReactions(const smeb200_problem &p) {
     std::ostringstream src;
     src << "#include <math.h>\n";
-    auto emit = [&](const std::string &name, uint32_t nVars,
+    auto emit = [&](const std::string &name, uint32_t nVars, uint32_t nExpr,
                     const char *const *expr) {
       src << "void " << name
           << "(double* sme_out, const double* sme_values) {\n";
@@ -467,22 +522,30 @@ struct Oracle {
         src << "  const double sme_param_" << i << " = " << buf
             << "; (void)sme_param_" << i << ";\n";
       }
-      for (uint32_t i = 0; i < nVars; ++i) {
+      for (uint32_t i = 0; i < nExpr; ++i) {
         src << "  sme_out[" << i << "] = " << expr[i] << ";\n";
       }
       src << "}\n";
     };
     for (uint32_t c = 0; c < p.n_compartments; ++c) {
       emit("reac" + std::to_string(c), p.compartments[c].n_species,
-           p.compartments[c].expressions);
+           p.compartments[c].n_species, p.compartments[c].expressions);
     }
     for (uint32_t m = 0; m < p.n_membranes; ++m) {
       const auto &mb = p.membranes[m];
-      const uint32_t nA =
-          mb.comp_a >= 0 ? p.compartments[mb.comp_a].n_species : 0;
-      const uint32_t nB =
-          mb.comp_b >= 0 ? p.compartments[mb.comp_b].n_species : 0;
-      emit("memb" + std::to_string(m), nA + nB, mb.expressions);
+      auto primary = [&](int ci) -> uint32_t {
+        if (ci < 0) {
+          return 0;
+        }
+        const auto &pc = p.compartments[ci];
+        return pc.n_primary_species != 0 ? pc.n_primary_species : pc.n_species;
+      };
+      auto extra = [&](int ci) -> uint32_t {
+        return ci < 0 ? 0 : p.compartments[ci].n_species - primary(ci);
+      };
+      const uint32_t nA = primary(mb.comp_a), nB = primary(mb.comp_b);
+      const uint32_t nE = mb.comp_b >= 0 ? extra(mb.comp_b) : extra(mb.comp_a);
+      emit("memb" + std::to_string(m), nA + nB + nE, nA + nB, mb.expressions);
     }
     char tmpl[] = "/tmp/smeb200_oracle_XXXXXX";
     const int fd = mkstemp(tmpl);
@@ -580,14 +643,29 @@ struct Oracle {
           }
         }
       }
+      c.nPrimarySpecies =
+          pc.n_primary_species != 0 ? pc.n_primary_species : pc.n_species;
+      for (uint32_t k = 0; k < pc.n_non_spatial; ++k) {
+        c.nonSpatialSpeciesIndices.push_back(pc.non_spatial[k]);
+      }
       for (uint32_t s = 0; s < pc.n_species; ++s) {
         c.diff.push_back({pc.diffusion[3 * s], pc.diffusion[3 * s + 1],
                           pc.diffusion[3 * s + 2]});
+        c.invStorage.push_back(pc.inv_storage != nullptr ? pc.inv_storage[s]
+                                                         : 1.0);
+        if (c.invStorage.back() == 0.0) {
+          throw std::runtime_error(
+              "oracle: zero-storage species are not restated");
+        }
+        if (c.invStorage.back() != 1.0) {
+          c.hasNonUnitStorage = true;
+        }
         // pixelsim_common.hpp:33-37, pixelsim_impl.cpp:249-255
         c.maxStableTimestep = std::min(
             c.maxStableTimestep,
-            1.0 / (2.0 * (c.diff.back()[0] + c.diff.back()[1] +
-                          c.diff.back()[2])));
+            1.0 / (2.0 * (c.diff.back()[0] * c.invStorage.back() +
+                          c.diff.back()[1] * c.invStorage.back() +
+                          c.diff.back()[2] * c.invStorage.back())));
         c.speciesNames.emplace_back(
             pc.species_names != nullptr && pc.species_names[s] != nullptr
                 ? pc.species_names[s]

@@ -108,7 +108,9 @@ int smeb200_get_lower_order(smeb200_sim *sim, size_t compartment,
   });
 }
 
-size_t smeb200_get_concentration_padding(const smeb200_sim *) { return 0; }
+size_t smeb200_get_concentration_padding(const smeb200_sim *s) {
+  return s != nullptr ? s->impl.concentrationPadding() : 0;
+}
 
 int smeb200_set_concentrations(smeb200_sim *sim, size_t compartment,
                                const double *data, size_t n) {

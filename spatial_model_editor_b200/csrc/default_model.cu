@@ -7,7 +7,11 @@
 #include "device_kernels.cuh"
 
 struct Reac0 {
-  static constexpr int S = 2;
+  static constexpr int S = 2, SP = 2, NNS = 0;
+  static constexpr bool STORAGE = false;
+  static __device__ __forceinline__ void nonSpatial(double *, const double *) {}
+  static __device__ __forceinline__ void nonSpatialPick(const double *, double *) {}
+  static __device__ __forceinline__ void storage(double *) {}
   static __device__ __forceinline__ void eval(double *sme_out,
                                               const double *sme_values,
                                               const double *) {
@@ -18,8 +22,31 @@ struct Reac0 {
   }
 };
 struct Reac1 : Reac0 {};
+// a model using every post-processing hook: 2 species + time + x,y,z padding,
+// species 1 non-spatial, storage 2 for species 0
+struct Reac2 {
+  static constexpr int S = 6, SP = 2, NNS = 1;
+  static constexpr bool STORAGE = true;
+  static __device__ __forceinline__ void nonSpatial(double *f, const double *av) {
+    f[1] = av[0];
+  }
+  static __device__ __forceinline__ void nonSpatialPick(const double *f, double *v) {
+    v[0] = f[1];
+  }
+  static __device__ __forceinline__ void storage(double *f) { f[0] *= 0.5; }
+  static __device__ __forceinline__ void eval(double *sme_out,
+                                              const double *sme_values,
+                                              const double *) {
+    sme_out[0] = sme_values[2] * sme_values[3] - sme_values[0];
+    sme_out[1] = sme_values[0] - sme_values[1] * sme_values[4];
+    sme_out[2] = 1.0;
+    sme_out[3] = 0.0;
+    sme_out[4] = 0.0;
+    sme_out[5] = 0.0;
+  }
+};
 struct Memb0 {
-  static constexpr int SA = 2, SB = 2, CA = 0, CB = 1;
+  static constexpr int SA = 2, SB = 2, SAP = 2, SBP = 2, NE = 0, CA = 0, CB = 1;
   static __device__ __forceinline__ void eval(double *sme_out,
                                               const double *sme_values,
                                               const double *) {
@@ -70,3 +97,18 @@ smeb_stage_nn<Reac0, F2>(const __grid_constant__ SmebStageArgs<2>);
 template __global__ void
 smeb_stage_memb<Reac0, F2>(const __grid_constant__ SmebStageArgs<2>,
                            const __grid_constant__ SmebMembArgs);
+// pre-pass and stage kernels of the model with non-spatial species / storage /
+// time-space padding
+#define F4 (SMEB_F_SUM_NS)
+template __global__ void
+smeb_stage_nn<Reac2, F4>(const __grid_constant__ SmebStageArgs<6>);
+template __global__ void
+smeb_stage_nn<Reac2, F2>(const __grid_constant__ SmebStageArgs<6>);
+template __global__ void
+smeb_stage_tile<Reac2, F4, 8, 32, 4, true>(const __grid_constant__ SmebStageArgs<6>,
+                                            const __grid_constant__ SmebTensorMap,
+                                            const smeb_u32);
+template __global__ void
+smeb_stage_tile<Reac2, F2, 8, 32, 4, true>(const __grid_constant__ SmebStageArgs<6>,
+                                            const __grid_constant__ SmebTensorMap,
+                                            const smeb_u32);

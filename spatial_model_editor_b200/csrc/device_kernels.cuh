@@ -39,6 +39,8 @@ typedef unsigned int smeb_u32;
 #define SMEB_F_OUT_DCDT 256u     // on demand: store dc/dt, nothing else
 #define SMEB_F_OUT_LOWER 512u    // on demand: store the lower-order solution
 #define SMEB_F_OUT_CNEW 1024u    // on demand: store the unclamped new state
+#define SMEB_F_SUM_NS 2048u      // pre-pass: block sums of dc/dt of the
+                                 // non-spatial species, nothing else
 
 #define SMEB_MEMB_FLAG 0x80000000u
 #define SMEB_BLOCK 256
@@ -57,6 +59,8 @@ template <int S> struct SmebStageArgs {
   double *cout;        // stage output (or the on-demand output)
   const smeb_u32 *nn;  // [6 n] neighbour list (voxel-list geometry)
   smeb_u64 *err;       // [2] bit patterns of max abs / max rel error
+  const double *nsAv;  // [R::NNS] spatial averages of dc/dt (non-spatial species)
+  double *nsPartial;   // [blocks][R::NNS] block sums written by the pre-pass
   smeb_u32 n;          // voxels in this launch's index space
   smeb_u32 nx, ny, nz; // box dims; voxel = (z*nx + x)*ny + y
   smeb_u32 z_begin, z_end; // planes updated by this launch (ghosts excluded)
@@ -167,16 +171,67 @@ __device__ __forceinline__ void smeb_block_max2(double eabs, double erel,
   }
 }
 
+// deterministic block sums of N per-thread accumulators (fixed shuffle tree,
+// then warp 0 over the warp results): dst[j] = sum over the block of acc[j]
+template <int N>
+__device__ __forceinline__ void smeb_block_sum(const double *acc, double *dst) {
+  __shared__ double ss[32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int j = 0; j < N; ++j) {
+    double v = acc[j];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      v += __shfl_xor_sync(0xffffffffu, v, o);
+    }
+    if (lane == 0) {
+      ss[w] = v;
+    }
+    __syncthreads();
+    if (w == 0) {
+      v = lane < nw ? ss[lane] : 0.0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        v += __shfl_xor_sync(0xffffffffu, v, o);
+      }
+      if (lane == 0) {
+        dst[j] = v;
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // RK stage update + error norm for one voxel, all in registers.
 //   c    stage input, f complete dc/dt, c0v pre-step state (if USE_C0),
 //   s2v  in: running sum from memory or 0; out: updated running sum,
 //   out  the value the caller stores to a.cout.
 // Association order: pixelsim_impl.cpp:627,675,699,718-719,741,783-788.
-template <int S, unsigned F>
+//
+// The model functor R carries what the CPU solver does to dc/dt after the
+// membranes (pixelsim.cpp:113-119): R::nonSpatial replaces dc/dt of the
+// non-spatial species by their spatial averages (computed by the SUM_NS
+// pre-pass), R::storage multiplies by 1/storage; R::SP is the number of model
+// species — the time/space padding components behind them are not clamped
+// (pixelsim_impl.cpp:643-654).
+template <class R, unsigned F>
 __device__ __forceinline__ void
-smeb_update(const SmebStageArgs<S> &a, const double *c, const double *f,
+smeb_update(const SmebStageArgs<R::S> &a, const double *c, const double *fin,
             const double *c0v, double *s2v, double *out, double &eabs,
             double &erel) {
+  constexpr int S = R::S;
+  double f[S];
+#pragma unroll
+  for (int s = 0; s < S; ++s) {
+    f[s] = fin[s];
+  }
+  if constexpr (R::NNS > 0) {
+    R::nonSpatial(f, a.nsAv);
+  }
+  if constexpr (R::STORAGE) {
+    R::storage(f);
+  }
   if constexpr ((F & SMEB_F_OUT_DCDT) != 0) {
 #pragma unroll
     for (int s = 0; s < S; ++s) {
@@ -229,7 +284,9 @@ smeb_update(const SmebStageArgs<S> &a, const double *c, const double *f,
     for (int s = 0; s < S; ++s) {
       double v = cn[s];
       if constexpr ((F & SMEB_F_CLAMP_OUT) != 0 && (F & SMEB_F_OUT_CNEW) == 0) {
-        v = v < 0.0 ? 0.0 : v;
+        if (s < R::SP) {
+          v = v < 0.0 ? 0.0 : v;
+        }
       }
       out[s] = v;
     }
@@ -238,10 +295,21 @@ smeb_update(const SmebStageArgs<S> &a, const double *c, const double *f,
 
 // complete per-voxel epilogue for the direct kernels: loads of c0 / s2,
 // update, stores
-template <int S, unsigned F>
+template <class R, unsigned F>
 __device__ __forceinline__ void
-smeb_finish_voxel(const SmebStageArgs<S> &a, size_t i, const double *c,
-                  const double *f, double &eabs, double &erel) {
+smeb_finish_voxel(const SmebStageArgs<R::S> &a, size_t i, const double *c,
+                  const double *f, double &eabs, double &erel, double *nsacc) {
+  constexpr int S = R::S;
+  if constexpr ((F & SMEB_F_SUM_NS) != 0) {
+    // pre-pass: only the sums of dc/dt of the non-spatial species are wanted
+    double v[R::NNS > 0 ? R::NNS : 1];
+    R::nonSpatialPick(f, v);
+#pragma unroll
+    for (int j = 0; j < R::NNS; ++j) {
+      nsacc[j] += v[j];
+    }
+    return;
+  }
   double c0v[S], s2v[S], out[S];
 #pragma unroll
   for (int s = 0; s < S; ++s) {
@@ -256,7 +324,7 @@ smeb_finish_voxel(const SmebStageArgs<S> &a, size_t i, const double *c,
       smeb_load_voxel<S>(a.s2in, i, s2v);
     }
   }
-  smeb_update<S, F>(a, c, f, c0v, s2v, out, eabs, erel);
+  smeb_update<R, F>(a, c, f, c0v, s2v, out, eabs, erel);
   constexpr bool onDemand =
       (F & (SMEB_F_OUT_DCDT | SMEB_F_OUT_LOWER | SMEB_F_OUT_CNEW)) != 0;
   if constexpr ((F & SMEB_F_WRITE_S2) != 0 && !onDemand) {
@@ -307,6 +375,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
     smeb_stage_nn(const __grid_constant__ SmebStageArgs<R::S> a) {
   constexpr int S = R::S;
   double eabs = 0.0, erel = 0.0;
+  double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
   for (smeb_u32 i = blockIdx.x * SMEB_BLOCK + threadIdx.x; i < a.n;
        i += gridDim.x * SMEB_BLOCK) {
     const uint2 *q = reinterpret_cast<const uint2 *>(a.nn) + (size_t)i * 3;
@@ -317,9 +386,11 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
     const smeb_u32 nb[6] = {n0.x, n0.y, n1.x, n1.y, n2.x, n2.y};
     double c[S], f[S];
     smeb_rhs_gather<R>(a, i, nb, c, f);
-    smeb_finish_voxel<S, F>(a, i, c, f, eabs, erel);
+    smeb_finish_voxel<R, F>(a, i, c, f, eabs, erel, nsacc);
   }
-  if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
+  if constexpr ((F & SMEB_F_SUM_NS) != 0) {
+    smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
+  } else if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
     smeb_block_max2(eabs, erel, a.err);
   }
 }
@@ -333,6 +404,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
     smeb_stage_box(const __grid_constant__ SmebStageArgs<R::S> a) {
   constexpr int S = R::S;
   double eabs = 0.0, erel = 0.0;
+  double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
   const smeb_u32 sx = a.ny, sz = a.nx * a.ny;
   const smeb_u32 iEnd = a.z_end * sz;
   for (smeb_u32 i = a.z_begin * sz + blockIdx.x * SMEB_BLOCK + threadIdx.x;
@@ -350,9 +422,11 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
     nb[5] = z > 0 ? i - sz : i;
     double c[S], f[S];
     smeb_rhs_gather<R>(a, i, nb, c, f);
-    smeb_finish_voxel<S, F>(a, i, c, f, eabs, erel);
+    smeb_finish_voxel<R, F>(a, i, c, f, eabs, erel, nsacc);
   }
-  if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
+  if constexpr ((F & SMEB_F_SUM_NS) != 0) {
+    smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
+  } else if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
     smeb_block_max2(eabs, erel, a.err);
   }
 }
@@ -367,39 +441,59 @@ template <class M, int S_OWN>
 __device__ __forceinline__ void
 smeb_memb_term(smeb_u32 info, smeb_u32 partner, const double *cown,
                const SmebMembArgs &m, const double *params, double *f) {
-  constexpr int SA = M::SA, SB = M::SB;
-  double in[SA + SB + 1], out[SA + SB + 1];
+  // SA / SB: state components per voxel of A / B (model species + NE padding
+  // components), SAP / SBP: model species.  Variables of the membrane
+  // expression: [A species | B species | padding of B's voxel, or of A's when
+  // B is not simulated] (pixelsim_impl.cpp:84-98).
+  constexpr int SA = M::SA, SB = M::SB, SAP = M::SAP, SBP = M::SBP,
+                NE = M::NE;
+  double in[SAP + SBP + NE + 1], out[SAP + SBP + NE + 1];
   const bool ownIsB = (info >> 16) & 1u;
   const smeb_u32 dir = (info >> 17) & 7u;
   const double L = m.flux_len[(info & 0xffffu) * 6 + dir];
   if (!ownIsB) {
-    if constexpr (S_OWN == SA) {
+    if constexpr (S_OWN == SA && SA > 0) {
 #pragma unroll
-      for (int s = 0; s < SA; ++s) {
+      for (int s = 0; s < SAP; ++s) {
         in[s] = cown[s];
       }
       if constexpr (SB > 0) {
-        smeb_load_voxel<SB>(m.comp_cin[M::CB], partner, in + SA);
+        double b[SB];
+        smeb_load_voxel<SB>(m.comp_cin[M::CB], partner, b);
+#pragma unroll
+        for (int s = 0; s < SB; ++s) {
+          in[SAP + s] = b[s];
+        }
+      } else {
+#pragma unroll
+        for (int s = 0; s < NE; ++s) {
+          in[SAP + s] = cown[SAP + s];
+        }
       }
       M::eval(out, in, params);
 #pragma unroll
-      for (int s = 0; s < SA; ++s) {
+      for (int s = 0; s < SAP; ++s) {
         f[s] += out[s] / L;
       }
     }
   } else {
-    if constexpr (S_OWN == SB) {
+    if constexpr (S_OWN == SB && SB > 0) {
 #pragma unroll
       for (int s = 0; s < SB; ++s) {
-        in[SA + s] = cown[s];
+        in[SAP + s] = cown[s];
       }
       if constexpr (SA > 0) {
-        smeb_load_voxel<SA>(m.comp_cin[M::CA], partner, in);
+        double av[SA];
+        smeb_load_voxel<SA>(m.comp_cin[M::CA], partner, av);
+#pragma unroll
+        for (int s = 0; s < SAP; ++s) {
+          in[s] = av[s];
+        }
       }
       M::eval(out, in, params);
 #pragma unroll
-      for (int s = 0; s < SB; ++s) {
-        f[s] += out[SA + s] / L;
+      for (int s = 0; s < SBP; ++s) {
+        f[s] += out[SAP + s] / L;
       }
     }
   }
@@ -417,6 +511,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
                     const __grid_constant__ SmebMembArgs m) {
   constexpr int S = R::S;
   double eabs = 0.0, erel = 0.0;
+  double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
   for (smeb_u32 k = blockIdx.x * SMEB_BLOCK + threadIdx.x; k < m.n_mvox;
        k += gridDim.x * SMEB_BLOCK) {
     const smeb_u32 i = m.mvox[k];
@@ -430,9 +525,11 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
       const SmebMembEntry ent = m.ent[e];
       smeb_memb_dispatch<S>(ent.info, ent.partner, c, m, a.D + 3 * S, f);
     }
-    smeb_finish_voxel<S, F>(a, i, c, f, eabs, erel);
+    smeb_finish_voxel<R, F>(a, i, c, f, eabs, erel, nsacc);
   }
-  if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
+  if constexpr ((F & SMEB_F_SUM_NS) != 0) {
+    smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
+  } else if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
     smeb_block_max2(eabs, erel, a.err);
   }
 }
@@ -531,10 +628,10 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   constexpr smeb_u32 BOX_BYTES = (TX + 2) * PITCH * 8;
   constexpr smeb_u32 SLOT_BYTES = (BOX_BYTES + 127u) & ~127u;
   constexpr int LOOK = M3 ? 2 : 0;     // planes needed beyond the current one
-  constexpr bool USE_C0 =
-      (F & SMEB_F_USE_C0) != 0 && (F & SMEB_F_OUT_DCDT) == 0;
-  constexpr bool USE_S2IN =
-      (F & SMEB_F_USE_S2IN) != 0 && (F & SMEB_F_OUT_DCDT) == 0;
+  constexpr bool USE_C0 = (F & SMEB_F_USE_C0) != 0 &&
+                          (F & (SMEB_F_OUT_DCDT | SMEB_F_SUM_NS)) == 0;
+  constexpr bool USE_S2IN = (F & SMEB_F_USE_S2IN) != 0 &&
+                            (F & (SMEB_F_OUT_DCDT | SMEB_F_SUM_NS)) == 0;
   constexpr bool ON_DEMAND =
       (F & (SMEB_F_OUT_DCDT | SMEB_F_OUT_LOWER | SMEB_F_OUT_CNEW)) != 0;
   static_assert(SMEB_BLOCK % TY == 0 && TX % G == 0, "tile shape");
@@ -567,6 +664,14 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   }
   const int nIter = m1 - m0;
   if (nIter <= 0) {
+    if constexpr ((F & SMEB_F_SUM_NS) != 0) {
+      const size_t blk =
+          ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x +
+          blockIdx.x;
+      if (threadIdx.x < R::NNS) {
+        a.nsPartial[blk * R::NNS + threadIdx.x] = 0.0;
+      }
+    }
     return;
   }
   const int nLoads = nIter + LOOK;
@@ -638,6 +743,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   }
 
   double eabs = 0.0, erel = 0.0;
+  double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
   // ring bookkeeping: slot / parity of load j = it + LOOK (the newest plane
   // this iteration needs), and slots of the current and previous plane
   int slotW = LOOK % NST, parW = (LOOK / NST) & 1;
@@ -710,7 +816,16 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
         smeb_lds<S>(sm + k * PITCH, zm);
         smeb_rhs_values<R>(a, col[k + 1], col[k + 2], col[k], yp, ym, zp, zm,
                            f);
-        smeb_update<S, F>(a, col[k + 1], f, c0cur[k], s2cur[k], out, eabs,
+        if constexpr ((F & SMEB_F_SUM_NS) != 0) {
+          double v[R::NNS > 0 ? R::NNS : 1];
+          R::nonSpatialPick(f, v);
+#pragma unroll
+          for (int j = 0; j < R::NNS; ++j) {
+            nsacc[j] += v[j];
+          }
+          continue;
+        }
+        smeb_update<R, F>(a, col[k + 1], f, c0cur[k], s2cur[k], out, eabs,
                           erel);
         if constexpr ((F & SMEB_F_WRITE_S2) != 0 && !ON_DEMAND) {
           smeb_store_voxel<S>(a.s2out, g + k * rowStride, s2cur[k]);
@@ -740,8 +855,32 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
       parW ^= 1;
     }
   }
-  if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
+  if constexpr ((F & SMEB_F_SUM_NS) != 0) {
+    const size_t blk =
+        ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    smeb_block_sum<R::NNS>(nsacc, a.nsPartial + blk * R::NNS);
+  } else if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
     smeb_block_max2(eabs, erel, a.err);
+  }
+}
+
+// ---- spatial average of dc/dt of the non-spatial species -----------------------
+// av[j] = (sum of the block sums of the pre-pass, in a fixed order) / n
+// (SimCompartment::spatiallyAverageDcdt, pixelsim_impl.cpp:150-163: the CPU sums
+// serially; the association order differs, the result agrees to rounding)
+__global__ void __launch_bounds__(SMEB_BLOCK)
+    smeb_ns_finish(const double *__restrict__ partial, smeb_u32 nBlocks,
+                   smeb_u32 nns, double n, double *__restrict__ av) {
+  for (smeb_u32 j = 0; j < nns; ++j) {
+    double acc = 0.0;
+    for (smeb_u32 b = threadIdx.x; b < nBlocks; b += SMEB_BLOCK) {
+      acc += partial[(size_t)b * nns + j];
+    }
+    smeb_block_sum<1>(&acc, av + j);
+    if (threadIdx.x == 0) {
+      av[j] = av[j] / n;
+    }
+    __syncthreads();
   }
 }
 

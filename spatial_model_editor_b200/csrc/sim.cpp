@@ -2,6 +2,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
 #include <mutex>
 #include <sstream>
@@ -132,23 +133,66 @@ void Sim::generateSource(const smeb200_problem &p) {
     }
     std::ostringstream h;
     h << "// compartment " << c << ": " << (comp.id ? comp.id : "") << "\n";
+    const uint32_t sp =
+        comp.n_primary_species != 0 ? comp.n_primary_species : comp.n_species;
+    bool storage = false;
+    for (uint32_t s = 0; comp.inv_storage != nullptr && s < comp.n_species;
+         ++s) {
+      storage = storage || comp.inv_storage[s] != 1.0;
+    }
     h << "struct Reac" << c << " {\n  static constexpr int S = "
-      << comp.n_species << ";\n";
+      << comp.n_species << ", SP = " << sp << ", NNS = " << comp.n_non_spatial
+      << ";\n  static constexpr bool STORAGE = "
+      << (storage ? "true" : "false") << ";\n";
+    // dc/dt post-processing of the CPU solver (pixelsim.cpp:113-119)
+    h << "  static __device__ __forceinline__ void nonSpatial(double* f, "
+         "const double* av) {\n    (void)f; (void)av;\n";
+    for (uint32_t j = 0; j < comp.n_non_spatial; ++j) {
+      h << "    f[" << comp.non_spatial[j] << "] = av[" << j << "];\n";
+    }
+    h << "  }\n  static __device__ __forceinline__ void "
+         "nonSpatialPick(const double* f, double* v) {\n    (void)f; "
+         "(void)v;\n";
+    for (uint32_t j = 0; j < comp.n_non_spatial; ++j) {
+      h << "    v[" << j << "] = f[" << comp.non_spatial[j] << "];\n";
+    }
+    h << "  }\n  static __device__ __forceinline__ void storage(double* f) "
+         "{\n    (void)f;\n";
+    for (uint32_t s = 0; storage && s < comp.n_species; ++s) {
+      if (comp.inv_storage[s] != 1.0) { // x * 1.0 is exact: skipped
+        char buf[64];
+        std::snprintf(buf, sizeof(buf), "%a", comp.inv_storage[s]);
+        h << "    f[" << s << "] *= " << buf << ";\n";
+      }
+    }
+    h << "  }\n";
     src << functorSource(h.str(), comp.n_species, comp.expressions,
                          comp.n_species, p.n_params);
   }
   for (uint32_t m = 0; m < p.n_membranes; ++m) {
     const auto &mb = p.membranes[m];
-    const uint32_t SA =
-        mb.comp_a >= 0 ? p.compartments[mb.comp_a].n_species : 0;
-    const uint32_t SB =
-        mb.comp_b >= 0 ? p.compartments[mb.comp_b].n_species : 0;
+    auto stride = [&p](int32_t ci) -> uint32_t {
+      return ci >= 0 ? p.compartments[ci].n_species : 0;
+    };
+    auto primary = [&p](int32_t ci) -> uint32_t {
+      if (ci < 0) {
+        return 0;
+      }
+      const auto &pc = p.compartments[ci];
+      return pc.n_primary_species != 0 ? pc.n_primary_species : pc.n_species;
+    };
+    const uint32_t SA = stride(mb.comp_a), SB = stride(mb.comp_b);
+    const uint32_t SAP = primary(mb.comp_a), SBP = primary(mb.comp_b);
+    // padding (time, x, y, z) comes from B's voxel, else from A's
+    // (pixelsim_impl.cpp:91-98)
+    const uint32_t NE = mb.comp_b >= 0 ? SB - SBP : SA - SAP;
     std::ostringstream h;
     h << "// membrane " << m << ": " << (mb.id ? mb.id : "") << "\n";
     h << "struct Memb" << m << " {\n  static constexpr int SA = " << SA
-      << ", SB = " << SB << ", CA = " << std::max(mb.comp_a, 0)
+      << ", SB = " << SB << ", SAP = " << SAP << ", SBP = " << SBP
+      << ", NE = " << NE << ", CA = " << std::max(mb.comp_a, 0)
       << ", CB = " << std::max(mb.comp_b, 0) << ";\n";
-    src << functorSource(h.str(), SA + SB, mb.expressions, SA + SB,
+    src << functorSource(h.str(), SAP + SBP + NE, mb.expressions, SAP + SBP,
                          p.n_params);
   }
   src << "template <int S_OWN>\n__device__ __forceinline__ void\n"
@@ -718,14 +762,47 @@ void Sim::build(const smeb200_problem &p) {
       c.voxels.assign(pc.voxels, pc.voxels + 3 * c.n);
     }
     c.D.assign(pc.diffusion, pc.diffusion + 3 * c.S);
+    c.SP = pc.n_primary_species != 0 ? pc.n_primary_species : c.S;
+    if (c.SP > c.S) {
+      throw Error("smeb200: n_primary_species exceeds n_species in '" + c.id +
+                  "'");
+    }
+    for (uint32_t k = 0; k < pc.n_non_spatial; ++k) {
+      if (pc.non_spatial[k] >= c.S) {
+        throw Error("smeb200: non-spatial species index out of range in '" +
+                    c.id + "'");
+      }
+      c.nonSpatial.push_back(pc.non_spatial[k]);
+    }
+    if (!c.nonSpatial.empty() && p.n_ranks > 1) {
+      throw Error("smeb200: non-spatial species are not supported in a "
+                  "z-slab decomposed simulation");
+    }
+    if (pc.inv_storage != nullptr) {
+      c.invStorage.assign(pc.inv_storage, pc.inv_storage + c.S);
+      for (double v : c.invStorage) {
+        if (v == 0.0) {
+          // pixelsim.cpp:23-90 (pseudo-time relaxation of algebraic species)
+          throw Error("smeb200: zero storage species (algebraic constraints) "
+                      "are not supported: the CUDA pixel backend requires "
+                      "non-zero storage, unit storage or otherwise");
+        }
+        if (!(v > 0.0)) {
+          throw Error("Invalid negative storage value for species in '" +
+                      c.id + "'");
+        }
+      }
+    }
     for (uint32_t s = 0; s < c.S; ++s) {
       c.speciesNames.emplace_back(
           pc.species_names != nullptr && pc.species_names[s] != nullptr
               ? pc.species_names[s]
               : "");
       // forwards-Euler stability bound, pixelsim_common.hpp:33-37 and
-      // pixelsim_impl.cpp:249-255 (unit storage)
-      const double sum = c.D[3 * s] + c.D[3 * s + 1] + c.D[3 * s + 2];
+      // pixelsim_impl.cpp:249-255 (D * invStorage per direction)
+      const double is = c.invStorage.empty() ? 1.0 : c.invStorage[s];
+      const double sum =
+          c.D[3 * s] * is + c.D[3 * s + 1] * is + c.D[3 * s + 2] * is;
       maxStableTimestep = std::min(maxStableTimestep, 1.0 / (2.0 * sum));
     }
   }
@@ -771,6 +848,14 @@ void Sim::build(const smeb200_problem &p) {
         addName(kernelName(ci, sd.flags(), true));
       }
     }
+    if (!comps[ci].nonSpatial.empty()) {
+      // pre-pass: block sums of dc/dt of the non-spatial species
+      addName(kernelName(ci, F_SUM_NS, false));
+      if (comps[ci].nMvox > 0) {
+        addName(kernelName(ci, F_SUM_NS, true));
+      }
+      addName(kNsFinishKernel);
+    }
   }
   mainModule = compile(names);
   if (compileOnly) {
@@ -801,6 +886,20 @@ void Sim::build(const smeb200_problem &p) {
     }
     for (const auto &sd : plan) {
       c.kStage.push_back(lookup(mainModule, ci, sd.flags()));
+    }
+    if (!c.nonSpatial.empty()) {
+      c.kSumNs = lookup(mainModule, ci, F_SUM_NS);
+      const std::size_t nns = c.nonSpatial.size();
+      const uint32_t mainBlocks =
+          c.geom == Geom::TILE
+              ? c.tile.grid[0] * c.tile.grid[1] * c.tile.grid[2]
+              : static_cast<uint32_t>(smCount) * 8u;
+      c.nsPartialBlocks = mainBlocks + static_cast<uint32_t>(smCount) * 8u;
+      c.dNsPartial = devAlloc<double>(c.nsPartialBlocks * nns,
+                                      "allocate non-spatial partial sums");
+      c.dNsAv = devAlloc<double>(nns, "allocate non-spatial averages");
+      check(cudaMemsetAsync(c.dNsAv, 0, nns * sizeof(double), stream),
+            "clear non-spatial averages");
     }
     check(cudaMallocHost(reinterpret_cast<void **>(&c.hostConc),
                          std::max<std::size_t>(nv, 1) * sizeof(double)),
@@ -997,6 +1096,8 @@ Sim::~Sim() {
     cudaFree(c.dMstart);
     cudaFree(c.dEnt);
     cudaFree(c.scratch);
+    cudaFree(c.dNsAv);
+    cudaFree(c.dNsPartial);
     cudaFreeHost(c.hostConc);
   }
   cudaFree(dFluxLen);
@@ -1067,6 +1168,13 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     a.eps = epsilon;
     std::copy(c.D.begin(), c.D.end(), a.D);
     std::copy(params.begin(), params.end(), a.D + 3 * c.S);
+    a.nsAv = c.dNsAv;
+    a.nsPartial = c.dNsPartial;
+    if (!c.nonSpatial.empty()) {
+      // SimCompartment::spatiallyAverageDcdt (pixelsim_impl.cpp:150-163): the
+      // averages need dc/dt of every voxel before any voxel can be updated
+      launchCompartment(ci, a, c.kSumNs, c.role[sd.cin], true);
+    }
     launchCompartment(ci, a, c.kStage[stageIndex], c.role[sd.cin]);
     if (last) {
       c.last = a;
@@ -1083,10 +1191,12 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
 // cinBuf: index of the buffer every compartment's stage input lives in (the
 // roles rotate in lock step, so one index serves all compartments)
 void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
-                            const StageKernels &k, int cinBuf) {
+                            const StageKernels &k, int cinBuf,
+                            bool nsPrepass) {
   const auto &drv = DriverApi::get();
   auto &c = comps[ci];
-  const bool timed = kernelTiming && ci == dominantComp;
+  const bool timed = kernelTiming && ci == dominantComp && !nsPrepass;
+  uint32_t nsBlocks = 0; // blocks that wrote partial sums (pre-pass)
   if (timed) {
     if (timerUsed == timerEvents.size()) {
       cudaEvent_t e0{}, e1{};
@@ -1105,6 +1215,7 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
                            c.tile.grid[2], BLOCK, 1, 1, c.tile.dynSmem, stream,
                            params, nullptr),
           "launch tile stage kernel");
+    nsBlocks = c.tile.grid[0] * c.tile.grid[1] * c.tile.grid[2];
   } else {
     uint64_t work = c.n;
     if (c.geom == Geom::BOX) {
@@ -1116,6 +1227,7 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     check(drv.LaunchKernel(k.main, grid, 1, 1, BLOCK, 1, 1, 0, stream, params,
                            nullptr),
           "launch stage kernel");
+    nsBlocks = grid;
   }
   ++launchCount;
   if (timed) {
@@ -1138,12 +1250,31 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
           comps[j].S > 0 ? comps[j].buf[cinBuf] : nullptr);
     }
     blob[4 + comps.size()] = static_cast<unsigned long long>(c.nMvox);
-    void *mparams[] = {&a, blob.data()};
     const unsigned mgrid =
         std::min((c.nMvox + BLOCK - 1) / BLOCK, persistent);
+    StageArgsHost am = a;
+    if (nsPrepass) { // the membrane voxels' partial sums follow the main ones
+      am.nsPartial = a.nsPartial + nsBlocks * c.nonSpatial.size();
+      nsBlocks += mgrid;
+    }
+    void *mparams[] = {&am, blob.data()};
     check(drv.LaunchKernel(k.memb, mgrid, 1, 1, BLOCK, 1, 1, 0, stream,
                            mparams, nullptr),
           "launch membrane stage kernel");
+    ++launchCount;
+  }
+  if (nsPrepass) {
+    if (nsBlocks > c.nsPartialBlocks) {
+      throw Error("smeb200: internal error (non-spatial partial sums)");
+    }
+    const double *partial = c.dNsPartial;
+    uint32_t nns = static_cast<uint32_t>(c.nonSpatial.size());
+    double nVox = static_cast<double>(c.n);
+    double *av = c.dNsAv;
+    void *fparams[] = {&partial, &nsBlocks, &nns, &nVox, &av};
+    check(drv.LaunchKernel(mainModule.fn.at(kNsFinishKernel), 1, 1, 1, BLOCK, 1,
+                           1, 0, stream, fparams, nullptr),
+          "launch non-spatial average kernel");
     ++launchCount;
   }
 }

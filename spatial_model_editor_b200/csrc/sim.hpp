@@ -8,6 +8,7 @@
 #include "../../include/smeb200.h"
 #include "comm.hpp"
 #include "cuda_api.hpp"
+#include <algorithm>
 #include <atomic>
 #include <cstdint>
 #include <limits>
@@ -23,7 +24,7 @@ namespace smeb200 {
 constexpr uint32_t F_USE_C0 = 1u, F_USE_S2 = 2u, F_USE_S2IN = 4u,
                    F_WRITE_S2 = 8u, F_FINAL = 16u, F_LOWER_IS_CIN = 32u,
                    F_CLAMP_OUT = 64u, F_GENERIC = 128u, F_OUT_DCDT = 256u,
-                   F_OUT_LOWER = 512u, F_OUT_CNEW = 1024u;
+                   F_OUT_LOWER = 512u, F_OUT_CNEW = 1024u, F_SUM_NS = 2048u;
 
 // host mirror of the device-side SmebStageArgs<S> (device_kernels.cuh); the
 // D[3*S] table is the tail.
@@ -35,6 +36,8 @@ struct StageArgsHost {
   double *cout;
   const uint32_t *nn;
   unsigned long long *err;
+  const double *nsAv;
+  double *nsPartial;
   uint32_t n;
   uint32_t nx, ny, nz;
   uint32_t z_begin, z_end;
@@ -69,6 +72,7 @@ struct StageKernels {
   CUfunction main{nullptr};
   CUfunction memb{nullptr};
 };
+constexpr const char *kNsFinishKernel = "smeb_ns_finish";
 
 struct TileConfig {
   int tx{0}, ty{0}, nst{0};
@@ -89,6 +93,14 @@ struct CompartmentState {
   TileConfig tile;
   std::vector<std::string> speciesNames;
   std::vector<double> D;
+  // CPU-solver semantics beyond the reference GPU backend (smeb200.h)
+  uint32_t SP{0};                    // model species; S - SP = t,x,y,z padding
+  std::vector<uint32_t> nonSpatial;  // species whose dc/dt is averaged
+  std::vector<double> invStorage;    // [S], empty = unit storage
+  double *dNsAv{nullptr};            // [nonSpatial.size()]
+  double *dNsPartial{nullptr};       // block sums of the pre-pass
+  uint32_t nsPartialBlocks{0};       // capacity of dNsPartial in blocks
+  StageKernels kSumNs;               // pre-pass kernels (F_SUM_NS)
   std::vector<int32_t> voxels;
   int nbuf{0};
   double *buf[4]{nullptr, nullptr, nullptr, nullptr};
@@ -154,6 +166,13 @@ public:
   bool compileOnly{false};
   std::size_t cubinBytes{0};
   std::size_t nCompartments() const { return comps.size(); }
+  std::size_t concentrationPadding() const {
+    std::size_t pad = 0;
+    for (const auto &c : comps) {
+      pad = std::max<std::size_t>(pad, c.S - c.SP);
+    }
+    return pad;
+  }
   smeb200_allreduce_max_fn allreduceMax{nullptr};
   void *allreduceUser{nullptr};
   uint64_t haloExchanges{0};
@@ -180,7 +199,8 @@ private:
   void doStep(double dt); // all stages of one RK step
   void launchStage(std::size_t stageIndex, double dt);
   void launchCompartment(std::size_t ci, StageArgsHost &a,
-                         const StageKernels &k, int cinBuf);
+                         const StageKernels &k, int cinBuf,
+                         bool nsPrepass = false);
   void rotateAfterAccept();
   void readError(double &eabs, double &erel);
   double doRK101(double dt);

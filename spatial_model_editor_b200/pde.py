@@ -37,7 +37,8 @@ def _scaled(node, factor: float):
 def build_rhs(species: Sequence[str], reactions: Sequence[ReactionDef],
               constants: Optional[Dict[str, float]] = None, scale: float = 1.0,
               functions=None, substitutions: Optional[Dict[str, float]] = None,
-              runtime_params: Sequence[str] = ()) -> List[str]:
+              runtime_params: Sequence[str] = (),
+              extra_vars: Sequence[str] = ()) -> List[str]:
     """C expressions (in sme_var_k, k = index into ``species``) of the reaction
     term of every species: what ``ReacExpr.expressions`` holds after the
     reference's Pde step, printed for the C-ABI.
@@ -45,10 +46,14 @@ def build_rhs(species: Sequence[str], reactions: Sequence[ReactionDef],
     ``runtime_params``: ids of global or reaction-local parameters that stay
     symbolic (printed as ``sme_param_<k>``, k = position in this list) instead
     of being inlined as numbers; a local parameter of one reaction can be named
-    ``"<reaction id>.<parameter id>"``."""
+    ``"<reaction id>.<parameter id>"``.
+
+    ``extra_vars``: the time / space variables ("time", x, y, z ids) the
+    expressions may use; they follow the species in the variable numbering
+    (ReacExpr, pixelsim_impl.cpp:124-138) and get no expression here."""
     constants = dict(constants or {})
     substitutions = substitutions or {}
-    names = {v: f"sme_var_{k}" for k, v in enumerate(species)}
+    names = {v: f"sme_var_{k}" for k, v in enumerate(list(species) + list(extra_vars))}
     for k, pid in enumerate(runtime_params):
         names[pid] = f"sme_param_{k}"
     out = []
@@ -63,7 +68,7 @@ def build_rhs(species: Sequence[str], reactions: Sequence[ReactionDef],
             for k, v in substitutions.items():  # pde.cpp:65-77
                 if k in env:
                     env[k] = v
-            for v in species:
+            for v in list(species) + list(extra_vars):
                 env.pop(v, None)
             for pid in runtime_params:
                 if pid.startswith(r.id + ".") and pid[len(r.id) + 1:] in env:

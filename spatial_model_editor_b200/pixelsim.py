@@ -157,7 +157,12 @@ class CSim:
         return self._vec("get_concentrations", compartmentIndex)
 
     def getConcentrationPadding(self) -> int:
-        return 0
+        """number of t,x,y,z components behind the species of every voxel
+        (pixelsim.cpp:478)"""
+        try:
+            return int(self._f("get_concentration_padding")(self._h))
+        except AttributeError:  # the oracle has no such entry point
+            return self._problem.padding
 
     def errorMessage(self) -> str:
         return self._f("error")(self._h).decode()

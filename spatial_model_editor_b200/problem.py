@@ -26,7 +26,7 @@ HAS_NON_SPATIAL_SPECIES = 4
 HAS_NON_UNIFORM_DIFFUSION = 8
 HAS_NON_UNIT_STORAGE = 16
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class CCompartment(C.Structure):
@@ -43,6 +43,10 @@ class CCompartment(C.Structure):
         ("conc0", C.POINTER(C.c_double)),
         ("expressions", C.POINTER(C.c_char_p)),
         ("species_names", C.POINTER(C.c_char_p)),
+        ("n_primary_species", C.c_uint32),
+        ("n_non_spatial", C.c_uint32),
+        ("non_spatial", C.POINTER(C.c_uint32)),
+        ("inv_storage", C.POINTER(C.c_double)),
     ]
 
 
@@ -96,6 +100,13 @@ class Compartment:
     nn: Optional[np.ndarray] = None       # [N, 6] uint32 or None for a box
     box: Optional[Tuple[int, int, int]] = None  # (nx, ny, nz) when nn is None
     voxels: Optional[np.ndarray] = None   # [N, 3] int32 (x, y, z) image coordinates
+    n_primary: Optional[int] = None       # model species; the rest is t,x,y,z padding
+    non_spatial: Sequence[int] = ()       # species whose dc/dt is spatially averaged
+    inv_storage: Optional[np.ndarray] = None  # [S] 1/storage, None = unit storage
+
+    @property
+    def n_primary_species(self) -> int:
+        return self.n_species if self.n_primary is None else int(self.n_primary)
 
     @property
     def n_voxels(self) -> int:
@@ -136,9 +147,16 @@ class Problem:
     params: Sequence[float] = ()          # values of sme_param_k (runtime parameters)
 
     def evals_per_step(self) -> int:
-        """voxel*species RHS evaluations in one RK step (the bench metric)."""
+        """voxel*species RHS evaluations in one RK step (the bench metric);
+        the t,x,y,z padding components do not count."""
         return STAGES[self.integrator] * sum(
-            c.n_voxels * c.n_species for c in self.compartments)
+            c.n_voxels * c.n_primary_species for c in self.compartments)
+
+    @property
+    def padding(self) -> int:
+        """getConcentrationPadding (pixelsim.cpp:478)"""
+        return max((c.n_species - c.n_primary_species for c in self.compartments),
+                   default=0)
 
     def to_c(self):
         """Returns (CProblem, keepalive).  keepalive owns every buffer the POD
@@ -178,6 +196,12 @@ class Problem:
             assert len(c.expressions) == c.n_species
             cc.expressions = strs(c.expressions)
             cc.species_names = strs(c.species)
+            cc.n_primary_species = c.n_primary_species
+            cc.n_non_spatial = len(c.non_spatial)
+            cc.non_spatial = arr(np.asarray(c.non_spatial, dtype=np.uint32), np.uint32,
+                                 C.c_uint32) if len(c.non_spatial) else None
+            cc.inv_storage = arr(np.asarray(c.inv_storage, dtype=np.float64).reshape(
+                c.n_species), np.float64, C.c_double) if c.inv_storage is not None else None
         membs = (CMembrane * max(len(self.membranes), 1))()
         for i, m in enumerate(self.membranes):
             cm = membs[i]

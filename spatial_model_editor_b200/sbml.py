@@ -569,51 +569,66 @@ def to_problem(m: SbmlModel, integrator: Optional[int] = None,
     env_rules = {k: v for k, v in rules.items()}
     nz, ny, nx = m.labels.shape
     unsupported = 0
-    time_or_space = set(m.coord_params) | {"time"}
+    # reactions that depend on time / space: every compartment's state is padded
+    # with "time" and / or "x, y, z" components (pixelsim.cpp:282-322,
+    # pixelsim_impl.cpp:124-147,312-349)
+    axis_id = {axis: pid for pid, axis in m.coord_params.items()}
+    coord_ids = [axis_id.get(a, f"sme_coord_{a}") for a in ("x", "y", "z")]
+    time_dependent = space_dependent = False
+    for r in m.reactions:
+        if not r.stoich:
+            continue
+        rate = E.substitute(r.rate, {k: v for k, v in env_rules.items()
+                                     if k not in r.local}, m.functions)
+        syms = E.symbols(rate)
+        time_dependent = time_dependent or "time" in syms
+        space_dependent = space_dependent or bool(syms & set(m.coord_params))
+    extra_vars = (["time"] if time_dependent else []) + (coord_ids if space_dependent else [])
+    extra_exprs = (["1.0"] if time_dependent else []) + (["0.0"] * 3 if space_dependent else [])
 
     def reaction_defs(location: str) -> List[ReactionDef]:
-        nonlocal unsupported
         out = []
         for r in m.reactions:
             if r.location != location or not r.stoich:
                 continue
             rate = E.substitute(r.rate, {k: v for k, v in env_rules.items()
                                          if k not in r.local}, m.functions)
-            syms = E.symbols(rate)
-            if "time" in syms:
-                unsupported |= P.HAS_TIME_DEPENDENCE
-            if syms & set(m.coord_params):
-                unsupported |= P.HAS_SPACE_DEPENDENCE
             out.append(ReactionDef(r.id, node_to_infix(rate), dict(r.stoich), dict(r.local)))
         return out
 
     comps: List[P.Compartment] = []
     comp_index: Dict[str, int] = {}
     for cid, _, dims in m.compartments:
-        if dims != 3 or cid not in m.label_of:
+        if cid not in m.label_of:  # membranes / unsampled compartments
             continue
         sim_species = [s for s in m.species_of(cid) if m.is_simulated(s)]
         if not sim_species:
             continue
         voxels = G.compartment_voxels(m.labels, m.label_of[cid])
         ids = [s.id for s in sim_species]
-        for s in sim_species:
-            if not s.spatial:
-                unsupported |= P.HAS_NON_SPATIAL_SPECIES
-            if s.storage != 1.0:
-                unsupported |= P.HAS_NON_UNIT_STORAGE
+        non_spatial = [k for k, s in enumerate(sim_species) if not s.spatial]
+        storage = [s.storage for s in sim_species] + [1.0] * len(extra_vars)
         dx, dy, dz = m.voxel_size
-        diffusion = np.array([[s.diffusion / (dx * dx), s.diffusion / (dy * dy),
-                               s.diffusion / (dz * dz)] for s in sim_species])
-        conc0 = np.stack([initial_concentration(m, s, voxels, constants)
-                          for s in sim_species], axis=1)
+        # constant species do not diffuse (pixelsim_impl.cpp:233-235)
+        dcs = [0.0 if s.constant else s.diffusion for s in sim_species] + [0.0] * len(extra_vars)
+        diffusion = np.array([[d / (dx * dx), d / (dy * dy), d / (dz * dz)] for d in dcs])
+        columns = [initial_concentration(m, s, voxels, constants) for s in sim_species]
+        if time_dependent:
+            columns.append(np.zeros(len(voxels)))
+        if space_dependent:
+            centres = voxel_centres(m, voxels)
+            columns += [centres["x"], centres["y"], centres["z"]]
+        conc0 = np.stack(columns, axis=1)
         exprs = build_rhs(ids, reaction_defs(cid), constants, functions=m.functions,
-                          substitutions=substitutions, runtime_params=runtime_params)
+                          substitutions=substitutions, runtime_params=runtime_params,
+                          extra_vars=extra_vars) + extra_exprs
         comp_index[cid] = len(comps)
         comps.append(P.Compartment(
-            id=cid, species=ids, expressions=exprs, diffusion=diffusion,
+            id=cid, species=ids + extra_vars, expressions=exprs, diffusion=diffusion,
             conc0=np.ascontiguousarray(conc0), nn=G.neighbour_table(m.labels.shape, voxels),
-            voxels=voxels))
+            voxels=voxels, n_primary=len(ids), non_spatial=non_spatial,
+            inv_storage=(None if all(v == 1.0 for v in storage)
+                         else np.array([1.0 / v if v != 0.0 else 0.0 for v in storage]))))
 
     membranes: List[P.Membrane] = []
     colour_index = {label: i for i, label in enumerate(sorted(set(m.label_of.values())))}
@@ -623,7 +638,8 @@ def to_problem(m: SbmlModel, integrator: Optional[int] = None,
         if not defs:
             continue
         ia, ib = comp_index.get(a, -1), comp_index.get(b, -1)
-        names = (comps[ia].species if ia >= 0 else []) + (comps[ib].species if ib >= 0 else [])
+        names = ((comps[ia].species[:comps[ia].n_primary_species] if ia >= 0 else [])
+                 + (comps[ib].species[:comps[ib].n_primary_species] if ib >= 0 else []))
         if not names:
             continue
         if pairs is None:
@@ -652,7 +668,7 @@ def to_problem(m: SbmlModel, integrator: Optional[int] = None,
         face_pairs = G.membrane_face_pairs(m.labels.shape, va, vb, vp)
         exprs = build_rhs(names, defs, constants, scale=m.vol_over_l3,
                           functions=m.functions, substitutions=substitutions,
-                          runtime_params=runtime_params)
+                          runtime_params=runtime_params, extra_vars=extra_vars)
         membranes.append(P.Membrane(id=mid, comp_a=ia, comp_b=ib, pairs=face_pairs,
                                     flux_length=G.flux_lengths(m.voxel_size),
                                     expressions=exprs))

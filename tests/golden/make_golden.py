@@ -39,6 +39,11 @@ MODELS = {
 
 
 def dump(name, m, problem):
+    if int(m.labels.max()) > 255:  # raw ARGB sample values: store small labels
+        values = sorted(set(m.labels.ravel().tolist()))
+        remap = {v: i for i, v in enumerate(values)}
+        m.labels = np.vectorize(remap.get)(m.labels).astype(np.int64)
+        m.label_of = {k: remap[v] for k, v in m.label_of.items()}
     meta = dict(
         name=name, source=os.path.relpath(m.path, REF), voxel_size=list(m.voxel_size),
         origin=list(m.origin), vol_over_l3=m.vol_over_l3, label_of=m.label_of,
@@ -47,7 +52,12 @@ def dump(name, m, problem):
         unsupported=problem.unsupported, params=list(problem.params),
         compartments=[dict(id=c.id, species=c.species, expressions=c.expressions,
                            diffusion_constants=[s.diffusion for s in m.species
-                                                if s.id in c.species])
+                                                if s.id in c.species]
+                           + [0.0] * (c.n_species - c.n_primary_species),
+                           n_primary=c.n_primary_species,
+                           non_spatial=[int(k) for k in c.non_spatial],
+                           inv_storage=None if c.inv_storage is None
+                           else [float(v) for v in c.inv_storage])
                       for c in problem.compartments],
         membranes=[dict(id=mb.id, comp_a=mb.comp_a, comp_b=mb.comp_b,
                         a=[a for i, a, b in m.membranes if i == mb.id][0],
@@ -88,6 +98,26 @@ def main():
         reaction_locations={"A_uptake": "c1_c2_membrane", "A_transport": "c2_c3_membrane",
                             "B_transport": "c2_c3_membrane", "B_excretion": "c1_c2_membrane"})
     dump("single-pixel-chain", m, sbml.to_problem(m, integrator=0))
+    # reactions that depend on t, x, y (simulate_t.cpp:2009-2207): dA/dt = x,
+    # dB/dt = y, dC/dt = time -> state padded with time, x, y, z
+    m = sbml.load_sbml(os.path.join(REF, "test/resources/models/txy.xml"))
+    dump("txy", m, sbml.to_problem(m, integrator=0))
+    # the same with non-unit storage (simulate_t.cpp:2054-2087 sets C to 2)
+    for sp in m.species:
+        sp.storage = {"A": 0.5, "C": 2.0}.get(sp.id, 1.0)
+    dump("txy-storage", m, sbml.to_problem(m, integrator=0))
+    # non-unit storage on the 3-d diffusion example (simulate_t.cpp:1153-1155)
+    m = sbml.load_sbml(os.path.join(REF, MODELS["single-compartment-diffusion-3d"]))
+    for sp in m.species:
+        sp.storage = {"slow": 2.0, "fast": 3.0}[sp.id]
+    dump("single-compartment-diffusion-3d-storage", m, sbml.to_problem(m))
+    # non-spatial species (SimCompartment::spatiallyAverageDcdt): very-simple-model
+    # with A_c2 and B_c3 made non-spatial (Species::setIsSpatial(id, false))
+    m = sbml.load_sbml(os.path.join(REF, MODELS["very-simple-model"]))
+    for sp in m.species:
+        if sp.id in ("A_c2", "B_c3"):
+            sp.spatial = False
+    dump("very-simple-model-non-spatial-species", m, sbml.to_problem(m))
 
 
 if __name__ == "__main__":

@@ -54,7 +54,10 @@ def load_golden(name, integrator=None):
         comps.append(P.Compartment(
             id=c["id"], species=c["species"], expressions=c["expressions"], diffusion=d,
             conc0=np.ascontiguousarray(conc, dtype=np.float64),
-            nn=G.neighbour_table(labels.shape, vox), voxels=vox))
+            nn=G.neighbour_table(labels.shape, vox), voxels=vox,
+            n_primary=c.get("n_primary"), non_spatial=c.get("non_spatial", ()),
+            inv_storage=None if c.get("inv_storage") is None
+            else np.array(c["inv_storage"], dtype=np.float64)))
     membs = []
     if meta["membranes"]:
         order = {}
