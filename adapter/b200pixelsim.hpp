@@ -41,6 +41,7 @@ private:
   std::unique_ptr<smeb200_sim, SimDeleter> sim;
   const model::Model &doc;
   std::size_t nCompartments{0};
+  std::size_t nExtraVars{0}; // time, x, y, z components behind the species
   // BaseSim returns references: host mirrors owned here
   mutable std::vector<std::vector<double>> conc;
   mutable std::vector<std::vector<double>> dcdt;
@@ -108,19 +109,21 @@ public:
       p.image_nx = imageSize.width();
       p.image_ny = imageSize.height();
       p.image_nz = static_cast<int32_t>(imageSize.depth());
-      // feature gates, same as cudapixelsim.cpp:789-809
+      // remaining feature gates (cudapixelsim.cpp:789-809): cross-diffusion
+      // and non-uniform diffusion.  Time / space dependent reactions,
+      // non-spatial species and non-unit storage are described to the library
+      // the way PixelSim handles them (pixelsim.cpp:282-322).
       if (hasAnyCrossDiffusion(doc, compartmentSpeciesIds)) {
         p.unsupported |= SMEB200_HAS_CROSS_DIFFUSION;
       }
       const auto &coords{doc.getParameters().getSpatialCoordinates()};
-      if (doc.getReactions().dependOnVariable("time")) {
-        p.unsupported |= SMEB200_HAS_TIME_DEPENDENCE;
-      }
-      if (doc.getReactions().dependOnVariable(coords.x.id.c_str()) ||
+      const bool timeDependent{doc.getReactions().dependOnVariable("time")};
+      const bool spaceDependent{
+          doc.getReactions().dependOnVariable(coords.x.id.c_str()) ||
           doc.getReactions().dependOnVariable(coords.y.id.c_str()) ||
-          doc.getReactions().dependOnVariable(coords.z.id.c_str())) {
-        p.unsupported |= SMEB200_HAS_SPACE_DEPENDENCE;
-      }
+          doc.getReactions().dependOnVariable(coords.z.id.c_str())};
+      nExtraVars = (timeDependent ? 1 : 0) + (spaceDependent ? 3 : 0);
+      const auto origin{doc.getGeometry().getPhysicalOrigin()};
       const auto voxelSize{doc.getGeometry().getVoxelSize()};
       const double dx2 = voxelSize.width() * voxelSize.width();
       const double dy2 = voxelSize.height() * voxelSize.height();
@@ -131,6 +134,8 @@ public:
       std::vector<std::vector<std::uint32_t>> nn(nCompartments);
       std::vector<std::vector<std::int32_t>> voxels(nCompartments);
       std::vector<std::vector<double>> diffusion(nCompartments);
+      std::vector<std::vector<double>> invStorage(nCompartments);
+      std::vector<std::vector<std::uint32_t>> nonSpatial(nCompartments);
       std::vector<std::vector<std::string>> exprs(nCompartments);
       std::vector<std::vector<const char *>> exprPtrs(nCompartments);
       std::vector<std::vector<const char *>> namePtrs(nCompartments);
@@ -143,11 +148,13 @@ public:
             compartmentIds[ci].c_str())};
         compIndexById[comp->getId()] = ci;
         const std::size_t n{comp->nVoxels()};
-        const std::size_t S{speciesIds.size()};
+        const std::size_t nPrimary{speciesIds.size()};
+        const std::size_t S{nPrimary + nExtraVars}; // + time, x, y, z padding
         auto &c{comps[ci]};
         c.id = comp->getId().c_str();
         c.n_voxels = n;
         c.n_species = static_cast<std::uint32_t>(S);
+        c.n_primary_species = static_cast<std::uint32_t>(nPrimary);
         // a compartment that fills the whole image needs no neighbour table:
         // the library then uses the TMA tile kernel with implicit neighbours
         const bool fillsImage{n == static_cast<std::size_t>(p.image_nx) *
@@ -184,30 +191,67 @@ public:
             throw std::runtime_error("could not find field for species '" +
                                      speciesId + "'");
           }
-          if (!field->getIsSpatial()) {
-            p.unsupported |= SMEB200_HAS_NON_SPATIAL_SPECIES;
+          if (!field->getIsSpatial()) { // pixelsim_impl.cpp:303-305
+            nonSpatial[ci].push_back(
+                static_cast<std::uint32_t>(fields.size()));
           }
-          if (!field->getIsUniformDiffusionConstant()) {
+          const bool isConstant{
+              doc.getSpecies().getIsConstant(speciesId.c_str())};
+          if (!isConstant && !field->getIsUniformDiffusionConstant()) {
             p.unsupported |= SMEB200_HAS_NON_UNIFORM_DIFFUSION;
           }
-          if (doc.getSpecies().getStorage(speciesId.c_str()) != 1.0) {
-            p.unsupported |= SMEB200_HAS_NON_UNIT_STORAGE;
+          // pixelsim_impl.cpp:214-232; storage 0 (algebraic species) is
+          // passed as 0 and refused by the library
+          const double storage{
+              doc.getSpecies().getStorage(speciesId.c_str())};
+          if (storage < 0.0) {
+            throw std::runtime_error(
+                "Invalid negative storage value for species '" + speciesId +
+                "'");
           }
+          invStorage[ci].push_back(storage == 0.0 ? 0.0 : 1.0 / storage);
           fields.push_back(field);
           const auto &d{field->getDiffusionConstant()};
-          const double dc{d.empty() ? 0.0 : d.front()};
+          const double dc{isConstant || d.empty() ? 0.0 : d.front()};
           diffusion[ci].push_back(dc / dx2);
           diffusion[ci].push_back(dc / dy2);
           diffusion[ci].push_back(dc / dz2);
           namePtrs[ci].push_back(speciesId.c_str());
         }
+        // the padding components: zero diffusion, unit storage
+        // (pixelsim_impl.cpp:312-349)
+        static const std::array<std::string, 4> padNames{"time", "x", "y", "z"};
+        for (std::size_t k = 0; k < nExtraVars; ++k) {
+          diffusion[ci].insert(diffusion[ci].end(), {0.0, 0.0, 0.0});
+          invStorage[ci].push_back(1.0);
+          namePtrs[ci].push_back(
+              padNames[(timeDependent ? 0 : 1) + k].c_str());
+        }
         c.diffusion = diffusion[ci].data();
         c.species_names = namePtrs[ci].data();
+        c.inv_storage = invStorage[ci].data();
+        c.n_non_spatial = static_cast<std::uint32_t>(nonSpatial[ci].size());
+        c.non_spatial = nonSpatial[ci].empty() ? nullptr : nonSpatial[ci].data();
         conc[ci].resize(n * S);
         auto it{conc[ci].begin()};
+        const int imageNy{comp->getCompartmentImages()[0].height()};
         for (std::size_t ix = 0; ix < n; ++ix) {
           for (const auto *field : fields) {
             *it++ = field->getConcentration()[ix];
+          }
+          // pixelsim_impl.cpp:405-423
+          if (timeDependent) {
+            *it++ = 0.0;
+          }
+          if (spaceDependent) {
+            const auto voxel{comp->getVoxel(ix)};
+            *it++ = origin.p.x() +
+                    (static_cast<double>(voxel.p.x()) + 0.5) * voxelSize.width();
+            *it++ = origin.p.y() +
+                    (static_cast<double>(imageNy - 1 - voxel.p.y()) + 0.5) *
+                        voxelSize.height();
+            *it++ = origin.z +
+                    (static_cast<double>(voxel.z) + 0.5) * voxelSize.depth();
           }
         }
         c.conc0 = conc[ci].data();
@@ -217,8 +261,8 @@ public:
             !r.isEmpty()) {
           reactionIDs = common::toStdString(r);
         }
-        const ReacExpr reacExpr(doc, speciesIds, reactionIDs, 1.0, false, false,
-                                substitutions);
+        const ReacExpr reacExpr(doc, speciesIds, reactionIDs, 1.0,
+                                timeDependent, spaceDependent, substitutions);
         exprs[ci] = cudaExpressions(reacExpr.variables, reacExpr.expressions);
         for (const auto &e : exprs[ci]) {
           exprPtrs[ci].push_back(e.c_str());
@@ -272,8 +316,11 @@ public:
         if (speciesIds.empty()) {
           continue;
         }
+        // variables: [A species | B species | time, x, y, z]; the library
+        // uses the first SA + SB expressions (pixelsim_impl.cpp:960-1005)
         const ReacExpr reacExpr(doc, speciesIds, common::toStdString(reacs),
-                                volOverL3, false, false, substitutions);
+                                volOverL3, timeDependent, spaceDependent,
+                                substitutions);
         mExprs.push_back(
             cudaExpressions(reacExpr.variables, reacExpr.expressions));
         mExprPtrs.emplace_back();
@@ -355,7 +402,7 @@ public:
   }
 
   [[nodiscard]] std::size_t getConcentrationPadding() const override {
-    return 0;
+    return nExtraVars; // pixelsim.cpp:478
   }
 
   [[nodiscard]] const std::vector<double> &
