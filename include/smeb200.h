@@ -104,6 +104,29 @@ typedef struct smeb200_compartment {
    * 214-232); NULL = unit storage.  A zero entry (zero-storage species,
    * algebraic constraint) is rejected. */
   const double *inv_storage;
+  /* Non-uniform diffusion (SimCompartment::evaluateDiffusionOperator, array
+   * branch, pixelsim_impl.cpp:453-485): [n_voxels*n_species] diffusion
+   * constant of species s at voxel i at diffusion_array[i*n_species + s] (NOT
+   * divided by the voxel size; the face-averaged stencil divides by
+   * smeb200_problem.voxel_size^2 per face).  The reference uses this branch
+   * for EVERY compartment as soon as one species of the model has a
+   * non-uniform constant (pixelsim.cpp:323-336), so the adapter passes arrays
+   * for all compartments or for none.  NULL = uniform (`diffusion` is used). */
+  const double *diffusion_array;
+  /* Cross-diffusion terms D_ts(c) grad c_s added to species t
+   * (pixelsim_impl.cpp:350-389,494-589): per term the target and source
+   * species index and a CUDA-C expression of the coefficient in
+   * sme_var_0..sme_var_{n_species-1}, evaluated at each voxel's own state and
+   * face-averaged.  With cross-diffusion `diffusion_raw` ([n_species] diffusion
+   * constants, or their per-species maxima, not divided by the voxel size;
+   * maxPrimaryDiagonalDiffusion of pixelsim_impl.cpp:256,291) is required: the
+   * forward-Euler bound is then re-evaluated every step
+   * (updateCrossDiffusionMaxStableTimestep, pixelsim_impl.cpp:506-543). */
+  uint32_t n_cross_diffusion;
+  const uint32_t *cross_target;
+  const uint32_t *cross_source;
+  const char *const *cross_expressions;
+  const double *diffusion_raw;
 } smeb200_compartment;
 
 /* One geometry::Membrane + SimMembrane (pixelsim_impl.cpp:929-1047). */
@@ -160,6 +183,9 @@ typedef struct smeb200_problem {
    * same string on all ranks and unique per simulation; NULL if n_ranks <= 1 */
   const char *comm_name;
   const double *params;    /* [n_params] */
+  /* voxel width, height, depth (model units): needed with diffusion_array or
+   * cross-diffusion only */
+  double voxel_size[3];
   uint32_t reserved[2];
 } smeb200_problem;
 

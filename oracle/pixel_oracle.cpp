@@ -55,6 +55,19 @@ struct OCompartment {
   std::vector<std::size_t> nonSpatialSpeciesIndices;
   std::vector<double> invStorage;
   bool hasNonUnitStorage{false};
+  // non-uniform diffusion: diffConstants[s][i] (pixelsim_impl.cpp:257-296)
+  bool useUniformDiffusionOperator{true};
+  std::vector<std::vector<double>> diffConstants;
+  double dx2{1}, dy2{1}, dz2{1};
+  // cross-diffusion (pixelsim_impl.cpp:350-389)
+  struct CrossTerm {
+    std::size_t targetSpeciesIndex, sourceSpeciesIndex;
+  };
+  std::vector<CrossTerm> crossDiffusionTerms;
+  std::vector<double> crossDiffusionCoefficients; // [nPixels * nTerms]
+  std::vector<double> maxPrimaryDiagonalDiffusion;
+  ReacFn crossFn{nullptr};
+  bool hasCrossDiffusion{false};
   std::vector<double> conc, dcdt, s2, s3;
   std::vector<int32_t> voxels;
   std::vector<std::string> speciesNames;
@@ -67,8 +80,129 @@ struct OCompartment {
       reac(dcdt.data() + i * nSpecies, conc.data() + i * nSpecies);
     }
   }
+  // pixelsim_impl.cpp:453-485 (array branch)
+  void evaluateDiffusionOperatorArray(std::size_t begin, std::size_t end) {
+    for (std::size_t i = begin; i < end; ++i) {
+      const std::size_t ix{i * nSpecies};
+      const std::size_t ix_upx{nn[6 * i] * nSpecies};
+      const std::size_t ix_dnx{nn[6 * i + 1] * nSpecies};
+      const std::size_t ix_upy{nn[6 * i + 2] * nSpecies};
+      const std::size_t ix_dny{nn[6 * i + 3] * nSpecies};
+      const std::size_t ix_upz{nn[6 * i + 4] * nSpecies};
+      const std::size_t ix_dnz{nn[6 * i + 5] * nSpecies};
+      for (std::size_t is = 0; is < nSpecies; ++is) {
+        const auto &d = diffConstants[is];
+        double d_i = d[i];
+        double d_upx = d[nn[6 * i]];
+        double d_dnx = d[nn[6 * i + 1]];
+        double d_upy = d[nn[6 * i + 2]];
+        double d_dny = d[nn[6 * i + 3]];
+        double d_upz = d[nn[6 * i + 4]];
+        double d_dnz = d[nn[6 * i + 5]];
+        double dxp = 0.5 * (d_i + d_upx) / dx2;
+        double dxm = 0.5 * (d_i + d_dnx) / dx2;
+        double dyp = 0.5 * (d_i + d_upy) / dy2;
+        double dym = 0.5 * (d_i + d_dny) / dy2;
+        double dzp = 0.5 * (d_i + d_upz) / dz2;
+        double dzm = 0.5 * (d_i + d_dnz) / dz2;
+        dcdt[ix + is] += dxp * (conc[ix_upx + is] - conc[ix + is]) -
+                         dxm * (conc[ix + is] - conc[ix_dnx + is]) +
+                         dyp * (conc[ix_upy + is] - conc[ix + is]) -
+                         dym * (conc[ix + is] - conc[ix_dny + is]) +
+                         dzp * (conc[ix_upz + is] - conc[ix + is]) -
+                         dzm * (conc[ix + is] - conc[ix_dnz + is]);
+      }
+    }
+  }
+  // pixelsim_impl.cpp:494-504
+  void evaluateCrossDiffusionCoefficients(std::size_t begin, std::size_t end) {
+    const auto nTerms{crossDiffusionTerms.size()};
+    for (std::size_t i = begin; i < end; ++i) {
+      crossFn(crossDiffusionCoefficients.data() + i * nTerms,
+              conc.data() + i * nSpecies);
+    }
+  }
+  // pixelsim_impl.cpp:506-543
+  void updateCrossDiffusionMaxStableTimestep() {
+    if (!hasCrossDiffusion || crossDiffusionTerms.empty()) {
+      return;
+    }
+    const auto nTerms{crossDiffusionTerms.size()};
+    std::vector<double> maxAbsCrossDiffusionByTerm(nTerms, 0.0);
+    for (std::size_t ix = 0; ix < nPixels; ++ix) {
+      const auto iBase{ix * nTerms};
+      for (std::size_t iTerm = 0; iTerm < nTerms; ++iTerm) {
+        maxAbsCrossDiffusionByTerm[iTerm] =
+            std::max(maxAbsCrossDiffusionByTerm[iTerm],
+                     std::abs(crossDiffusionCoefficients[iBase + iTerm]));
+      }
+    }
+    auto maxEffectiveDiffusion{maxPrimaryDiagonalDiffusion};
+    for (std::size_t iTerm = 0; iTerm < nTerms; ++iTerm) {
+      const auto &term{crossDiffusionTerms[iTerm]};
+      maxEffectiveDiffusion[term.targetSpeciesIndex] +=
+          maxAbsCrossDiffusionByTerm[iTerm];
+    }
+    maxStableTimestep = std::numeric_limits<double>::max();
+    for (std::size_t iTarget = 0; iTarget < nPrimarySpecies; ++iTarget) {
+      const double invStorageValue{invStorage[iTarget]};
+      if (invStorageValue == 0.0) {
+        continue;
+      }
+      const double maxEffectiveD{maxEffectiveDiffusion[iTarget]};
+      if (maxEffectiveD <= 0.0) {
+        continue;
+      }
+      maxStableTimestep = std::min(
+          maxStableTimestep,
+          1.0 / (2.0 * (maxEffectiveD * invStorageValue / dx2 +
+                        maxEffectiveD * invStorageValue / dy2 +
+                        maxEffectiveD * invStorageValue / dz2)));
+    }
+  }
+  // pixelsim_impl.cpp:545-589
+  void evaluateCrossDiffusionOperator(std::size_t begin, std::size_t end) {
+    const auto nTerms{crossDiffusionTerms.size()};
+    for (std::size_t i = begin; i < end; ++i) {
+      const std::size_t ix{i * nSpecies};
+      const std::size_t iupx{nn[6 * i]}, idnx{nn[6 * i + 1]};
+      const std::size_t iupy{nn[6 * i + 2]}, idny{nn[6 * i + 3]};
+      const std::size_t iupz{nn[6 * i + 4]}, idnz{nn[6 * i + 5]};
+      const std::size_t ixUpx{iupx * nSpecies}, ixDnx{idnx * nSpecies};
+      const std::size_t ixUpy{iupy * nSpecies}, ixDny{idny * nSpecies};
+      const std::size_t ixUpz{iupz * nSpecies}, ixDnz{idnz * nSpecies};
+      for (std::size_t iTerm = 0; iTerm < nTerms; ++iTerm) {
+        const auto &term{crossDiffusionTerms[iTerm]};
+        const std::size_t target{term.targetSpeciesIndex};
+        const std::size_t source{term.sourceSpeciesIndex};
+        const double dCenter{crossDiffusionCoefficients[i * nTerms + iTerm]};
+        const double dUpx{crossDiffusionCoefficients[iupx * nTerms + iTerm]};
+        const double dDnx{crossDiffusionCoefficients[idnx * nTerms + iTerm]};
+        const double dUpy{crossDiffusionCoefficients[iupy * nTerms + iTerm]};
+        const double dDny{crossDiffusionCoefficients[idny * nTerms + iTerm]};
+        const double dUpz{crossDiffusionCoefficients[iupz * nTerms + iTerm]};
+        const double dDnz{crossDiffusionCoefficients[idnz * nTerms + iTerm]};
+        const double dxp{0.5 * (dCenter + dUpx) / dx2};
+        const double dxm{0.5 * (dCenter + dDnx) / dx2};
+        const double dyp{0.5 * (dCenter + dUpy) / dy2};
+        const double dym{0.5 * (dCenter + dDny) / dy2};
+        const double dzp{0.5 * (dCenter + dUpz) / dz2};
+        const double dzm{0.5 * (dCenter + dDnz) / dz2};
+        dcdt[ix + target] += dxp * (conc[ixUpx + source] - conc[ix + source]) -
+                             dxm * (conc[ix + source] - conc[ixDnx + source]) +
+                             dyp * (conc[ixUpy + source] - conc[ix + source]) -
+                             dym * (conc[ix + source] - conc[ixDny + source]) +
+                             dzp * (conc[ixUpz + source] - conc[ix + source]) -
+                             dzm * (conc[ix + source] - conc[ixDnz + source]);
+      }
+    }
+  }
   // pixelsim_impl.cpp:434-452 (uniform branch)
   void evaluateDiffusionOperator(std::size_t begin, std::size_t end) {
+    if (!useUniformDiffusionOperator) {
+      evaluateDiffusionOperatorArray(begin, end);
+      return;
+    }
     for (std::size_t i = begin; i < end; ++i) {
       const std::size_t ix = i * nSpecies;
       const std::size_t upx = nn[6 * i] * nSpecies;
@@ -212,9 +346,20 @@ struct Oracle {
       parallelFor(useThreads, c.nPixels, [&](std::size_t b, std::size_t e) {
         c.evaluateReactions(b, e);
       });
+      if (c.hasCrossDiffusion) { // pixelsim_impl.cpp:591-599
+        parallelFor(useThreads, c.nPixels, [&](std::size_t b, std::size_t e) {
+          c.evaluateCrossDiffusionCoefficients(b, e);
+        });
+        c.updateCrossDiffusionMaxStableTimestep();
+      }
       parallelFor(useThreads, c.nPixels, [&](std::size_t b, std::size_t e) {
         c.evaluateDiffusionOperator(b, e);
       });
+      if (c.hasCrossDiffusion) {
+        parallelFor(useThreads, c.nPixels, [&](std::size_t b, std::size_t e) {
+          c.evaluateCrossDiffusionOperator(b, e);
+        });
+      }
       maxStableTimestep = std::min(maxStableTimestep, c.maxStableTimestep);
     }
     for (auto &m : membs) {
@@ -503,6 +648,7 @@ struct Oracle {
 
   // stands in for Symbolic::parse + compile (LLVM JIT): the expressions are
   // compiled by the host C compiler without contraction or fast-math
+  double maxStableTimestepAfterCtor{std::numeric_limits<double>::max()};
   void compileReactions(const smeb200_problem &p) {
     std::ostringstream src;
     src << "#include <math.h>\n";
@@ -530,6 +676,11 @@ struct Oracle {
     for (uint32_t c = 0; c < p.n_compartments; ++c) {
       emit("reac" + std::to_string(c), p.compartments[c].n_species,
            p.compartments[c].n_species, p.compartments[c].expressions);
+      if (p.compartments[c].n_cross_diffusion > 0) {
+        emit("cross" + std::to_string(c), p.compartments[c].n_species,
+             p.compartments[c].n_cross_diffusion,
+             p.compartments[c].cross_expressions);
+      }
     }
     for (uint32_t m = 0; m < p.n_membranes; ++m) {
       const auto &mb = p.membranes[m];
@@ -585,6 +736,18 @@ struct Oracle {
     for (uint32_t c = 0; c < p.n_compartments; ++c) {
       comps[c].reac = reinterpret_cast<ReacFn>(
           dlsym(dl, ("reac" + std::to_string(c)).c_str()));
+      if (comps[c].hasCrossDiffusion) {
+        comps[c].crossFn = reinterpret_cast<ReacFn>(
+            dlsym(dl, ("cross" + std::to_string(c)).c_str()));
+        // SimCompartment ctor, pixelsim_impl.cpp:425-428
+        comps[c].evaluateCrossDiffusionCoefficients(0, comps[c].nPixels);
+        comps[c].updateCrossDiffusionMaxStableTimestep();
+        maxStableTimestepAfterCtor =
+            std::min(maxStableTimestepAfterCtor, comps[c].maxStableTimestep);
+      } else {
+        maxStableTimestepAfterCtor =
+            std::min(maxStableTimestepAfterCtor, comps[c].maxStableTimestep);
+      }
     }
     for (uint32_t m = 0; m < p.n_membranes; ++m) {
       membs[m].reac = reinterpret_cast<ReacFn>(
@@ -645,6 +808,23 @@ struct Oracle {
       }
       c.nPrimarySpecies =
           pc.n_primary_species != 0 ? pc.n_primary_species : pc.n_species;
+      c.dx2 = p.voxel_size[0] * p.voxel_size[0];
+      c.dy2 = p.voxel_size[1] * p.voxel_size[1];
+      c.dz2 = p.voxel_size[2] * p.voxel_size[2];
+      c.useUniformDiffusionOperator = pc.diffusion_array == nullptr;
+      for (uint32_t k = 0; k < pc.n_cross_diffusion; ++k) {
+        c.crossDiffusionTerms.push_back({pc.cross_target[k], pc.cross_source[k]});
+      }
+      c.hasCrossDiffusion = pc.n_cross_diffusion > 0;
+      if (c.hasCrossDiffusion) {
+        if (pc.diffusion_raw == nullptr) {
+          throw std::runtime_error("oracle: cross-diffusion needs diffusion_raw");
+        }
+        c.maxPrimaryDiagonalDiffusion.assign(
+            pc.diffusion_raw, pc.diffusion_raw + c.nPrimarySpecies);
+        c.crossDiffusionCoefficients.assign(
+            c.nPixels * pc.n_cross_diffusion, 0.0);
+      }
       for (uint32_t k = 0; k < pc.n_non_spatial; ++k) {
         c.nonSpatialSpeciesIndices.push_back(pc.non_spatial[k]);
       }
@@ -660,12 +840,28 @@ struct Oracle {
         if (c.invStorage.back() != 1.0) {
           c.hasNonUnitStorage = true;
         }
-        // pixelsim_common.hpp:33-37, pixelsim_impl.cpp:249-255
-        c.maxStableTimestep = std::min(
-            c.maxStableTimestep,
-            1.0 / (2.0 * (c.diff.back()[0] * c.invStorage.back() +
-                          c.diff.back()[1] * c.invStorage.back() +
-                          c.diff.back()[2] * c.invStorage.back())));
+        if (c.useUniformDiffusionOperator) {
+          // pixelsim_common.hpp:33-37, pixelsim_impl.cpp:249-255
+          c.maxStableTimestep = std::min(
+              c.maxStableTimestep,
+              1.0 / (2.0 * (c.diff.back()[0] * c.invStorage.back() +
+                            c.diff.back()[1] * c.invStorage.back() +
+                            c.diff.back()[2] * c.invStorage.back())));
+        } else {
+          // pixelsim_impl.cpp:257-290: per-voxel constants, bound from max D
+          c.diffConstants.emplace_back(c.nPixels);
+          double maxD = 0.0;
+          for (std::size_t i = 0; i < c.nPixels; ++i) {
+            const double d = pc.diffusion_array[i * pc.n_species + s];
+            c.diffConstants.back()[i] = d;
+            maxD = i == 0 ? d : std::max(maxD, d);
+          }
+          c.maxStableTimestep = std::min(
+              c.maxStableTimestep,
+              1.0 / (2.0 * (maxD * c.invStorage.back() / c.dx2 +
+                            maxD * c.invStorage.back() / c.dy2 +
+                            maxD * c.invStorage.back() / c.dz2)));
+        }
         c.speciesNames.emplace_back(
             pc.species_names != nullptr && pc.species_names[s] != nullptr
                 ? pc.species_names[s]
@@ -689,6 +885,9 @@ struct Oracle {
       }
     }
     compileReactions(p);
+    if (p.n_compartments > 0) { // pixelsim.cpp:353-354
+      maxStableTimestep = maxStableTimestepAfterCtor;
+    }
   }
 };
 

@@ -7,8 +7,8 @@
 #include "device_kernels.cuh"
 
 struct Reac0 {
-  static constexpr int S = 2, SP = 2, NNS = 0;
-  static constexpr bool STORAGE = false;
+  static constexpr int S = 2, SP = 2, NNS = 0, NX = 0;
+  static constexpr bool STORAGE = false, NUD = false;
   static __device__ __forceinline__ void nonSpatial(double *, const double *) {}
   static __device__ __forceinline__ void nonSpatialPick(const double *, double *) {}
   static __device__ __forceinline__ void storage(double *) {}
@@ -25,8 +25,35 @@ struct Reac1 : Reac0 {};
 // a model using every post-processing hook: 2 species + time + x,y,z padding,
 // species 1 non-spatial, storage 2 for species 0
 struct Reac2 {
-  static constexpr int S = 6, SP = 2, NNS = 1;
-  static constexpr bool STORAGE = true;
+  static constexpr int S = 6, SP = 2, NNS = 1, NX = 1;
+  static constexpr bool STORAGE = true, NUD = true;
+  // one cross-diffusion term: target 0, source 1, coefficient 0.1 * c0
+  static __device__ __forceinline__ void crossCoef(double *k, const double *v,
+                                                   const double *) {
+    k[0] = 0.1 * v[0];
+  }
+  static __device__ __forceinline__ void
+  cross(double *f, const double *c, const double *xp, const double *xm,
+        const double *yp, const double *ym, const double *zp, const double *zm,
+        const double *h2, const double *p) {
+    double kc[1], k0[1], k1[1], k2[1], k3[1], k4[1], k5[1];
+    crossCoef(kc, c, p);
+    crossCoef(k0, xp, p);
+    crossCoef(k1, xm, p);
+    crossCoef(k2, yp, p);
+    crossCoef(k3, ym, p);
+    crossCoef(k4, zp, p);
+    crossCoef(k5, zm, p);
+    const double dxp = 0.5 * (kc[0] + k0[0]) / h2[0];
+    const double dxm = 0.5 * (kc[0] + k1[0]) / h2[0];
+    const double dyp = 0.5 * (kc[0] + k2[0]) / h2[1];
+    const double dym = 0.5 * (kc[0] + k3[0]) / h2[1];
+    const double dzp = 0.5 * (kc[0] + k4[0]) / h2[2];
+    const double dzm = 0.5 * (kc[0] + k5[0]) / h2[2];
+    f[0] += dxp * (xp[1] - c[1]) - dxm * (c[1] - xm[1]) +
+            dyp * (yp[1] - c[1]) - dym * (c[1] - ym[1]) +
+            dzp * (zp[1] - c[1]) - dzm * (c[1] - zm[1]);
+  }
   static __device__ __forceinline__ void nonSpatial(double *f, const double *av) {
     f[1] = av[0];
   }
@@ -112,3 +139,6 @@ template __global__ void
 smeb_stage_tile<Reac2, F2, 8, 32, 4, true>(const __grid_constant__ SmebStageArgs<6>,
                                             const __grid_constant__ SmebTensorMap,
                                             const smeb_u32);
+template __global__ void
+smeb_stage_box<Reac2, F2>(const __grid_constant__ SmebStageArgs<6>);
+template __global__ void smeb_xd_max<Reac2>(const __grid_constant__ SmebStageArgs<6>);

@@ -61,6 +61,9 @@ template <int S> struct SmebStageArgs {
   smeb_u64 *err;       // [2] bit patterns of max abs / max rel error
   const double *nsAv;  // [R::NNS] spatial averages of dc/dt (non-spatial species)
   double *nsPartial;   // [blocks][R::NNS] block sums written by the pre-pass
+  const double *darr;  // [n][S] per-voxel diffusion constants (R::NUD)
+  smeb_u64 *xdMax;     // [R::NX] max |cross-diffusion coefficient| (bit patterns)
+  double h2[3];        // voxel width^2, height^2, depth^2 (R::NUD / R::NX)
   smeb_u32 n;          // voxels in this launch's index space
   smeb_u32 nx, ny, nz; // box dims; voxel = (z*nx + x)*ny + y
   smeb_u32 z_begin, z_end; // planes updated by this launch (ghosts excluded)
@@ -351,6 +354,37 @@ smeb_rhs_values(const SmebStageArgs<R::S> &a, const double *c,
   }
 }
 
+// non-uniform diffusion: face-averaged constants, conservative form
+// (pixelsim_impl.cpp:453-485, same association order)
+template <int S>
+__device__ __forceinline__ void
+smeb_diffusion_array(const double *h2, const double *d, const double *dxp_,
+                     const double *dxm_, const double *dyp_, const double *dym_,
+                     const double *dzp_, const double *dzm_, const double *c,
+                     const double *xp, const double *xm, const double *yp,
+                     const double *ym, const double *zp, const double *zm,
+                     double *f) {
+#pragma unroll
+  for (int s = 0; s < S; ++s) {
+    const double dxp = 0.5 * (d[s] + dxp_[s]) / h2[0];
+    const double dxm = 0.5 * (d[s] + dxm_[s]) / h2[0];
+    const double dyp = 0.5 * (d[s] + dyp_[s]) / h2[1];
+    const double dym = 0.5 * (d[s] + dym_[s]) / h2[1];
+    const double dzp = 0.5 * (d[s] + dzp_[s]) / h2[2];
+    const double dzm = 0.5 * (d[s] + dzm_[s]) / h2[2];
+    f[s] += dxp * (xp[s] - c[s]) - dxm * (c[s] - xm[s]) +
+            dyp * (yp[s] - c[s]) - dym * (c[s] - ym[s]) +
+            dzp * (zp[s] - c[s]) - dzm * (c[s] - zm[s]);
+  }
+}
+
+// Direct kernels: the voxel and its six neighbours are gathered from global
+// memory (neighbour lines come from L1/L2).  Besides the uniform stencil this
+// path carries the CPU solver's other diffusion operators: per-voxel diffusion
+// constants (R::NUD) and cross-diffusion (R::NX terms).  The cross-diffusion
+// coefficient of a neighbour is a function of that neighbour's state, which is
+// already in registers, so it is re-evaluated instead of being stored per voxel
+// as the CPU solver does (pixelsim_impl.cpp:494-504,545-589).
 template <class R>
 __device__ __forceinline__ void
 smeb_rhs_gather(const SmebStageArgs<R::S> &a, smeb_u32 i, const smeb_u32 *nb,
@@ -364,7 +398,58 @@ smeb_rhs_gather(const SmebStageArgs<R::S> &a, smeb_u32 i, const smeb_u32 *nb,
   smeb_load_voxel<S>(a.cin, nb[3], ym);
   smeb_load_voxel<S>(a.cin, nb[4], zp);
   smeb_load_voxel<S>(a.cin, nb[5], zm);
-  smeb_rhs_values<R>(a, c, xp, xm, yp, ym, zp, zm, f);
+  if constexpr (R::NUD) {
+    double d[S], d0[S], d1[S], d2[S], d3[S], d4[S], d5[S];
+    smeb_load_voxel<S>(a.darr, i, d);
+    smeb_load_voxel<S>(a.darr, nb[0], d0);
+    smeb_load_voxel<S>(a.darr, nb[1], d1);
+    smeb_load_voxel<S>(a.darr, nb[2], d2);
+    smeb_load_voxel<S>(a.darr, nb[3], d3);
+    smeb_load_voxel<S>(a.darr, nb[4], d4);
+    smeb_load_voxel<S>(a.darr, nb[5], d5);
+    R::eval(f, c, a.D + 3 * S);
+    smeb_diffusion_array<S>(a.h2, d, d0, d1, d2, d3, d4, d5, c, xp, xm, yp, ym,
+                            zp, zm, f);
+  } else {
+    smeb_rhs_values<R>(a, c, xp, xm, yp, ym, zp, zm, f);
+  }
+  if constexpr (R::NX > 0) {
+    R::cross(f, c, xp, xm, yp, ym, zp, zm, a.h2, a.D + 3 * S);
+  }
+}
+
+// max |cross-diffusion coefficient| per term over the voxels of a compartment:
+// the input of the forward-Euler bound RK101 re-evaluates every step
+// (updateCrossDiffusionMaxStableTimestep, pixelsim_impl.cpp:506-543)
+template <class R>
+__global__ void __launch_bounds__(SMEB_BLOCK)
+    smeb_xd_max(const __grid_constant__ SmebStageArgs<R::S> a) {
+  constexpr int S = R::S;
+  constexpr int NX = R::NX > 0 ? R::NX : 1;
+  double mx[NX] = {};
+  for (smeb_u32 i = blockIdx.x * SMEB_BLOCK + threadIdx.x; i < a.n;
+       i += gridDim.x * SMEB_BLOCK) {
+    double c[S], k[NX];
+    smeb_load_voxel<S>(a.cin, i, c);
+    R::crossCoef(k, c, a.D + 3 * S);
+#pragma unroll
+    for (int t = 0; t < R::NX; ++t) {
+      const double v = fabs(k[t]);
+      mx[t] = mx[t] < v ? v : mx[t];
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < R::NX; ++t) {
+    double v = mx[t];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double w = __shfl_xor_sync(0xffffffffu, v, o);
+      v = w > v ? w : v;
+    }
+    if ((threadIdx.x & 31) == 0 && v > 0.0) {
+      atomicMax(a.xdMax + t, (smeb_u64)__double_as_longlong(v));
+    }
+  }
 }
 
 // ---- direct-gather stage kernels: grid-stride loop, one voxel at a time -----

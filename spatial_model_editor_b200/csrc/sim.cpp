@@ -142,8 +142,67 @@ void Sim::generateSource(const smeb200_problem &p) {
     }
     h << "struct Reac" << c << " {\n  static constexpr int S = "
       << comp.n_species << ", SP = " << sp << ", NNS = " << comp.n_non_spatial
+      << ", NX = " << comp.n_cross_diffusion
       << ";\n  static constexpr bool STORAGE = "
-      << (storage ? "true" : "false") << ";\n";
+      << (storage ? "true" : "false")
+      << ", NUD = " << (comp.diffusion_array != nullptr ? "true" : "false")
+      << ";\n";
+    if (comp.n_cross_diffusion > 0) {
+      // coefficients of all terms at one voxel (symCrossDiffusion,
+      // pixelsim_impl.cpp:372-389), then the face-averaged operator per term
+      // (pixelsim_impl.cpp:545-589), unrolled
+      const uint32_t nx = comp.n_cross_diffusion;
+      h << "  static __device__ __forceinline__ void crossCoef(double* "
+           "sme_out, const double* sme_values, const double* sme_params) {\n";
+      for (uint32_t i = 0; i < comp.n_species; ++i) {
+        h << "    const double sme_var_" << i << " = sme_values[" << i
+          << "]; (void)sme_var_" << i << ";\n";
+      }
+      for (uint32_t i = 0; i < p.n_params; ++i) {
+        h << "    const double sme_param_" << i << " = sme_params[" << i
+          << "]; (void)sme_param_" << i << ";\n";
+      }
+      h << "    (void)sme_params;\n";
+      for (uint32_t t = 0; t < nx; ++t) {
+        h << "    sme_out[" << t << "] = " << comp.cross_expressions[t]
+          << ";\n";
+      }
+      h << "  }\n";
+      h << "  static __device__ __forceinline__ void cross(double* f, const "
+           "double* c, const double* xp, const double* xm, const double* yp, "
+           "const double* ym, const double* zp, const double* zm, const "
+           "double* h2, const double* p) {\n";
+      h << "    double kc[" << nx << "], k0[" << nx << "], k1[" << nx
+        << "], k2[" << nx << "], k3[" << nx << "], k4[" << nx << "], k5["
+        << nx << "];\n";
+      h << "    crossCoef(kc, c, p); crossCoef(k0, xp, p); crossCoef(k1, xm, "
+           "p); crossCoef(k2, yp, p); crossCoef(k3, ym, p); crossCoef(k4, zp, "
+           "p); crossCoef(k5, zm, p);\n";
+      // the terms read the state only, so their order matters per target
+      // species, where it is the reference's (term order)
+      for (uint32_t t = 0; t < nx; ++t) {
+        const uint32_t tg = comp.cross_target[t], sr = comp.cross_source[t];
+        h << "    {\n"
+          << "      const double dxp = 0.5 * (kc[" << t << "] + k0[" << t
+          << "]) / h2[0];\n"
+          << "      const double dxm = 0.5 * (kc[" << t << "] + k1[" << t
+          << "]) / h2[0];\n"
+          << "      const double dyp = 0.5 * (kc[" << t << "] + k2[" << t
+          << "]) / h2[1];\n"
+          << "      const double dym = 0.5 * (kc[" << t << "] + k3[" << t
+          << "]) / h2[1];\n"
+          << "      const double dzp = 0.5 * (kc[" << t << "] + k4[" << t
+          << "]) / h2[2];\n"
+          << "      const double dzm = 0.5 * (kc[" << t << "] + k5[" << t
+          << "]) / h2[2];\n"
+          << "      f[" << tg << "] += dxp * (xp[" << sr << "] - c[" << sr
+          << "]) - dxm * (c[" << sr << "] - xm[" << sr << "]) + dyp * (yp["
+          << sr << "] - c[" << sr << "]) - dym * (c[" << sr << "] - ym[" << sr
+          << "]) + dzp * (zp[" << sr << "] - c[" << sr << "]) - dzm * (c["
+          << sr << "] - zm[" << sr << "]);\n    }\n";
+      }
+      h << "  }\n";
+    }
     // dc/dt post-processing of the CPU solver (pixelsim.cpp:113-119)
     h << "  static __device__ __forceinline__ void nonSpatial(double* f, "
          "const double* av) {\n    (void)f; (void)av;\n";
@@ -363,7 +422,10 @@ void Sim::chooseGeometry(int variant) {
       continue;
     }
     c.geom = Geom::BOX;
-    if (variant == 1 || c.S == 0 || c.n == 0) {
+    // per-voxel diffusion constants and cross-diffusion live in the direct
+    // kernels only
+    if (variant == 1 || c.S == 0 || c.n == 0 || c.nonUniform ||
+        !c.crossTarget.empty()) {
       continue;
     }
     const bool pitchOk = (static_cast<uint64_t>(c.ny) * c.S) % 2 == 0;
@@ -793,6 +855,40 @@ void Sim::build(const smeb200_problem &p) {
         }
       }
     }
+    for (int k = 0; k < 3; ++k) {
+      h2[k] = p.voxel_size[k] * p.voxel_size[k];
+    }
+    c.nonUniform = pc.diffusion_array != nullptr;
+    if (pc.n_cross_diffusion > 0) {
+      if (pc.diffusion_raw == nullptr || pc.cross_target == nullptr ||
+          pc.cross_source == nullptr || pc.cross_expressions == nullptr) {
+        throw Error("smeb200: cross-diffusion terms need targets, sources, "
+                    "expressions and diffusion_raw");
+      }
+      if (pc.n_cross_diffusion > 64) {
+        throw Error("smeb200: at most 64 cross-diffusion terms per "
+                    "compartment");
+      }
+      for (uint32_t k = 0; k < pc.n_cross_diffusion; ++k) {
+        if (pc.cross_target[k] >= c.SP || pc.cross_source[k] >= c.SP) {
+          throw Error("smeb200: cross-diffusion species index out of range "
+                      "in '" + c.id + "'");
+        }
+        c.crossTarget.push_back(pc.cross_target[k]);
+        c.crossSource.push_back(pc.cross_source[k]);
+      }
+      c.diffusionRaw.assign(pc.diffusion_raw, pc.diffusion_raw + c.SP);
+      anyCross = true;
+    }
+    if ((c.nonUniform || !c.crossTarget.empty()) &&
+        !(h2[0] > 0.0 && h2[1] > 0.0 && h2[2] > 0.0)) {
+      throw Error("smeb200: voxel_size is required with non-uniform or "
+                  "cross-diffusion");
+    }
+    if ((c.nonUniform || !c.crossTarget.empty()) && p.n_ranks > 1) {
+      throw Error("smeb200: non-uniform and cross-diffusion are not supported "
+                  "in a z-slab decomposed simulation");
+    }
     for (uint32_t s = 0; s < c.S; ++s) {
       c.speciesNames.emplace_back(
           pc.species_names != nullptr && pc.species_names[s] != nullptr
@@ -801,8 +897,18 @@ void Sim::build(const smeb200_problem &p) {
       // forwards-Euler stability bound, pixelsim_common.hpp:33-37 and
       // pixelsim_impl.cpp:249-255 (D * invStorage per direction)
       const double is = c.invStorage.empty() ? 1.0 : c.invStorage[s];
-      const double sum =
-          c.D[3 * s] * is + c.D[3 * s + 1] * is + c.D[3 * s + 2] * is;
+      double sum = c.D[3 * s] * is + c.D[3 * s + 1] * is + c.D[3 * s + 2] * is;
+      if (c.nonUniform) {
+        // per-voxel constants: bound from the species' maximum
+        // (pixelsim_impl.cpp:257-290)
+        double maxD = 0.0;
+        for (uint64_t i = 0; i < c.n; ++i) {
+          const double d = pc.diffusion_array[i * c.S + s];
+          maxD = i == 0 ? d : std::max(maxD, d);
+        }
+        sum = maxD * is / h2[0] + maxD * is / h2[1] + maxD * is / h2[2];
+      }
+      c.maxStable = std::min(c.maxStable, 1.0 / (2.0 * sum));
       maxStableTimestep = std::min(maxStableTimestep, 1.0 / (2.0 * sum));
     }
   }
@@ -856,6 +962,9 @@ void Sim::build(const smeb200_problem &p) {
       }
       addName(kNsFinishKernel);
     }
+    if (!comps[ci].crossTarget.empty()) {
+      addName("smeb_xd_max<Reac" + std::to_string(ci) + ">");
+    }
   }
   mainModule = compile(names);
   if (compileOnly) {
@@ -887,6 +996,19 @@ void Sim::build(const smeb200_problem &p) {
     for (const auto &sd : plan) {
       c.kStage.push_back(lookup(mainModule, ci, sd.flags()));
     }
+    if (c.nonUniform) {
+      c.dDarr = devAlloc<double>(nv, "allocate diffusion constant array");
+      check(cudaMemcpyAsync(c.dDarr, p.compartments[ci].diffusion_array,
+                            nv * sizeof(double), cudaMemcpyHostToDevice,
+                            stream),
+            "upload diffusion constant array");
+    }
+    if (!c.crossTarget.empty()) {
+      c.dXdMax = devAlloc<unsigned long long>(c.crossTarget.size(),
+                                              "allocate cross-diffusion maxima");
+      c.kXdMax =
+          mainModule.fn.at("smeb_xd_max<Reac" + std::to_string(ci) + ">");
+    }
     if (!c.nonSpatial.empty()) {
       c.kSumNs = lookup(mainModule, ci, F_SUM_NS);
       const std::size_t nns = c.nonSpatial.size();
@@ -916,6 +1038,14 @@ void Sim::build(const smeb200_problem &p) {
   check(cudaMallocHost(reinterpret_cast<void **>(&hErr), 16),
         "allocate pinned error mirror");
   check(cudaStreamSynchronize(stream), "initial upload");
+  if (anyCross) {
+    check(cudaMallocHost(reinterpret_cast<void **>(&hXdMax),
+                         64 * sizeof(unsigned long long)),
+          "allocate pinned cross-diffusion maxima");
+    // SimCompartment ctor: coefficients of the initial state and their bound
+    // (pixelsim_impl.cpp:425-428)
+    updateCrossDiffusionMaxStableTimestep();
+  }
   if (comm) {
     connectSlabs();
   }
@@ -1097,12 +1227,15 @@ Sim::~Sim() {
     cudaFree(c.dEnt);
     cudaFree(c.scratch);
     cudaFree(c.dNsAv);
+    cudaFree(c.dDarr);
+    cudaFree(c.dXdMax);
     cudaFree(c.dNsPartial);
     cudaFreeHost(c.hostConc);
   }
   cudaFree(dFluxLen);
   cudaFree(dErr);
   cudaFreeHost(hErr);
+  cudaFreeHost(hXdMax);
   if (runEv0 != nullptr) {
     cudaEventDestroy(runEv0);
     cudaEventDestroy(runEv1);
@@ -1170,6 +1303,9 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     std::copy(params.begin(), params.end(), a.D + 3 * c.S);
     a.nsAv = c.dNsAv;
     a.nsPartial = c.dNsPartial;
+    a.darr = c.dDarr;
+    a.xdMax = c.dXdMax;
+    std::copy(h2, h2 + 3, a.h2);
     if (!c.nonSpatial.empty()) {
       // SimCompartment::spatiallyAverageDcdt (pixelsim_impl.cpp:150-163): the
       // averages need dc/dt of every voxel before any voxel can be updated
@@ -1335,7 +1471,75 @@ void Sim::readError(double &eabs, double &erel) {
 }
 
 // ---- controller: pixelsim.cpp:122-140, 207-270, 423-471 ----------------------
+// RK101 with cross-diffusion: the forward-Euler bound depends on the state
+// (calculateDcdt refreshes it before the step is taken, pixelsim.cpp:122-129,
+// pixelsim_impl.cpp:506-543): one max-reduction kernel per compartment with
+// cross-diffusion terms, one small D2H, then the reference's formula on the
+// host.
+void Sim::updateCrossDiffusionMaxStableTimestep() {
+  const auto &drv = DriverApi::get();
+  std::size_t off = 0;
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    auto &c = comps[ci];
+    if (c.crossTarget.empty() || c.n == 0) {
+      continue;
+    }
+    const std::size_t nx = c.crossTarget.size();
+    check(cudaMemsetAsync(c.dXdMax, 0, nx * sizeof(unsigned long long), stream),
+          "clear cross-diffusion maxima");
+    StageArgsHost a{};
+    a.cin = c.buf[c.role[CUR]];
+    a.n = static_cast<uint32_t>(c.n);
+    a.xdMax = c.dXdMax;
+    std::copy(params.begin(), params.end(), a.D + 3 * c.S);
+    const unsigned grid = static_cast<unsigned>(std::max<uint64_t>(
+        1, std::min<uint64_t>((c.n + BLOCK - 1) / BLOCK,
+                              static_cast<uint64_t>(smCount) * 8u)));
+    void *kparams[] = {&a};
+    check(drv.LaunchKernel(c.kXdMax, grid, 1, 1, BLOCK, 1, 1, 0, stream,
+                           kparams, nullptr),
+          "launch cross-diffusion maximum kernel");
+    ++launchCount;
+    check(cudaMemcpyAsync(hXdMax + off, c.dXdMax,
+                          nx * sizeof(unsigned long long),
+                          cudaMemcpyDeviceToHost, stream),
+          "download cross-diffusion maxima");
+    off += nx;
+  }
+  check(cudaStreamSynchronize(stream), "cross-diffusion maxima");
+  maxStableTimestep = std::numeric_limits<double>::max();
+  off = 0;
+  for (auto &c : comps) {
+    if (!c.crossTarget.empty() && c.n > 0) {
+      auto maxEffectiveDiffusion = c.diffusionRaw;
+      for (std::size_t t = 0; t < c.crossTarget.size(); ++t) {
+        double m = 0.0;
+        std::memcpy(&m, hXdMax + off + t, sizeof(double));
+        maxEffectiveDiffusion[c.crossTarget[t]] += m;
+      }
+      off += c.crossTarget.size();
+      c.maxStable = std::numeric_limits<double>::max();
+      for (uint32_t s = 0; s < c.SP; ++s) {
+        const double is = c.invStorage.empty() ? 1.0 : c.invStorage[s];
+        const double d = maxEffectiveDiffusion[s];
+        if (is == 0.0 || d <= 0.0) {
+          continue;
+        }
+        c.maxStable = std::min(
+            c.maxStable,
+            1.0 / (2.0 * (d * is / h2[0] + d * is / h2[1] + d * is / h2[2])));
+      }
+    }
+    if (c.S > 0) {
+      maxStableTimestep = std::min(maxStableTimestep, c.maxStable);
+    }
+  }
+}
+
 double Sim::doRK101(double dt) {
+  if (anyCross) {
+    updateCrossDiffusionMaxStableTimestep();
+  }
   dt = std::min(dt, maxStableTimestep);
   doStep(dt);
   rotateAfterAccept();

@@ -38,6 +38,9 @@ struct StageArgsHost {
   unsigned long long *err;
   const double *nsAv;
   double *nsPartial;
+  const double *darr;
+  unsigned long long *xdMax;
+  double h2[3];
   uint32_t n;
   uint32_t nx, ny, nz;
   uint32_t z_begin, z_end;
@@ -101,6 +104,13 @@ struct CompartmentState {
   double *dNsPartial{nullptr};       // block sums of the pre-pass
   uint32_t nsPartialBlocks{0};       // capacity of dNsPartial in blocks
   StageKernels kSumNs;               // pre-pass kernels (F_SUM_NS)
+  double *dDarr{nullptr};            // [n][S] per-voxel diffusion constants
+  bool nonUniform{false};
+  std::vector<uint32_t> crossTarget, crossSource; // cross-diffusion terms
+  std::vector<double> diffusionRaw;  // maxPrimaryDiagonalDiffusion
+  unsigned long long *dXdMax{nullptr};
+  CUfunction kXdMax{nullptr};
+  double maxStable{std::numeric_limits<double>::max()};
   std::vector<int32_t> voxels;
   int nbuf{0};
   double *buf[4]{nullptr, nullptr, nullptr, nullptr};
@@ -212,6 +222,10 @@ private:
   void setupSlabs(const smeb200_problem &p);
   void connectSlabs();
   void haloExchange(int coutBuf);
+  void updateCrossDiffusionMaxStableTimestep();
+  double h2[3]{1.0, 1.0, 1.0}; // voxel width^2, height^2, depth^2
+  bool anyCross{false};
+  unsigned long long *hXdMax{nullptr}; // pinned
 
   // z-slab decomposition (n_ranks > 1): communicator, neighbours' buffers
   // (CUDA IPC), device addresses of the stream-ordered handshake flags

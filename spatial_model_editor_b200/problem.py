@@ -47,6 +47,12 @@ class CCompartment(C.Structure):
         ("n_non_spatial", C.c_uint32),
         ("non_spatial", C.POINTER(C.c_uint32)),
         ("inv_storage", C.POINTER(C.c_double)),
+        ("diffusion_array", C.POINTER(C.c_double)),
+        ("n_cross_diffusion", C.c_uint32),
+        ("cross_target", C.POINTER(C.c_uint32)),
+        ("cross_source", C.POINTER(C.c_uint32)),
+        ("cross_expressions", C.POINTER(C.c_char_p)),
+        ("diffusion_raw", C.POINTER(C.c_double)),
     ]
 
 
@@ -84,6 +90,7 @@ class CProblem(C.Structure):
         ("n_params", C.c_uint32),
         ("comm_name", C.c_char_p),
         ("params", C.POINTER(C.c_double)),
+        ("voxel_size", C.c_double * 3),
         ("reserved", C.c_uint32 * 2),
     ]
 
@@ -103,6 +110,9 @@ class Compartment:
     n_primary: Optional[int] = None       # model species; the rest is t,x,y,z padding
     non_spatial: Sequence[int] = ()       # species whose dc/dt is spatially averaged
     inv_storage: Optional[np.ndarray] = None  # [S] 1/storage, None = unit storage
+    diffusion_array: Optional[np.ndarray] = None  # [N, S] raw D per voxel (non-uniform)
+    cross_diffusion: Sequence[Tuple[int, int, str]] = ()  # (target, source, expression)
+    diffusion_raw: Optional[np.ndarray] = None    # [S] raw D (needed with cross-diffusion)
 
     @property
     def n_primary_species(self) -> int:
@@ -145,6 +155,7 @@ class Problem:
     n_ranks: int = 1
     comm_name: Optional[str] = None
     params: Sequence[float] = ()          # values of sme_param_k (runtime parameters)
+    voxel_size: Tuple[float, float, float] = (1.0, 1.0, 1.0)
 
     def evals_per_step(self) -> int:
         """voxel*species RHS evaluations in one RK step (the bench metric);
@@ -202,6 +213,18 @@ class Problem:
                                  C.c_uint32) if len(c.non_spatial) else None
             cc.inv_storage = arr(np.asarray(c.inv_storage, dtype=np.float64).reshape(
                 c.n_species), np.float64, C.c_double) if c.inv_storage is not None else None
+            if c.diffusion_array is not None:
+                assert c.diffusion_array.shape == (c.n_voxels, c.n_species)
+                cc.diffusion_array = arr(c.diffusion_array, np.float64, C.c_double)
+            cc.n_cross_diffusion = len(c.cross_diffusion)
+            if len(c.cross_diffusion):
+                cc.cross_target = arr([t for t, _, _ in c.cross_diffusion], np.uint32, C.c_uint32)
+                cc.cross_source = arr([s_ for _, s_, _ in c.cross_diffusion], np.uint32,
+                                      C.c_uint32)
+                cc.cross_expressions = strs([e for _, _, e in c.cross_diffusion])
+            if c.diffusion_raw is not None:
+                cc.diffusion_raw = arr(np.asarray(c.diffusion_raw, dtype=np.float64).reshape(
+                    c.n_species), np.float64, C.c_double)
         membs = (CMembrane * max(len(self.membranes), 1))()
         for i, m in enumerate(self.membranes):
             cm = membs[i]
@@ -232,6 +255,7 @@ class Problem:
         p.n_ranks = self.n_ranks
         p.comm_name = self.comm_name.encode() if self.comm_name else None
         p.kernel_variant = self.kernel_variant
+        p.voxel_size[0], p.voxel_size[1], p.voxel_size[2] = self.voxel_size
         p.n_params = len(self.params)
         p.params = arr(np.asarray(self.params, dtype=np.float64), np.float64, C.c_double) \
             if len(self.params) else None

@@ -204,3 +204,104 @@ def test_non_spatial_species_are_averaged():
     s2.run(0.5)
     c = s2.getConcentrations(1)
     assert np.ptp(c[:, 0]) <= 1e-12 * abs(c[0, 0])
+
+
+# ---- non-uniform diffusion and cross-diffusion (SURVEY.md section 8(a) rows a7', a13) ----
+def diffusion_disc(integrator=smeb.RK101):
+    p, meta, _ = load_golden("single-compartment-diffusion", integrator=integrator)
+    p.voxel_size = tuple(meta["voxel_size"])
+    return p, meta
+
+
+def with_array_diffusion(p, meta, scale=None):
+    """Field::setDiffusionConstant(array): per-voxel constants, here the uniform
+    value at every voxel (optionally modulated)"""
+    c = p.compartments[0]
+    D = np.array(meta["compartments"][0]["diffusion_constants"])
+    arr = np.repeat(D[None, :], c.n_voxels, axis=0)
+    if scale is not None:
+        arr = arr * scale[:, None]
+    c.diffusion_array = np.ascontiguousarray(arr)
+    return p
+
+
+def test_k4_uniform_matches_array_diffusion():
+    """pixelsim_t.cpp:21-49: the uniform stencil and the face-averaged array stencil
+    agree to 1e-14 after one RK101 run of 1e-3 (first step 1e-3, maxTimestep 1e-3)"""
+    pu, meta = diffusion_disc()
+    pa, _ = diffusion_disc()
+    with_array_diffusion(pa, meta)
+    for p in (pu, pa):
+        p.max_timestep = 1e-3
+    su, sa = OraclePixelSim(pu), OraclePixelSim(pa)
+    assert su.run(1e-3) == sa.run(1e-3) == 1
+    cu, ca = su.getConcentrations(0), sa.getConcentrations(0)
+    assert np.all(np.abs(cu - ca) <= 1e-14 * np.maximum(np.abs(cu), np.abs(ca)))
+    assert math.isclose(su.maxStableTimestep, sa.maxStableTimestep, rel_tol=1e-15)
+
+
+def test_array_diffusion_zero_region_blocks_flux():
+    """simulate_t.cpp:1304-1398 restated: with D = 0 in the left half the field there
+    does not move (the face average with a D = 1 neighbour is 1/2, so only the
+    interface column changes); the total amount is conserved"""
+    p, meta = diffusion_disc(smeb.RK212)
+    c = p.compartments[0]
+    left = c.voxels[:, 0] < 50
+    with_array_diffusion(p, meta, scale=np.where(left, 0.0, 1.0))
+    p.max_err_abs, p.max_err_rel = smeb.DBL_MAX, 0.001
+    total0 = c.conc0.sum(axis=0)
+    sim = OraclePixelSim(p)
+    sim.run(5.0)
+    out = sim.getConcentrations(0)
+    interior = c.voxels[:, 0] + 2 < 50
+    assert np.max(np.abs(out[interior] - c.conc0[interior])) < 1e-8
+    assert np.max(np.abs(out[~left] - c.conc0[~left])) > 1e-3
+    assert np.all(np.abs(out.sum(axis=0) - total0) <= 1e-9 * total0)
+
+
+def cross_diffusion_disc(integrator=None):
+    """simulate_t.cpp:2780-2790: D_fast = 0, cross-diffusion constant 1 from slow"""
+    p, meta, _ = load_golden("single-compartment-diffusion", integrator=integrator)
+    p.voxel_size = tuple(meta["voxel_size"])
+    c = p.compartments[0]
+    c.diffusion = c.diffusion.copy()
+    c.diffusion[1, :] = 0.0
+    c.diffusion_raw = np.array([meta["compartments"][0]["diffusion_constants"][0], 0.0])
+    c.cross_diffusion = [(1, 0, "1.0")]
+    return p, meta
+
+
+def test_cross_diffusion_equivalent_to_diffusion():
+    """simulate_t.cpp:2780-2816: "fast" (D = 0, cross-diffusion 1 from "slow", D_slow =
+    1, equal initial fields) follows "slow": average |slow - fast| < 1e-11, average
+    relative difference < 1e-7 at t = 0 and t = 5"""
+    p, meta = cross_diffusion_disc()
+    assert meta["compartments"][0]["diffusion_constants"][0] == 1.0
+    sim = OraclePixelSim(p)
+    for t in (0.0, 5.0):
+        if t > 0:
+            sim.run(t)
+        c = sim.getConcentrations(0)
+        d = np.abs(c[:, 0] - c[:, 1])
+        assert d.mean() < 1e-11
+        assert (2.0 * d / (np.abs(c[:, 0] + c[:, 1]) + 1e-15)).mean() < 1e-7
+    assert sim.errorMessage() == ""
+
+
+def test_cross_diffusion_dynamic_stability_bound():
+    """updateCrossDiffusionMaxStableTimestep (pixelsim_impl.cpp:506-543): bound from
+    max(D_ii) + sum of max |D_ij| per target; with a state-dependent coefficient it
+    follows the state"""
+    p, meta = cross_diffusion_disc(smeb.RK101)
+    sim = OraclePixelSim(p)
+    # slow: D = 1; fast: 0 + |1| -> 1 / (2 * (1 + 1)) in 2-D unit voxels, z term included
+    assert math.isclose(sim.maxStableTimestep, 1.0 / (2.0 * 3.0), rel_tol=1e-15)
+    p2, _ = cross_diffusion_disc(smeb.RK101)
+    p2.compartments[0].cross_diffusion = [(1, 0, "(4.0 * sme_var_0)")]
+    s2 = OraclePixelSim(p2)
+    cmax = p2.compartments[0].conc0[:, 0].max()
+    assert math.isclose(s2.maxStableTimestep, 1.0 / (2.0 * 3.0 * 4.0 * cmax), rel_tol=1e-14)
+    s2.run(0.5)  # RK101 steps are capped by the bound of the current state
+    cmax2 = s2.getConcentrations(0)[:, 0].max()
+    assert cmax2 < cmax
+    assert s2.maxStableTimestep > 1.0 / (2.0 * 3.0 * 4.0 * cmax)

@@ -173,3 +173,109 @@ def test_zero_storage_is_rejected():
     gpu = smeb.PixelSim(p)
     assert "zero storage" in gpu.errorMessage()
     assert gpu.run(1.0) == 0
+
+
+# ---- non-uniform diffusion and cross-diffusion ------------------------------------
+def nonuniform_problem(integ, box, seed=5):
+    """voxel list (the example disc) or full box with smoothly varying per-voxel
+    diffusion constants"""
+    rng = np.random.default_rng(seed)
+    if box is None:
+        p, meta, _ = load_golden("single-compartment-diffusion", integrator=integ)
+        p.voxel_size = tuple(meta["voxel_size"])
+        D = np.array(meta["compartments"][0]["diffusion_constants"])
+    else:
+        p = M.box_problem(M.GRAY_SCOTT, *box, integrator=integ, voxel_size=(1.0, 1.5, 2.0))
+        p.voxel_size = (1.0, 1.5, 2.0)
+        D = np.array(M.GRAY_SCOTT["D"])
+    c = p.compartments[0]
+    c.diffusion_array = np.ascontiguousarray(
+        D[None, :] * rng.uniform(0.0, 1.5, size=(c.n_voxels, c.n_species)))
+    return p
+
+
+@pytest.mark.parametrize("box", [None, (24, 40, 1), (16, 30, 5)])
+@pytest.mark.parametrize("integ", INTEGRATORS)
+def test_non_uniform_diffusion(box, integ):
+    p = nonuniform_problem(integ, box)
+    p.max_err_abs = p.max_err_rel = smeb.DBL_MAX
+    p.max_timestep = 0.02
+    gpu, cpu = both(p)
+    assert abs(gpu.maxStableTimestep - cpu.maxStableTimestep) <= 1e-15 * cpu.maxStableTimestep
+    assert gpu.run(1e-7) == cpu.run(1e-7) == 1
+    compare(p, gpu, cpu, "non-uniform first step")
+    ng, nc = gpu.run(0.4), cpu.run(0.4)
+    assert ng == nc and ng >= 20
+    compare(p, gpu, cpu, "non-uniform run")
+
+
+def cross_problem(integ, box, expr="(0.3 + 0.5 * sme_var_0)"):
+    if box is None:
+        p, meta, _ = load_golden("single-compartment-diffusion", integrator=integ)
+        p.voxel_size = tuple(meta["voxel_size"])
+        raw = np.array(meta["compartments"][0]["diffusion_constants"])
+    else:
+        p = M.box_problem(M.GRAY_SCOTT, *box, integrator=integ, voxel_size=(1.0, 1.5, 2.0))
+        p.voxel_size = (1.0, 1.5, 2.0)
+        raw = np.array(M.GRAY_SCOTT["D"])
+    c = p.compartments[0]
+    c.diffusion_raw = raw
+    c.cross_diffusion = [(1, 0, expr), (0, 1, "(0.05 * sme_var_1)")]
+    return p
+
+
+@pytest.mark.parametrize("box", [None, (24, 40, 1), (16, 30, 5)])
+@pytest.mark.parametrize("integ", INTEGRATORS)
+def test_cross_diffusion(box, integ):
+    p = cross_problem(integ, box)
+    p.max_err_abs = p.max_err_rel = smeb.DBL_MAX
+    p.max_timestep = 0.01
+    gpu, cpu = both(p)
+    # the bound of the initial state (SimCompartment ctor)
+    assert abs(gpu.maxStableTimestep - cpu.maxStableTimestep) <= 1e-15 * cpu.maxStableTimestep
+    assert gpu.run(1e-7) == cpu.run(1e-7) == 1
+    compare(p, gpu, cpu, "cross-diffusion first step")
+    ng, nc = gpu.run(0.2), cpu.run(0.2)
+    assert ng == nc and ng >= 20
+    compare(p, gpu, cpu, "cross-diffusion run")
+
+
+def test_cross_diffusion_rk101_follows_dynamic_bound():
+    """RK101 steps are capped by the forward-Euler bound of the CURRENT state
+    (pixelsim.cpp:122-129): same step counts and states as the CPU solver when
+    the bound, not maxTimestep, decides the step"""
+    p = cross_problem(smeb.RK101, None, expr="(6.0 * sme_var_0)")
+    p.max_err_abs = p.max_err_rel = smeb.DBL_MAX
+    gpu, cpu = both(p)
+    ng, nc = gpu.run(2.0), cpu.run(2.0)
+    assert ng == nc and ng > 20
+    assert abs(gpu.maxStableTimestep - cpu.maxStableTimestep) <= 1e-14 * cpu.maxStableTimestep
+    compare(p, gpu, cpu, "cross-diffusion RK101 dynamic bound", rel=1e-11)
+
+
+def test_cross_diffusion_known_answer_on_gpu():
+    """simulate_t.cpp:2780-2816 through the CUDA path"""
+    p, meta, _ = load_golden("single-compartment-diffusion")
+    p.voxel_size = tuple(meta["voxel_size"])
+    c = p.compartments[0]
+    c.diffusion = c.diffusion.copy()
+    c.diffusion[1, :] = 0.0
+    c.diffusion_raw = np.array([1.0, 0.0])
+    c.cross_diffusion = [(1, 0, "1.0")]
+    p.device = 0
+    gpu = smeb.PixelSim(p)
+    gpu.run(5.0)
+    assert gpu.errorMessage() == ""
+    out = gpu.getConcentrations(0)
+    d = np.abs(out[:, 0] - out[:, 1])
+    assert d.mean() < 1e-11
+    assert (2.0 * d / (np.abs(out[:, 0] + out[:, 1]) + 1e-15)).mean() < 1e-7
+
+
+@pytest.mark.parametrize("integ", [smeb.RK212, smeb.RK435])
+def test_diffusion_variants_adaptive(integ):
+    for p in (nonuniform_problem(integ, None), cross_problem(integ, (16, 30, 5))):
+        gpu, cpu = both(p)
+        ng, nc = gpu.run(0.5), cpu.run(0.5)
+        assert ng == nc and gpu.discardedSteps == cpu.discardedSteps
+        compare(p, gpu, cpu, "diffusion variants adaptive", rel=1e-9)
