@@ -46,15 +46,16 @@ private:
   mutable std::vector<std::vector<double>> conc;
   mutable std::vector<std::vector<double>> dcdt;
 
-  static std::vector<std::string>
-  cudaExpressions(const std::vector<std::string> &variables,
-                  const std::vector<std::string> &expressions) {
+  static std::vector<std::string> cudaExpressions(
+      const std::vector<std::string> &variables,
+      const std::vector<std::string> &expressions,
+      const std::vector<std::pair<std::string, double>> &constants = {}) {
     // cudapixelsim.cpp:108-136
     std::vector<std::string> safe;
     for (std::size_t i = 0; i < variables.size(); ++i) {
       safe.push_back("sme_var_" + std::to_string(i));
     }
-    common::Symbolic symbolic{expressions, variables};
+    common::Symbolic symbolic{expressions, variables, constants};
     if (!symbolic.isValid()) {
       throw std::runtime_error("Failed to convert reaction expression to CUDA "
                                "code: " +
@@ -113,15 +114,53 @@ public:
       // and non-uniform diffusion.  Time / space dependent reactions,
       // non-spatial species and non-unit storage are described to the library
       // the way PixelSim handles them (pixelsim.cpp:282-322).
-      if (hasAnyCrossDiffusion(doc, compartmentSpeciesIds)) {
-        p.unsupported |= SMEB200_HAS_CROSS_DIFFUSION;
-      }
       const auto &coords{doc.getParameters().getSpatialCoordinates()};
-      const bool timeDependent{doc.getReactions().dependOnVariable("time")};
+      // pixelsim.cpp:286-322: reactions or cross-diffusion coefficients that
+      // use time / x, y, z
+      const auto crossDependsOn = [&](const std::string &variableId) {
+        for (const auto &speciesIds : compartmentSpeciesIds) {
+          for (const auto &target : speciesIds) {
+            for (const auto &source : speciesIds) {
+              if (target == source) {
+                continue;
+              }
+              const auto expression{doc.getSpecies().getCrossDiffusionConstant(
+                  target.c_str(), source.c_str())};
+              if (!expression.isEmpty() &&
+                  common::SimpleSymbolic::contains(expression.toStdString(),
+                                                   variableId)) {
+                return true;
+              }
+            }
+          }
+        }
+        return false;
+      };
+      const bool timeDependent{doc.getReactions().dependOnVariable("time") ||
+                               crossDependsOn("time")};
       const bool spaceDependent{
           doc.getReactions().dependOnVariable(coords.x.id.c_str()) ||
           doc.getReactions().dependOnVariable(coords.y.id.c_str()) ||
-          doc.getReactions().dependOnVariable(coords.z.id.c_str())};
+          doc.getReactions().dependOnVariable(coords.z.id.c_str()) ||
+          crossDependsOn(coords.x.id) || crossDependsOn(coords.y.id) ||
+          crossDependsOn(coords.z.id)};
+      // pixelsim.cpp:323-336: one non-uniform species switches every
+      // compartment to the per-voxel (array) diffusion operator
+      bool allUniformDiffusion{true};
+      for (const auto &speciesIds : compartmentSpeciesIds) {
+        for (const auto &speciesId : speciesIds) {
+          if (doc.getSpecies().getIsConstant(speciesId.c_str())) {
+            continue;
+          }
+          const auto *field{doc.getSpecies().getField(speciesId.c_str())};
+          if (field == nullptr || !field->getIsUniformDiffusionConstant()) {
+            allUniformDiffusion = false;
+          }
+        }
+      }
+      p.voxel_size[0] = doc.getGeometry().getVoxelSize().width();
+      p.voxel_size[1] = doc.getGeometry().getVoxelSize().height();
+      p.voxel_size[2] = doc.getGeometry().getVoxelSize().depth();
       nExtraVars = (timeDependent ? 1 : 0) + (spaceDependent ? 3 : 0);
       const auto origin{doc.getGeometry().getPhysicalOrigin()};
       const auto voxelSize{doc.getGeometry().getVoxelSize()};
@@ -135,6 +174,12 @@ public:
       std::vector<std::vector<std::int32_t>> voxels(nCompartments);
       std::vector<std::vector<double>> diffusion(nCompartments);
       std::vector<std::vector<double>> invStorage(nCompartments);
+      std::vector<std::vector<double>> diffusionArray(nCompartments);
+      std::vector<std::vector<double>> diffusionRaw(nCompartments);
+      std::vector<std::vector<std::uint32_t>> crossTarget(nCompartments);
+      std::vector<std::vector<std::uint32_t>> crossSource(nCompartments);
+      std::vector<std::vector<std::string>> crossExprs(nCompartments);
+      std::vector<std::vector<const char *>> crossExprPtrs(nCompartments);
       std::vector<std::vector<std::uint32_t>> nonSpatial(nCompartments);
       std::vector<std::vector<std::string>> exprs(nCompartments);
       std::vector<std::vector<const char *>> exprPtrs(nCompartments);
@@ -197,9 +242,6 @@ public:
           }
           const bool isConstant{
               doc.getSpecies().getIsConstant(speciesId.c_str())};
-          if (!isConstant && !field->getIsUniformDiffusionConstant()) {
-            p.unsupported |= SMEB200_HAS_NON_UNIFORM_DIFFUSION;
-          }
           // pixelsim_impl.cpp:214-232; storage 0 (algebraic species) is
           // passed as 0 and refused by the library
           const double storage{
@@ -213,6 +255,11 @@ public:
           fields.push_back(field);
           const auto &d{field->getDiffusionConstant()};
           const double dc{isConstant || d.empty() ? 0.0 : d.front()};
+          // maxPrimaryDiagonalDiffusion (pixelsim_impl.cpp:256,291)
+          diffusionRaw[ci].push_back(
+              allUniformDiffusion ? dc
+                                  : (isConstant || d.empty() ? 0.0
+                                                             : common::max(d)));
           diffusion[ci].push_back(dc / dx2);
           diffusion[ci].push_back(dc / dy2);
           diffusion[ci].push_back(dc / dz2);
@@ -230,6 +277,23 @@ public:
         c.diffusion = diffusion[ci].data();
         c.species_names = namePtrs[ci].data();
         c.inv_storage = invStorage[ci].data();
+        c.diffusion_raw = diffusionRaw[ci].data();
+        if (!allUniformDiffusion) {
+          // per-voxel constants, species-interleaved like the concentrations
+          // (pixelsim_impl.cpp:257-266)
+          diffusionArray[ci].assign(n * S, 0.0);
+          for (std::size_t is = 0; is < nPrimary; ++is) {
+            const auto &d{fields[is]->getDiffusionConstant()};
+            if (doc.getSpecies().getIsConstant(speciesIds[is].c_str()) ||
+                d.empty()) {
+              continue;
+            }
+            for (std::size_t ix = 0; ix < n; ++ix) {
+              diffusionArray[ci][ix * S + is] = d[ix];
+            }
+          }
+          c.diffusion_array = diffusionArray[ci].data();
+        }
         c.n_non_spatial = static_cast<std::uint32_t>(nonSpatial[ci].size());
         c.non_spatial = nonSpatial[ci].empty() ? nullptr : nonSpatial[ci].data();
         conc[ci].resize(n * S);
@@ -268,6 +332,51 @@ public:
           exprPtrs[ci].push_back(e.c_str());
         }
         c.expressions = exprPtrs[ci].data();
+        // sparse cross-diffusion terms D_ij grad c_j, i != j
+        // (pixelsim_impl.cpp:350-389)
+        std::vector<std::string> crossDiffusionExpressions;
+        for (std::size_t iTarget = 0; iTarget < nPrimary; ++iTarget) {
+          const QString targetId{speciesIds[iTarget].c_str()};
+          if (doc.getSpecies().getIsConstant(targetId)) {
+            continue;
+          }
+          for (std::size_t iSource = 0; iSource < nPrimary; ++iSource) {
+            if (iSource == iTarget) {
+              continue;
+            }
+            const auto expression{doc.getSpecies().getCrossDiffusionConstant(
+                targetId, speciesIds[iSource].c_str())};
+            if (expression.isEmpty()) {
+              continue;
+            }
+            crossDiffusionExpressions.push_back(
+                doc.inlineExpr(expression.toStdString()));
+            crossTarget[ci].push_back(static_cast<std::uint32_t>(iTarget));
+            crossSource[ci].push_back(static_cast<std::uint32_t>(iSource));
+          }
+        }
+        if (!crossDiffusionExpressions.empty()) {
+          std::vector<std::pair<std::string, double>> constants;
+          for (const auto &constant :
+               doc.getParameters().getGlobalConstants()) {
+            double value{constant.value};
+            if (auto it{substitutions.find(constant.id)};
+                it != substitutions.end()) {
+              value = it->second;
+            }
+            constants.emplace_back(constant.id, value);
+          }
+          crossExprs[ci] = cudaExpressions(reacExpr.variables,
+                                           crossDiffusionExpressions, constants);
+          for (const auto &e : crossExprs[ci]) {
+            crossExprPtrs[ci].push_back(e.c_str());
+          }
+          c.n_cross_diffusion =
+              static_cast<std::uint32_t>(crossExprs[ci].size());
+          c.cross_target = crossTarget[ci].data();
+          c.cross_source = crossSource[ci].data();
+          c.cross_expressions = crossExprPtrs[ci].data();
+        }
       }
       // restart concentrations (pixelsim.cpp:399-406)
       const auto &data{doc.getSimulationData()};

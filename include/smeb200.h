@@ -127,6 +127,17 @@ typedef struct smeb200_compartment {
   const uint32_t *cross_source;
   const char *const *cross_expressions;
   const double *diffusion_raw;
+  /* z-slab decomposition of a VOXEL-LIST compartment (n_ranks > 1, nn != NULL).
+   * The voxel order is z-major, so the voxels of the planes a rank owns are a
+   * contiguous range of the list; the local list is
+   *   [slab_ghost_lo voxels of the plane below][owned voxels][slab_ghost_hi
+   *    voxels of the plane above],
+   * nn holds LOCAL indices (rows of ghost voxels are ignored), membrane pairs
+   * hold local indices and list every pair with at least one owned voxel.
+   * slab_first_plane / slab_last_plane = number of owned voxels in the first /
+   * last owned plane: they are what the lower / upper neighbour rank holds as
+   * its slab_ghost_hi / slab_ghost_lo voxels. */
+  uint32_t slab_ghost_lo, slab_ghost_hi, slab_first_plane, slab_last_plane;
 } smeb200_compartment;
 
 /* One geometry::Membrane + SimMembrane (pixelsim_impl.cpp:929-1047). */
@@ -162,10 +173,12 @@ typedef struct smeb200_problem {
   int32_t image_nx, image_ny, image_nz;
   uint32_t unsupported;    /* enum smeb200_unsupported bits */
   int32_t device;          /* CUDA device ordinal; -1 = current device */
-  /* z-slab decomposition of box compartments over `n_ranks` processes on one
-   * node, one GPU each (0/1 = single GPU).  Rank r then describes only ITS
-   * slab: box_nz = owned planes + one ghost plane below (r > 0) + one above
-   * (r < n_ranks-1), conc0 including the ghost planes.  See "multi-GPU". */
+  /* z-slab decomposition over `n_ranks` processes on one node, one GPU each
+   * (0/1 = single GPU).  Rank r then describes only ITS slab.  Box
+   * compartments: box_nz = owned planes + one ghost plane below (r > 0) + one
+   * above (r < n_ranks-1), conc0 including the ghost planes.  Voxel-list
+   * compartments (and membranes between them): see
+   * smeb200_compartment::slab_ghost_lo.  See "multi-GPU". */
   int32_t rank, n_ranks;
   /* kernel variant: 0 = auto (TMA tile-marching kernel for box compartments
    * where the shape allows it), 1 = direct-gather kernels only, 2 = require
@@ -222,7 +235,16 @@ int smeb200_get_dcdt(smeb200_sim *sim, size_t compartment, const double **data,
 /* PixelSim::getLowerOrderConcentration (pixelsim.cpp:486-490) */
 int smeb200_get_lower_order(smeb200_sim *sim, size_t compartment,
                             size_t species, size_t pixel, double *value);
-/* BaseSim::getConcentrationPadding — always 0 on this backend */
+/* Per-species {average, minimum, maximum} of a compartment's current state,
+ * reduced on the device: what Simulation::updateConcentrations computes from
+ * the downloaded state after every image interval (calculateAvgMinMax,
+ * simulate.cpp:272-290; minimum starts at DBL_MAX and maximum at 0 like
+ * sme::simulate::AvgMinMax).  out[3*s .. 3*s+2] for the n_primary_species model
+ * species; n_out must be 3 * n_primary_species. */
+int smeb200_get_avg_min_max(smeb200_sim *sim, size_t compartment, double *out,
+                            size_t n_out);
+/* BaseSim::getConcentrationPadding (pixelsim.cpp:478): number of time / x, y, z
+ * components behind the model species of every voxel */
 size_t smeb200_get_concentration_padding(const smeb200_sim *sim);
 /* restart: overwrite the state of one compartment (SimCompartment::
  * setConcentrations, used with SimulationData, pixelsim.cpp:399-406) */

@@ -108,6 +108,12 @@ int smeb200_get_lower_order(smeb200_sim *sim, size_t compartment,
   });
 }
 
+int smeb200_get_avg_min_max(smeb200_sim *sim, size_t compartment, double *out,
+                            size_t n_out) {
+  return guarded(sim,
+                 [&] { sim->impl.getAvgMinMax(compartment, out, n_out); });
+}
+
 size_t smeb200_get_concentration_padding(const smeb200_sim *s) {
   return s != nullptr ? s->impl.concentrationPadding() : 0;
 }

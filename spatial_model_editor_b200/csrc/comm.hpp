@@ -31,8 +31,12 @@ struct CommRankSlot {
   std::atomic<uint64_t> reduceSeq; // last allreduce epoch this rank published
   double reduceVals[2][4];         // double-buffered by epoch parity
   int device;
-  uint32_t nz[kCommMaxCompartments]; // local planes (incl. ghosts) per compartment
-  int pad_[11];
+  // ghost regions of the local arrays, in doubles, per compartment: the LOW
+  // ghosts start at 0, the HIGH ghosts at ghostHiOff
+  uint64_t ghostHiOff[kCommMaxCompartments];
+  uint64_t ghostLoCnt[kCommMaxCompartments];
+  uint64_t ghostHiCnt[kCommMaxCompartments];
+  int pad_[3];
 };
 
 struct CommSegment {

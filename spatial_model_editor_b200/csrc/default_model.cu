@@ -142,3 +142,5 @@ smeb_stage_tile<Reac2, F2, 8, 32, 4, true>(const __grid_constant__ SmebStageArgs
 template __global__ void
 smeb_stage_box<Reac2, F2>(const __grid_constant__ SmebStageArgs<6>);
 template __global__ void smeb_xd_max<Reac2>(const __grid_constant__ SmebStageArgs<6>);
+template __global__ void smeb_stats<Reac0>(const double *, smeb_u32, smeb_u32, double *);
+template __global__ void smeb_stats<Reac2>(const double *, smeb_u32, smeb_u32, double *);

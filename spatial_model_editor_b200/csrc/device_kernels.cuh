@@ -64,7 +64,8 @@ template <int S> struct SmebStageArgs {
   const double *darr;  // [n][S] per-voxel diffusion constants (R::NUD)
   smeb_u64 *xdMax;     // [R::NX] max |cross-diffusion coefficient| (bit patterns)
   double h2[3];        // voxel width^2, height^2, depth^2 (R::NUD / R::NX)
-  smeb_u32 n;          // voxels in this launch's index space
+  smeb_u32 n;          // voxel list: one past the last voxel updated
+  smeb_u32 v0;         // voxel list: first voxel updated (z-slab ghosts before it)
   smeb_u32 nx, ny, nz; // box dims; voxel = (z*nx + x)*ny + y
   smeb_u32 z_begin, z_end; // planes updated by this launch (ghosts excluded)
   double g1, g2, g3, bdt, delta; // stage coefficients (bdt = beta*dt)
@@ -427,7 +428,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   constexpr int S = R::S;
   constexpr int NX = R::NX > 0 ? R::NX : 1;
   double mx[NX] = {};
-  for (smeb_u32 i = blockIdx.x * SMEB_BLOCK + threadIdx.x; i < a.n;
+  for (smeb_u32 i = a.v0 + blockIdx.x * SMEB_BLOCK + threadIdx.x; i < a.n;
        i += gridDim.x * SMEB_BLOCK) {
     double c[S], k[NX];
     smeb_load_voxel<S>(a.cin, i, c);
@@ -461,7 +462,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   constexpr int S = R::S;
   double eabs = 0.0, erel = 0.0;
   double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
-  for (smeb_u32 i = blockIdx.x * SMEB_BLOCK + threadIdx.x; i < a.n;
+  for (smeb_u32 i = a.v0 + blockIdx.x * SMEB_BLOCK + threadIdx.x; i < a.n;
        i += gridDim.x * SMEB_BLOCK) {
     const uint2 *q = reinterpret_cast<const uint2 *>(a.nn) + (size_t)i * 3;
     const uint2 n0 = q[0], n1 = q[1], n2 = q[2];
@@ -964,6 +965,107 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
     smeb_block_sum<1>(&acc, av + j);
     if (threadIdx.x == 0) {
       av[j] = av[j] / n;
+    }
+    __syncthreads();
+  }
+}
+
+// ---- per-species average / minimum / maximum of the state -------------------------
+// What Simulation::updateConcentrations computes on one CPU thread from the
+// downloaded state after every image interval (calculateAvgMinMax,
+// simulate.cpp:272-290), done where the state lives: block partials
+// [blocks][3*SP] = {sum, min, max} per model species (padding skipped), then one
+// block folds them in a fixed order; min starts at DBL_MAX, max at 0 like
+// sme::simulate::AvgMinMax (simulate_options.hpp:226-238).
+template <class R>
+__global__ void __launch_bounds__(SMEB_BLOCK)
+    smeb_stats(const double *__restrict__ c, smeb_u32 i0, smeb_u32 i1,
+               double *__restrict__ partial) {
+  constexpr int S = R::S, SP = R::SP;
+  double sum[SP], mn[SP], mx[SP];
+#pragma unroll
+  for (int s = 0; s < SP; ++s) {
+    sum[s] = 0.0;
+    mn[s] = 1.7976931348623157e308;
+    mx[s] = 0.0;
+  }
+  // [i0, i1): the owned voxels (z-slab ghosts are skipped)
+  for (smeb_u32 i = i0 + blockIdx.x * SMEB_BLOCK + threadIdx.x; i < i1;
+       i += gridDim.x * SMEB_BLOCK) {
+    double v[S];
+    smeb_load_voxel<S>(c, i, v);
+#pragma unroll
+    for (int s = 0; s < SP; ++s) {
+      sum[s] += v[s];
+      mn[s] = v[s] < mn[s] ? v[s] : mn[s];
+      mx[s] = v[s] > mx[s] ? v[s] : mx[s];
+    }
+  }
+  __shared__ double ss[3][32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int s = 0; s < SP; ++s) {
+    double a = sum[s], b = mn[s], d = mx[s];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      const double b2 = __shfl_xor_sync(0xffffffffu, b, o);
+      const double d2 = __shfl_xor_sync(0xffffffffu, d, o);
+      b = b2 < b ? b2 : b;
+      d = d2 > d ? d2 : d;
+    }
+    if (lane == 0) {
+      ss[0][w] = a;
+      ss[1][w] = b;
+      ss[2][w] = d;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double ta = 0.0, tb = 1.7976931348623157e308, td = 0.0;
+      for (int k = 0; k < SMEB_BLOCK / 32; ++k) {
+        ta += ss[0][k];
+        tb = ss[1][k] < tb ? ss[1][k] : tb;
+        td = ss[2][k] > td ? ss[2][k] : td;
+      }
+      double *dst = partial + ((size_t)blockIdx.x * SP + s) * 3;
+      dst[0] = ta;
+      dst[1] = tb;
+      dst[2] = td;
+    }
+    __syncthreads();
+  }
+}
+
+// out[3*s .. 3*s+2] = {average, min, max} of species s
+__global__ void __launch_bounds__(SMEB_BLOCK)
+    smeb_stats_finish(const double *__restrict__ partial, smeb_u32 nBlocks,
+                      smeb_u32 sp, double nVoxels, double *__restrict__ out) {
+  __shared__ double ss[3][SMEB_BLOCK];
+  for (smeb_u32 s = 0; s < sp; ++s) {
+    double a = 0.0, b = 1.7976931348623157e308, d = 0.0;
+    for (smeb_u32 k = threadIdx.x; k < nBlocks; k += SMEB_BLOCK) {
+      const double *src = partial + ((size_t)k * sp + s) * 3;
+      a += src[0];
+      b = src[1] < b ? src[1] : b;
+      d = src[2] > d ? src[2] : d;
+    }
+    ss[0][threadIdx.x] = a;
+    ss[1][threadIdx.x] = b;
+    ss[2][threadIdx.x] = d;
+    __syncthreads();
+    for (int o = SMEB_BLOCK / 2; o > 0; o >>= 1) {
+      if ((int)threadIdx.x < o) {
+        ss[0][threadIdx.x] += ss[0][threadIdx.x + o];
+        const double b2 = ss[1][threadIdx.x + o], d2 = ss[2][threadIdx.x + o];
+        ss[1][threadIdx.x] = b2 < ss[1][threadIdx.x] ? b2 : ss[1][threadIdx.x];
+        ss[2][threadIdx.x] = d2 > ss[2][threadIdx.x] ? d2 : ss[2][threadIdx.x];
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      out[3 * s] = ss[0][0] / nVoxels;
+      out[3 * s + 1] = ss[1][0];
+      out[3 * s + 2] = ss[2][0];
     }
     __syncthreads();
   }

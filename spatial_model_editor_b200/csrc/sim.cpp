@@ -558,10 +558,14 @@ void Sim::setupMembranes(const smeb200_problem &p,
       for (uint64_t k = 0; k < mb.n_pairs[d]; ++k) {
         const uint32_t ixA = mb.pairs[d][2 * k];
         const uint32_t ixB = mb.pairs[d][2 * k + 1];
-        if (mb.comp_a >= 0 && comps[mb.comp_a].S > 0) {
+        // z-slabs: only owned voxels are updated; a partner may be a ghost
+        auto owned = [this](int32_t ci, uint32_t ix) {
+          return ix >= comps[ci].ownedBegin() && ix < comps[ci].ownedEnd();
+        };
+        if (mb.comp_a >= 0 && comps[mb.comp_a].S > 0 && owned(mb.comp_a, ixA)) {
           faces[mb.comp_a].push_back({ixA, {ixB, m | (0u << 16) | (d << 17)}});
         }
-        if (mb.comp_b >= 0 && comps[mb.comp_b].S > 0) {
+        if (mb.comp_b >= 0 && comps[mb.comp_b].S > 0 && owned(mb.comp_b, ixB)) {
           faces[mb.comp_b].push_back({ixB, {ixA, m | (1u << 16) | (d << 17)}});
         }
       }
@@ -1060,16 +1064,27 @@ void Sim::setupSlabs(const smeb200_problem &p) {
   if (rank < 0 || rank >= nRanks || nRanks > kCommMaxRanks) {
     throw Error("smeb200: invalid rank / n_ranks");
   }
-  if (p.n_membranes > 0) {
-    throw Error("smeb200: z-slab decomposition does not support membranes yet");
-  }
   if (comps.size() > static_cast<std::size_t>(kCommMaxCompartments)) {
     throw Error("smeb200: too many compartments for z-slab decomposition");
   }
-  for (auto &c : comps) {
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    auto &c = comps[ci];
     if (!c.box) {
-      throw Error("smeb200: z-slab decomposition needs box compartments "
-                  "(implicit neighbours)");
+      // voxel list: [ghosts of the plane below][owned][ghosts of the plane above]
+      const auto &pc = p.compartments[ci];
+      c.vGhostLo = pc.slab_ghost_lo;
+      c.vGhostHi = pc.slab_ghost_hi;
+      c.vFirstPlane = pc.slab_first_plane;
+      c.vLastPlane = pc.slab_last_plane;
+      const uint64_t owned = c.n - std::min<uint64_t>(c.n, uint64_t{c.vGhostLo} +
+                                                                c.vGhostHi);
+      if (uint64_t{c.vGhostLo} + c.vGhostHi > c.n || c.vFirstPlane > owned ||
+          c.vLastPlane > owned || (rank == 0 && c.vGhostLo != 0) ||
+          (rank + 1 == nRanks && c.vGhostHi != 0)) {
+        throw Error("smeb200: inconsistent slab description of compartment '" +
+                    c.id + "'");
+      }
+      continue;
     }
     c.zLoGhost = rank > 0 ? 1u : 0u;
     c.zHiGhost = rank + 1 < nRanks ? 1u : 0u;
@@ -1094,8 +1109,12 @@ void Sim::connectSlabs() {
   mine.device = device;
   for (std::size_t ci = 0; ci < comps.size(); ++ci) {
     auto &c = comps[ci];
-    mine.nz[ci] = c.nz;
-    for (int b = 0; b < c.nbuf; ++b) {
+    const uint64_t plane = uint64_t{c.nx} * c.ny * c.S;
+    mine.ghostHiOff[ci] = c.box ? (c.nz - c.zHiGhost) * plane
+                                : (c.n - c.vGhostHi) * c.S;
+    mine.ghostLoCnt[ci] = c.box ? c.zLoGhost * plane : uint64_t{c.vGhostLo} * c.S;
+    mine.ghostHiCnt[ci] = c.box ? c.zHiGhost * plane : uint64_t{c.vGhostHi} * c.S;
+    for (int b = 0; b < c.nbuf && c.n > 0 && c.S > 0; ++b) {
       cudaIpcMemHandle_t h{};
       check(cudaIpcGetMemHandle(&h, c.buf[b]), "cudaIpcGetMemHandle");
       static_assert(sizeof(h) == 64, "CUDA IPC handle size");
@@ -1110,7 +1129,23 @@ void Sim::connectSlabs() {
       continue;
     }
     for (std::size_t ci = 0; ci < comps.size(); ++ci) {
-      for (int b = 0; b < comps[ci].nbuf; ++b) {
+      auto &c = comps[ci];
+      // what this rank sends towards `side` must be what the neighbour holds
+      // as ghosts on its facing side
+      const uint64_t plane = uint64_t{c.nx} * c.ny * c.S;
+      const uint64_t sendCnt =
+          c.box ? plane
+                : uint64_t{side == 0 ? c.vFirstPlane : c.vLastPlane} * c.S;
+      const uint64_t peerCnt = side == 0 ? seg->slot[nb].ghostHiCnt[ci]
+                                         : seg->slot[nb].ghostLoCnt[ci];
+      if (sendCnt != peerCnt) {
+        throw Error("smeb200: slab boundary of compartment '" + c.id +
+                    "' does not match the neighbouring rank's ghost voxels");
+      }
+      if (peerCnt == 0) {
+        continue;
+      }
+      for (int b = 0; b < c.nbuf; ++b) {
         cudaIpcMemHandle_t h{};
         std::memcpy(&h, seg->slot[nb].memHandle[ci][b], sizeof(h));
         void *ptr = nullptr;
@@ -1154,18 +1189,25 @@ void Sim::haloExchange(int coutBuf) {
     if (c.S == 0 || c.n == 0) {
       continue;
     }
+    // box: whole planes; voxel list: the voxels of the first / last owned plane
     const std::size_t plane = static_cast<std::size_t>(c.nx) * c.ny * c.S;
-    if (rank > 0) { // my first owned plane -> HIGH ghost of rank-1
-      const std::size_t peerNz = seg->slot[rank - 1].nz[ci];
-      check(cudaMemcpyAsync(peerBuf[0][ci][coutBuf] + (peerNz - 1) * plane,
-                            c.buf[coutBuf] + c.zLoGhost * plane,
-                            plane * sizeof(double), cudaMemcpyDefault, stream),
+    const std::size_t loOff =
+        c.box ? c.zLoGhost * plane : std::size_t{c.vGhostLo} * c.S;
+    const std::size_t loCnt = c.box ? plane : std::size_t{c.vFirstPlane} * c.S;
+    const std::size_t hiCnt = c.box ? plane : std::size_t{c.vLastPlane} * c.S;
+    const std::size_t hiOff =
+        c.box ? (c.nz - 1 - c.zHiGhost) * plane
+              : (c.n - c.vGhostHi) * c.S - hiCnt;
+    if (rank > 0 && loCnt > 0) { // first owned plane -> HIGH ghosts of rank-1
+      check(cudaMemcpyAsync(peerBuf[0][ci][coutBuf] +
+                                seg->slot[rank - 1].ghostHiOff[ci],
+                            c.buf[coutBuf] + loOff, loCnt * sizeof(double),
+                            cudaMemcpyDefault, stream),
             "halo push (low neighbour)");
     }
-    if (rank + 1 < nRanks) { // my last owned plane -> LOW ghost of rank+1
-      check(cudaMemcpyAsync(peerBuf[1][ci][coutBuf],
-                            c.buf[coutBuf] + (c.nz - 1 - c.zHiGhost) * plane,
-                            plane * sizeof(double), cudaMemcpyDefault, stream),
+    if (rank + 1 < nRanks && hiCnt > 0) { // last owned plane -> LOW ghosts of rank+1
+      check(cudaMemcpyAsync(peerBuf[1][ci][coutBuf], c.buf[coutBuf] + hiOff,
+                            hiCnt * sizeof(double), cudaMemcpyDefault, stream),
             "halo push (high neighbour)");
     }
   }
@@ -1227,6 +1269,8 @@ Sim::~Sim() {
     cudaFree(c.dEnt);
     cudaFree(c.scratch);
     cudaFree(c.dNsAv);
+    cudaFree(c.dStats);
+    cudaFree(c.dStatsPartial);
     cudaFree(c.dDarr);
     cudaFree(c.dXdMax);
     cudaFree(c.dNsPartial);
@@ -1276,7 +1320,8 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     a.c0 = c.buf[c.role[CUR]];
     a.nn = c.dNn;
     a.err = dErr;
-    a.n = static_cast<uint32_t>(c.n);
+    a.n = static_cast<uint32_t>(c.n - c.vGhostHi);
+    a.v0 = c.vGhostLo;
     a.nx = c.nx;
     a.ny = c.ny;
     a.nz = c.nz;
@@ -1353,7 +1398,7 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
           "launch tile stage kernel");
     nsBlocks = c.tile.grid[0] * c.tile.grid[1] * c.tile.grid[2];
   } else {
-    uint64_t work = c.n;
+    uint64_t work = c.n - c.vGhostLo - c.vGhostHi;
     if (c.geom == Geom::BOX) {
       work = static_cast<uint64_t>(a.z_end - a.z_begin) * c.nx * c.ny;
     }
@@ -1739,6 +1784,70 @@ void Sim::runOnDemand(std::size_t ci, uint32_t flags, double *out) {
   kernelTiming = false;
   launchCompartment(ci, a, k, c.lastCinBuf);
   kernelTiming = timing;
+}
+
+// Per-species {average, min, max} of the current state, reduced on the device
+// (calculateAvgMinMax, simulate.cpp:272-290, runs on one CPU thread over the
+// downloaded state after every image interval): 24 bytes per species cross
+// PCIe instead of the whole state.  In a z-slab decomposed simulation the
+// values cover this rank's owned planes.
+void Sim::getAvgMinMax(std::size_t comp, double *out, std::size_t nOut) {
+  if (comp >= comps.size()) {
+    throw Error("compartment index out of range");
+  }
+  auto &c = comps[comp];
+  if (nOut != 3 * static_cast<std::size_t>(c.SP) || out == nullptr) {
+    throw Error("getAvgMinMax: output must hold 3 values per model species");
+  }
+  if (ctorFailed) {
+    throw Error(errorMessage);
+  }
+  if (c.S == 0 || c.n == 0) {
+    return;
+  }
+  bindDevice();
+  const auto &drv = DriverApi::get();
+  const std::string name = "smeb_stats<Reac" + std::to_string(comp) + ">";
+  const std::string finish = "smeb_stats_finish";
+  if (auxFn.find(name) == auxFn.end()) {
+    auxModules.push_back(compile({name, finish}));
+    for (const auto &[k, f] : auxModules.back().fn) {
+      auxFn[k] = f;
+    }
+  }
+  const unsigned blocks = static_cast<unsigned>(smCount) * 8u;
+  if (c.dStats == nullptr) {
+    c.dStatsPartial = devAlloc<double>(static_cast<std::size_t>(blocks) * 3 * c.SP,
+                                       "allocate statistics partials");
+    c.dStats = devAlloc<double>(3 * c.SP, "allocate statistics");
+  }
+  const double *state = c.buf[c.role[CUR]];
+  uint32_t i0 = static_cast<uint32_t>(c.ownedBegin());
+  uint32_t i1 = static_cast<uint32_t>(c.ownedEnd());
+  uint64_t counted = i1 - i0;
+  if (counted == 0) {
+    return;
+  }
+  unsigned grid = static_cast<unsigned>(std::max<uint64_t>(
+      1, std::min<uint64_t>((counted + BLOCK - 1) / BLOCK, blocks)));
+  double *partial = c.dStatsPartial;
+  void *p1[] = {&state, &i0, &i1, &partial};
+  check(drv.LaunchKernel(auxFn.at(name), grid, 1, 1, BLOCK, 1, 1, 0, stream, p1,
+                         nullptr),
+        "launch statistics kernel");
+  const double *cpartial = c.dStatsPartial;
+  uint32_t sp = c.SP;
+  double nVox = static_cast<double>(counted);
+  double *dout = c.dStats;
+  void *p2[] = {&cpartial, &grid, &sp, &nVox, &dout};
+  check(drv.LaunchKernel(auxFn.at(finish), 1, 1, 1, BLOCK, 1, 1, 0, stream, p2,
+                         nullptr),
+        "launch statistics finish kernel");
+  launchCount += 2;
+  check(cudaMemcpyAsync(out, c.dStats, nOut * sizeof(double),
+                        cudaMemcpyDeviceToHost, stream),
+        "download statistics");
+  check(cudaStreamSynchronize(stream), "download statistics");
 }
 
 // dc/dt of the last evaluated stage (PixelSim::getDcdt).  The fused stages

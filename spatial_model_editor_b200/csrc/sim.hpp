@@ -42,6 +42,7 @@ struct StageArgsHost {
   unsigned long long *xdMax;
   double h2[3];
   uint32_t n;
+  uint32_t v0;
   uint32_t nx, ny, nz;
   uint32_t z_begin, z_end;
   double g1, g2, g3, bdt, delta;
@@ -93,6 +94,13 @@ struct CompartmentState {
   Geom geom{Geom::NN};
   uint32_t nx{0}, ny{0}, nz{0};
   uint32_t zLoGhost{0}, zHiGhost{0}; // z-slab ghost planes (read, not updated)
+  // z-slab of a voxel list: ghost voxels at both ends of the local list and the
+  // sizes of the first / last owned plane (what the neighbours hold as ghosts)
+  uint32_t vGhostLo{0}, vGhostHi{0}, vFirstPlane{0}, vLastPlane{0};
+  uint64_t ownedBegin() const { return box ? uint64_t{zLoGhost} * nx * ny : vGhostLo; }
+  uint64_t ownedEnd() const {
+    return box ? uint64_t{nz - zHiGhost} * nx * ny : n - vGhostHi;
+  }
   TileConfig tile;
   std::vector<std::string> speciesNames;
   std::vector<double> D;
@@ -111,6 +119,8 @@ struct CompartmentState {
   unsigned long long *dXdMax{nullptr};
   CUfunction kXdMax{nullptr};
   double maxStable{std::numeric_limits<double>::max()};
+  double *dStatsPartial{nullptr};    // [blocks][3*SP]
+  double *dStats{nullptr};           // [3*SP] avg, min, max per species
   std::vector<int32_t> voxels;
   int nbuf{0};
   double *buf[4]{nullptr, nullptr, nullptr, nullptr};
@@ -149,6 +159,7 @@ public:
   const double *getDcdt(std::size_t comp, std::size_t *n);
   double getLowerOrder(std::size_t comp, std::size_t species, std::size_t pixel);
   void setConcentrations(std::size_t comp, const double *data, std::size_t n);
+  void getAvgMinMax(std::size_t comp, double *out, std::size_t nOut);
   double benchSteps(double dt, std::size_t nSteps);
 
   std::string errorMessage;

@@ -1,5 +1,7 @@
-"""z-slab decomposition of a box compartment over the GPUs of one node, one
-process per GPU (the reference has no multi-GPU path).
+"""z-slab decomposition over the GPUs of one node, one process per GPU
+(the reference has no multi-GPU path): box compartments
+as whole planes, voxel-list compartments (and the membranes between them) cut at
+plane boundaries.
 
 The voxel order is z-outermost (geometry.cpp:55-72), so a slab is a contiguous
 range of the voxel list.  Rank r owns planes ``slab_range(nz, r, world)`` and
@@ -47,30 +49,94 @@ def default_comm_name(tag: str = "") -> str:
     return f"smeb200_{os.getuid()}_{job}_{tag}"
 
 
+def list_slab(voxels: np.ndarray, nz: int, rank: int, world: int
+              ) -> Tuple[int, int, int, int]:
+    """(g0, o0, o1, g1) for a voxel-list compartment: the local list is the global
+    slice [g0, g1), the owned voxels are [o0, o1).  The voxel order is z-major
+    (geometry.cpp:55-72), so the ghost voxels (the compartment's voxels in the
+    planes just below / above the owned planes) are adjacent to the owned range."""
+    z = voxels[:, 2]
+    z0, z1 = slab_range(nz, rank, world)
+    o0, o1 = int(np.searchsorted(z, z0, "left")), int(np.searchsorted(z, z1, "left"))
+    g0 = int(np.searchsorted(z, z0 - 1, "left")) if rank > 0 else o0
+    g1 = int(np.searchsorted(z, z1 + 1, "left")) if rank < world - 1 else o1
+    return g0, o0, o1, g1
+
+
 def local_problem(problem: Problem, rank: int, world: int, comm_name: str,
                   make_slab: Optional[Callable[[int, int], np.ndarray]] = None) -> Problem:
     """the Problem rank ``rank`` hands to the C library.  ``problem`` describes the
-    GLOBAL box; its ``conc0`` may be a placeholder when ``make_slab(g0, g1)``
-    supplies the local initial state (planes g0..g1, ghosts included) — at 512^3
-    per GPU nobody wants to build the global array on every rank."""
-    if problem.membranes:
-        raise ValueError("z-slab decomposition does not support membranes yet")
+    GLOBAL geometry.  Box compartments: ``conc0`` may be a placeholder when
+    ``make_slab(g0, g1)`` supplies the local initial state (planes g0..g1, ghosts
+    included) — at 512^3 per GPU nobody wants to build the global array on every
+    rank.  Voxel-list compartments (with ``voxels``) are cut at plane boundaries:
+    local list = [ghost voxels of the plane below | owned | ghost voxels of the
+    plane above], local neighbour indices, and every membrane pair that has at
+    least one owned voxel (the partner may be a ghost: each rank accumulates the
+    fluxes of its own voxels only, no remote writes)."""
     out = copy.copy(problem)
     out.compartments = []
+    nz_image = problem.image_size[2]
+    slabs = []
     for c in problem.compartments:
-        if c.box is None:
-            raise ValueError("z-slab decomposition needs box compartments")
-        nx, ny, nz = c.box
-        g0, g1, _, _ = ghost_range(nz, rank, world)
-        plane = nx * ny
-        if make_slab is not None:
-            conc = np.ascontiguousarray(make_slab(g0, g1), dtype=np.float64)
-            conc = conc.reshape((g1 - g0) * plane, c.n_species)
+        if c.box is not None and c.nn is None:
+            nx, ny, nz = c.box
+            g0, g1, _, _ = ghost_range(nz, rank, world)
+            plane = nx * ny
+            if make_slab is not None:
+                conc = np.ascontiguousarray(make_slab(g0, g1), dtype=np.float64)
+                conc = conc.reshape((g1 - g0) * plane, c.n_species)
+            else:
+                conc = np.ascontiguousarray(c.conc0[g0 * plane:g1 * plane])
+            lc = copy.copy(c)
+            lc.conc0, lc.box = conc, (nx, ny, g1 - g0)
+            slabs.append(None)
         else:
-            conc = np.ascontiguousarray(c.conc0[g0 * plane:g1 * plane])
-        lc = Compartment(id=c.id, species=c.species, expressions=c.expressions,
-                         diffusion=c.diffusion, conc0=conc, box=(nx, ny, g1 - g0))
+            if c.voxels is None:
+                raise ValueError("z-slab decomposition of a voxel-list compartment needs "
+                                 "its voxel coordinates")
+            g0, o0, o1, g1 = list_slab(c.voxels, nz_image, rank, world)
+            z = c.voxels[:, 2]
+            z0, z1 = slab_range(nz_image, rank, world)
+            nn = c.nn[g0:g1].astype(np.int64) - g0
+            own = np.arange(g1 - g0, dtype=np.int64)
+            ghost = (own < o0 - g0) | (own >= o1 - g0)
+            nn[ghost] = own[ghost, None]          # rows of ghost voxels are ignored
+            assert nn.min(initial=0) >= 0 and nn.max(initial=0) < max(g1 - g0, 1)
+            lc = copy.copy(c)
+            lc.conc0 = np.ascontiguousarray(c.conc0[g0:g1])
+            lc.nn = nn.astype(np.uint32)
+            lc.voxels = np.ascontiguousarray(c.voxels[g0:g1])
+            if c.diffusion_array is not None:
+                lc.diffusion_array = np.ascontiguousarray(c.diffusion_array[g0:g1])
+            lc.box = None
+            first = int(np.count_nonzero(z[o0:o1] == z0)) if o1 > o0 else 0
+            last = int(np.count_nonzero(z[o0:o1] == z1 - 1)) if o1 > o0 else 0
+            lc.slab = (o0 - g0, g1 - o1, first, last)
+            slabs.append((g0, o0, o1, g1))
         out.compartments.append(lc)
+    out.membranes = []
+    for m in problem.membranes:
+        sa = slabs[m.comp_a] if m.comp_a >= 0 else None
+        sb = slabs[m.comp_b] if m.comp_b >= 0 else None
+        lm = copy.copy(m)
+        lm.pairs = []
+        for d in range(6):
+            pr = np.asarray(m.pairs[d], dtype=np.int64).reshape(-1, 2)
+            keep = np.zeros(len(pr), dtype=bool)
+            if sa is not None:
+                keep |= (pr[:, 0] >= sa[1]) & (pr[:, 0] < sa[2])
+            if sb is not None:
+                keep |= (pr[:, 1] >= sb[1]) & (pr[:, 1] < sb[2])
+            pr = pr[keep].copy()
+            if sa is not None:
+                pr[:, 0] -= sa[0]
+                assert np.all((pr[:, 0] >= 0) & (pr[:, 0] < sa[3] - sa[0]))
+            if sb is not None:
+                pr[:, 1] -= sb[0]
+                assert np.all((pr[:, 1] >= 0) & (pr[:, 1] < sb[3] - sb[0]))
+            lm.pairs.append(pr.astype(np.uint32))
+        out.membranes.append(lm)
     out.rank, out.n_ranks, out.comm_name = rank, world, comm_name
     return out
 
@@ -91,6 +157,10 @@ class SlabPixelSim(PixelSim):
         super().__init__(lp)
 
     def _owned(self, ci: int, a: np.ndarray) -> np.ndarray:
+        c = self._problem.compartments[ci]
+        if c.nn is not None:
+            lo, hi = c.slab[0], c.slab[1]
+            return a[lo: a.shape[0] - hi]
         nx, ny, nz = self.global_problem.compartments[ci].box
         _, _, lo, hi = ghost_range(nz, self.rank, self.world)
         plane = nx * ny

@@ -61,6 +61,8 @@ def _bind(lib, prefix: str):
     fn("compile_only", C.c_int, [C.POINTER(CProblem), C.POINTER(vp)], optional=True)
     fn("get_concentration_padding", C.c_size_t, [vp], optional=True)
     fn("set_error", None, [vp, C.c_char_p], optional=True)
+    fn("get_avg_min_max", C.c_int, [vp, C.c_size_t, C.POINTER(C.c_double), C.c_size_t],
+       optional=True)
     fn("bench_steps", C.c_double, [vp, C.c_double, C.c_size_t], optional=True)
     fn("launch_count", C.c_uint64, [vp], optional=True)
     fn("last_run_ms", C.c_double, [vp], optional=True)
@@ -257,6 +259,17 @@ class PixelSim(CSim):
         rc = self._f("set_params")(self._h, a.ctypes.data_as(C.POINTER(C.c_double)), a.size)
         if rc != 0:
             raise RuntimeError(self.errorMessage())
+
+    def getAvgMinMax(self, compartmentIndex: int) -> np.ndarray:
+        """[n_primary_species, 3] average, minimum, maximum per species, reduced on
+        the device (calculateAvgMinMax, simulate.cpp:272-290)"""
+        sp = self._problem.compartments[compartmentIndex].n_primary_species
+        out = np.zeros((sp, 3), dtype=np.float64)
+        rc = self._f("get_avg_min_max")(self._h, compartmentIndex,
+                                        out.ctypes.data_as(C.POINTER(C.c_double)), out.size)
+        if rc != 0:
+            raise RuntimeError(self.errorMessage())
+        return out
 
     def dominantKernel(self) -> str:
         return self._f("dominant_kernel")(self._h).decode()

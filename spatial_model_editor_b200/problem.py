@@ -53,6 +53,10 @@ class CCompartment(C.Structure):
         ("cross_source", C.POINTER(C.c_uint32)),
         ("cross_expressions", C.POINTER(C.c_char_p)),
         ("diffusion_raw", C.POINTER(C.c_double)),
+        ("slab_ghost_lo", C.c_uint32),
+        ("slab_ghost_hi", C.c_uint32),
+        ("slab_first_plane", C.c_uint32),
+        ("slab_last_plane", C.c_uint32),
     ]
 
 
@@ -113,6 +117,7 @@ class Compartment:
     diffusion_array: Optional[np.ndarray] = None  # [N, S] raw D per voxel (non-uniform)
     cross_diffusion: Sequence[Tuple[int, int, str]] = ()  # (target, source, expression)
     diffusion_raw: Optional[np.ndarray] = None    # [S] raw D (needed with cross-diffusion)
+    slab: Tuple[int, int, int, int] = (0, 0, 0, 0)  # ghost_lo, ghost_hi, first/last plane
 
     @property
     def n_primary_species(self) -> int:
@@ -216,6 +221,8 @@ class Problem:
             if c.diffusion_array is not None:
                 assert c.diffusion_array.shape == (c.n_voxels, c.n_species)
                 cc.diffusion_array = arr(c.diffusion_array, np.float64, C.c_double)
+            (cc.slab_ghost_lo, cc.slab_ghost_hi, cc.slab_first_plane,
+             cc.slab_last_plane) = c.slab
             cc.n_cross_diffusion = len(c.cross_diffusion)
             if len(c.cross_diffusion):
                 cc.cross_target = arr([t for t, _, _ in c.cross_diffusion], np.uint32, C.c_uint32)

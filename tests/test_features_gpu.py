@@ -279,3 +279,41 @@ def test_diffusion_variants_adaptive(integ):
         ng, nc = gpu.run(0.5), cpu.run(0.5)
         assert ng == nc and gpu.discardedSteps == cpu.discardedSteps
         compare(p, gpu, cpu, "diffusion variants adaptive", rel=1e-9)
+
+
+# ---- device-side result statistics -----------------
+def avg_min_max_host(conc, n_primary):
+    """calculateAvgMinMax (simulate.cpp:272-290) on the downloaded state"""
+    out = np.zeros((n_primary, 3))
+    for s in range(n_primary):
+        col = conc[:, s]
+        out[s] = [col.sum() / len(col), min(np.finfo(np.float64).max, col.min()),
+                  max(0.0, col.max())]
+    return out
+
+
+@pytest.mark.parametrize("name", ["very-simple-model", "liver-simplified", "txy", "gray-scott-3d"])
+def test_avg_min_max_on_device(name):
+    p, _, _ = load_golden(name)
+    p.device = 0
+    gpu = smeb.PixelSim(p)
+    for t in (0.0, 0.05):
+        if t > 0:
+            assert gpu.run(t) > 0
+        for ci, c in enumerate(p.compartments):
+            dev = gpu.getAvgMinMax(ci)
+            host = avg_min_max_host(gpu.getConcentrations(ci), c.n_primary_species)
+            assert dev.shape == host.shape
+            assert np.array_equal(dev[:, 1:], host[:, 1:])      # min / max: exact
+            assert np.allclose(dev[:, 0], host[:, 0], rtol=1e-13, atol=1e-300)
+
+
+def test_avg_min_max_box():
+    p = M.box_problem(M.GRAY_SCOTT, 64, 48, 20)
+    p.device = 0
+    gpu = smeb.PixelSim(p)
+    gpu.run(0.3)
+    dev = gpu.getAvgMinMax(0)
+    host = avg_min_max_host(gpu.getConcentrations(0), 2)
+    assert np.array_equal(dev[:, 1:], host[:, 1:])
+    assert np.allclose(dev[:, 0], host[:, 0], rtol=1e-13, atol=0)

@@ -45,8 +45,104 @@ def test_local_problems_tile_the_global_state():
         lp2 = MG.local_problem(p, r, 3, "x", make_slab=lambda a, b: glob[a * plane:b * plane])
         assert np.array_equal(lp2.compartments[0].conc0, c.conc0)
     assert np.array_equal(np.concatenate(owned), glob)
-    with pytest.raises(ValueError):
-        MG.local_problem(M.two_compartment_brusselator(8, 8), 0, 2, "x")
+
+
+def _cell_problem():
+    """outer box / inner box in x, y and z with a membrane between them: pairs in
+    all six face directions, some straddling the slab boundaries"""
+    from spatial_model_editor_b200.pde import ReactionDef
+    lab = np.ones((9, 8, 7), dtype=np.int32)
+    lab[2:7, 2:6, 2:5] = 2
+    mem = dict(a=0, b=1, species_a=["X_a", "Y_a"], species_b=["X_b", "Y_b"],
+               constants={"km": 0.3},
+               reactions=[ReactionDef("flux", "km * (X_a - X_b)", {"X_a": -1.0, "X_b": 1.0})])
+    p = M.labelled_problem(lab, [dict(label=1, id="outer", kin=M.BRUSSELATOR),
+                                 dict(label=2, id="inner", kin=M.BRUSSELATOR)], [mem],
+                           integrator=smeb.RK101)
+    p.max_err_abs = p.max_err_rel = smeb.DBL_MAX
+    p.max_timestep = 0.01
+    return p
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_listed_local_problems_partition_voxels_and_pairs(world):
+    p = _cell_problem()
+    locs = [MG.local_problem(p, r, world, "x") for r in range(world)]
+    for ci, c in enumerate(p.compartments):
+        owned = []
+        for r, lp in enumerate(locs):
+            lc = lp.compartments[ci]
+            lo, hi, first, last = lc.slab
+            assert (lo == 0) == (r == 0 or lo == 0) and (r < world - 1 or hi == 0)
+            owned.append(lc.conc0[lo:lc.n_voxels - hi])
+            if r > 0:  # my low ghosts are the previous rank's last owned plane
+                assert lo == locs[r - 1].compartments[ci].slab[3]
+                assert locs[r - 1].compartments[ci].slab[1] == first
+            # neighbours of owned voxels stay inside the local list
+            assert lc.nn.max(initial=0) < max(lc.n_voxels, 1)
+        assert np.array_equal(np.concatenate(owned), c.conc0)
+    # every membrane pair is listed by the rank(s) owning its A voxel and its B voxel
+    m = p.membranes[0]
+    for d in range(6):
+        n_a = n_b = 0
+        for lp in locs:
+            a, b = lp.compartments[0], lp.compartments[1]
+            pr = lp.membranes[0].pairs[d].astype(np.int64).reshape(-1, 2)
+            n_a += int(np.count_nonzero((pr[:, 0] >= a.slab[0])
+                                        & (pr[:, 0] < a.n_voxels - a.slab[1])))
+            n_b += int(np.count_nonzero((pr[:, 1] >= b.slab[0])
+                                        & (pr[:, 1] < b.n_voxels - b.slab[1])))
+        assert n_a == n_b == len(m.pairs[d])
+    assert sum(len(x) for x in m.pairs[4:]) > 0  # there are z faces
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_listed_slabs_emulated_on_cpu(world):
+    """the decomposition itself, without GPUs: every rank's local problem stepped by
+    the CPU oracle (forward Euler, one stage per step), ghosts refreshed from the
+    neighbours after every step like the halo push does — bit-identical to the
+    global run (ghost voxels are also stepped by the oracle, then overwritten)"""
+    from oracle.oracle_sim import OraclePixelSim
+    p = _cell_problem()
+    dt, steps = p.max_timestep, 12
+    ref = OraclePixelSim(p)
+    ref.nextTimestep = dt
+    locs = [MG.local_problem(p, r, world, "x") for r in range(world)]
+    for lp in locs:
+        lp.rank, lp.n_ranks, lp.comm_name = 0, 1, None
+    sims = [OraclePixelSim(lp) for lp in locs]
+    for _ in range(steps):
+        assert ref.run(dt) == 1
+        state = []
+        for sim, lp in zip(sims, locs):
+            assert sim.run(dt) == 1
+            state.append([np.array(sim.getConcentrations(ci))
+                          for ci in range(len(lp.compartments))])
+        for r, lp in enumerate(locs):
+            for ci, lc in enumerate(lp.compartments):
+                lo, hi, first, last = lc.slab
+                cur = state[r][ci]
+                if lo:
+                    prev, pc = state[r - 1][ci], locs[r - 1].compartments[ci]
+                    end = pc.n_voxels - pc.slab[1]
+                    cur[:lo] = prev[end - pc.slab[3]:end]
+                if hi:
+                    nxt, nc = state[r + 1][ci], locs[r + 1].compartments[ci]
+                    cur[lc.n_voxels - hi:] = nxt[nc.slab[0]:nc.slab[0] + nc.slab[2]]
+                sims[r].setConcentrations(ci, cur)
+    for ci, c in enumerate(p.compartments):
+        owned = [np.array(sims[r].getConcentrations(ci))[
+            locs[r].compartments[ci].slab[0]:
+            locs[r].compartments[ci].n_voxels - locs[r].compartments[ci].slab[1]]
+            for r in range(world)]
+        assert np.array_equal(np.concatenate(owned), ref.getConcentrations(ci))
+
+
+def test_listed_slab_module_compiles():
+    lp = MG.local_problem(_cell_problem(), 1, 3, "x")
+    sim = smeb.PixelSim(lp, compile_only=True)
+    assert sim.errorMessage() == ""
+    assert "smeb_stage_memb" in sim.kernelSource()
 
 
 def test_slab_module_compiles_with_ghost_planes():
