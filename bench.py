@@ -334,11 +334,15 @@ def main():
         if world > 1:
             raise SystemExit("bench: voxel-list workloads run on one GPU")
         p, workload_text = make_listed_problem(args, integrator, local_rank)
+        p.kernel_variant = args.variant
         sim = smeb.PixelSim(p)
         evals_per_step = p.evals_per_step()
         dom = max(p.compartments, key=lambda c: c.n_voxels * c.n_species)
         values_per_rank = dom.n_voxels * dom.n_species
-        nn_bytes = 24 * dom.n_voxels
+        dom_index = p.compartments.index(dom)
+        nn_bytes = sim.neighbourBytesPerVoxel(dom_index) * dom.n_voxels
+        workload_text += (f"; neighbour data {sim.neighbourBytesPerVoxel(dom_index)} B/voxel"
+                          f" ({sim.neighbourRuns(dom_index)} runs)")
     elif world > 1:
         from spatial_model_editor_b200.multigpu import SlabPixelSim
         # the global box is only described (no global array is ever built);

@@ -182,7 +182,9 @@ typedef struct smeb200_problem {
   int32_t rank, n_ranks;
   /* kernel variant: 0 = auto (TMA tile-marching kernel for box compartments
    * where the shape allows it), 1 = direct-gather kernels only, 2 = require
-   * the TMA tile kernel for box compartments (error if it cannot be used) */
+   * the TMA tile kernel for box compartments (error if it cannot be used),
+   * 3 = keep the plain six-index neighbour table of voxel-list compartments
+   * (default: run-compressed to one 32-bit code per voxel where possible) */
   int32_t kernel_variant;
   /* runtime model parameters: expressions may refer to sme_param_0 ..
    * sme_param_{n_params-1}; their values are kernel arguments, so simulators
@@ -243,6 +245,21 @@ int smeb200_get_lower_order(smeb200_sim *sim, size_t compartment,
  * species; n_out must be 3 * n_primary_species. */
 int smeb200_get_avg_min_max(smeb200_sim *sim, size_t compartment, double *out,
                             size_t n_out);
+/* The device layout of a voxel-list compartment's neighbour table, exposed for
+ * inspection and tests (no device needed): nn[6*i+k] as in
+ * smeb200_compartment -> one code per voxel (bits 0-24 run id, bits 25-30
+ * "neighbour exists" for +x,-x,+y,-y,+z,-z, bit 31 membrane flag) and four index
+ * deltas (+x,-x,+z,-z) per run.  On entry *n_runs is the capacity of `runs` in
+ * runs (codes needs n_voxels entries; either may be NULL), on return the number
+ * of runs.  Returns 0, or 1 if the table cannot be compressed. */
+int smeb200_compress_neighbours(const uint32_t *nn, uint64_t n_voxels,
+                                uint32_t *codes, int32_t *runs,
+                                uint64_t *n_runs);
+/* neighbour-index bytes the stage kernels read per voxel of a compartment: 0
+ * (box, implicit neighbours), 4 (run-compressed codes) or 24 (plain table); and
+ * the number of runs of the compressed layout */
+size_t smeb200_neighbour_bytes_per_voxel(const smeb200_sim *sim, size_t compartment);
+size_t smeb200_neighbour_runs(const smeb200_sim *sim, size_t compartment);
 /* BaseSim::getConcentrationPadding (pixelsim.cpp:478): number of time / x, y, z
  * components behind the model species of every voxel */
 size_t smeb200_get_concentration_padding(const smeb200_sim *sim);

@@ -114,6 +114,41 @@ int smeb200_get_avg_min_max(smeb200_sim *sim, size_t compartment, double *out,
                  [&] { sim->impl.getAvgMinMax(compartment, out, n_out); });
 }
 
+size_t smeb200_neighbour_bytes_per_voxel(const smeb200_sim *s, size_t comp) {
+  return s != nullptr && comp < s->impl.nCompartments()
+             ? s->impl.neighbourBytesPerVoxel(comp)
+             : 0;
+}
+
+size_t smeb200_neighbour_runs(const smeb200_sim *s, size_t comp) {
+  return s != nullptr && comp < s->impl.nCompartments()
+             ? s->impl.neighbourRuns(comp)
+             : 0;
+}
+
+int smeb200_compress_neighbours(const uint32_t *nn, uint64_t n_voxels,
+                                uint32_t *codes, int32_t *runs,
+                                uint64_t *n_runs) {
+  try {
+    std::vector<uint32_t> c;
+    std::vector<int> r;
+    if (nn == nullptr || n_runs == nullptr ||
+        !smeb200::compressNeighbourTable(nn, n_voxels, c, r)) {
+      return 1;
+    }
+    if (codes != nullptr) {
+      std::copy(c.begin(), c.end(), codes);
+    }
+    if (runs != nullptr && r.size() / 4 <= *n_runs) {
+      std::copy(r.begin(), r.end(), runs);
+    }
+    *n_runs = r.size() / 4;
+    return 0;
+  } catch (...) {
+    return 2;
+  }
+}
+
 size_t smeb200_get_concentration_padding(const smeb200_sim *s) {
   return s != nullptr ? s->impl.concentrationPadding() : 0;
 }

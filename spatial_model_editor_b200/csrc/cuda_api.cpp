@@ -52,6 +52,8 @@ const DriverApi &DriverApi::get() {
       resolve("cuModuleGetFunction", api.ModuleGetFunction);
       resolve("cuLaunchKernel", api.LaunchKernel);
       resolve("cuFuncSetAttribute", api.FuncSetAttribute);
+      resolve("cuOccupancyMaxActiveBlocksPerMultiprocessor",
+              api.OccupancyMaxActiveBlocksPerMultiprocessor);
       resolve("cuTensorMapEncodeTiled", api.TensorMapEncodeTiled);
       resolve("cuStreamWriteValue32", api.StreamWriteValue32);
       resolve("cuStreamWaitValue32", api.StreamWaitValue32);

@@ -25,6 +25,8 @@ struct DriverApi {
                            unsigned, unsigned, unsigned, CUstream, void **,
                            void **) = nullptr;
   CUresult (*FuncSetAttribute)(CUfunction, CUfunction_attribute, int) = nullptr;
+  CUresult (*OccupancyMaxActiveBlocksPerMultiprocessor)(int *, CUfunction, int,
+                                                        size_t) = nullptr;
   CUresult (*GetErrorString)(CUresult, const char **) = nullptr;
   CUresult (*TensorMapEncodeTiled)(
       CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,

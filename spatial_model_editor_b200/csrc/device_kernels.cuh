@@ -57,7 +57,9 @@ template <int S> struct SmebStageArgs {
   const double *s2in;  // low-storage running sum in (reference: s2)
   double *s2out;       // running sum out (may alias s2in)
   double *cout;        // stage output (or the on-demand output)
-  const smeb_u32 *nn;  // [6 n] neighbour list (voxel-list geometry)
+  const smeb_u32 *nn;  // voxel-list geometry: [6 n] neighbour indices, or (runs
+                       // != 0) [n] run-compressed neighbour codes
+  const int *runs;     // [4 n_runs] index deltas of the +x, -x, +z, -z neighbours
   smeb_u64 *err;       // [2] bit patterns of max abs / max rel error
   const double *nsAv;  // [R::NNS] spatial averages of dc/dt (non-spatial species)
   double *nsPartial;   // [blocks][R::NNS] block sums written by the pre-pass
@@ -454,8 +456,44 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
 }
 
 // ---- direct-gather stage kernels: grid-stride loop, one voxel at a time -----
-// voxel-list geometry: neighbour indices from the uint32 list (24 B per
-// voxel); voxels flagged SMEB_MEMB_FLAG are left to smeb_stage_memb.
+// voxel-list geometry.  The neighbour table of the reference (six indices per
+// voxel, geometry.cpp:98-110; 24 B per voxel as uint32) is stored run-compressed
+// where the host could build it: the voxel order is z, x, y with y fastest
+// (geometry.cpp:55-72), so the -y / +y neighbours are i -/+ 1 and along a run of
+// consecutive voxels of one column the index distance to the neighbouring
+// column / plane is constant.  One 32-bit code per voxel — run id (25 bits), six
+// "neighbour exists" bits (missing neighbour = own index, the zero-flux
+// boundary), membrane flag — plus a table of four deltas per run that stays in
+// L1/L2: 4 B of index traffic per voxel instead of 24.  Voxels flagged
+// SMEB_MEMB_FLAG are left to smeb_stage_memb.
+#define SMEB_RUN_BITS 25
+__device__ __forceinline__ bool
+smeb_neighbours(const smeb_u32 *__restrict__ nn, const int *__restrict__ runs,
+                smeb_u32 i, smeb_u32 *nb) {
+  if (runs != nullptr) {
+    const smeb_u32 code = nn[i];
+    const int4 d = reinterpret_cast<const int4 *>(
+        runs)[code & ((1u << SMEB_RUN_BITS) - 1u)];
+    const smeb_u32 fl = code >> SMEB_RUN_BITS;
+    nb[0] = (fl & 1u) ? i + d.x : i;
+    nb[1] = (fl & 2u) ? i + d.y : i;
+    nb[2] = (fl & 4u) ? i + 1u : i;
+    nb[3] = (fl & 8u) ? i - 1u : i;
+    nb[4] = (fl & 16u) ? i + d.z : i;
+    nb[5] = (fl & 32u) ? i + d.w : i;
+    return (code & SMEB_MEMB_FLAG) != 0;
+  }
+  const uint2 *q = reinterpret_cast<const uint2 *>(nn) + (size_t)i * 3;
+  const uint2 n0 = q[0], n1 = q[1], n2 = q[2];
+  nb[0] = n0.x & ~SMEB_MEMB_FLAG;
+  nb[1] = n0.y;
+  nb[2] = n1.x;
+  nb[3] = n1.y;
+  nb[4] = n2.x;
+  nb[5] = n2.y;
+  return (n0.x & SMEB_MEMB_FLAG) != 0;
+}
+
 template <class R, unsigned F>
 __global__ void __launch_bounds__(SMEB_BLOCK)
     smeb_stage_nn(const __grid_constant__ SmebStageArgs<R::S> a) {
@@ -464,12 +502,10 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
   for (smeb_u32 i = a.v0 + blockIdx.x * SMEB_BLOCK + threadIdx.x; i < a.n;
        i += gridDim.x * SMEB_BLOCK) {
-    const uint2 *q = reinterpret_cast<const uint2 *>(a.nn) + (size_t)i * 3;
-    const uint2 n0 = q[0], n1 = q[1], n2 = q[2];
-    if (n0.x & SMEB_MEMB_FLAG) {
+    smeb_u32 nb[6];
+    if (smeb_neighbours(a.nn, a.runs, i, nb)) {
       continue;
     }
-    const smeb_u32 nb[6] = {n0.x, n0.y, n1.x, n1.y, n2.x, n2.y};
     double c[S], f[S];
     smeb_rhs_gather<R>(a, i, nb, c, f);
     smeb_finish_voxel<R, F>(a, i, c, f, eabs, erel, nsacc);
@@ -601,9 +637,8 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   for (smeb_u32 k = blockIdx.x * SMEB_BLOCK + threadIdx.x; k < m.n_mvox;
        k += gridDim.x * SMEB_BLOCK) {
     const smeb_u32 i = m.mvox[k];
-    const uint2 *q = reinterpret_cast<const uint2 *>(a.nn) + (size_t)i * 3;
-    const uint2 n0 = q[0], n1 = q[1], n2 = q[2];
-    const smeb_u32 nb[6] = {n0.x & ~SMEB_MEMB_FLAG, n0.y, n1.x, n1.y, n2.x, n2.y};
+    smeb_u32 nb[6];
+    smeb_neighbours(a.nn, a.runs, i, nb);
     double c[S], f[S];
     smeb_rhs_gather<R>(a, i, nb, c, f);
     const smeb_u32 e1 = m.mstart[k + 1];

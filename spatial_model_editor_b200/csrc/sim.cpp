@@ -1,7 +1,9 @@
 #include "sim.hpp"
 #include <algorithm>
 #include <chrono>
+#include <climits>
 #include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -408,6 +410,88 @@ StageKernels Sim::onDemandKernels(std::size_t ci, uint32_t flags) {
   Module view;
   view.fn = auxFn;
   return lookup(view, ci, flags);
+}
+
+// ---- run-compressed neighbour codes (device_kernels.cuh: smeb_neighbours) -----
+// nn: the reference's table (six indices per voxel, own index = no neighbour,
+// bit 31 of the first entry = membrane flag).  A run is a maximal range of
+// consecutive voxels whose existing +x, -x, +z, -z neighbours all sit at one
+// index distance per direction; -y / +y neighbours must be i -/+ 1 (they are, in
+// the reference's voxel order).  Returns false if the table does not have that
+// structure or needs more than 2^25 runs: the caller keeps the plain table.
+namespace {
+bool compressNeighbours(const std::vector<uint32_t> &nn, uint64_t n,
+                        std::vector<uint32_t> &codes, std::vector<int> &runs) {
+  constexpr uint32_t runBits = 25;
+  codes.assign(n, 0u);
+  runs.clear();
+  int64_t cur[4] = {0, 0, 0, 0};
+  bool set[4] = {false, false, false, false};
+  bool open = false;
+  static const int dirOf[4] = {0, 1, 4, 5};
+  for (uint64_t i = 0; i < n; ++i) {
+    uint32_t nb[6];
+    for (int k = 0; k < 6; ++k) {
+      nb[k] = nn[6 * i + k];
+    }
+    const uint32_t memb = nb[0] & MEMB_FLAG;
+    nb[0] &= ~MEMB_FLAG;
+    uint32_t flags = 0;
+    if (nb[2] != i) {
+      if (nb[2] != i + 1) {
+        return false;
+      }
+      flags |= 4u;
+    }
+    if (nb[3] != i) {
+      if (nb[3] + 1 != i) {
+        return false;
+      }
+      flags |= 8u;
+    }
+    int64_t d[4];
+    bool exists[4];
+    bool conflict = !open;
+    for (int j = 0; j < 4; ++j) {
+      exists[j] = nb[dirOf[j]] != i;
+      d[j] = static_cast<int64_t>(nb[dirOf[j]]) - static_cast<int64_t>(i);
+      if (exists[j] && (d[j] > INT32_MAX || d[j] < INT32_MIN)) {
+        return false;
+      }
+      if (exists[j] && set[j] && cur[j] != d[j]) {
+        conflict = true;
+      }
+    }
+    if (conflict) {
+      if (runs.size() / 4 >= (std::size_t{1} << runBits)) {
+        return false;
+      }
+      runs.insert(runs.end(), {0, 0, 0, 0});
+      std::fill(set, set + 4, false);
+      open = true;
+    }
+    const std::size_t run = runs.size() / 4 - 1;
+    for (int j = 0; j < 4; ++j) {
+      if (exists[j]) {
+        if (!set[j]) {
+          set[j] = true;
+          cur[j] = d[j];
+          runs[4 * run + j] = static_cast<int>(d[j]);
+        }
+        flags |= (j == 0 ? 1u : j == 1 ? 2u : j == 2 ? 16u : 32u);
+      }
+    }
+    codes[i] = static_cast<uint32_t>(run) | (flags << runBits) | memb;
+  }
+  return true;
+}
+} // namespace
+
+bool compressNeighbourTable(const uint32_t *nn, uint64_t n,
+                            std::vector<uint32_t> &codes,
+                            std::vector<int> &runs) {
+  return compressNeighbours(std::vector<uint32_t>(nn, nn + 6 * n), n, codes,
+                            runs);
 }
 
 // ---- geometry path per compartment -------------------------------------------
@@ -992,7 +1076,16 @@ void Sim::build(const smeb200_problem &p) {
                           nv * sizeof(double), cudaMemcpyHostToDevice, stream),
           "upload initial concentrations");
     if (!c.box) {
-      c.dNn = devUpload(nnHost[ci], stream, "upload neighbour list");
+      std::vector<uint32_t> codes;
+      std::vector<int> runs;
+      if (p.kernel_variant != 3 && compressNeighbours(nnHost[ci], c.n, codes, runs)) {
+        c.nRuns = static_cast<uint32_t>(runs.size() / 4);
+        c.dNn = devUpload(codes, stream, "upload neighbour codes");
+        c.dRuns = devUpload(runs, stream, "upload neighbour runs");
+        check(cudaStreamSynchronize(stream), "upload neighbour codes");
+      } else {
+        c.dNn = devUpload(nnHost[ci], stream, "upload neighbour list");
+      }
     }
     if (c.geom == Geom::TILE) {
       encodeTensorMaps(c);
@@ -1264,6 +1357,7 @@ Sim::~Sim() {
       cudaFree(b);
     }
     cudaFree(c.dNn);
+    cudaFree(c.dRuns);
     cudaFree(c.dMvox);
     cudaFree(c.dMstart);
     cudaFree(c.dEnt);
@@ -1319,6 +1413,7 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     a.cout = c.buf[c.role[sd.cout]];
     a.c0 = c.buf[c.role[CUR]];
     a.nn = c.dNn;
+    a.runs = c.dRuns;
     a.err = dErr;
     a.n = static_cast<uint32_t>(c.n - c.vGhostHi);
     a.v0 = c.vGhostLo;
@@ -1388,7 +1483,8 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     check(cudaEventRecord(timerEvents[timerUsed].first, stream),
           "cudaEventRecord");
   }
-  const unsigned persistent = static_cast<unsigned>(smCount) * 8u;
+  const unsigned persistent =
+      c.geom == Geom::TILE ? 0u : persistentGrid(k.main);
   if (c.geom == Geom::TILE) {
     uint32_t chunk = c.tile.chunk;
     void *params[] = {&a, &c.tmap[cinBuf], &chunk};
@@ -1432,7 +1528,7 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     }
     blob[4 + comps.size()] = static_cast<unsigned long long>(c.nMvox);
     const unsigned mgrid =
-        std::min((c.nMvox + BLOCK - 1) / BLOCK, persistent);
+        std::min((c.nMvox + BLOCK - 1) / BLOCK, persistentGrid(k.memb));
     StageArgsHost am = a;
     if (nsPrepass) { // the membrane voxels' partial sums follow the main ones
       am.nsPartial = a.nsPartial + nsBlocks * c.nonSpatial.size();
@@ -1458,6 +1554,26 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
           "launch non-spatial average kernel");
     ++launchCount;
   }
+}
+
+// Grid-stride kernels are launched as exactly one wave of resident CTAs: with
+// more CTAs than fit (e.g. 8 per SM when 6 are resident) the second, partial
+// wave runs at a fraction of the occupancy while holding a full share of the
+// work (ncu: 53 % achieved warps on smeb_stage_nn before this).
+unsigned Sim::persistentGrid(CUfunction f) {
+  if (auto it = persistentGridOf.find(f); it != persistentGridOf.end()) {
+    return it->second;
+  }
+  int perSm = 0;
+  const auto &drv = DriverApi::get();
+  if (drv.OccupancyMaxActiveBlocksPerMultiprocessor(
+          &perSm, f, static_cast<int>(BLOCK), 0) != CUDA_SUCCESS ||
+      perSm <= 0) {
+    perSm = 4;
+  }
+  const unsigned g = static_cast<unsigned>(smCount) * static_cast<unsigned>(perSm);
+  persistentGridOf[f] = g;
+  return g;
 }
 
 void Sim::flushTimers() {

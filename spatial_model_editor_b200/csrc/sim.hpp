@@ -35,6 +35,7 @@ struct StageArgsHost {
   double *s2out;
   double *cout;
   const uint32_t *nn;
+  const int *runs;
   unsigned long long *err;
   const double *nsAv;
   double *nsPartial;
@@ -127,6 +128,8 @@ struct CompartmentState {
   CUtensorMap tmap[4]{};
   int role[4]{0, 1, 2, 3};
   uint32_t *dNn{nullptr};
+  int *dRuns{nullptr};               // run table of the compressed neighbour codes
+  uint32_t nRuns{0};
   uint32_t nMvox{0};
   uint32_t *dMvox{nullptr};
   uint32_t *dMstart{nullptr};
@@ -145,6 +148,12 @@ struct CompartmentState {
   int lastCinBuf{0};
   uint32_t lastFlags{0};
 };
+
+// run-compressed neighbour codes of a voxel-list compartment (sim.cpp); false if
+// the table does not have the reference's voxel-order structure
+bool compressNeighbourTable(const uint32_t *nn, uint64_t n,
+                            std::vector<uint32_t> &codes,
+                            std::vector<int> &runs);
 
 class Sim {
 public:
@@ -187,6 +196,13 @@ public:
   bool compileOnly{false};
   std::size_t cubinBytes{0};
   std::size_t nCompartments() const { return comps.size(); }
+  // bytes of neighbour-index data the stage kernels read per voxel: 0 (box,
+  // implicit), 4 (run-compressed codes) or 24 (plain table)
+  std::size_t neighbourBytesPerVoxel(std::size_t comp) const {
+    const auto &c = comps.at(comp);
+    return c.box ? 0 : (c.dRuns != nullptr ? 4 : 24);
+  }
+  std::size_t neighbourRuns(std::size_t comp) const { return comps.at(comp).nRuns; }
   std::size_t concentrationPadding() const {
     std::size_t pad = 0;
     for (const auto &c : comps) {
@@ -234,6 +250,10 @@ private:
   void connectSlabs();
   void haloExchange(int coutBuf);
   void updateCrossDiffusionMaxStableTimestep();
+  // one full wave of resident CTAs for a grid-stride kernel: SMs x the CTAs of
+  // this kernel that fit on one SM (cached per function)
+  unsigned persistentGrid(CUfunction f);
+  std::map<CUfunction, unsigned> persistentGridOf;
   double h2[3]{1.0, 1.0, 1.0}; // voxel width^2, height^2, depth^2
   bool anyCross{false};
   unsigned long long *hXdMax{nullptr}; // pinned

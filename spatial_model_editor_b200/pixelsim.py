@@ -61,6 +61,8 @@ def _bind(lib, prefix: str):
     fn("compile_only", C.c_int, [C.POINTER(CProblem), C.POINTER(vp)], optional=True)
     fn("get_concentration_padding", C.c_size_t, [vp], optional=True)
     fn("set_error", None, [vp, C.c_char_p], optional=True)
+    fn("neighbour_bytes_per_voxel", C.c_size_t, [vp, C.c_size_t], optional=True)
+    fn("neighbour_runs", C.c_size_t, [vp, C.c_size_t], optional=True)
     fn("get_avg_min_max", C.c_int, [vp, C.c_size_t, C.POINTER(C.c_double), C.c_size_t],
        optional=True)
     fn("bench_steps", C.c_double, [vp, C.c_double, C.c_size_t], optional=True)
@@ -270,6 +272,13 @@ class PixelSim(CSim):
         if rc != 0:
             raise RuntimeError(self.errorMessage())
         return out
+
+    def neighbourBytesPerVoxel(self, compartmentIndex: int) -> int:
+        """0 (box), 4 (run-compressed neighbour codes) or 24 (plain table)"""
+        return int(self._f("neighbour_bytes_per_voxel")(self._h, compartmentIndex))
+
+    def neighbourRuns(self, compartmentIndex: int) -> int:
+        return int(self._f("neighbour_runs")(self._h, compartmentIndex))
 
     def dominantKernel(self) -> str:
         return self._f("dominant_kernel")(self._h).decode()

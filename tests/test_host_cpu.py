@@ -1,5 +1,8 @@
 """Host-side logic: geometry tables, expression printing, RHS assembly."""
 import numpy as np
+import pytest
+
+import spatial_model_editor_b200 as smeb
 
 from spatial_model_editor_b200 import expr as E
 from spatial_model_editor_b200 import geometry as G
@@ -75,3 +78,73 @@ def test_two_compartment_problem_tables():
     for d in range(6):
         for ia, ib in m.pairs[d]:
             assert ia < a.n_voxels and ib < b.n_voxels
+
+
+# ---- run-compressed neighbour codes (device layout of voxel-list compartments) ----
+def _compress(nn):
+    import ctypes as C
+    lib = smeb.load_library()
+    lib.smeb200_compress_neighbours.restype = C.c_int
+    lib.smeb200_compress_neighbours.argtypes = [
+        C.POINTER(C.c_uint32), C.c_uint64, C.POINTER(C.c_uint32), C.POINTER(C.c_int32),
+        C.POINTER(C.c_uint64)]
+    nn = np.ascontiguousarray(nn, dtype=np.uint32)
+    n = nn.shape[0]
+    codes = np.zeros(n, dtype=np.uint32)
+    runs = np.zeros((max(n, 1), 4), dtype=np.int32)
+    n_runs = C.c_uint64(runs.shape[0])
+    rc = lib.smeb200_compress_neighbours(
+        nn.ctypes.data_as(C.POINTER(C.c_uint32)), n,
+        codes.ctypes.data_as(C.POINTER(C.c_uint32)),
+        runs.ctypes.data_as(C.POINTER(C.c_int32)), C.byref(n_runs))
+    return rc, codes, runs[:n_runs.value]
+
+
+def _decode(codes, runs):
+    """what smeb_neighbours (device_kernels.cuh) computes"""
+    i = np.arange(len(codes), dtype=np.int64)
+    run = (codes & ((1 << 25) - 1)).astype(np.int64)
+    fl = (codes >> 25) & 63
+    d = runs[run].astype(np.int64)
+    nb = np.stack([np.where(fl & 1, i + d[:, 0], i), np.where(fl & 2, i + d[:, 1], i),
+                   np.where(fl & 4, i + 1, i), np.where(fl & 8, i - 1, i),
+                   np.where(fl & 16, i + d[:, 2], i), np.where(fl & 32, i + d[:, 3], i)], axis=1)
+    return nb.astype(np.uint32), (codes >> 31).astype(bool)
+
+
+@pytest.mark.parametrize("case", ["disc", "cell3d", "blob", "speckle"])
+def test_neighbour_codes_decode_to_the_reference_table(case):
+    from spatial_model_editor_b200 import geometry as G
+    rng = np.random.default_rng(3)
+    if case == "disc":
+        lab = M.disc_labels(100, 100, inner_fraction=0.5)
+    elif case == "cell3d":
+        lab = np.ones((9, 14, 11), dtype=np.int32)
+        lab[2:7, 3:10, 4:9] = 2
+    elif case == "blob":
+        z, y, x = np.meshgrid(np.arange(20), np.arange(24), np.arange(28), indexing="ij")
+        lab = (((x - 13) ** 2 + (y - 11) ** 2 + 2 * (z - 9) ** 2 < 90)
+               | ((x - 20) ** 2 + (y - 6) ** 2 + (z - 14) ** 2 < 30)).astype(np.int32)
+    else:  # random speckle: many short runs, several runs per column
+        lab = (rng.uniform(size=(4, 30, 30)) < 0.6).astype(np.int32)
+    for label in [v for v in np.unique(lab) if v != 0]:
+        vox = G.compartment_voxels(lab, int(label))
+        nn = G.neighbour_table(lab.shape, vox)
+        flagged = nn.copy()
+        memb = rng.uniform(size=len(vox)) < 0.1
+        flagged[memb, 0] |= np.uint32(0x80000000)
+        rc, codes, runs = _compress(flagged)
+        assert rc == 0
+        dec, mflag = _decode(codes, runs)
+        assert np.array_equal(dec, nn)
+        assert np.array_equal(mflag, memb)
+        if case == "disc":  # one run per column, give or take the rim
+            assert len(runs) < 4 * 100
+
+
+def test_neighbour_codes_refuse_foreign_orderings():
+    """a table whose +y neighbour is not i + 1 (not the reference's voxel order) keeps
+    the plain layout"""
+    nn = np.array([[1, 0, 2, 0, 0, 0], [1, 0, 1, 1, 1, 1], [2, 2, 2, 0, 2, 2]], dtype=np.uint32)
+    rc, _, _ = _compress(nn)
+    assert rc == 1
