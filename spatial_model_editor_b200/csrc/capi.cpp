@@ -160,12 +160,7 @@ int smeb200_set_concentrations(smeb200_sim *sim, size_t compartment,
 }
 
 int smeb200_set_params(smeb200_sim *sim, const double *values, size_t n) {
-  return guarded(sim, [&] {
-    if (n != sim->impl.params.size()) {
-      throw smeb200::Error("set_params: wrong number of values");
-    }
-    sim->impl.params.assign(values, values + n);
-  });
+  return guarded(sim, [&] { sim->impl.setParams(values, n); });
 }
 
 const char *smeb200_error(const smeb200_sim *sim) {

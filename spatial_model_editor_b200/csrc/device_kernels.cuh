@@ -71,6 +71,10 @@ template <int S> struct SmebStageArgs {
   smeb_u32 nx, ny, nz; // box dims; voxel = (z*nx + x)*ny + y
   smeb_u32 z_begin, z_end; // planes updated by this launch (ghosts excluded)
   double g1, g2, g3, bdt, delta; // stage coefficients (bdt = beta*dt)
+  // CUDA-graph replay of a step: the step size lives in device memory (a
+  // captured launch cannot carry a new bdt); bdt = beta * *dtp when dtp != 0
+  double beta;
+  const double *dtp;
   double cF, s2F, s3F, eps;      // finalise factors, error epsilon
   // D/dx^2, D/dy^2, D/dz^2 per species, then the runtime model parameters
   // (values of sme_param_k: scanned parameters of an ensemble stay symbolic so
@@ -245,6 +249,8 @@ smeb_update(const SmebStageArgs<R::S> &a, const double *c, const double *fin,
     }
     return;
   }
+  // same product as the host's sd.beta * dt
+  const double bdt = a.dtp != nullptr ? a.beta * (*a.dtp) : a.bdt;
   double cn[S];
 #pragma unroll
   for (int s = 0; s < S; ++s) {
@@ -252,11 +258,11 @@ smeb_update(const SmebStageArgs<R::S> &a, const double *c, const double *fin,
       s2v[s] = s2v[s] + a.delta * c[s];
     }
     if constexpr ((F & SMEB_F_GENERIC) != 0) {
-      cn[s] = a.g1 * c[s] + a.g2 * s2v[s] + a.g3 * c0v[s] + a.bdt * f[s];
+      cn[s] = a.g1 * c[s] + a.g2 * s2v[s] + a.g3 * c0v[s] + bdt * f[s];
     } else if constexpr ((F & SMEB_F_USE_C0) != 0) {
-      cn[s] = a.g3 * c0v[s] + a.g1 * c[s] + a.bdt * f[s];
+      cn[s] = a.g3 * c0v[s] + a.g1 * c[s] + bdt * f[s];
     } else {
-      cn[s] = c[s] + a.bdt * f[s];
+      cn[s] = c[s] + bdt * f[s];
     }
   }
   if constexpr ((F & SMEB_F_FINAL) != 0) {

@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <sstream>
@@ -1092,6 +1093,13 @@ void Sim::build(const smeb200_problem &p) {
     }
     for (const auto &sd : plan) {
       c.kStage.push_back(lookup(mainModule, ci, sd.flags()));
+      // occupancy queries up front: none while a step is being captured
+      if (c.geom != Geom::TILE && c.kStage.back().main != nullptr) {
+        persistentGrid(c.kStage.back().main);
+      }
+      if (c.kStage.back().memb != nullptr) {
+        persistentGrid(c.kStage.back().memb);
+      }
     }
     if (c.nonUniform) {
       c.dDarr = devAlloc<double>(nv, "allocate diffusion constant array");
@@ -1108,6 +1116,12 @@ void Sim::build(const smeb200_problem &p) {
     }
     if (!c.nonSpatial.empty()) {
       c.kSumNs = lookup(mainModule, ci, F_SUM_NS);
+      if (c.geom != Geom::TILE && c.kSumNs.main != nullptr) {
+        persistentGrid(c.kSumNs.main);
+      }
+      if (c.kSumNs.memb != nullptr) {
+        persistentGrid(c.kSumNs.memb);
+      }
       const std::size_t nns = c.nonSpatial.size();
       const uint32_t mainBlocks =
           c.geom == Geom::TILE
@@ -1134,6 +1148,39 @@ void Sim::build(const smeb200_problem &p) {
   check(cudaMemsetAsync(dErr, 0, 32, stream), "clear error accumulators");
   check(cudaMallocHost(reinterpret_cast<void **>(&hErr), 16),
         "allocate pinned error mirror");
+  check(cudaMallocHost(reinterpret_cast<void **>(&hDt), sizeof(double)),
+        "allocate pinned step size");
+  dDt = devAlloc<double>(1, "allocate step size");
+  {
+    // graphs pay off where a step is launch bound; SMEB200_GRAPHS=0/1 overrides
+    uint64_t values = 0;
+    for (const auto &c : comps) {
+      values += c.n * c.S;
+    }
+    useGraphs = !comm && values <= (uint64_t{1} << 22);
+    if (const char *env = std::getenv("SMEB200_GRAPHS"); env != nullptr) {
+      useGraphs = !comm && env[0] == '1';
+    }
+    std::size_t active = 0;
+    for (const auto &c : comps) {
+      active += c.S > 0 && c.n > 0 ? 1 : 0;
+    }
+    if (useGraphs && (active > 1 || nMembranes > 0)) {
+      // capture-time fork streams: two per compartment (main, membrane)
+      check(cudaEventCreateWithFlags(&forkEvent, cudaEventDisableTiming),
+            "cudaEventCreate");
+      for (std::size_t k = 0; k < 2 * comps.size(); ++k) {
+        cudaStream_t s{};
+        cudaEvent_t e{};
+        check(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking),
+              "cudaStreamCreate");
+        check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming),
+              "cudaEventCreate");
+        forkStreams.push_back(s);
+        joinEvents.push_back(e);
+      }
+    }
+  }
   check(cudaStreamSynchronize(stream), "initial upload");
   if (anyCross) {
     check(cudaMallocHost(reinterpret_cast<void **>(&hXdMax),
@@ -1374,6 +1421,22 @@ Sim::~Sim() {
   cudaFree(dErr);
   cudaFreeHost(hErr);
   cudaFreeHost(hXdMax);
+  cudaFreeHost(hDt);
+  cudaFree(dDt);
+  for (auto s2 : forkStreams) {
+    cudaStreamDestroy(s2);
+  }
+  for (auto e : joinEvents) {
+    cudaEventDestroy(e);
+  }
+  if (forkEvent != nullptr) {
+    cudaEventDestroy(forkEvent);
+  }
+  for (auto &[k, g] : stepGraphs) {
+    if (g.exec != nullptr) {
+      cudaGraphExecDestroy(g.exec);
+    }
+  }
   if (runEv0 != nullptr) {
     cudaEventDestroy(runEv0);
     cudaEventDestroy(runEv1);
@@ -1403,6 +1466,15 @@ Sim::~Sim() {
 void Sim::launchStage(std::size_t stageIndex, double dt) {
   const StageDesc &sd = plan[stageIndex];
   const bool last = stageIndex + 1 == plan.size();
+  // Captured step: within a stage the kernels of different compartments, and a
+  // compartment's main and membrane kernels, touch disjoint voxels and only read
+  // the stage input, so they become parallel branches of the graph (a step of a
+  // small multi-compartment model is a chain of latencies otherwise).
+  const bool fork = capturing && !forkStreams.empty();
+  std::size_t forksUsed = 0;
+  if (fork) {
+    check(cudaEventRecord(forkEvent, stream), "fork event");
+  }
   for (std::size_t ci = 0; ci < comps.size(); ++ci) {
     auto &c = comps[ci];
     if (c.S == 0 || c.n == 0) {
@@ -1434,6 +1506,8 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     a.g2 = sd.g2;
     a.g3 = sd.g3;
     a.bdt = sd.beta * dt;
+    a.beta = sd.beta;
+    a.dtp = capturing ? dDt : nullptr;
     a.delta = sd.delta;
     a.cF = sd.cF;
     a.s2F = sd.s2F;
@@ -1441,6 +1515,17 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     a.eps = epsilon;
     std::copy(c.D.begin(), c.D.end(), a.D);
     std::copy(params.begin(), params.end(), a.D + 3 * c.S);
+    if (fork && forksUsed + 2 <= forkStreams.size()) {
+      forkMain = forkStreams[forksUsed];
+      // with a pre-pass the membrane kernels stay ordered with the main ones
+      forkMemb = c.nonSpatial.empty() && c.nMvox > 0 ? forkStreams[forksUsed + 1]
+                                                     : forkMain;
+      check(cudaStreamWaitEvent(forkMain, forkEvent, 0), "fork wait");
+      if (forkMemb != forkMain) {
+        check(cudaStreamWaitEvent(forkMemb, forkEvent, 0), "fork wait");
+      }
+      forksUsed += 2;
+    }
     a.nsAv = c.dNsAv;
     a.nsPartial = c.dNsPartial;
     a.darr = c.dDarr;
@@ -1452,6 +1537,16 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
       launchCompartment(ci, a, c.kSumNs, c.role[sd.cin], true);
     }
     launchCompartment(ci, a, c.kStage[stageIndex], c.role[sd.cin]);
+    if (forkMain != nullptr) { // join the branches of this compartment
+      const bool two = forkMemb != forkMain;
+      check(cudaEventRecord(joinEvents[forksUsed - 2], forkMain), "join event");
+      check(cudaStreamWaitEvent(stream, joinEvents[forksUsed - 2], 0), "join");
+      if (two) {
+        check(cudaEventRecord(joinEvents[forksUsed - 1], forkMemb), "join event");
+        check(cudaStreamWaitEvent(stream, joinEvents[forksUsed - 1], 0), "join");
+      }
+      forkMain = forkMemb = nullptr;
+    }
     if (last) {
       c.last = a;
       c.lastCinBuf = c.role[sd.cin];
@@ -1473,6 +1568,10 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
   auto &c = comps[ci];
   const bool timed = kernelTiming && ci == dominantComp && !nsPrepass;
   uint32_t nsBlocks = 0; // blocks that wrote partial sums (pre-pass)
+  // while a step is captured the kernels of one stage fork onto per-compartment
+  // streams (parallel graph branches); otherwise everything is on `stream`
+  cudaStream_t sMain = forkMain != nullptr ? forkMain : stream;
+  cudaStream_t sMemb = forkMemb != nullptr ? forkMemb : stream;
   if (timed) {
     if (timerUsed == timerEvents.size()) {
       cudaEvent_t e0{}, e1{};
@@ -1489,7 +1588,7 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     uint32_t chunk = c.tile.chunk;
     void *params[] = {&a, &c.tmap[cinBuf], &chunk};
     check(drv.LaunchKernel(k.main, c.tile.grid[0], c.tile.grid[1],
-                           c.tile.grid[2], BLOCK, 1, 1, c.tile.dynSmem, stream,
+                           c.tile.grid[2], BLOCK, 1, 1, c.tile.dynSmem, sMain,
                            params, nullptr),
           "launch tile stage kernel");
     nsBlocks = c.tile.grid[0] * c.tile.grid[1] * c.tile.grid[2];
@@ -1501,7 +1600,7 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     const unsigned grid = static_cast<unsigned>(std::max<uint64_t>(
         1, std::min<uint64_t>((work + BLOCK - 1) / BLOCK, persistent)));
     void *params[] = {&a};
-    check(drv.LaunchKernel(k.main, grid, 1, 1, BLOCK, 1, 1, 0, stream, params,
+    check(drv.LaunchKernel(k.main, grid, 1, 1, BLOCK, 1, 1, 0, sMain, params,
                            nullptr),
           "launch stage kernel");
     nsBlocks = grid;
@@ -1535,7 +1634,7 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
       nsBlocks += mgrid;
     }
     void *mparams[] = {&am, blob.data()};
-    check(drv.LaunchKernel(k.memb, mgrid, 1, 1, BLOCK, 1, 1, 0, stream,
+    check(drv.LaunchKernel(k.memb, mgrid, 1, 1, BLOCK, 1, 1, 0, sMemb,
                            mparams, nullptr),
           "launch membrane stage kernel");
     ++launchCount;
@@ -1550,7 +1649,7 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     double *av = c.dNsAv;
     void *fparams[] = {&partial, &nsBlocks, &nns, &nVox, &av};
     check(drv.LaunchKernel(mainModule.fn.at(kNsFinishKernel), 1, 1, 1, BLOCK, 1,
-                           1, 0, stream, fparams, nullptr),
+                           1, 0, sMain, fparams, nullptr),
           "launch non-spatial average kernel");
     ++launchCount;
   }
@@ -1592,9 +1691,106 @@ void Sim::flushTimers() {
   timerUsed = 0;
 }
 
-void Sim::doStep(double dt) {
+void Sim::setParams(const double *values, std::size_t n) {
+  if (n != params.size()) {
+    throw Error("set_params: wrong number of values");
+  }
+  params.assign(values, values + n);
+  if (stream != nullptr && !stepGraphs.empty()) {
+    bindDevice();
+    check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+    for (auto &[k, g] : stepGraphs) {
+      if (g.exec != nullptr) {
+        cudaGraphExecDestroy(g.exec);
+      }
+    }
+    stepGraphs.clear();
+  }
+}
+
+void Sim::launchAllStages(double dt) {
   for (std::size_t i = 0; i < plan.size(); ++i) {
     launchStage(i, dt);
+  }
+}
+
+// One cudaGraphLaunch per step instead of (stages x compartments x {main,
+// membrane, pre-pass}) kernel launches plus the error-norm copies: what a step
+// costs for the small models (ABtoC, liver-simplified ensembles) is launch
+// latency, not bandwidth.
+void Sim::graphStep(double dt) {
+  uint32_t key = 0;
+  if (!comps.empty()) {
+    for (int b = 0; b < 4; ++b) {
+      key = key * 4u + static_cast<uint32_t>(comps[0].role[b]);
+    }
+  }
+  auto it = stepGraphs.find(key);
+  if (it == stepGraphs.end()) {
+    StepGraph g;
+    const uint64_t launches0 = launchCount;
+    cudaGraph_t graph{};
+    check(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal),
+          "cudaStreamBeginCapture");
+    capturing = true;
+    try {
+      check(cudaMemcpyAsync(dDt, hDt, sizeof(double), cudaMemcpyHostToDevice,
+                            stream),
+            "capture step size upload");
+      launchAllStages(dt);
+      if (integrator != SMEB200_RK101) {
+        check(cudaMemcpyAsync(hErr, dErr, 16, cudaMemcpyDeviceToHost, stream),
+              "capture error norm download");
+        check(cudaMemsetAsync(dErr, 0, 16, stream), "capture error norm clear");
+      }
+    } catch (...) {
+      capturing = false;
+      cudaStreamEndCapture(stream, &graph);
+      if (graph != nullptr) {
+        cudaGraphDestroy(graph);
+      }
+      throw;
+    }
+    capturing = false;
+    check(cudaStreamEndCapture(stream, &graph), "cudaStreamEndCapture");
+    g.launches = launchCount - launches0;
+    launchCount = launches0;
+    const cudaError_t e = cudaGraphInstantiate(&g.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    check(e, "cudaGraphInstantiate");
+    for (auto &c : comps) {
+      g.last.push_back({c.last, c.lastCinBuf, c.lastFlags});
+    }
+    it = stepGraphs.emplace(key, std::move(g)).first;
+  }
+  if (dt != graphDt) {
+    // the upload node of an earlier, still running replay reads hDt
+    if (integrator == SMEB200_RK101) {
+      check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+    }
+    *hDt = dt;
+    graphDt = dt;
+  }
+  check(cudaGraphLaunch(it->second.exec, stream), "cudaGraphLaunch");
+  launchCount += it->second.launches;
+  errCopyInGraph = integrator != SMEB200_RK101;
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    auto &c = comps[ci];
+    if (c.S == 0 || c.n == 0) {
+      continue;
+    }
+    c.last = it->second.last[ci].last;
+    c.lastCinBuf = it->second.last[ci].lastCinBuf;
+    c.lastFlags = it->second.last[ci].lastFlags;
+    c.haveLast = true;
+  }
+}
+
+void Sim::doStep(double dt) {
+  if (useGraphs && !kernelTiming) {
+    graphStep(dt);
+  } else {
+    launchAllStages(dt);
   }
   for (auto &c : comps) {
     c.dcdtStale = true;
@@ -1616,9 +1812,13 @@ void Sim::rotateAfterAccept() {
 }
 
 void Sim::readError(double &eabs, double &erel) {
-  check(cudaMemcpyAsync(hErr, dErr, 16, cudaMemcpyDeviceToHost, stream),
-        "download error norms");
-  check(cudaMemsetAsync(dErr, 0, 16, stream), "clear error accumulators");
+  if (errCopyInGraph) {
+    errCopyInGraph = false; // the replayed graph ends with these two nodes
+  } else {
+    check(cudaMemcpyAsync(hErr, dErr, 16, cudaMemcpyDeviceToHost, stream),
+          "download error norms");
+    check(cudaMemsetAsync(dErr, 0, 16, stream), "clear error accumulators");
+  }
   check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
   double v[2];
   std::memcpy(v, hErr, 16);

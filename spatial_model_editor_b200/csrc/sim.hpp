@@ -47,6 +47,8 @@ struct StageArgsHost {
   uint32_t nx, ny, nz;
   uint32_t z_begin, z_end;
   double g1, g2, g3, bdt, delta;
+  double beta;
+  const double *dtp;
   double cF, s2F, s3F, eps;
   double D[3 * 64 + 64]; // + runtime parameters
 };
@@ -169,6 +171,9 @@ public:
   double getLowerOrder(std::size_t comp, std::size_t species, std::size_t pixel);
   void setConcentrations(std::size_t comp, const double *data, std::size_t n);
   void getAvgMinMax(std::size_t comp, double *out, std::size_t nOut);
+  // new values of the runtime parameters: captured step graphs carry the old
+  // ones in their kernel arguments and are dropped
+  void setParams(const double *values, std::size_t n);
   double benchSteps(double dt, std::size_t nSteps);
 
   std::string errorMessage;
@@ -234,6 +239,33 @@ private:
   void makePlan();
   void bindDevice() const;
   void doStep(double dt); // all stages of one RK step
+  void launchAllStages(double dt);
+  void graphStep(double dt);
+  // CUDA-graph replay of a whole step (all stage launches of all compartments,
+  // the error-norm download): for small models a step is launch-latency bound.
+  // One graph per rotation state of the buffers; the step size is read from
+  // device memory (dDt), refreshed from pinned hDt by the graph's first node.
+  struct LastRecord {
+    StageArgsHost last;
+    int lastCinBuf;
+    uint32_t lastFlags;
+  };
+  struct StepGraph {
+    cudaGraphExec_t exec{nullptr};
+    uint64_t launches{0};
+    std::vector<LastRecord> last;
+  };
+  std::map<uint32_t, StepGraph> stepGraphs;
+  bool useGraphs{false};
+  bool capturing{false};
+  bool errCopyInGraph{false}; // the replayed step already queued the download
+  double *hDt{nullptr};       // pinned
+  double *dDt{nullptr};
+  double graphDt{-1.0};
+  std::vector<cudaStream_t> forkStreams; // capture-time parallel branches
+  std::vector<cudaEvent_t> joinEvents;
+  cudaEvent_t forkEvent{nullptr};
+  cudaStream_t forkMain{nullptr}, forkMemb{nullptr};
   void launchStage(std::size_t stageIndex, double dt);
   void launchCompartment(std::size_t ci, StageArgsHost &a,
                          const StageKernels &k, int cinBuf,

@@ -214,3 +214,31 @@ def test_ctor_and_run_on_different_threads():
     t.join()
     assert out["n"] == cpu.run(0.1)
     compare_state(gpu, cpu, p, "threads")
+
+
+# ---- CUDA-graph replay of a step (small models) vs plain launches -----------------
+@pytest.mark.parametrize("name", ["liver-simplified", "very-simple-model", "ABtoC"])
+@pytest.mark.parametrize("integ", [smeb.RK101, smeb.RK212, smeb.RK435])
+def test_graph_replay_is_bit_identical_to_plain_launches(name, integ, monkeypatch):
+    """one cudaGraphLaunch per step (step size read from device memory) gives the
+    bits of the kernel-by-kernel path, same step sequence, same on-demand outputs"""
+    import sys, os
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from util import load_golden
+    out = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("SMEB200_GRAPHS", mode)
+        p, _, _ = load_golden(name, integrator=integ)
+        p.device = 0
+        sim = smeb.PixelSim(p)
+        assert sim.errorMessage() == ""
+        n = sim.run(0.05) + sim.run(0.05)
+        out[mode] = (n, sim.discardedSteps, sim.launchCount(),
+                     [sim.getConcentrations(i).copy() for i in range(len(p.compartments))],
+                     [sim.getDcdt(i).copy() for i in range(len(p.compartments))],
+                     sim.getLowerOrderConcentration(0, 0, 3))
+    g, pl = out["1"], out["0"]
+    assert g[0] == pl[0] and g[1] == pl[1] and g[2] == pl[2]
+    for a, b in zip(g[3] + g[4], pl[3] + pl[4]):
+        assert np.array_equal(a, b)
+    assert g[5] == pl[5]
