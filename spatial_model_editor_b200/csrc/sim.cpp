@@ -495,6 +495,8 @@ bool compressNeighbourTable(const uint32_t *nn, uint64_t n,
                             runs);
 }
 
+constexpr unsigned SMEB_TILE_CTAS_PER_SM = 2; // device_kernels.cuh SMEB_TILE_MIN_CTAS
+
 // ---- geometry path per compartment -------------------------------------------
 // Box compartments (implicit neighbours) use the TMA tile-marching kernel when
 // the array can be described by a tensor map (16-byte row pitch) and the tile
@@ -561,14 +563,54 @@ void Sim::chooseGeometry(int variant) {
       continue;
     }
     const unsigned tilesY = (c.ny + t.ty - 1) / t.ty;
-    const unsigned target = static_cast<unsigned>(smCount) * 2u * 4u;
+    // Split of the march direction into chunks: the CTA count should fill whole
+    // waves of resident CTAs (2 per SM) — a last wave that is 10 % full costs a
+    // full CTA's time at a fraction of the bandwidth — while every chunk re-reads
+    // its halo (2 planes in 3-D, 2 rows of a brick in 2-D).  Pick the chunk count
+    // with the least (wave rounding x halo re-read) cost among those that give
+    // at least two waves.
+    const unsigned wave = static_cast<unsigned>(smCount) * SMEB_TILE_CTAS_PER_SM;
+    auto pickChunks = [&](unsigned units, unsigned tiles, double haloUnits) {
+      unsigned best = 1;
+      double bestCost = 1e300;
+      const unsigned maxChunks = std::min(units, 65535u);
+      if (static_cast<double>(tiles) * units < 2.0 * wave) {
+        // too small to fill the GPU whatever the split: chunks of ~8 units
+        return std::max(1u, units / 8u);
+      }
+      for (unsigned chunks = 1; chunks <= maxChunks; ++chunks) {
+        const unsigned chunk = (units + chunks - 1) / chunks;
+        const unsigned used = (units + chunk - 1) / chunk; // non-empty chunks
+        if (used != chunks) {
+          continue;
+        }
+        const double total = static_cast<double>(tiles) * chunks;
+        if (total < 2.0 * wave && chunks < maxChunks && chunk > 1) {
+          continue;
+        }
+        const double waves = std::ceil(total / wave);
+        const double cost =
+            waves * wave / total * (chunk + haloUnits) / chunk;
+        if (cost < bestCost - 1e-12) {
+          bestCost = cost;
+          best = chunks;
+        }
+        if (total > 64.0 * wave) {
+          break;
+        }
+      }
+      return best;
+    };
+    unsigned forced = 0;
+    if (const char *env = std::getenv("SMEB200_TILE_CHUNKS"); env != nullptr) {
+      forced = static_cast<unsigned>(std::atoi(env));
+    }
     if (t.m3) {
       const unsigned tilesX = (c.nx + t.tx - 1) / t.tx;
       const unsigned owned = c.nz - c.zLoGhost - c.zHiGhost;
       const unsigned tiles = tilesX * tilesY;
-      unsigned chunks = std::max(1u, std::min(owned, (target + tiles - 1) / tiles));
+      unsigned chunks = forced ? std::min(forced, owned) : pickChunks(owned, tiles, 2.0);
       unsigned chunk = (owned + chunks - 1) / chunks;
-      chunk = std::max(chunk, std::min(owned, 32u));
       chunks = (owned + chunk - 1) / chunk;
       t.chunk = chunk;
       t.grid[0] = tilesY;
@@ -576,10 +618,9 @@ void Sim::chooseGeometry(int variant) {
       t.grid[2] = chunks;
     } else {
       const unsigned bricks = (c.nx + t.tx - 1) / t.tx;
-      unsigned chunks =
-          std::max(1u, std::min(bricks, (target + tilesY - 1) / tilesY));
+      unsigned chunks = forced ? std::min(forced, bricks)
+                               : pickChunks(bricks, tilesY, 2.0 / t.tx);
       unsigned chunk = (bricks + chunks - 1) / chunks;
-      chunk = std::max(chunk, std::min(bricks, 8u));
       chunks = (bricks + chunk - 1) / chunk;
       t.chunk = chunk;
       t.grid[0] = tilesY;
