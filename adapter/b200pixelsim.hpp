@@ -243,7 +243,7 @@ public:
           const bool isConstant{
               doc.getSpecies().getIsConstant(speciesId.c_str())};
           // pixelsim_impl.cpp:214-232; storage 0 (algebraic species) is
-          // passed as 0 and refused by the library
+          // passed as 0: the library relaxes it like pixelsim.cpp:23-90
           const double storage{
               doc.getSpecies().getStorage(speciesId.c_str())};
           if (storage < 0.0) {

@@ -101,8 +101,12 @@ typedef struct smeb200_compartment {
   uint32_t n_non_spatial;
   const uint32_t *non_spatial;  /* [n_non_spatial] species indices */
   /* [n_species] 1/storage per state component (pixelsim_impl.cpp:165-189,
-   * 214-232); NULL = unit storage.  A zero entry (zero-storage species,
-   * algebraic constraint) is rejected. */
+   * 214-232); NULL = unit storage.  A zero entry marks a zero-storage species
+   * (algebraic constraint 0 = R(c) + div(D grad c)): it is relaxed in
+   * pseudo-time before every Runge-Kutta stage
+   * (PixelSim::solveZeroStorageConstraints, pixelsim.cpp:23-90), its dc/dt is
+   * zero and it is left out of the error norm (pixelsim_impl.cpp:778-781).
+   * Not available in a z-slab decomposed simulation. */
   const double *inv_storage;
   /* Non-uniform diffusion (SimCompartment::evaluateDiffusionOperator, array
    * branch, pixelsim_impl.cpp:453-485): [n_voxels*n_species] diffusion

@@ -55,6 +55,11 @@ struct OCompartment {
   std::vector<std::size_t> nonSpatialSpeciesIndices;
   std::vector<double> invStorage;
   bool hasNonUnitStorage{false};
+  // zero-storage (algebraic) species, pixelsim_impl.cpp:218-224,826-891
+  bool hasZeroStorageSpecies{false};
+  std::vector<std::size_t> zeroStorageSpeciesIndices;
+  std::vector<double> relaxOld, relaxFirstOrder;
+  double maxRelaxStableTimestep{std::numeric_limits<double>::max()};
   // non-uniform diffusion: diffConstants[s][i] (pixelsim_impl.cpp:257-296)
   bool useUniformDiffusionOperator{true};
   std::vector<std::vector<double>> diffConstants;
@@ -194,6 +199,55 @@ struct OCompartment {
                              dym * (conc[ix + source] - conc[ixDny + source]) +
                              dzp * (conc[ixUpz + source] - conc[ix + source]) -
                              dzm * (conc[ix + source] - conc[ixDnz + source]);
+      }
+    }
+  }
+  // pixelsim_impl.cpp:834-891
+  void doRelaxSubstep1(double dt) {
+    for (std::size_t is : zeroStorageSpeciesIndices) {
+      for (std::size_t ix = 0; ix < nPixels; ++ix) {
+        std::size_t i = ix * nSpecies + is;
+        relaxOld[i] = conc[i];
+        conc[i] += dt * dcdt[i];
+      }
+    }
+  }
+  void doRelaxSubstep2(double dt) {
+    for (std::size_t is : zeroStorageSpeciesIndices) {
+      for (std::size_t ix = 0; ix < nPixels; ++ix) {
+        std::size_t i = ix * nSpecies + is;
+        relaxFirstOrder[i] = conc[i];
+        conc[i] = 0.5 * relaxOld[i] + 0.5 * conc[i] + 0.5 * dt * dcdt[i];
+      }
+    }
+  }
+  void undoRelaxStep() {
+    for (std::size_t is : zeroStorageSpeciesIndices) {
+      for (std::size_t ix = 0; ix < nPixels; ++ix) {
+        std::size_t i = ix * nSpecies + is;
+        conc[i] = relaxOld[i];
+      }
+    }
+  }
+  void calculateRelaxError(double epsilon, double &eabs, double &erel) const {
+    for (std::size_t is : zeroStorageSpeciesIndices) {
+      for (std::size_t ix = 0; ix < nPixels; ++ix) {
+        std::size_t i = ix * nSpecies + is;
+        double localErr = std::abs(conc[i] - relaxFirstOrder[i]);
+        eabs = std::max(eabs, localErr);
+        double localNorm = 0.5 * (conc[i] + relaxOld[i] + epsilon);
+        erel = std::max(erel, localErr / localNorm);
+      }
+    }
+  }
+  void getZeroStorageResidual(double epsilon, double &rabs, double &rrel) const {
+    for (std::size_t is : zeroStorageSpeciesIndices) {
+      for (std::size_t ix = 0; ix < nPixels; ++ix) {
+        std::size_t i = ix * nSpecies + is;
+        double absRes = std::abs(dcdt[i]);
+        rabs = std::max(rabs, absRes);
+        double norm = std::abs(conc[i]) + epsilon;
+        rrel = std::max(rrel, absRes / norm);
       }
     }
   }
@@ -339,8 +393,70 @@ struct Oracle {
     }
   }
 
+  bool hasAnyZeroStorageSpecies{false};
+  double maxRelaxStableTimestep{std::numeric_limits<double>::max()};
+
+  // pixelsim.cpp:23-90: pseudo-time relaxation of the zero-storage species to
+  // 0 = R(c) + div(D grad c) with an adaptive RK212 iteration
+  void solveZeroStorageConstraints() {
+    if (!hasAnyZeroStorageSpecies) {
+      return;
+    }
+    constexpr std::size_t maxIterations{100};
+    double nextRelaxDt = maxRelaxStableTimestep;
+    auto computeResidual = [this]() {
+      evaluateCompartmentsAndMembranes();
+      for (auto &c : comps) {
+        spatiallyAverageDcdt(c);
+      }
+    };
+    for (std::size_t iter = 0; iter < maxIterations; ++iter) {
+      computeResidual();
+      double rabs = 0.0, rrel = 0.0;
+      for (const auto &c : comps) {
+        c.getZeroStorageResidual(epsilon, rabs, rrel);
+      }
+      if (rabs < errMaxAbs && rrel < errMaxRel) {
+        return;
+      }
+      double dt = nextRelaxDt;
+      for (auto &c : comps) {
+        c.doRelaxSubstep1(dt);
+      }
+      computeResidual();
+      for (auto &c : comps) {
+        c.doRelaxSubstep2(dt);
+      }
+      double eabs = 0.0, erel = 0.0;
+      for (const auto &c : comps) {
+        c.calculateRelaxError(epsilon, eabs, erel);
+      }
+      double errFactor = std::min(errMaxAbs / (eabs + 1e-300),
+                                  errMaxRel / (erel + 1e-300));
+      errFactor = std::sqrt(errFactor);
+      nextRelaxDt = std::min(0.95 * dt * errFactor, maxRelaxStableTimestep);
+      if (eabs > errMaxAbs || erel > errMaxRel) {
+        for (auto &c : comps) {
+          c.undoRelaxStep();
+        }
+      }
+    }
+  }
+
   // pixelsim.cpp:92-120
   void calculateDcdt() {
+    evaluateCompartmentsAndMembranes();
+    for (auto &c : comps) {
+      spatiallyAverageDcdt(c);
+      if (c.hasNonUnitStorage) {
+        parallelFor(useThreads, c.nPixels, [&](std::size_t b, std::size_t e) {
+          applyStorage(c, b, e);
+        });
+      }
+    }
+  }
+
+  void evaluateCompartmentsAndMembranes() {
     maxStableTimestep = std::numeric_limits<double>::max();
     for (auto &c : comps) {
       parallelFor(useThreads, c.nPixels, [&](std::size_t b, std::size_t e) {
@@ -372,14 +488,6 @@ struct Oracle {
                     });
       }
     }
-    for (auto &c : comps) {
-      spatiallyAverageDcdt(c);
-      if (c.hasNonUnitStorage) {
-        parallelFor(useThreads, c.nPixels, [&](std::size_t b, std::size_t e) {
-          applyStorage(c, b, e);
-        });
-      }
-    }
   }
 
   template <typename F> void forValues(OCompartment &c, const F &f) {
@@ -406,6 +514,7 @@ struct Oracle {
 
   // pixelsim.cpp:122-140
   double doRK101(double dt) {
+    solveZeroStorageConstraints();
     calculateDcdt();
     dt = std::min(dt, maxStableTimestep);
     for (auto &c : comps) {
@@ -417,6 +526,7 @@ struct Oracle {
 
   // pixelsim.cpp:142-164; pixelsim_impl.cpp:672-701
   void doRK212(double dt) {
+    solveZeroStorageConstraints();
     calculateDcdt();
     for (auto &c : comps) {
       c.s2.resize(c.conc.size());
@@ -426,6 +536,7 @@ struct Oracle {
         c.conc[i] += dt * c.dcdt[i];
       });
     }
+    solveZeroStorageConstraints();
     calculateDcdt();
     for (auto &c : comps) {
       forValues(c, [&](std::size_t i) {
@@ -438,6 +549,7 @@ struct Oracle {
   // pixelsim.cpp:194-205; pixelsim_impl.cpp:714-721
   void doRKSubstep(double dt, double g1, double g2, double g3, double beta,
                    double delta) {
+    solveZeroStorageConstraints(); // pixelsim.cpp:196
     calculateDcdt();
     for (auto &c : comps) {
       forValues(c, [&](std::size_t i) {
@@ -833,12 +945,37 @@ struct Oracle {
                           pc.diffusion[3 * s + 2]});
         c.invStorage.push_back(pc.inv_storage != nullptr ? pc.inv_storage[s]
                                                          : 1.0);
-        if (c.invStorage.back() == 0.0) {
-          throw std::runtime_error(
-              "oracle: zero-storage species are not restated");
-        }
         if (c.invStorage.back() != 1.0) {
           c.hasNonUnitStorage = true;
+        }
+        if (c.invStorage.back() == 0.0) {
+          // zero storage: algebraic species; the bound of the relaxation
+          // iteration comes from its diffusion constant
+          // (pixelsim_impl.cpp:218-224,238-247,273-282)
+          c.hasZeroStorageSpecies = true;
+          c.zeroStorageSpeciesIndices.push_back(s);
+          double dsum = c.diff.back()[0] + c.diff.back()[1] + c.diff.back()[2];
+          if (!c.useUniformDiffusionOperator) {
+            double maxD = 0.0;
+            for (std::size_t i = 0; i < c.nPixels; ++i) {
+              const double d = pc.diffusion_array[i * pc.n_species + s];
+              maxD = i == 0 ? d : std::max(maxD, d);
+            }
+            dsum = maxD / c.dx2 + maxD / c.dy2 + maxD / c.dz2;
+            c.diffConstants.emplace_back(c.nPixels);
+            for (std::size_t i = 0; i < c.nPixels; ++i) {
+              c.diffConstants.back()[i] = pc.diffusion_array[i * pc.n_species + s];
+            }
+          }
+          if (dsum > 0.0) {
+            c.maxRelaxStableTimestep =
+                std::min(c.maxRelaxStableTimestep, 1.0 / (2.0 * dsum));
+          }
+          c.speciesNames.emplace_back(
+              pc.species_names != nullptr && pc.species_names[s] != nullptr
+                  ? pc.species_names[s]
+                  : "");
+          continue;
         }
         if (c.useUniformDiffusionOperator) {
           // pixelsim_common.hpp:33-37, pixelsim_impl.cpp:249-255
@@ -869,6 +1006,13 @@ struct Oracle {
       }
       c.conc.assign(pc.conc0, pc.conc0 + c.nPixels * c.nSpecies);
       c.dcdt.assign(c.conc.size(), 0.0);
+      if (c.hasZeroStorageSpecies) { // pixelsim.cpp:355-365
+        c.relaxOld.resize(c.conc.size());
+        c.relaxFirstOrder.resize(c.conc.size());
+        hasAnyZeroStorageSpecies = true;
+        maxRelaxStableTimestep =
+            std::min(maxRelaxStableTimestep, c.maxRelaxStableTimestep);
+      }
       maxStableTimestep = std::min(maxStableTimestep, c.maxStableTimestep);
     }
     membs.resize(p.n_membranes);
@@ -883,6 +1027,10 @@ struct Oracle {
           m.pairs[d].emplace_back(pm.pairs[d][2 * k], pm.pairs[d][2 * k + 1]);
         }
       }
+    }
+    if (hasAnyZeroStorageSpecies &&
+        maxRelaxStableTimestep == std::numeric_limits<double>::max()) {
+      maxRelaxStableTimestep = 1.0; // all zero-storage species have D = 0
     }
     compileReactions(p);
     if (p.n_compartments > 0) { // pixelsim.cpp:353-354

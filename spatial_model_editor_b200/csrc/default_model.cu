@@ -12,6 +12,7 @@ struct Reac0 {
   static __device__ __forceinline__ void nonSpatial(double *, const double *) {}
   static __device__ __forceinline__ void nonSpatialPick(const double *, double *) {}
   static __device__ __forceinline__ void storage(double *) {}
+  static __device__ __forceinline__ bool zeroStorage(int) { return false; }
   static __device__ __forceinline__ void eval(double *sme_out,
                                               const double *sme_values,
                                               const double *) {
@@ -60,7 +61,11 @@ struct Reac2 {
   static __device__ __forceinline__ void nonSpatialPick(const double *f, double *v) {
     v[0] = f[1];
   }
-  static __device__ __forceinline__ void storage(double *f) { f[0] *= 0.5; }
+  static __device__ __forceinline__ void storage(double *f) {
+    f[0] *= 0.5;
+    f[1] *= 0.0;
+  }
+  static __device__ __forceinline__ bool zeroStorage(int s) { return s == 1; }
   static __device__ __forceinline__ void eval(double *sme_out,
                                               const double *sme_values,
                                               const double *) {
@@ -144,3 +149,14 @@ smeb_stage_box<Reac2, F2>(const __grid_constant__ SmebStageArgs<6>);
 template __global__ void smeb_xd_max<Reac2>(const __grid_constant__ SmebStageArgs<6>);
 template __global__ void smeb_stats<Reac0>(const double *, smeb_u32, smeb_u32, double *);
 template __global__ void smeb_stats<Reac2>(const double *, smeb_u32, smeb_u32, double *);
+// zero-storage relaxation kernels
+#define F5 (SMEB_F_RELAX_A)
+#define F6 (SMEB_F_RELAX_B | SMEB_F_USE_C0)
+template __global__ void
+smeb_stage_nn<Reac2, F5>(const __grid_constant__ SmebStageArgs<6>);
+template __global__ void
+smeb_stage_nn<Reac2, F6>(const __grid_constant__ SmebStageArgs<6>);
+template __global__ void
+smeb_stage_tile<Reac2, F6, 8, 32, 4, true>(const __grid_constant__ SmebStageArgs<6>,
+                                           const __grid_constant__ SmebTensorMap,
+                                           const smeb_u32);

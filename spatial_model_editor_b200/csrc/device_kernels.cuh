@@ -41,6 +41,9 @@ typedef unsigned int smeb_u32;
 #define SMEB_F_OUT_CNEW 1024u    // on demand: store the unclamped new state
 #define SMEB_F_SUM_NS 2048u      // pre-pass: block sums of dc/dt of the
                                  // non-spatial species, nothing else
+#define SMEB_F_RELAX_A 4096u     // zero-storage relaxation, first half: residual
+                                 // norms, out = c + dt f for those species
+#define SMEB_F_RELAX_B 8192u     // second half: out = c0/2 + c/2 + dt/2 f, error
 
 #define SMEB_MEMB_FLAG 0x80000000u
 #define SMEB_BLOCK 256
@@ -239,6 +242,42 @@ smeb_update(const SmebStageArgs<R::S> &a, const double *c, const double *fin,
   if constexpr (R::NNS > 0) {
     R::nonSpatial(f, a.nsAv);
   }
+  // Pseudo-time relaxation of the zero-storage (algebraic) species towards
+  // 0 = R(c) + div(D grad c): one adaptive RK212 iteration of
+  // PixelSim::solveZeroStorageConstraints (pixelsim.cpp:23-90) is two launches.
+  // The residual is dc/dt before the storage factor; the other species are
+  // copied.  a.bdt = dt (A) or dt/2 (B), a.c0 = the state before the iteration.
+  if constexpr ((F & SMEB_F_RELAX_A) != 0) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      out[s] = c[s];
+      if (R::zeroStorage(s)) {
+        // getZeroStorageResidual, pixelsim_impl.cpp:877-891
+        const double r = fabs(f[s]);
+        eabs = eabs < r ? r : eabs;
+        const double q = r / (fabs(c[s]) + a.eps);
+        erel = erel < q ? q : erel;
+        out[s] = c[s] + a.bdt * f[s]; // doRelaxSubstep1, :834-842
+      }
+    }
+    return;
+  }
+  if constexpr ((F & SMEB_F_RELAX_B) != 0) {
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      out[s] = c[s];
+      if (R::zeroStorage(s)) {
+        // doRelaxSubstep2 (:844-852) and calculateRelaxError (:864-876)
+        const double cn = 0.5 * c0v[s] + 0.5 * c[s] + a.bdt * f[s];
+        const double e = fabs(cn - c[s]);
+        eabs = eabs < e ? e : eabs;
+        const double q = e / (0.5 * (cn + c0v[s] + a.eps));
+        erel = erel < q ? q : erel;
+        out[s] = cn;
+      }
+    }
+    return;
+  }
   if constexpr (R::STORAGE) {
     R::storage(f);
   }
@@ -276,7 +315,7 @@ smeb_update(const SmebStageArgs<R::S> &a, const double *c, const double *fin,
       }
       if constexpr ((F & SMEB_F_OUT_LOWER) != 0) {
         out[s] = lower;
-      } else {
+      } else if (!R::zeroStorage(s)) { // pixelsim_impl.cpp:778-781
         const double e = fabs(cn[s] - lower);
         eabs = eabs < e ? e : eabs;
         const double norm = 0.5 * (cn[s] + c0v[s] + a.eps);
@@ -518,7 +557,8 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   }
   if constexpr ((F & SMEB_F_SUM_NS) != 0) {
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
-  } else if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
+  } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
+                       (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
     smeb_block_max2(eabs, erel, a.err);
   }
 }
@@ -554,7 +594,8 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   }
   if constexpr ((F & SMEB_F_SUM_NS) != 0) {
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
-  } else if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
+  } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
+                       (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
     smeb_block_max2(eabs, erel, a.err);
   }
 }
@@ -656,7 +697,8 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   }
   if constexpr ((F & SMEB_F_SUM_NS) != 0) {
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
-  } else if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
+  } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
+                       (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
     smeb_block_max2(eabs, erel, a.err);
   }
 }
@@ -986,7 +1028,8 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
     const size_t blk =
         ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + blk * R::NNS);
-  } else if constexpr ((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) {
+  } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
+                       (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
     smeb_block_max2(eabs, erel, a.err);
   }
 }

@@ -228,6 +228,15 @@ void Sim::generateSource(const smeb200_problem &p) {
       }
     }
     h << "  }\n";
+    h << "  static __device__ __forceinline__ bool zeroStorage(int s) {\n"
+         "    (void)s;\n    return false";
+    for (uint32_t s = 0; comp.inv_storage != nullptr && s < comp.n_species;
+         ++s) {
+      if (comp.inv_storage[s] == 0.0) {
+        h << " || s == " << s;
+      }
+    }
+    h << ";\n  }\n";
     src << functorSource(h.str(), comp.n_species, comp.expressions,
                          comp.n_species, p.n_params);
   }
@@ -640,24 +649,28 @@ void Sim::chooseGeometry(int variant) {
 
 // one tensor map per concentration buffer: fp64 [nz][nx][ny*S], box
 // [(TY+2)*S, TX+2, 1], no swizzle, out-of-bounds cells read as zero
-void Sim::encodeTensorMaps(CompartmentState &c) {
+void Sim::encodeTensorMap(const CompartmentState &c, double *buffer,
+                          CUtensorMap *out) {
   const auto &drv = DriverApi::get();
+  const cuuint64_t dims[3] = {static_cast<cuuint64_t>(c.ny) * c.S, c.nx, c.nz};
+  const cuuint64_t strides[2] = {
+      static_cast<cuuint64_t>(c.ny) * c.S * 8,
+      static_cast<cuuint64_t>(c.nx) * c.ny * c.S * 8};
+  const cuuint32_t box[3] = {
+      static_cast<cuuint32_t>((c.tile.ty + 2) * c.S + 2 * (c.S % 2)),
+      static_cast<cuuint32_t>(c.tile.tx + 2), 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  check(drv.TensorMapEncodeTiled(
+            out, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, buffer, dims, strides, box,
+            estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE),
+        "cuTensorMapEncodeTiled");
+}
+
+void Sim::encodeTensorMaps(CompartmentState &c) {
   for (int b = 0; b < c.nbuf; ++b) {
-    const cuuint64_t dims[3] = {static_cast<cuuint64_t>(c.ny) * c.S, c.nx,
-                                c.nz};
-    const cuuint64_t strides[2] = {
-        static_cast<cuuint64_t>(c.ny) * c.S * 8,
-        static_cast<cuuint64_t>(c.nx) * c.ny * c.S * 8};
-    const cuuint32_t box[3] = {static_cast<cuuint32_t>((c.tile.ty + 2) * c.S +
-                                                       2 * (c.S % 2)),
-                               static_cast<cuuint32_t>(c.tile.tx + 2), 1};
-    const cuuint32_t estr[3] = {1, 1, 1};
-    check(drv.TensorMapEncodeTiled(
-              &c.tmap[b], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, c.buf[b], dims,
-              strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE),
-          "cuTensorMapEncodeTiled");
+    encodeTensorMap(c, c.buf[b], &c.tmap[b]);
   }
 }
 
@@ -974,10 +987,7 @@ void Sim::build(const smeb200_problem &p) {
       c.invStorage.assign(pc.inv_storage, pc.inv_storage + c.S);
       for (double v : c.invStorage) {
         if (v == 0.0) {
-          // pixelsim.cpp:23-90 (pseudo-time relaxation of algebraic species)
-          throw Error("smeb200: zero storage species (algebraic constraints) "
-                      "are not supported: the CUDA pixel backend requires "
-                      "non-zero storage, unit storage or otherwise");
+          continue; // zero-storage (algebraic) species, see below
         }
         if (!(v > 0.0)) {
           throw Error("Invalid negative storage value for species in '" +
@@ -1027,6 +1037,31 @@ void Sim::build(const smeb200_problem &p) {
       // forwards-Euler stability bound, pixelsim_common.hpp:33-37 and
       // pixelsim_impl.cpp:249-255 (D * invStorage per direction)
       const double is = c.invStorage.empty() ? 1.0 : c.invStorage[s];
+      if (is == 0.0) {
+        // Zero storage: an algebraic species, relaxed in pseudo-time before
+        // every stage (pixelsim.cpp:23-90).  Its diffusion bounds the
+        // relaxation step, not the time step (pixelsim_impl.cpp:238-247).
+        if (p.n_ranks > 1) {
+          throw Error("smeb200: zero-storage species are not supported in a "
+                      "z-slab decomposed simulation");
+        }
+        c.zeroStorage.push_back(s);
+        anyZeroStorage = true;
+        double dsum = c.D[3 * s] + c.D[3 * s + 1] + c.D[3 * s + 2];
+        if (c.nonUniform) {
+          double maxD = 0.0;
+          for (uint64_t i = 0; i < c.n; ++i) {
+            const double d = pc.diffusion_array[i * c.S + s];
+            maxD = i == 0 ? d : std::max(maxD, d);
+          }
+          dsum = maxD / h2[0] + maxD / h2[1] + maxD / h2[2];
+        }
+        if (dsum > 0.0) {
+          maxRelaxStableTimestep =
+              std::min(maxRelaxStableTimestep, 1.0 / (2.0 * dsum));
+        }
+        continue;
+      }
       double sum = c.D[3 * s] * is + c.D[3 * s + 1] * is + c.D[3 * s + 2] * is;
       if (c.nonUniform) {
         // per-voxel constants: bound from the species' maximum
@@ -1041,6 +1076,10 @@ void Sim::build(const smeb200_problem &p) {
       c.maxStable = std::min(c.maxStable, 1.0 / (2.0 * sum));
       maxStableTimestep = std::min(maxStableTimestep, 1.0 / (2.0 * sum));
     }
+  }
+  if (anyZeroStorage &&
+      maxRelaxStableTimestep == std::numeric_limits<double>::max()) {
+    maxRelaxStableTimestep = 1.0; // every zero-storage species has D = 0
   }
   for (std::size_t ci = 0; ci < comps.size(); ++ci) {
     if (comps[ci].n * comps[ci].S >
@@ -1094,6 +1133,14 @@ void Sim::build(const smeb200_problem &p) {
     }
     if (!comps[ci].crossTarget.empty()) {
       addName("smeb_xd_max<Reac" + std::to_string(ci) + ">");
+    }
+    if (!comps[ci].zeroStorage.empty()) {
+      for (uint32_t f : {F_RELAX_A, F_RELAX_B | F_USE_C0}) {
+        addName(kernelName(ci, f, false));
+        if (comps[ci].nMvox > 0) {
+          addName(kernelName(ci, f, true));
+        }
+      }
     }
   }
   mainModule = compile(names);
@@ -1149,6 +1196,25 @@ void Sim::build(const smeb200_problem &p) {
                             stream),
             "upload diffusion constant array");
     }
+    if (!c.zeroStorage.empty()) {
+      c.kRelaxA = lookup(mainModule, ci, F_RELAX_A);
+      c.kRelaxB = lookup(mainModule, ci, F_RELAX_B | F_USE_C0);
+      for (const auto &k : {c.kRelaxA, c.kRelaxB}) {
+        if (c.geom != Geom::TILE && k.main != nullptr) {
+          persistentGrid(k.main);
+        }
+        if (k.memb != nullptr) {
+          persistentGrid(k.memb);
+        }
+      }
+      c.pool.resize(3);
+      for (auto &pb : c.pool) {
+        pb.p = devAlloc<double>(nv, "allocate relaxation buffers");
+        if (c.geom == Geom::TILE) {
+          encodeTensorMap(c, pb.p, &pb.t);
+        }
+      }
+    }
     if (!c.crossTarget.empty()) {
       c.dXdMax = devAlloc<unsigned long long>(c.crossTarget.size(),
                                               "allocate cross-diffusion maxima");
@@ -1198,9 +1264,10 @@ void Sim::build(const smeb200_problem &p) {
     for (const auto &c : comps) {
       values += c.n * c.S;
     }
-    useGraphs = !comm && values <= (uint64_t{1} << 22);
+    // (the zero-storage relaxation needs the host between the launches)
+    useGraphs = !comm && !anyZeroStorage && values <= (uint64_t{1} << 22);
     if (const char *env = std::getenv("SMEB200_GRAPHS"); env != nullptr) {
-      useGraphs = !comm && env[0] == '1';
+      useGraphs = !comm && !anyZeroStorage && env[0] == '1';
     }
     std::size_t active = 0;
     for (const auto &c : comps) {
@@ -1451,6 +1518,9 @@ Sim::~Sim() {
     cudaFree(c.dEnt);
     cudaFree(c.scratch);
     cudaFree(c.dNsAv);
+    for (auto &pb : c.pool) {
+      cudaFree(pb.p);
+    }
     cudaFree(c.dStats);
     cudaFree(c.dStatsPartial);
     cudaFree(c.dDarr);
@@ -1511,6 +1581,21 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
   // compartment's main and membrane kernels, touch disjoint voxels and only read
   // the stage input, so they become parallel branches of the graph (a step of a
   // small multi-compartment model is a chain of latencies otherwise).
+  if (anyZeroStorage) {
+    solveZeroStorageConstraints(stageIndex);
+  }
+  // stage inputs of all compartments as the membrane kernels see them (a
+  // relaxed copy may stand in for the buffer of the stage's input role)
+  membCinOverride.clear();
+  if (anyZeroStorage) {
+    for (auto &c : comps) {
+      const double *pj = c.S > 0 ? c.buf[c.role[sd.cin]] : nullptr;
+      if (c.haveOverride && stageIndex == 0) {
+        pj = c.stageInOverride.p;
+      }
+      membCinOverride.push_back(pj);
+    }
+  }
   const bool fork = capturing && !forkStreams.empty();
   std::size_t forksUsed = 0;
   if (fork) {
@@ -1535,8 +1620,17 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     a.nz = c.nz;
     a.z_begin = c.zLoGhost;
     a.z_end = c.nz - c.zHiGhost;
+    tmapOverride = nullptr;
+    if (c.haveOverride && stageIndex == 0) {
+      // RK323 / RK435: the stage works on the relaxed copy, the pre-step state
+      // c0 stays what doRKInit saved before the relaxation (pixelsim.cpp:166-171)
+      a.cin = c.stageInOverride.p;
+      tmapOverride = &c.stageInOverride.t;
+    }
     if (sd.s2mode == 2) {
-      a.s2in = c.buf[c.role[CUR]];
+      // s2 after stage 0 is exactly its input (0 + 1 * c): the relaxed copy if
+      // there is one
+      a.s2in = c.haveOverride ? c.stageInOverride.p : c.buf[c.role[CUR]];
     } else if (sd.s2mode == 3) {
       a.s2in = c.buf[c.role[RS]];
     }
@@ -1578,6 +1672,7 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
       launchCompartment(ci, a, c.kSumNs, c.role[sd.cin], true);
     }
     launchCompartment(ci, a, c.kStage[stageIndex], c.role[sd.cin]);
+    tmapOverride = nullptr;
     if (forkMain != nullptr) { // join the branches of this compartment
       const bool two = forkMemb != forkMain;
       check(cudaEventRecord(joinEvents[forksUsed - 2], forkMain), "join event");
@@ -1595,8 +1690,138 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
       c.haveLast = true;
     }
   }
+  membCinOverride.clear();
   if (comm && !comps.empty()) {
     haloExchange(comps[0].role[sd.cout]);
+  }
+}
+
+// PixelSim::solveZeroStorageConstraints (pixelsim.cpp:23-90) before the stage
+// `stageIndex`: adaptive RK212 iteration in pseudo-time on the zero-storage
+// species of the stage input until the residual of 0 = R(c) + div(D grad c)
+// meets the integrator's tolerances (at most 100 iterations).  One iteration =
+// two fused launches per compartment (residual norm + first half; second half +
+// error norm), each followed by a 16-byte read of the norms.  The reference
+// updates conc in place; here an accepted iterate is a buffer that takes the
+// place of the stage input (pointer swap with a pool of three scratch buffers).
+void Sim::solveZeroStorageConstraints(std::size_t stageIndex) {
+  const StageDesc &sd = plan[stageIndex];
+  const bool protect =
+      stageIndex == 0 &&
+      (integrator == SMEB200_RK323 || integrator == SMEB200_RK435);
+  using PoolBuf = CompartmentState::PoolBuf;
+  std::vector<PoolBuf> in(comps.size());
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    auto &c = comps[ci];
+    if (stageIndex == 0) {
+      c.haveOverride = false;
+    }
+    if (c.S == 0) {
+      continue;
+    }
+    const int idx = c.role[sd.cin];
+    in[ci].p = c.buf[idx];
+    in[ci].t = c.tmap[idx];
+    if (protect && !c.zeroStorage.empty() && c.n > 0) {
+      // the pre-step state (s3) must keep the un-relaxed values: relax a copy
+      check(cudaMemcpyAsync(c.pool[2].p, c.buf[idx], c.n * c.S * sizeof(double),
+                            cudaMemcpyDeviceToDevice, stream),
+            "copy stage input for relaxation");
+      in[ci] = c.pool[2];
+    }
+  }
+  auto launchHalf = [&](bool second, double dt) {
+    std::vector<const double *> cins(comps.size(), nullptr);
+    for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+      const auto &c = comps[ci];
+      // second half: the compartments with zero-storage species are at c1
+      cins[ci] = second && !c.zeroStorage.empty() && c.n > 0 ? c.pool[0].p
+                                                              : in[ci].p;
+    }
+    for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+      auto &c = comps[ci];
+      if (c.zeroStorage.empty() || c.n == 0) {
+        continue;
+      }
+      StageArgsHost a{};
+      a.cin = cins[ci];
+      a.c0 = in[ci].p;
+      a.cout = second ? c.pool[1].p : c.pool[0].p;
+      a.nn = c.dNn;
+      a.runs = c.dRuns;
+      a.err = dErr;
+      a.n = static_cast<uint32_t>(c.n);
+      a.v0 = 0;
+      a.nx = c.nx;
+      a.ny = c.ny;
+      a.nz = c.nz;
+      a.z_begin = 0;
+      a.z_end = c.nz;
+      a.bdt = second ? 0.5 * dt : dt;
+      a.eps = epsilon;
+      std::copy(c.D.begin(), c.D.end(), a.D);
+      std::copy(params.begin(), params.end(), a.D + 3 * c.S);
+      a.nsAv = c.dNsAv;
+      a.nsPartial = c.dNsPartial;
+      a.darr = c.dDarr;
+      a.xdMax = c.dXdMax;
+      std::copy(h2, h2 + 3, a.h2);
+      membCinOverride = cins;
+      tmapOverride = second ? &c.pool[0].t : &in[ci].t;
+      if (!c.nonSpatial.empty()) {
+        launchCompartment(ci, a, c.kSumNs, 0, true);
+      }
+      launchCompartment(ci, a, second ? c.kRelaxB : c.kRelaxA, 0);
+    }
+    membCinOverride.clear();
+    tmapOverride = nullptr;
+  };
+  relaxing = true;
+  try {
+    constexpr std::size_t maxIterations{100};
+    double nextRelaxDt = maxRelaxStableTimestep;
+    for (std::size_t iter = 0; iter < maxIterations; ++iter) {
+      const double dt = nextRelaxDt;
+      launchHalf(false, dt);
+      double rabs = 0.0, rrel = 0.0;
+      readError(rabs, rrel);
+      if (rabs < errMaxAbs && rrel < errMaxRel) {
+        break;
+      }
+      launchHalf(true, dt);
+      double eabs = 0.0, erel = 0.0;
+      readError(eabs, erel);
+      double errFactor = std::min(errMaxAbs / (eabs + 1e-300),
+                                  errMaxRel / (erel + 1e-300));
+      errFactor = std::sqrt(errFactor);
+      nextRelaxDt = std::min(0.95 * dt * errFactor, maxRelaxStableTimestep);
+      if (!(eabs > errMaxAbs || erel > errMaxRel)) {
+        for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+          if (!comps[ci].zeroStorage.empty() && comps[ci].n > 0) {
+            std::swap(in[ci], comps[ci].pool[1]); // accepted: c2 is the state
+          }
+        }
+      }
+    }
+  } catch (...) {
+    relaxing = false;
+    throw;
+  }
+  relaxing = false;
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    auto &c = comps[ci];
+    if (c.zeroStorage.empty() || c.n == 0) {
+      continue;
+    }
+    if (protect) {
+      c.pool[2] = in[ci];
+      c.stageInOverride = in[ci];
+      c.haveOverride = true;
+    } else {
+      const int idx = c.role[sd.cin];
+      c.buf[idx] = in[ci].p;
+      c.tmap[idx] = in[ci].t;
+    }
   }
 }
 
@@ -1607,7 +1832,8 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
                             bool nsPrepass) {
   const auto &drv = DriverApi::get();
   auto &c = comps[ci];
-  const bool timed = kernelTiming && ci == dominantComp && !nsPrepass;
+  const bool timed =
+      kernelTiming && ci == dominantComp && !nsPrepass && !relaxing;
   uint32_t nsBlocks = 0; // blocks that wrote partial sums (pre-pass)
   // while a step is captured the kernels of one stage fork onto per-compartment
   // streams (parallel graph branches); otherwise everything is on `stream`
@@ -1627,7 +1853,8 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
       c.geom == Geom::TILE ? 0u : persistentGrid(k.main);
   if (c.geom == Geom::TILE) {
     uint32_t chunk = c.tile.chunk;
-    void *params[] = {&a, &c.tmap[cinBuf], &chunk};
+    const CUtensorMap *tm = tmapOverride != nullptr ? tmapOverride : &c.tmap[cinBuf];
+    void *params[] = {&a, const_cast<CUtensorMap *>(tm), &chunk};
     check(drv.LaunchKernel(k.main, c.tile.grid[0], c.tile.grid[1],
                            c.tile.grid[2], BLOCK, 1, 1, c.tile.dynSmem, sMain,
                            params, nullptr),
@@ -1663,8 +1890,11 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     blob[2] = reinterpret_cast<unsigned long long>(c.dEnt);
     blob[3] = reinterpret_cast<unsigned long long>(dFluxLen);
     for (std::size_t j = 0; j < comps.size(); ++j) {
-      blob[4 + j] = reinterpret_cast<unsigned long long>(
-          comps[j].S > 0 ? comps[j].buf[cinBuf] : nullptr);
+      const double *pj = comps[j].S > 0 ? comps[j].buf[cinBuf] : nullptr;
+      if (!membCinOverride.empty()) {
+        pj = membCinOverride[j];
+      }
+      blob[4 + j] = reinterpret_cast<unsigned long long>(pj);
     }
     blob[4 + comps.size()] = static_cast<unsigned long long>(c.nMvox);
     const unsigned mgrid =

@@ -24,7 +24,8 @@ namespace smeb200 {
 constexpr uint32_t F_USE_C0 = 1u, F_USE_S2 = 2u, F_USE_S2IN = 4u,
                    F_WRITE_S2 = 8u, F_FINAL = 16u, F_LOWER_IS_CIN = 32u,
                    F_CLAMP_OUT = 64u, F_GENERIC = 128u, F_OUT_DCDT = 256u,
-                   F_OUT_LOWER = 512u, F_OUT_CNEW = 1024u, F_SUM_NS = 2048u;
+                   F_OUT_LOWER = 512u, F_OUT_CNEW = 1024u, F_SUM_NS = 2048u,
+                   F_RELAX_A = 4096u, F_RELAX_B = 8192u;
 
 // host mirror of the device-side SmebStageArgs<S> (device_kernels.cuh); the
 // D[3*S] table is the tail.
@@ -122,6 +123,18 @@ struct CompartmentState {
   unsigned long long *dXdMax{nullptr};
   CUfunction kXdMax{nullptr};
   double maxStable{std::numeric_limits<double>::max()};
+  // zero-storage (algebraic) species: relaxation kernels, scratch buffers and
+  // the relaxed copy that replaces the stage-0 input when the pre-step state
+  // must survive (RK323 / RK435)
+  struct PoolBuf {
+    double *p{nullptr};
+    CUtensorMap t{};
+  };
+  std::vector<uint32_t> zeroStorage;
+  std::vector<PoolBuf> pool;
+  StageKernels kRelaxA, kRelaxB;
+  bool haveOverride{false};
+  PoolBuf stageInOverride;
   double *dStatsPartial{nullptr};    // [blocks][3*SP]
   double *dStats{nullptr};           // [3*SP] avg, min, max per species
   std::vector<int32_t> voxels;
@@ -282,6 +295,15 @@ private:
   void connectSlabs();
   void haloExchange(int coutBuf);
   void updateCrossDiffusionMaxStableTimestep();
+  void solveZeroStorageConstraints(std::size_t stageIndex);
+  void encodeTensorMap(const CompartmentState &c, double *buffer,
+                       CUtensorMap *out);
+  bool anyZeroStorage{false};
+  bool relaxing{false};
+  double maxRelaxStableTimestep{std::numeric_limits<double>::max()};
+  // per-launch overrides of launchCompartment (zero-storage relaxation)
+  const CUtensorMap *tmapOverride{nullptr};
+  std::vector<const double *> membCinOverride;
   // one full wave of resident CTAs for a grid-stride kernel: SMs x the CTAs of
   // this kernel that fit on one SM (cached per function)
   unsigned persistentGrid(CUfunction f);

@@ -305,3 +305,68 @@ def test_cross_diffusion_dynamic_stability_bound():
     cmax2 = s2.getConcentrations(0)[:, 0].max()
     assert cmax2 < cmax
     assert s2.maxStableTimestep > 1.0 / (2.0 * 3.0 * 4.0 * cmax)
+
+
+# ---- zero-storage species: algebraic constraints by pseudo-time relaxation --------
+def zero_storage_problem(name, species_index, integrator=smeb.RK101, d_zero=False):
+    p, meta, _ = load_golden(name, integrator=integrator)
+    c = p.compartments[0]
+    inv = np.ones(c.n_species)
+    inv[species_index] = 0.0      # Species::setStorage(id, 0)
+    c.inv_storage = inv
+    if d_zero:
+        c.diffusion = c.diffusion.copy()
+        c.diffusion[species_index, :] = 0.0
+    p.max_timestep = 1e-3
+    return p
+
+
+@pytest.mark.parametrize("d_zero", [False, True])
+def test_zero_storage_accepted_and_dcdt_zero(d_zero):
+    """pixelsim_t.cpp:50-91: ABtoC with storage(C) = 0 (and D_C = 0): one RK101 run of
+    1e-3 without error, dc/dt of C is zero after applyStorage"""
+    p = zero_storage_problem("ABtoC", 2, d_zero=d_zero)
+    sim = OraclePixelSim(p)
+    assert sim.errorMessage() == ""
+    sim.run(1e-3)
+    assert sim.errorMessage() == ""
+    assert np.all(sim.getDcdt(0)[:, 2] == 0.0)
+    # A and B are ordinary species: they did change
+    assert np.any(sim.getConcentrations(0)[:, 0] != p.compartments[0].conc0[:, 0])
+
+
+def test_zero_storage_constraint_solver_reduces_residual():
+    """pixelsim_t.cpp:92-131: single-compartment-diffusion with storage(slow) = 0:
+    after run(0.01) "slow" is more uniform (relative range < 0.75); the other
+    species evolves as without the constraint"""
+    p = zero_storage_problem("single-compartment-diffusion", 0)
+    sim = OraclePixelSim(p)
+    sim.run(0.01)
+    assert sim.errorMessage() == ""
+    c = sim.getConcentrations(0)
+    lo, hi = c[:, 0].min(), c[:, 0].max()
+    c0 = p.compartments[0].conc0[:, 0]
+    assert (c0.max() - c0.min()) / c0.max() > 0.99
+    assert hi > 1e-12 and (hi - lo) / hi < 0.75
+    # maxStableTimestep ignores the zero-storage species (pixelsim_impl.cpp:238-255)
+    pu, meta, _ = load_golden("single-compartment-diffusion", integrator=smeb.RK101)
+    D_fast = meta["compartments"][0]["diffusion_constants"][1]
+    assert math.isclose(sim.maxStableTimestep, 1.0 / (2.0 * 3.0 * D_fast), rel_tol=1e-14)
+
+
+@pytest.mark.parametrize("integrator", [smeb.RK212, smeb.RK323, smeb.RK435])
+def test_zero_storage_adaptive_integrators_run(integrator):
+    """the relaxation runs before every stage (pixelsim.cpp:146,155,196); the
+    zero-storage species is excluded from the error norm (pixelsim_impl.cpp:778-781)"""
+    p = zero_storage_problem("single-compartment-diffusion", 0, integrator)
+    p.max_timestep = smeb.DBL_MAX
+    sim = OraclePixelSim(p)
+    n = sim.run(0.05)
+    assert sim.errorMessage() == "" and n > 3
+    c = sim.getConcentrations(0)
+    assert np.all(np.isfinite(c))
+    if integrator == smeb.RK212:
+        # RK212 keeps the relaxed values (s3 is taken after the relaxation,
+        # pixelsim.cpp:146-154); RK323 / RK435 mix them with the pre-relaxation
+        # state again (doRKInit runs before the first relaxation, pixelsim.cpp:168)
+        assert (c[:, 0].max() - c[:, 0].min()) / c[:, 0].max() < 0.75

@@ -165,14 +165,60 @@ def test_box_features_adaptive(integ):
     assert np.max(np.abs(a - b) / (0.5 * (np.abs(a) + np.abs(b)) + 1e-14)) <= p.max_err_rel
 
 
-def test_zero_storage_is_rejected():
-    """zero-storage species need the pseudo-time relaxation of pixelsim.cpp:23-90"""
-    p = box_with_features(16, 16, 1, smeb.RK212, False, True, False)
-    p.compartments[0].inv_storage = np.array([0.0, 1.0])
+def zero_storage_problem(kind, integ):
+    """storage 0 for one species: voxel list (the example disc / ABtoC), a full box
+    (tile kernel), and a two-compartment cell with a membrane"""
+    if kind in ("single-compartment-diffusion", "ABtoC"):
+        p, _, _ = load_golden(kind, integrator=integ)
+        zs = {"single-compartment-diffusion": 0, "ABtoC": 2}[kind]
+    elif kind == "box":
+        p = M.box_problem(M.ABTOC, 32, 64, 6, integrator=integ)
+        zs = 2
+    else:
+        p = M.two_compartment_brusselator(24, 20, 3, integrator=integ)
+        zs = 1
+    for c in p.compartments[:1] if kind != "cell" else p.compartments:
+        inv = np.ones(c.n_species)
+        inv[zs] = 0.0
+        c.inv_storage = inv
+    return p
+
+
+@pytest.mark.parametrize("kind", ["single-compartment-diffusion", "ABtoC", "box", "cell"])
+@pytest.mark.parametrize("integ", INTEGRATORS)
+def test_zero_storage_relaxation_fixed_step(kind, integ):
+    """PixelSim::solveZeroStorageConstraints (pixelsim.cpp:23-90) before every
+    stage: same iteration decisions (max norms are exact), same states"""
+    p = zero_storage_problem(kind, integ)
+    p.max_err_abs, p.max_err_rel = smeb.DBL_MAX, 0.01   # tolerances of the relaxation
+    p.max_timestep = 1e-3
+    gpu, cpu = both(p)
+    assert abs(gpu.maxStableTimestep - cpu.maxStableTimestep) <= 1e-15 * cpu.maxStableTimestep
+    if integ != smeb.RK101:
+        gpu.nextTimestep = cpu.nextTimestep = 1e-3
+    ng, nc = gpu.run(5e-3), cpu.run(5e-3)
+    assert ng == nc and ng >= 1
+    compare(p, gpu, cpu, f"zero storage {kind}", rel=1e-11)
+    assert gpu.errorMessage() == cpu.errorMessage() == ""
+
+
+def test_zero_storage_reference_checks_on_gpu():
+    """pixelsim_t.cpp:50-131 through the CUDA path"""
+    p = zero_storage_problem("ABtoC", smeb.RK101)
+    p.max_timestep = 1e-3
     p.device = 0
     gpu = smeb.PixelSim(p)
-    assert "zero storage" in gpu.errorMessage()
-    assert gpu.run(1.0) == 0
+    assert gpu.errorMessage() == ""
+    gpu.run(1e-3)
+    assert gpu.errorMessage() == ""
+    assert np.all(gpu.getDcdt(0)[:, 2] == 0.0)
+    p = zero_storage_problem("single-compartment-diffusion", smeb.RK101)
+    p.max_timestep = 1e-3
+    p.device = 0
+    gpu = smeb.PixelSim(p)
+    gpu.run(0.01)
+    c = gpu.getConcentrations(0)[:, 0]
+    assert c.max() > 1e-12 and (c.max() - c.min()) / c.max() < 0.75
 
 
 # ---- non-uniform diffusion and cross-diffusion ------------------------------------
