@@ -95,3 +95,17 @@ def test_adaptive_failure_on_gpu():
     assert ng == nc
     assert gpu.errorImages().shape == (1, 100, 100)
     assert np.array_equal(gpu.errorImages(), cpu.errorImages())
+
+
+def test_k7_voxel_size_invariance_on_gpu():
+    """simulate_t.cpp:515-680 through the CUDA path, with the device-side
+    avg / min / max that replaces calculateAvgMinMax"""
+    from test_golden_cpu import k7_problems
+    stats = []
+    for p in k7_problems():
+        p.device = 0
+        sim = smeb.PixelSim(p)
+        assert sim.run(0.20) == 20 and sim.errorMessage() == ""
+        stats.append([sim.getAvgMinMax(ci) for ci in range(3)])
+    for a, b in zip(*stats):
+        assert np.all(np.abs(a - b) <= np.maximum(1e-13, 1e-8 * np.maximum(np.abs(a), np.abs(b))))
