@@ -1159,6 +1159,7 @@ void Sim::build(const smeb200_problem &p) {
     const std::size_t nv = c.n * c.S;
     for (int b = 0; b < c.nbuf; ++b) {
       c.buf[b] = devAlloc<double>(nv, "allocate concentration buffers");
+      c.stateAllocs.push_back(c.buf[b]);
       c.role[b] = b;
     }
     check(cudaMemcpyAsync(c.buf[0], p.compartments[ci].conc0,
@@ -1210,6 +1211,7 @@ void Sim::build(const smeb200_problem &p) {
       c.pool.resize(3);
       for (auto &pb : c.pool) {
         pb.p = devAlloc<double>(nv, "allocate relaxation buffers");
+        c.stateAllocs.push_back(pb.p);
         if (c.geom == Geom::TILE) {
           encodeTensorMap(c, pb.p, &pb.t);
         }
@@ -1412,17 +1414,28 @@ void Sim::connectSlabs() {
   check(cudaHostGetDevicePointer(&dev, comm->flagPages(), 0),
         "cudaHostGetDevicePointer(halo flags)");
   flagBaseDev = reinterpret_cast<CUdeviceptr>(dev);
+  // halos are pushed on their own stream while the interior of the slab is
+  // computed (SMEB200_HALO_OVERLAP=0: everything on the main stream)
+  const char *ov = std::getenv("SMEB200_HALO_OVERLAP");
+  if (ov == nullptr || std::string(ov) != "0") {
+    check(cudaStreamCreateWithFlags(&haloStream, cudaStreamNonBlocking),
+          "cudaStreamCreate(halo)");
+    check(cudaEventCreateWithFlags(&boundaryDone, cudaEventDisableTiming),
+          "cudaEventCreate");
+    check(cudaEventCreateWithFlags(&haloPushed, cudaEventDisableTiming),
+          "cudaEventCreate");
+  }
   comm->barrier();
 }
 
-// after a stage wrote buffer `coutBuf`: push the two owned boundary planes into
-// the neighbours' ghost planes of the same buffer, signal, and make the stream
-// wait for the neighbours' pushes.  Everything is stream-ordered; the host does
-// not wait.  (A neighbour can only overwrite a ghost plane of buffer B after
-// this rank's earlier readers of B finished: it pushes stage k only after it
-// saw this rank's flag of stage k-1, which this rank writes after its own
-// stage k-1 kernel.)
-void Sim::haloExchange(int coutBuf) {
+// after the boundary planes of a stage wrote buffer `coutBuf`: push them into the
+// neighbours' ghost planes of the same buffer and signal (on stream `s`).
+// Everything is stream-ordered; the host does not wait.  (A neighbour can only
+// overwrite a ghost plane of buffer B after this rank's earlier readers of B
+// finished: it pushes stage k only after it saw this rank's flag of stage k-1,
+// which this rank writes after the boundary-plane and membrane kernels of its
+// stage k-1 -- the only kernels that read ghost voxels.)
+void Sim::haloPush(int coutBuf, cudaStream_t s) {
   const auto &drv = DriverApi::get();
   auto *seg = comm->segment();
   ++haloSeq;
@@ -1450,25 +1463,37 @@ void Sim::haloExchange(int coutBuf) {
       check(cudaMemcpyAsync(peerBuf[0][ci][coutBuf] +
                                 seg->slot[rank - 1].ghostHiOff[ci],
                             c.buf[coutBuf] + loOff, loCnt * sizeof(double),
-                            cudaMemcpyDefault, stream),
+                            cudaMemcpyDefault, s),
             "halo push (low neighbour)");
     }
     if (rank + 1 < nRanks && hiCnt > 0) { // last owned plane -> LOW ghosts of rank+1
       check(cudaMemcpyAsync(peerBuf[1][ci][coutBuf], c.buf[coutBuf] + hiOff,
-                            hiCnt * sizeof(double), cudaMemcpyDefault, stream),
+                            hiCnt * sizeof(double), cudaMemcpyDefault, s),
             "halo push (high neighbour)");
     }
   }
   if (rank > 0) {
-    check(drv.StreamWriteValue32(stream, flagDev(rank - 1, 1), haloSeq,
+    check(drv.StreamWriteValue32(s, flagDev(rank - 1, 1), haloSeq,
                                  CU_STREAM_WRITE_VALUE_DEFAULT),
           "cuStreamWriteValue32");
   }
   if (rank + 1 < nRanks) {
-    check(drv.StreamWriteValue32(stream, flagDev(rank + 1, 0), haloSeq,
+    check(drv.StreamWriteValue32(s, flagDev(rank + 1, 0), haloSeq,
                                  CU_STREAM_WRITE_VALUE_DEFAULT),
           "cuStreamWriteValue32");
   }
+  ++haloExchanges;
+}
+
+// make the main stream wait for the neighbours' pushes of the current stage
+void Sim::haloWait() {
+  const auto &drv = DriverApi::get();
+  auto flagDev = [&](int r, int side) {
+    return flagBaseDev +
+           static_cast<CUdeviceptr>(
+               reinterpret_cast<unsigned char *>(comm->haloFlag(r, side)) -
+               static_cast<unsigned char *>(comm->flagPages()));
+  };
   if (rank > 0) {
     check(drv.StreamWaitValue32(stream, flagDev(rank, 0), haloSeq,
                                 CU_STREAM_WAIT_VALUE_GEQ),
@@ -1479,7 +1504,6 @@ void Sim::haloExchange(int coutBuf) {
                                 CU_STREAM_WAIT_VALUE_GEQ),
           "cuStreamWaitValue32");
   }
-  ++haloExchanges;
 }
 
 Sim::~Sim() {
@@ -1488,6 +1512,12 @@ Sim::~Sim() {
   }
   cudaSetDevice(device);
   cudaStreamSynchronize(stream);
+  if (haloStream != nullptr) {
+    cudaStreamSynchronize(haloStream);
+    cudaStreamDestroy(haloStream);
+    cudaEventDestroy(boundaryDone);
+    cudaEventDestroy(haloPushed);
+  }
   if (comm) {
     // nobody may still be pushing halos into this rank's buffers
     try {
@@ -1508,7 +1538,7 @@ Sim::~Sim() {
     }
   }
   for (auto &c : comps) {
-    for (double *b : c.buf) {
+    for (void *b : c.stateAllocs) {
       cudaFree(b);
     }
     cudaFree(c.dNn);
@@ -1518,9 +1548,6 @@ Sim::~Sim() {
     cudaFree(c.dEnt);
     cudaFree(c.scratch);
     cudaFree(c.dNsAv);
-    for (auto &pb : c.pool) {
-      cudaFree(pb.p);
-    }
     cudaFree(c.dStats);
     cudaFree(c.dStatsPartial);
     cudaFree(c.dDarr);
@@ -1597,6 +1624,8 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     }
   }
   const bool fork = capturing && !forkStreams.empty();
+  const bool overlapHalo = comm != nullptr && haloStream != nullptr;
+  std::vector<std::pair<std::size_t, StageArgsHost>> interior;
   std::size_t forksUsed = 0;
   if (fork) {
     check(cudaEventRecord(forkEvent, stream), "fork event");
@@ -1671,7 +1700,47 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
       // averages need dc/dt of every voxel before any voxel can be updated
       launchCompartment(ci, a, c.kSumNs, c.role[sd.cin], true);
     }
-    launchCompartment(ci, a, c.kStage[stageIndex], c.role[sd.cin]);
+    if (overlapHalo) {
+      // z-slab: the owned boundary planes (what the neighbours need) and the
+      // membrane kernels first; the interior follows once their halos are on
+      // the way (below)
+      StageArgsHost lo = a, hi = a, mid = a;
+      if (c.box) {
+        const uint32_t zb = a.z_begin, ze = a.z_end;
+        const uint32_t loEnd = rank > 0 ? std::min(zb + 1, ze) : zb;
+        const uint32_t hiBegin = rank + 1 < nRanks ? std::max(ze - 1, loEnd) : ze;
+        lo.z_end = loEnd;
+        hi.z_begin = hiBegin;
+        mid.z_begin = loEnd;
+        mid.z_end = hiBegin;
+      } else {
+        const uint32_t v0 = a.v0, v1 = a.n;
+        const uint32_t loEnd = rank > 0 ? v0 + c.vFirstPlane : v0;
+        const uint32_t hiBegin =
+            rank + 1 < nRanks ? std::max(v1 - c.vLastPlane, loEnd) : v1;
+        lo.n = loEnd;
+        hi.v0 = hiBegin;
+        mid.v0 = loEnd;
+        mid.n = hiBegin;
+      }
+      const auto empty = [&](const StageArgsHost &r) {
+        return c.box ? r.z_begin >= r.z_end : r.v0 >= r.n;
+      };
+      suppressTiming = true;
+      if (!empty(lo)) {
+        launchCompartment(ci, lo, c.kStage[stageIndex], c.role[sd.cin], false, 1);
+      }
+      if (!empty(hi)) {
+        launchCompartment(ci, hi, c.kStage[stageIndex], c.role[sd.cin], false, 1);
+      }
+      launchCompartment(ci, a, c.kStage[stageIndex], c.role[sd.cin], false, 2);
+      suppressTiming = false;
+      if (!empty(mid)) {
+        interior.emplace_back(ci, mid);
+      }
+    } else {
+      launchCompartment(ci, a, c.kStage[stageIndex], c.role[sd.cin]);
+    }
     tmapOverride = nullptr;
     if (forkMain != nullptr) { // join the branches of this compartment
       const bool two = forkMemb != forkMain;
@@ -1692,7 +1761,24 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
   }
   membCinOverride.clear();
   if (comm && !comps.empty()) {
-    haloExchange(comps[0].role[sd.cout]);
+    const int coutBuf = comps[0].role[sd.cout];
+    if (overlapHalo) {
+      // the halos travel (and the neighbours' arrive) while the interior is
+      // computed; the next stage needs both directions to be complete
+      check(cudaEventRecord(boundaryDone, stream), "boundary event");
+      check(cudaStreamWaitEvent(haloStream, boundaryDone, 0), "halo stream wait");
+      haloPush(coutBuf, haloStream);
+      check(cudaEventRecord(haloPushed, haloStream), "halo event");
+      for (auto &[ci, mid] : interior) {
+        launchCompartment(ci, mid, comps[ci].kStage[stageIndex],
+                          comps[ci].role[sd.cin], false, 1);
+      }
+      haloWait();
+      check(cudaStreamWaitEvent(stream, haloPushed, 0), "halo pushed wait");
+    } else {
+      haloPush(coutBuf, stream);
+      haloWait();
+    }
   }
 }
 
@@ -1829,11 +1915,12 @@ void Sim::solveZeroStorageConstraints(std::size_t stageIndex) {
 // roles rotate in lock step, so one index serves all compartments)
 void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
                             const StageKernels &k, int cinBuf,
-                            bool nsPrepass) {
+                            bool nsPrepass, unsigned parts) {
   const auto &drv = DriverApi::get();
   auto &c = comps[ci];
-  const bool timed =
-      kernelTiming && ci == dominantComp && !nsPrepass && !relaxing;
+  const bool doMain = (parts & 1u) != 0, doMemb = (parts & 2u) != 0;
+  const bool timed = kernelTiming && ci == dominantComp && !nsPrepass &&
+                     !relaxing && doMain && !suppressTiming;
   uint32_t nsBlocks = 0; // blocks that wrote partial sums (pre-pass)
   // while a step is captured the kernels of one stage fork onto per-compartment
   // streams (parallel graph branches); otherwise everything is on `stream`
@@ -1850,18 +1937,24 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
           "cudaEventRecord");
   }
   const unsigned persistent =
-      c.geom == Geom::TILE ? 0u : persistentGrid(k.main);
-  if (c.geom == Geom::TILE) {
+      c.geom == Geom::TILE || !doMain ? 0u : persistentGrid(k.main);
+  if (!doMain) {
+    // membrane kernel only
+  } else if (c.geom == Geom::TILE) {
     uint32_t chunk = c.tile.chunk;
+    unsigned gridZ = c.tile.grid[2];
+    if (c.tile.m3) { // the planes of this launch (a z-slab may be launched in parts)
+      gridZ = std::max(1u, (a.z_end - a.z_begin + chunk - 1) / chunk);
+    }
     const CUtensorMap *tm = tmapOverride != nullptr ? tmapOverride : &c.tmap[cinBuf];
     void *params[] = {&a, const_cast<CUtensorMap *>(tm), &chunk};
     check(drv.LaunchKernel(k.main, c.tile.grid[0], c.tile.grid[1],
-                           c.tile.grid[2], BLOCK, 1, 1, c.tile.dynSmem, sMain,
-                           params, nullptr),
+                           c.tile.m3 ? gridZ : c.tile.grid[2], BLOCK, 1, 1,
+                           c.tile.dynSmem, sMain, params, nullptr),
           "launch tile stage kernel");
     nsBlocks = c.tile.grid[0] * c.tile.grid[1] * c.tile.grid[2];
   } else {
-    uint64_t work = c.n - c.vGhostLo - c.vGhostHi;
+    uint64_t work = a.n > a.v0 ? a.n - a.v0 : 0;
     if (c.geom == Geom::BOX) {
       work = static_cast<uint64_t>(a.z_end - a.z_begin) * c.nx * c.ny;
     }
@@ -1873,7 +1966,9 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
           "launch stage kernel");
     nsBlocks = grid;
   }
-  ++launchCount;
+  if (doMain) {
+    ++launchCount;
+  }
   if (timed) {
     check(cudaEventRecord(timerEvents[timerUsed].second, stream),
           "cudaEventRecord");
@@ -1882,7 +1977,7 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
       flushTimers();
     }
   }
-  if (c.nMvox > 0) {
+  if (c.nMvox > 0 && doMemb) {
     // SmebMembArgs: 4 pointers, SMEB_NCOMP pointers, 2 x u32
     std::vector<unsigned long long> blob(4 + comps.size() + 1);
     blob[0] = reinterpret_cast<unsigned long long>(c.dMvox);

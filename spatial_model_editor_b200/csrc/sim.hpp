@@ -140,6 +140,7 @@ struct CompartmentState {
   std::vector<int32_t> voxels;
   int nbuf{0};
   double *buf[4]{nullptr, nullptr, nullptr, nullptr};
+  std::vector<void *> stateAllocs; // what buf[] / pool[] point into (freed once)
   CUtensorMap tmap[4]{};
   int role[4]{0, 1, 2, 3};
   uint32_t *dNn{nullptr};
@@ -280,9 +281,11 @@ private:
   cudaEvent_t forkEvent{nullptr};
   cudaStream_t forkMain{nullptr}, forkMemb{nullptr};
   void launchStage(std::size_t stageIndex, double dt);
+  // parts: 1 = main kernel over the range in `a` (z_begin..z_end / v0..n),
+  // 2 = membrane kernel, 3 = both
   void launchCompartment(std::size_t ci, StageArgsHost &a,
                          const StageKernels &k, int cinBuf,
-                         bool nsPrepass = false);
+                         bool nsPrepass = false, unsigned parts = 3);
   void rotateAfterAccept();
   void readError(double &eabs, double &erel);
   double doRK101(double dt);
@@ -293,7 +296,11 @@ private:
   void flushTimers();
   void setupSlabs(const smeb200_problem &p);
   void connectSlabs();
-  void haloExchange(int coutBuf);
+  void haloPush(int coutBuf, cudaStream_t s);
+  void haloWait();
+  cudaStream_t haloStream{nullptr};
+  cudaEvent_t boundaryDone{nullptr}, haloPushed{nullptr};
+  bool suppressTiming{false};
   void updateCrossDiffusionMaxStableTimestep();
   void solveZeroStorageConstraints(std::size_t stageIndex);
   void encodeTensorMap(const CompartmentState &c, double *buffer,
