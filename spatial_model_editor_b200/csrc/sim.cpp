@@ -1418,11 +1418,15 @@ void Sim::connectSlabs() {
   // computed (SMEB200_HALO_OVERLAP=0: everything on the main stream)
   const char *ov = std::getenv("SMEB200_HALO_OVERLAP");
   if (ov == nullptr || std::string(ov) != "0") {
-    check(cudaStreamCreateWithFlags(&haloStream, cudaStreamNonBlocking),
+    int prLow = 0, prHigh = 0; // boundary CTAs are scheduled ahead of interior ones
+    check(cudaDeviceGetStreamPriorityRange(&prLow, &prHigh), "stream priorities");
+    check(cudaStreamCreateWithPriority(&haloStream, cudaStreamNonBlocking, prHigh),
           "cudaStreamCreate(halo)");
-    check(cudaEventCreateWithFlags(&boundaryDone, cudaEventDisableTiming),
+    check(cudaEventCreateWithFlags(&stageInputReady, cudaEventDisableTiming),
           "cudaEventCreate");
     check(cudaEventCreateWithFlags(&haloPushed, cudaEventDisableTiming),
+          "cudaEventCreate");
+    check(cudaEventCreateWithFlags(&boundaryDone, cudaEventDisableTiming),
           "cudaEventCreate");
   }
   comm->barrier();
@@ -1485,8 +1489,8 @@ void Sim::haloPush(int coutBuf, cudaStream_t s) {
   ++haloExchanges;
 }
 
-// make the main stream wait for the neighbours' pushes of the current stage
-void Sim::haloWait() {
+// make stream `s` wait for the neighbours' pushes of the latest stage
+void Sim::haloWait(cudaStream_t s) {
   const auto &drv = DriverApi::get();
   auto flagDev = [&](int r, int side) {
     return flagBaseDev +
@@ -1495,15 +1499,27 @@ void Sim::haloWait() {
                static_cast<unsigned char *>(comm->flagPages()));
   };
   if (rank > 0) {
-    check(drv.StreamWaitValue32(stream, flagDev(rank, 0), haloSeq,
+    check(drv.StreamWaitValue32(s, flagDev(rank, 0), haloSeq,
                                 CU_STREAM_WAIT_VALUE_GEQ),
           "cuStreamWaitValue32");
   }
   if (rank + 1 < nRanks) {
-    check(drv.StreamWaitValue32(stream, flagDev(rank, 1), haloSeq,
+    check(drv.StreamWaitValue32(s, flagDev(rank, 1), haloSeq,
                                 CU_STREAM_WAIT_VALUE_GEQ),
           "cuStreamWaitValue32");
   }
+}
+
+// Outside run() / benchSteps() nothing is in flight on the halo stream and all
+// ghost voxels of the current state have arrived.
+void Sim::haloQuiesce() {
+  if (!haloPending) {
+    return;
+  }
+  check(cudaEventRecord(haloPushed, haloStream), "halo event");
+  haloWait(stream);
+  check(cudaStreamWaitEvent(stream, haloPushed, 0), "halo pushed wait");
+  haloPending = false;
 }
 
 Sim::~Sim() {
@@ -1515,8 +1531,9 @@ Sim::~Sim() {
   if (haloStream != nullptr) {
     cudaStreamSynchronize(haloStream);
     cudaStreamDestroy(haloStream);
-    cudaEventDestroy(boundaryDone);
+    cudaEventDestroy(stageInputReady);
     cudaEventDestroy(haloPushed);
+    cudaEventDestroy(boundaryDone);
   }
   if (comm) {
     // nobody may still be pushing halos into this rank's buffers
@@ -1630,6 +1647,15 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
   if (fork) {
     check(cudaEventRecord(forkEvent, stream), "fork event");
   }
+  if (overlapHalo) {
+    // halo stream: the stage input is complete once the main stream got here
+    // and the neighbours' halos of the previous stage have arrived
+    check(cudaEventRecord(stageInputReady, stream), "stage input event");
+    check(cudaStreamWaitEvent(haloStream, stageInputReady, 0), "halo stream wait");
+    if (haloSeq > 0) {
+      haloWait(haloStream);
+    }
+  }
   for (std::size_t ci = 0; ci < comps.size(); ++ci) {
     auto &c = comps[ci];
     if (c.S == 0 || c.n == 0) {
@@ -1702,8 +1728,9 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     }
     if (overlapHalo) {
       // z-slab: the owned boundary planes (what the neighbours need) and the
-      // membrane kernels first; the interior follows once their halos are on
-      // the way (below)
+      // membrane kernels go to the high-priority halo stream, which pushes the
+      // halos as soon as they are done; the interior runs beside them on the
+      // main stream (below)
       StageArgsHost lo = a, hi = a, mid = a;
       if (c.box) {
         const uint32_t zb = a.z_begin, ze = a.z_end;
@@ -1727,6 +1754,7 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
         return c.box ? r.z_begin >= r.z_end : r.v0 >= r.n;
       };
       suppressTiming = true;
+      forkMain = forkMemb = haloStream; // concurrent with the interior launch
       if (!empty(lo)) {
         launchCompartment(ci, lo, c.kStage[stageIndex], c.role[sd.cin], false, 1);
       }
@@ -1734,6 +1762,7 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
         launchCompartment(ci, hi, c.kStage[stageIndex], c.role[sd.cin], false, 1);
       }
       launchCompartment(ci, a, c.kStage[stageIndex], c.role[sd.cin], false, 2);
+      forkMain = forkMemb = nullptr;
       suppressTiming = false;
       if (!empty(mid)) {
         interior.emplace_back(ci, mid);
@@ -1764,20 +1793,21 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     const int coutBuf = comps[0].role[sd.cout];
     if (overlapHalo) {
       // the halos travel (and the neighbours' arrive) while the interior is
-      // computed; the next stage needs both directions to be complete
-      check(cudaEventRecord(boundaryDone, stream), "boundary event");
-      check(cudaStreamWaitEvent(haloStream, boundaryDone, 0), "halo stream wait");
+      // computed
+      check(cudaEventRecord(boundaryDone, haloStream), "boundary event");
       haloPush(coutBuf, haloStream);
-      check(cudaEventRecord(haloPushed, haloStream), "halo event");
       for (auto &[ci, mid] : interior) {
         launchCompartment(ci, mid, comps[ci].kStage[stageIndex],
                           comps[ci].role[sd.cin], false, 1);
       }
-      haloWait();
-      check(cudaStreamWaitEvent(stream, haloPushed, 0), "halo pushed wait");
+      // the main stream never reads ghost voxels: it only needs this rank's own
+      // boundary planes before the next stage (the flags of the neighbours are
+      // awaited by the halo stream, and by haloQuiesce() when stepping ends)
+      check(cudaStreamWaitEvent(stream, boundaryDone, 0), "boundary wait");
+      haloPending = true;
     } else {
       haloPush(coutBuf, stream);
-      haloWait();
+      haloWait(stream);
     }
   }
 }
@@ -2333,6 +2363,7 @@ std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
       } else {
         tNow += doRKAdaptive(maxDt);
         if (!errorMessage.empty()) {
+          haloQuiesce();
           flushTimers();
           return steps;
         }
@@ -2361,6 +2392,7 @@ std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
         break;
       }
     }
+    haloQuiesce();
     check(cudaEventRecord(runEv1, stream), "cudaEventRecord");
     flushTimers();
     check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
@@ -2392,6 +2424,7 @@ double Sim::benchSteps(double dt, std::size_t nSteps) {
       }
       rotateAfterAccept();
     }
+    haloQuiesce();
     check(cudaEventRecord(e1, stream), "cudaEventRecord");
     check(cudaEventSynchronize(e1), "cudaEventSynchronize");
     float ms = 0;

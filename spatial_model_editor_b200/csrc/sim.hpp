@@ -297,9 +297,11 @@ private:
   void setupSlabs(const smeb200_problem &p);
   void connectSlabs();
   void haloPush(int coutBuf, cudaStream_t s);
-  void haloWait();
+  void haloWait(cudaStream_t s);
+  void haloQuiesce();
+  bool haloPending{false};
   cudaStream_t haloStream{nullptr};
-  cudaEvent_t boundaryDone{nullptr}, haloPushed{nullptr};
+  cudaEvent_t stageInputReady{nullptr}, haloPushed{nullptr}, boundaryDone{nullptr};
   bool suppressTiming{false};
   void updateCrossDiffusionMaxStableTimestep();
   void solveZeroStorageConstraints(std::size_t stageIndex);
