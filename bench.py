@@ -232,6 +232,41 @@ def run_reference(args, rank, world):
         "gpu_launches": 0}))
 
 
+def run_refcuda_port(args, rank):
+    """--impl refcuda-port (not a driver arm; SURVEY §8(d) "Reference-CUDA baseline"):
+    the unfused kernel sequence of the reference's own GPU backend, restated in
+    baselines/refcuda_port.cu, on the headline workload on ONE GPU — "the kernel to
+    beat", recompiled for sm_100a.  Same metric, same timing rules."""
+    if rank != 0:
+        return
+    from baselines.refcuda_port import RefCudaPort
+    nx = ny = args.size
+    nz = args.nz or args.size
+    W, K = max(args.warmup, 3), args.steps
+    sim = RefCudaPort(nx, ny, nz, gray_scott_3d_state(nx, ny, nz, 0))
+    sim.steps(args.dt, W)
+    l0 = sim.launches()
+    sampler = ClockSampler(0)
+    sampler.start()
+    ms, _ = sim.steps(args.dt, K)
+    clocks = sampler.stop()
+    launches = sim.launches() - l0
+    evals = 2 * nx * ny * nz * 2  # RK212: 2 stages x voxels x species
+    value = evals * K / (ms * 1e-3)
+    print(json.dumps({
+        "impl": "reference-cuda-port", "metric": METRIC, "value": value, "unit": UNIT,
+        "n_gpus": 1, "steps": K, "warmup": W, "ms_per_step": ms / K,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": f"gray-scott-3d kinetics, {nx}x{ny}x{nz} full-box compartment, "
+                               f"S=2, RK212 fixed step dt={args.dt}",
+                   "l2": "inputs larger than L2" if nx * ny * nz * 16 > 2 ** 28 else "small",
+                   "kernels": "reference GPU backend restated: reaction, diffusion (uint32 nn "
+                              "gather), rk212 substep 1/2, error, 1-block reduce, clamp; "
+                              "blocking error download per step"},
+        "gpu_launches": launches, "clocks": clocks}))
+
+
 def run_ensemble(args, rank, world, local_rank):
     """--workload ensemble: BASELINE config 5 — liver-simplified (7800 x 8 + 481 x 6
     voxel-species, one membrane), 64 members scanning one rate constant
@@ -305,6 +340,9 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.impl == "refcuda-port":
+        run_refcuda_port(args, rank)
         return
     if args.workload == "ensemble":
         run_ensemble(args, rank, world, local_rank)
