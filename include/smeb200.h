@@ -249,6 +249,19 @@ int smeb200_get_lower_order(smeb200_sim *sim, size_t compartment,
  * species; n_out must be 3 * n_primary_species. */
 int smeb200_get_avg_min_max(smeb200_sim *sim, size_t compartment, double *out,
                             size_t n_out);
+/* One species of every (stride[0], stride[1], stride[2]) = (x, y, z)-th voxel of a
+ * compartment's current state, gathered on the device and downloaded into a
+ * pinned buffer owned by the simulator (valid until the next call on `sim`):
+ * the decimated image a front end draws after an image interval instead of the
+ * whole state Simulation::updateConcentrations copies (simulate.cpp:313-314,
+ * SURVEY 8(f) rank 2).  Box compartments: data[(zi * mx + xi) * my + yi] with
+ * mx = ceil(nx / stride[0]) etc., dims[0..2] = {mx, my, mz} (z-slabs: the owned
+ * planes).  Voxel-list compartments: every stride[0]-th voxel of the (owned)
+ * list, stride[1] = stride[2] = 1, dims = {n_out, 1, 1}.  `species` counts the
+ * stored values of a voxel (padding included). */
+int smeb200_get_species_decimated(smeb200_sim *sim, size_t compartment,
+                                  size_t species, const uint32_t stride[3],
+                                  const double **data, size_t dims[3]);
 /* The device layout of a voxel-list compartment's neighbour table, exposed for
  * inspection and tests (no device needed): nn[6*i+k] as in
  * smeb200_compartment -> one code per voxel (bits 0-24 run id, bits 25-30

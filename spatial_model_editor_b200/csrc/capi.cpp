@@ -114,6 +114,17 @@ int smeb200_get_avg_min_max(smeb200_sim *sim, size_t compartment, double *out,
                  [&] { sim->impl.getAvgMinMax(compartment, out, n_out); });
 }
 
+int smeb200_get_species_decimated(smeb200_sim *sim, size_t compartment,
+                                  size_t species, const uint32_t stride[3],
+                                  const double **data, size_t dims[3]) {
+  return guarded(sim, [&] {
+    if (stride == nullptr || data == nullptr || dims == nullptr) {
+      throw smeb200::Error("getSpeciesDecimated: null argument");
+    }
+    *data = sim->impl.getSpeciesDecimated(compartment, species, stride, dims);
+  });
+}
+
 size_t smeb200_neighbour_bytes_per_voxel(const smeb200_sim *s, size_t comp) {
   return s != nullptr && comp < s->impl.nCompartments()
              ? s->impl.neighbourBytesPerVoxel(comp)

@@ -1120,6 +1120,24 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   }
 }
 
+// One species of every (sx, sy, sz)-th voxel of a z,x,y-ordered block of voxels:
+// out[(zi * mx + xi) * my + yi] = c[(((z0 + zi*sz) * nx + xi*sx) * ny + yi*sy) * S + s].
+// A voxel list is the block nx = nz = 1, ny = n.  The decimated image of a
+// species is all that leaves the device (Simulation::updateConcentrations copies
+// the whole state per image interval, simulate.cpp:313-314).
+__global__ void __launch_bounds__(SMEB_BLOCK)
+    smeb_gather_species(const double *__restrict__ c, double *__restrict__ out,
+                        smeb_u32 S, smeb_u32 s, smeb_u32 nx, smeb_u32 ny,
+                        smeb_u32 z0, smeb_u32 sx, smeb_u32 sy, smeb_u32 sz,
+                        smeb_u32 mx, smeb_u32 my, unsigned long long nOut) {
+  for (unsigned long long j = (unsigned long long)blockIdx.x * SMEB_BLOCK + threadIdx.x;
+       j < nOut; j += (unsigned long long)gridDim.x * SMEB_BLOCK) {
+    const unsigned long long yi = j % my, xi = (j / my) % mx, zi = j / ((unsigned long long)my * mx);
+    const unsigned long long v = ((z0 + zi * sz) * nx + xi * sx) * ny + yi * sy;
+    out[j] = c[v * S + s];
+  }
+}
+
 // out[3*s .. 3*s+2] = {average, min, max} of species s
 __global__ void __launch_bounds__(SMEB_BLOCK)
     smeb_stats_finish(const double *__restrict__ partial, smeb_u32 nBlocks,

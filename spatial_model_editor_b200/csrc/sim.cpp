@@ -1528,6 +1528,8 @@ Sim::~Sim() {
   }
   cudaSetDevice(device);
   cudaStreamSynchronize(stream);
+  cudaFree(dGather);
+  cudaFreeHost(hGather);
   if (haloStream != nullptr) {
     cudaStreamSynchronize(haloStream);
     cudaStreamDestroy(haloStream);
@@ -2563,6 +2565,96 @@ void Sim::getAvgMinMax(std::size_t comp, double *out, std::size_t nOut) {
                         cudaMemcpyDeviceToHost, stream),
         "download statistics");
   check(cudaStreamSynchronize(stream), "download statistics");
+}
+
+// a decimated image of one species leaves the device instead
+// of the whole state (Simulation::updateConcentrations, simulate.cpp:313-314)
+const double *Sim::getSpeciesDecimated(std::size_t comp, std::size_t species,
+                                       const uint32_t stride[3],
+                                       std::size_t dims[3]) {
+  if (comp >= comps.size()) {
+    throw Error("compartment index out of range");
+  }
+  if (ctorFailed) {
+    throw Error(errorMessage);
+  }
+  auto &c = comps[comp];
+  if (species >= c.S) {
+    throw Error("getSpeciesDecimated: species index out of range");
+  }
+  uint32_t sx = stride[0], sy = stride[1], sz = stride[2];
+  if (sx == 0 || sy == 0 || sz == 0) {
+    throw Error("getSpeciesDecimated: strides must be positive");
+  }
+  uint32_t nx = c.nx, ny = c.ny, z0 = c.zLoGhost;
+  uint64_t nzOwned = c.nz - c.zLoGhost - c.zHiGhost;
+  std::size_t voxelOffset = 0;
+  if (!c.box) {
+    // a voxel list is one row: every sx-th voxel of the owned range
+    if (sy != 1 || sz != 1) {
+      throw Error("getSpeciesDecimated: a voxel-list compartment takes one "
+                  "stride (stride[1] = stride[2] = 1)");
+    }
+    voxelOffset = c.ownedBegin();
+    ny = static_cast<uint32_t>(c.ownedEnd() - c.ownedBegin());
+    nx = 1;
+    nzOwned = ny > 0 ? 1 : 0;
+    z0 = 0;
+    sy = sx;
+    sx = 1;
+  }
+  uint32_t mx = (nx + sx - 1) / sx, my = (ny + sy - 1) / sy;
+  const uint64_t mz = (nzOwned + sz - 1) / sz;
+  const uint64_t nOut = mz * mx * my;
+  if (c.box) {
+    dims[0] = mx;
+    dims[1] = my;
+    dims[2] = mz;
+  } else {
+    dims[0] = nOut;
+    dims[1] = dims[2] = 1;
+  }
+  if (nOut == 0) {
+    return hGather;
+  }
+  bindDevice();
+  if (nOut > gatherCapacity) {
+    check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+    cudaFree(dGather);
+    cudaFreeHost(hGather);
+    dGather = hGather = nullptr;
+    gatherCapacity = 0;
+    dGather = devAlloc<double>(nOut, "allocate decimated image");
+    check(cudaMallocHost(reinterpret_cast<void **>(&hGather), nOut * sizeof(double)),
+          "allocate pinned decimated image");
+    gatherCapacity = nOut;
+  }
+  const std::string name = "smeb_gather_species";
+  if (auxFn.find(name) == auxFn.end()) {
+    auxModules.push_back(compile({name}));
+    for (const auto &[k, f] : auxModules.back().fn) {
+      auxFn[k] = f;
+    }
+  }
+  const auto &drv = DriverApi::get();
+  const double *state = c.buf[c.role[CUR]] + voxelOffset * c.S;
+  double *dout = dGather;
+  uint32_t S = c.S, s = static_cast<uint32_t>(species);
+  unsigned long long n = nOut;
+  const unsigned grid = static_cast<unsigned>(std::max<uint64_t>(
+      1, std::min<uint64_t>((nOut + BLOCK - 1) / BLOCK,
+                            static_cast<uint64_t>(smCount) * 8u)));
+  void *params[] = {&state, &dout, &S, &s,  &nx, &ny, &z0,
+                    &sx,    &sy,   &sz, &mx, &my, &n};
+  check(drv.LaunchKernel(auxFn.at(name), grid, 1, 1, BLOCK, 1, 1, 0, stream, params,
+                         nullptr),
+        "launch gather kernel");
+  ++launchCount;
+  check(cudaMemcpyAsync(hGather, dGather, nOut * sizeof(double),
+                        cudaMemcpyDeviceToHost, stream),
+        "download decimated image");
+  check(cudaStreamSynchronize(stream), "download decimated image");
+  return hGather;
 }
 
 // dc/dt of the last evaluated stage (PixelSim::getDcdt).  The fused stages

@@ -185,6 +185,8 @@ public:
   double getLowerOrder(std::size_t comp, std::size_t species, std::size_t pixel);
   void setConcentrations(std::size_t comp, const double *data, std::size_t n);
   void getAvgMinMax(std::size_t comp, double *out, std::size_t nOut);
+  const double *getSpeciesDecimated(std::size_t comp, std::size_t species,
+                                    const uint32_t stride[3], std::size_t dims[3]);
   // new values of the runtime parameters: captured step graphs carry the old
   // ones in their kernel arguments and are dropped
   void setParams(const double *values, std::size_t n);
@@ -333,6 +335,8 @@ private:
   int device{0};
   cudaStream_t stream{nullptr};
   Module mainModule;
+  double *dGather{nullptr}, *hGather{nullptr}; // decimated species image
+  std::size_t gatherCapacity{0};
   std::vector<Module> auxModules;
   std::map<std::string, CUfunction> auxFn;
   std::vector<CompartmentState> comps;

@@ -63,6 +63,9 @@ def _bind(lib, prefix: str):
     fn("set_error", None, [vp, C.c_char_p], optional=True)
     fn("neighbour_bytes_per_voxel", C.c_size_t, [vp, C.c_size_t], optional=True)
     fn("neighbour_runs", C.c_size_t, [vp, C.c_size_t], optional=True)
+    fn("get_species_decimated", C.c_int,
+       [vp, C.c_size_t, C.c_size_t, C.POINTER(C.c_uint32),
+        C.POINTER(C.POINTER(C.c_double)), C.POINTER(C.c_size_t)], optional=True)
     fn("get_avg_min_max", C.c_int, [vp, C.c_size_t, C.POINTER(C.c_double), C.c_size_t],
        optional=True)
     fn("bench_steps", C.c_double, [vp, C.c_double, C.c_size_t], optional=True)
@@ -272,6 +275,24 @@ class PixelSim(CSim):
         if rc != 0:
             raise RuntimeError(self.errorMessage())
         return out
+
+    def getSpeciesDecimated(self, compartmentIndex: int, species: int,
+                            stride=(1, 1, 1)) -> np.ndarray:
+        """one stored species of every (sx, sy, sz)-th voxel, gathered on the device:
+        box compartments -> array [mz, mx, my]; voxel lists -> every sx-th voxel"""
+        st = (C.c_uint32 * 3)(*[int(v) for v in stride])
+        data = C.POINTER(C.c_double)()
+        dims = (C.c_size_t * 3)()
+        rc = self._f("get_species_decimated")(self._h, compartmentIndex, species, st,
+                                              C.byref(data), dims)
+        if rc != 0:
+            raise RuntimeError(self.errorMessage())
+        mx, my, mz = int(dims[0]), int(dims[1]), int(dims[2])
+        n = mx * my * mz
+        if n == 0:
+            return np.zeros((0,), dtype=np.float64)
+        a = np.ctypeslib.as_array(data, shape=(n,)).copy()
+        return a.reshape(mz, mx, my) if (my > 1 or mz > 1) else a
 
     def neighbourBytesPerVoxel(self, compartmentIndex: int) -> int:
         """0 (box), 4 (run-compressed neighbour codes) or 24 (plain table)"""

@@ -363,3 +363,46 @@ def test_avg_min_max_box():
     host = avg_min_max_host(gpu.getConcentrations(0), 2)
     assert np.array_equal(dev[:, 1:], host[:, 1:])
     assert np.allclose(dev[:, 0], host[:, 0], rtol=1e-13, atol=0)
+
+
+# ---- decimated species image -----------------------------
+@pytest.mark.parametrize("stride", [(1, 1, 1), (2, 3, 4), (5, 1, 7), (64, 64, 64)])
+def test_species_decimated_box(stride):
+    nx, ny, nz = 37, 29, 11
+    p = M.box_problem(M.GRAY_SCOTT, nx, ny, nz)
+    p.device = 0
+    gpu = smeb.PixelSim(p)
+    gpu.run(0.2)
+    full = gpu.getConcentrations(0).reshape(nz, nx, ny, 2)
+    sx, sy, sz = stride
+    for s in (0, 1):
+        img = gpu.getSpeciesDecimated(0, s, stride)
+        want = full[::sz, ::sx, ::sy, s]
+        assert np.array_equal(img.reshape(want.shape), want)
+
+
+@pytest.mark.parametrize("k", [1, 3, 1000])
+def test_species_decimated_voxel_list(k):
+    p, _, _ = load_golden("very-simple-model")
+    p.device = 0
+    gpu = smeb.PixelSim(p)
+    gpu.run(0.01)
+    for ci, c in enumerate(p.compartments):
+        stride_values = gpu.getConcentrationPadding() + c.n_primary_species
+        full = gpu.getConcentrations(ci).reshape(c.n_voxels, -1)
+        assert full.shape[1] == stride_values or full.shape[1] == c.n_species
+        for s in range(full.shape[1]):
+            img = gpu.getSpeciesDecimated(ci, s, (k, 1, 1))
+            assert np.array_equal(img.ravel(), full[::k, s])
+
+
+def test_species_decimated_errors():
+    p = M.box_problem(M.GRAY_SCOTT, 8, 8, 2)
+    p.device = 0
+    gpu = smeb.PixelSim(p)
+    with pytest.raises(RuntimeError, match="species index"):
+        gpu.getSpeciesDecimated(0, 2, (1, 1, 1))
+    with pytest.raises(RuntimeError, match="positive"):
+        gpu.getSpeciesDecimated(0, 0, (0, 1, 1))
+    with pytest.raises(RuntimeError, match="compartment index"):
+        gpu.getSpeciesDecimated(3, 0, (1, 1, 1))
