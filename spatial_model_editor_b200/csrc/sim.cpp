@@ -1025,10 +1025,6 @@ void Sim::build(const smeb200_problem &p) {
       throw Error("smeb200: voxel_size is required with non-uniform or "
                   "cross-diffusion");
     }
-    if ((c.nonUniform || !c.crossTarget.empty()) && p.n_ranks > 1) {
-      throw Error("smeb200: non-uniform and cross-diffusion are not supported "
-                  "in a z-slab decomposed simulation");
-    }
     for (uint32_t s = 0; s < c.S; ++s) {
       c.speciesNames.emplace_back(
           pc.species_names != nullptr && pc.species_names[s] != nullptr
@@ -1302,6 +1298,8 @@ void Sim::build(const smeb200_problem &p) {
   }
   if (comm) {
     connectSlabs();
+    slabsConnected = true;
+    syncMaxStableTimestep(); // per-voxel diffusion constants differ per slab
   }
 }
 
@@ -2248,11 +2246,14 @@ void Sim::updateCrossDiffusionMaxStableTimestep() {
           "clear cross-diffusion maxima");
     StageArgsHost a{};
     a.cin = c.buf[c.role[CUR]];
-    a.n = static_cast<uint32_t>(c.n);
+    // z-slabs: the owned voxels (the ghosts are other ranks' voxels, and their
+    // halos may still be on the way)
+    a.v0 = static_cast<uint32_t>(c.ownedBegin());
+    a.n = static_cast<uint32_t>(c.ownedEnd());
     a.xdMax = c.dXdMax;
     std::copy(params.begin(), params.end(), a.D + 3 * c.S);
     const unsigned grid = static_cast<unsigned>(std::max<uint64_t>(
-        1, std::min<uint64_t>((c.n + BLOCK - 1) / BLOCK,
+        1, std::min<uint64_t>((a.n - a.v0 + BLOCK - 1) / BLOCK,
                               static_cast<uint64_t>(smCount) * 8u)));
     void *kparams[] = {&a};
     check(drv.LaunchKernel(c.kXdMax, grid, 1, 1, BLOCK, 1, 1, 0, stream,
@@ -2293,6 +2294,17 @@ void Sim::updateCrossDiffusionMaxStableTimestep() {
       maxStableTimestep = std::min(maxStableTimestep, c.maxStable);
     }
   }
+  syncMaxStableTimestep();
+}
+
+// z-slabs: the forward-Euler bound is the minimum over the ranks' voxels
+void Sim::syncMaxStableTimestep() {
+  if (!comm || !slabsConnected) {
+    return;
+  }
+  double v = -maxStableTimestep; // exact under negation
+  comm->allreduceMax(&v, 1);
+  maxStableTimestep = -v;
 }
 
 double Sim::doRK101(double dt) {

@@ -301,6 +301,8 @@ private:
   void haloPush(int coutBuf, cudaStream_t s);
   void haloWait(cudaStream_t s);
   void haloQuiesce();
+  void syncMaxStableTimestep();
+  bool slabsConnected{false};
   bool haloPending{false};
   cudaStream_t haloStream{nullptr};
   cudaEvent_t stageInputReady{nullptr}, haloPushed{nullptr}, boundaryDone{nullptr};

@@ -90,6 +90,9 @@ def local_problem(problem: Problem, rank: int, world: int, comm_name: str,
                 conc = np.ascontiguousarray(c.conc0[g0 * plane:g1 * plane])
             lc = copy.copy(c)
             lc.conc0, lc.box = conc, (nx, ny, g1 - g0)
+            if c.diffusion_array is not None:
+                lc.diffusion_array = np.ascontiguousarray(
+                    c.diffusion_array[g0 * plane:g1 * plane])
             slabs.append(None)
         else:
             if c.voxels is None:

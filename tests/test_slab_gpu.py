@@ -160,3 +160,88 @@ def test_listed_slabs_match_single_gpu(kind, integ, adaptive):
         # per-rank device statistics cover the owned voxels: min / max combine exactly
         mn = min(r[7][i][:, 1].min() for r in res if len(r[4][i]))
         assert mn == c_ref[i][:, :].min(axis=0).min()
+
+
+# ---- non-uniform (per-voxel) diffusion and cross-diffusion in slabs ----------------
+def _diffusion_problem(feature, geom, integ):
+    """feature "nonuniform" / "cross" / "cross-dynamic" (RK101 whose step follows the
+    state-dependent forward-Euler bound, allreduced over the ranks every step);
+    geom "box" or "list" (the 3-D single-compartment-diffusion example)"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from util import load_golden
+    rng = np.random.default_rng(11)
+    if geom == "box":
+        p = M.box_problem(M.GRAY_SCOTT, 20, 24, 15, integrator=integ,
+                          voxel_size=(1.0, 1.5, 2.0))
+        p.voxel_size = (1.0, 1.5, 2.0)
+        D = np.array(M.GRAY_SCOTT["D"])
+    else:
+        p, meta, _ = load_golden("single-compartment-diffusion-3d", integrator=integ)
+        p.voxel_size = tuple(meta["voxel_size"])
+        D = np.array(meta["compartments"][0]["diffusion_constants"])
+    c = p.compartments[0]
+    if feature == "nonuniform":
+        c.diffusion_array = np.ascontiguousarray(
+            D[None, :] * rng.uniform(0.0, 1.5, size=(c.n_voxels, c.n_species)))
+    else:
+        c.diffusion_raw = D
+        k = "(6.0 * sme_var_0)" if feature == "cross-dynamic" else "(0.3 + 0.5 * sme_var_0)"
+        c.cross_diffusion = [(1, 0, k), (0, 1, "(0.05 * sme_var_1)")]
+    p.max_err_abs = p.max_err_rel = smeb.DBL_MAX
+    if feature != "cross-dynamic":
+        p.max_timestep = 0.01
+    return p
+
+
+def _diffusion_worker(rank, world, name, feature, geom, integ, t_end, q):
+    sys.path.insert(0, ROOT)
+    from spatial_model_editor_b200.multigpu import SlabPixelSim
+    try:
+        p = _diffusion_problem(feature, geom, integ)
+        p.device = rank
+        sim = SlabPixelSim(p, rank, world, comm_name=name)
+        err0 = sim.errorMessage()
+        dt0 = sim.maxStableTimestep
+        n = sim.run(t_end / 2) + sim.run(t_end / 2)
+        q.put((rank, err0 + sim.errorMessage(), n, dt0, sim.maxStableTimestep,
+               sim.getConcentrations(0).copy(), sim.getDcdt(0).copy()))
+        sim.close()
+    except Exception as e:  # noqa: BLE001
+        q.put((rank, f"exception: {e!r}", 0, 0.0, 0.0, None, None))
+
+
+@pytest.mark.parametrize("geom", ["box", "list"])
+@pytest.mark.parametrize("feature,integ", [("nonuniform", smeb.RK212), ("nonuniform", smeb.RK101),
+                                           ("cross", smeb.RK323), ("cross-dynamic", smeb.RK101)])
+def test_diffusion_features_in_slabs_match_single_gpu(feature, integ, geom):
+    world = min(smeb.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs >= 2 GPUs")
+    import torch.multiprocessing as mp
+    t_end = 1.0 if feature == "cross-dynamic" else 0.1
+    p = _diffusion_problem(feature, geom, integ)
+    p.device = 0
+    ref = smeb.PixelSim(p)
+    assert ref.errorMessage() == ""
+    dt0 = ref.maxStableTimestep
+    n_ref = ref.run(t_end / 2) + ref.run(t_end / 2)
+    assert n_ref >= 10
+    c_ref, d_ref = ref.getConcentrations(0).copy(), ref.getDcdt(0).copy()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    name = f"smeb200_difftest_{os.getpid()}_{feature}_{geom}_{integ}"
+    procs = [ctx.Process(target=_diffusion_worker,
+                         args=(r, world, name, feature, geom, integ, t_end, q))
+             for r in range(world)]
+    for pr in procs:
+        pr.start()
+    res = sorted((q.get(timeout=300) for _ in range(world)), key=lambda r: r[0])
+    for pr in procs:
+        pr.join(timeout=60)
+    for r in res:
+        assert r[1] == "", r[1]
+        assert r[2] == n_ref
+        # the forward-Euler bound is the global one on every rank
+        assert r[3] == dt0 and r[4] == ref.maxStableTimestep
+    assert np.array_equal(np.concatenate([r[5] for r in res]), c_ref)
+    assert np.array_equal(np.concatenate([r[6] for r in res]), d_ref)
