@@ -35,6 +35,10 @@ MODELS = {
     "single-compartment-diffusion": "core/resources/models/single-compartment-diffusion.xml",
     "single-compartment-diffusion-3d":
         "core/resources/models/single-compartment-diffusion-3d.xml",
+    # 30-voxel disc of simulate_t.cpp:1158-1303 (steady states: uniform, zero-storage,
+    # spatially varying diffusion)
+    "small-single-compartment-diffusion":
+        "test/resources/models/small-single-compartment-diffusion.xml",
 }
 
 
