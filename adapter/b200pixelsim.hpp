@@ -10,16 +10,22 @@
 // concentrations, ReacExpr -> Symbolic -> relabel -> cudaCode strings, per-face
 // membrane pair lists, restart concentrations.
 //
-// It is written against the reference headers and is NOT compiled in this
-// repository (Qt6 / SymEngine / libSBML are not installed here); INTEGRATION.md
-// shows the patch to simulate.cpp that selects it.
+// It is written against the reference headers.  SME cannot be linked in this
+// repository (Qt6 / SymEngine / libSBML are not installed here), but the header
+// is type-checked against the reference's own headers by tests/test_adapter_cpu.py
+// (g++ -fsyntax-only, declaration-only stand-ins for the third-party includes:
+// tests/adapter_check/).  INTEGRATION.md shows the patch to simulate.cpp that
+// selects it.
 #pragma once
+
+#include <functional> // basesim.hpp uses std::function without including it
 
 #include "pixelsim_base.hpp"
 #include "pixelsim_common.hpp"
 #include "pixelsim_impl.hpp" // ReacExpr
 #include "sme/geometry.hpp"
 #include "sme/model.hpp"
+#include "sme/simple_symbolic.hpp"
 #include "sme/symbolic.hpp"
 #include "sme/utils.hpp"
 #include "smeb200.h"
@@ -448,7 +454,7 @@ public:
           }
           m.n_pairs[d] = facePairs.size();
           m.pairs[d] = flat.data();
-          m.flux_length[d] = getFaceFluxLength(dir, voxelSize);
+          m.flux_length[d] = detail::getFaceFluxLength(dir, voxelSize);
         }
         membs.push_back(m);
       }
