@@ -413,7 +413,12 @@ def main():
         assert sim.run(W * DTs) == W
     launches0 = sim.launchCount()
     disc0 = sim.discardedSteps
-    sim.setKernelTiming(True)
+    # dominant-kernel durations by CUDA events inside the timed region: on every
+    # step when a step is long, on every 4th step when the two event records per
+    # launch (a few microseconds of stream time) would show in the step time
+    warm_ms_per_step = sim.lastRunMs() / max(W, 1)
+    timing_stride = 1 if warm_ms_per_step > 1.0 or K < 8 else 4
+    sim.setKernelTiming(timing_stride)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -495,7 +500,8 @@ def main():
                     "kernel": sim.dominantKernel(), "launches_timed": klaunches,
                     "avg_launch_ms": kms / klaunches,
                     "algorithmic_bytes_per_launch": alg_bytes_per_launch,
-                    "launch_scope": launch_scope}
+                    "launch_scope": launch_scope,
+                    "timed_steps": f"every {timing_stride}" if timing_stride > 1 else "all"}
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline(args, integrator, threads=0)

@@ -318,7 +318,9 @@ double smeb200_last_run_ms(const smeb200_sim *sim);
 uint64_t smeb200_launch_count(const smeb200_sim *sim);
 /* device time of the dominant stage kernel over the last bench/run window:
  * sum of ms and number of launches (CUDA events, only if profiling enabled
- * with smeb200_set_kernel_timing(sim, 1)) */
+ * with smeb200_set_kernel_timing(sim, n): n = 1 brackets the launches of every
+ * step, n > 1 those of every n-th step — the two event records cost a few
+ * microseconds of stream time per launch, which shows on 100 us kernels) */
 void smeb200_set_kernel_timing(smeb200_sim *sim, int enable);
 int smeb200_get_kernel_timing(const smeb200_sim *sim, double *total_ms,
                               uint64_t *launches);

@@ -241,6 +241,8 @@ uint64_t smeb200_launch_count(const smeb200_sim *sim) {
 void smeb200_set_kernel_timing(smeb200_sim *sim, int enable) {
   if (sim != nullptr) {
     sim->impl.kernelTiming = enable != 0;
+    sim->impl.kernelTimingStride = enable > 1 ? static_cast<unsigned>(enable) : 1u;
+    sim->impl.timingStep = 0;
     sim->impl.kernelMs = 0;
     sim->impl.kernelLaunchesTimed = 0;
   }

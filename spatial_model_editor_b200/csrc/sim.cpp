@@ -20,6 +20,12 @@ namespace {
 constexpr uint32_t MEMB_FLAG = 0x80000000u;
 constexpr unsigned BLOCK = 256;
 
+// NAME=0 in the environment switches an optimisation off (A/B measurements)
+bool envFlagOff(const char *name) {
+  const char *env = std::getenv(name);
+  return env != nullptr && env[0] == '0';
+}
+
 // RK tableaux: pixelsim_common.hpp:138-171
 namespace rk323 {
 constexpr double g1[3]{1.0, 0.25, 0.666666666666666666666};
@@ -1253,6 +1259,11 @@ void Sim::build(const smeb200_problem &p) {
   check(cudaMemsetAsync(dErr, 0, 32, stream), "clear error accumulators");
   check(cudaMallocHost(reinterpret_cast<void **>(&hErr), 16),
         "allocate pinned error mirror");
+  check(cudaMallocHost(reinterpret_cast<void **>(&hErrRing), 16 * kErrRing),
+        "allocate pinned error ring");
+  for (auto &e : errEvents) {
+    check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate");
+  }
   check(cudaMallocHost(reinterpret_cast<void **>(&hDt), sizeof(double)),
         "allocate pinned step size");
   dDt = devAlloc<double>(1, "allocate step size");
@@ -1575,6 +1586,12 @@ Sim::~Sim() {
   cudaFree(dFluxLen);
   cudaFree(dErr);
   cudaFreeHost(hErr);
+  cudaFreeHost(hErrRing);
+  for (auto e : errEvents) {
+    if (e != nullptr) {
+      cudaEventDestroy(e);
+    }
+  }
   cudaFreeHost(hXdMax);
   cudaFreeHost(hDt);
   cudaFree(dDt);
@@ -1950,7 +1967,8 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
   auto &c = comps[ci];
   const bool doMain = (parts & 1u) != 0, doMemb = (parts & 2u) != 0;
   const bool timed = kernelTiming && ci == dominantComp && !nsPrepass &&
-                     !relaxing && doMain && !suppressTiming;
+                     !relaxing && doMain && !suppressTiming &&
+                     timingStep % kernelTimingStride == 0;
   uint32_t nsBlocks = 0; // blocks that wrote partial sums (pre-pass)
   // while a step is captured the kernels of one stage fork onto per-compartment
   // streams (parallel graph branches); otherwise everything is on `stream`
@@ -2188,6 +2206,7 @@ void Sim::doStep(double dt) {
   } else {
     launchAllStages(dt);
   }
+  ++timingStep;
   for (auto &c : comps) {
     c.dcdtStale = true;
     c.lowerStale = true;
@@ -2317,9 +2336,82 @@ double Sim::doRK101(double dt) {
   return dt;
 }
 
+// The error norms of a step, queued behind it: 16 bytes into the next ring slot
+// and an event; nobody waits here.
+void Sim::enqueueErrorRead(double dt, double dtMax) {
+  const std::size_t slot = errTail % kErrRing;
+  check(cudaMemcpyAsync(hErrRing + 2 * slot, dErr, 16, cudaMemcpyDeviceToHost,
+                        stream),
+        "download error norms");
+  check(cudaMemsetAsync(dErr, 0, 16, stream), "clear error accumulators");
+  check(cudaEventRecord(errEvents[slot], stream), "cudaEventRecord");
+  errPending[slot] = {dt, dtMax};
+  ++errTail;
+}
+
+// Checks queued error norms until at most `keep` are in flight.  Each one goes
+// through the controller's own formula (pixelsim.cpp:231-233); with unbounded
+// tolerances that yields "accept, next step = dtMax" for every finite norm, which
+// is what was assumed when the following steps were launched.  A norm for which
+// it does not (infinite: the state blew up) ends the run with the reference's
+// message for a collapsed step size.
+bool Sim::drainErrors(std::size_t keep) {
+  const double errPower = integrator == SMEB200_RK323   ? 1.0 / 3.0
+                          : integrator == SMEB200_RK435 ? 1.0 / 4.0
+                                                        : 1.0 / 2.0;
+  while (errTail - errHead > keep) {
+    const std::size_t slot = errHead % kErrRing;
+    check(cudaEventSynchronize(errEvents[slot]), "cudaEventSynchronize");
+    double v[2];
+    std::memcpy(v, hErrRing + 2 * slot, 16);
+    ++errHead;
+    if (allreduceMax != nullptr) {
+      allreduceMax(v, 2, allreduceUser);
+    } else if (comm) {
+      comm->allreduceMax(v, 2);
+    }
+    const auto [dt, dtMax] = errPending[slot];
+    double errFactor = std::min(errMaxAbs / v[0], errMaxRel / v[1]);
+    errFactor = std::pow(errFactor, errPower);
+    const double next = std::min(0.95 * dt * errFactor, dtMax);
+    if (next != dtMax || v[0] > errMaxAbs || v[1] > errMaxRel) {
+      // keep the ranks of a decomposed run in step: everybody reads every slot
+      while (errTail > errHead) {
+        check(cudaEventSynchronize(errEvents[errHead % kErrRing]),
+              "cudaEventSynchronize");
+        ++errHead;
+      }
+      check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+      nextTimestep = next;
+      std::string problemSpecies{"unknown"};
+      plotRKError(v[1], problemSpecies);
+      errorMessage =
+          "Failed to solve model to required accuracy. The largest "
+          "relative integration error comes from species '" +
+          problemSpecies +
+          "'. The location "
+          "of the pixels with the largest relative integration error are shown "
+          "below in red:";
+      return false;
+    }
+  }
+  return true;
+}
+
 double Sim::doRKAdaptive(double dtMax) {
   double eabs = 0.0, erel = 0.0;
   double dt = 0.0;
+  if (laggedError) {
+    if (!drainErrors(kErrLag)) {
+      return nextTimestep;
+    }
+    dt = std::min(nextTimestep, dtMax);
+    doStep(dt);
+    enqueueErrorRead(dt, dtMax);
+    nextTimestep = dtMax; // min(0.95 dt (DBL_MAX / err)^p, dtMax), err finite
+    rotateAfterAccept();
+    return dt;
+  }
   const double errPower = integrator == SMEB200_RK323   ? 1.0 / 3.0
                           : integrator == SMEB200_RK435 ? 1.0 / 4.0
                                                         : 1.0 / 2.0;
@@ -2369,6 +2461,10 @@ std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
     double tNow = 0;
     discardedSteps = 0;
     constexpr double relativeTolerance = 1e-12;
+    laggedError = integrator != SMEB200_RK101 && !useGraphs && !anyZeroStorage &&
+                  errMaxAbs == std::numeric_limits<double>::max() &&
+                  errMaxRel == std::numeric_limits<double>::max() &&
+                  !envFlagOff("SMEB200_LAGGED_ERROR");
     while (tNow + time * relativeTolerance < time) {
       const double maxDt = std::min(maxTimestep, time - tNow);
       if (integrator == SMEB200_RK101) {
@@ -2405,6 +2501,11 @@ std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
         errorMessage = "Simulation stopped early";
         break;
       }
+    }
+    if (laggedError && !drainErrors(0)) {
+      haloQuiesce();
+      flushTimers();
+      return steps;
     }
     haloQuiesce();
     check(cudaEventRecord(runEv1, stream), "cudaEventRecord");

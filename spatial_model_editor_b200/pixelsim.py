@@ -249,8 +249,9 @@ class PixelSim(CSim):
     def launchCount(self) -> int:
         return int(self._f("launch_count")(self._h))
 
-    def setKernelTiming(self, enable: bool) -> None:
-        self._f("set_kernel_timing")(self._h, 1 if enable else 0)
+    def setKernelTiming(self, enable) -> None:
+        """False / 0: off; True / 1: every step; n > 1: every n-th step"""
+        self._f("set_kernel_timing")(self._h, int(enable))
 
     def kernelTiming(self):
         ms = C.c_double()

@@ -242,3 +242,69 @@ def test_graph_replay_is_bit_identical_to_plain_launches(name, integ, monkeypatc
     for a, b in zip(g[3] + g[4], pl[3] + pl[4]):
         assert np.array_equal(a, b)
     assert g[5] == pl[5]
+
+
+# ---- unbounded tolerances: error norms checked two steps late ----------------------
+@pytest.mark.parametrize("geom", ["box3d_tiles", "box2d_tiles", "abtoc_disc", "membranes3d"])
+@pytest.mark.parametrize("integ", [smeb.RK212, smeb.RK323, smeb.RK435])
+def test_lagged_error_check_is_bit_identical(geom, integ, monkeypatch):
+    """maxErr = {DBL_MAX, DBL_MAX} (benchmark.cpp:214-216): the controller accepts
+    every finite error norm and sets the next step to dtMax (pixelsim.cpp:231-233),
+    so the stream is not stalled after each step and the norms are checked two
+    steps late.  Same steps, same bits as the step-by-step controller, same state
+    as the CPU solver; getters, restarts and short intervals in between"""
+    monkeypatch.setenv("SMEB200_GRAPHS", "0")  # small models would replay graphs
+    out = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("SMEB200_LAGGED_ERROR", mode)
+        p = fixed_step(GEOMETRIES[geom](integ), 0.01)
+        gpu, cpu = make_pair(p)
+        n = [gpu.run(1e-7), gpu.run(0.3), gpu.run(0.005), gpu.run(0.2)]
+        assert n == [cpu.run(1e-7), cpu.run(0.3), cpu.run(0.005), cpu.run(0.2)]
+        assert gpu.errorMessage() == "" and gpu.discardedSteps == 0
+        assert gpu.nextTimestep == cpu.nextTimestep
+        compare_state(gpu, cpu, p, f"{geom} lagged={mode}")
+        out[mode] = [gpu.getConcentrations(i).copy() for i in range(len(p.compartments))]
+    for a, b in zip(out["1"], out["0"]):
+        assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("lagged", ["1", "0"])
+def test_unbounded_tolerances_blow_up_is_reported(lagged, monkeypatch):
+    """a state that overflows makes the error norm infinite: errFactor = 0, the next
+    step collapses and the run ends with the reference's message
+    (pixelsim.cpp:231-251) — also when the norm is looked at two steps late"""
+    monkeypatch.setenv("SMEB200_GRAPHS", "0")
+    monkeypatch.setenv("SMEB200_LAGGED_ERROR", lagged)
+    grow = dict(species=["A", "B"], D=[0.1, 0.1], constants={},
+                reactions=[ReactionDef("r", "1e30 * A * A", {"A": 1.0})])
+    p = fixed_step(M.box_problem(grow, 32, 16, 1, integrator=smeb.RK212), 0.05)
+    gpu, cpu = make_pair(p)
+    cpu.run(5.0)
+    assert cpu.errorMessage().startswith("Failed to solve model to required accuracy")
+    gpu.run(5.0)
+    assert gpu.errorMessage().startswith("Failed to solve model to required accuracy")
+    assert gpu.errorImages().size == cpu.errorImages().size > 0
+
+
+def test_lagged_error_check_with_stop_and_timeout(monkeypatch):
+    """stop callback and deadline still end the run after whole steps"""
+    monkeypatch.setenv("SMEB200_GRAPHS", "0")
+    p = fixed_step(M.box_problem(M.GRAY_SCOTT, 64, 48, 1, integrator=smeb.RK212), 0.01)
+    gpu, cpu = make_pair(p)
+    def stop_after(n):
+        calls = {"n": 0}
+
+        def cb():
+            calls["n"] += 1
+            return calls["n"] >= n
+        return cb
+
+    assert gpu.run(10.0, -1.0, stop_after(5)) == 5
+    assert gpu.errorMessage() == "Simulation stopped early"
+    gpu.setStopRequested(False)
+    assert cpu.run(10.0, -1.0, stop_after(5)) == 5
+    cpu.setStopRequested(False)
+    compare_state(gpu, cpu, p, "stopped after 5 steps")
+    assert gpu.run(1e9, 50.0) >= 1
+    assert gpu.errorMessage() == "Simulation stopped early"
