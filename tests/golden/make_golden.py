@@ -39,6 +39,14 @@ MODELS = {
     # spatially varying diffusion)
     "small-single-compartment-diffusion":
         "test/resources/models/small-single-compartment-diffusion.xml",
+    # the rest of the reference's example models (cudapixelsim_t.cpp:542-575 sweeps
+    # all of them); NFkappaB.xml does not parse here (unbound XML prefix)
+    "CalciumWavePropagation3D": "core/resources/models/CalciumWavePropagation3D.xml",
+    "FitzhughNagumo3D": "core/resources/models/FitzhughNagumo3D.xml",
+    "SelKov3D": "core/resources/models/SelKov3D.xml",
+    "circadian-clock": "core/resources/models/circadian-clock.xml",
+    "liver-cells": "core/resources/models/liver-cells.xml",
+    "very-simple-model-3d": "core/resources/models/very-simple-model-3d.xml",
 }
 
 

@@ -261,3 +261,21 @@ def stop_then_continue(make):
     assert sim.errorMessage() == ""
     assert all(s >= 1 for s in steps)
     return sim
+
+
+def example_3d_models_tiny_step(make, names=("gray-scott-3d", "single-compartment-diffusion-3d",
+                                             "very-simple-model-3d", "FitzhughNagumo3D",
+                                             "SelKov3D")):
+    """simulate_t.cpp:2954-2976 "Simulate example 3d models: do a tiny step, don't
+    crash": one interval of 0.01 with the model's own options completes"""
+    sims = []
+    for name in names:
+        p, _, _ = load_golden(name)
+        sim = make(p)
+        assert sim.errorMessage() == "", name
+        assert sim.run(0.01) >= 1, name
+        assert sim.errorMessage() == "", name
+        for ci in range(len(p.compartments)):
+            assert np.all(np.isfinite(sim.getConcentrations(ci))), name
+        sims.append(sim)
+    return sims

@@ -8,7 +8,8 @@ from oracle.oracle_sim import OraclePixelSim
 SCENARIOS = [K.uniform_steady_state, K.zero_storage_uniform, K.varying_diffusion_steady_state,
              K.storage_scales_dcdt, K.cross_diffusion_vanishes_for_uniform_source,
              K.voxel_centre_coordinates, K.cross_diffusion_z_only_3d,
-             K.rk101_capped_by_cross_diffusion, K.timeout, K.stop_then_continue]
+             K.rk101_capped_by_cross_diffusion, K.timeout, K.stop_then_continue,
+             K.example_3d_models_tiny_step]
 
 
 @pytest.mark.parametrize("scenario", SCENARIOS, ids=lambda f: f.__name__)

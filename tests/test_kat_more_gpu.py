@@ -74,6 +74,7 @@ CASES = [
     (K.rk101_capped_by_cross_diffusion, FIXED),
     (K.timeout, WALL_CLOCK),
     (K.stop_then_continue, ADAPTIVE),
+    (K.example_3d_models_tiny_step, ADAPTIVE),
 ]
 
 
