@@ -486,7 +486,7 @@ def main():
     peak, peak_src = measured_peak()
     traffic = None
     try:  # ncu dram__bytes of the same kernel on the headline config (profiles/)
-        with open(os.path.join(ROOT, "profiles", "r1_v2_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r1_v4_traffic.json")) as f:
             tj = json.load(f)
         if (nx, ny, nz, args.integrator) == (512, 512, 512, "rk212") and not listed:
             traffic = tj["dram_bytes_per_launch"]["mean"]

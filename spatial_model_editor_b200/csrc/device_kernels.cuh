@@ -50,6 +50,14 @@ typedef unsigned int smeb_u32;
 #ifndef SMEB_NPARAMS
 #define SMEB_NPARAMS 0 // runtime model parameters (sme_param_k), per module
 #endif
+#ifndef SMEB_C0_AHEAD
+// planes the register prefetch of c0 / s2 runs ahead of their use; 0 = chosen per
+// kernel: 2 when a stage reads c0 and not s2 (B200, 512^3 RK212 stage 2: 87 % ->
+// 97 % of the HBM copy rate — one plane of lead, about 2 us, is less than the
+// loaded DRAM latency), 1 when it also streams s2 (RK435: a deeper second queue
+// costs 16 more registers and the kernels get slower)
+#define SMEB_C0_AHEAD 0
+#endif
 #ifndef SMEB_TILE_MIN_CTAS
 #define SMEB_TILE_MIN_CTAS 2 // resident CTAs per SM the tile kernel is built for
 #endif
@@ -887,26 +895,47 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   size_t g = M3 ? ((size_t)m0 * a.nx + gx0) * a.ny + gy
                 : ((size_t)m0 * TX + r0) * a.ny + gy;
 
-  double c0cur[RPT][S], s2cur[RPT][S];
+  // register prefetch queue of c0 / s2: entry q holds the values of iteration
+  // it + q; entry 0 is consumed, entry AH is loaded AH iterations early
+  constexpr int AH = SMEB_C0_AHEAD > 0 ? SMEB_C0_AHEAD
+                     : (USE_C0 && !USE_S2IN) ? 2
+                                             : 1;
+  double c0q[AH + 1][RPT][S], s2q[AH + 1][RPT][S];
 #pragma unroll
-  for (int k = 0; k < RPT; ++k) {
+  for (int q = 0; q <= AH; ++q) {
 #pragma unroll
-    for (int s = 0; s < S; ++s) {
-      c0cur[k][s] = 0.0;
-      s2cur[k][s] = 0.0;
+    for (int k = 0; k < RPT; ++k) {
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        c0q[q][k][s] = 0.0;
+        s2q[q][k][s] = 0.0;
+      }
     }
   }
   if constexpr (!M3) {
     active = gy < (int)a.ny && m0 * TX + r0 < (int)a.nx;
   }
-  if (active) {
+  // whether this thread's voxels exist in iteration `it` (2-D: the brick moves)
+  auto activeAt = [&](int it) {
+    if constexpr (M3) {
+      return active;
+    } else {
+      return gy < (int)a.ny && (m0 + it) * TX + r0 < (int)a.nx;
+    }
+  };
 #pragma unroll
-    for (int k = 0; k < RPT; ++k) {
-      if constexpr (USE_C0) {
-        smeb_load_voxel<S>(a.c0, g + k * rowStride, c0cur[k]);
-      }
-      if constexpr (USE_S2IN) {
-        smeb_load_voxel<S>(a.s2in, g + k * rowStride, s2cur[k]);
+  for (int q = 0; q < AH; ++q) {
+    if (q < nIter && activeAt(q)) {
+#pragma unroll
+      for (int k = 0; k < RPT; ++k) {
+        if constexpr (USE_C0) {
+          smeb_load_voxel<S>(a.c0, g + q * marchStride + k * rowStride,
+                             c0q[q][k]);
+        }
+        if constexpr (USE_S2IN) {
+          smeb_load_voxel<S>(a.s2in, g + q * marchStride + k * rowStride,
+                             s2q[q][k]);
+        }
       }
     }
   }
@@ -924,33 +953,31 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   for (int it = 0; it < nIter; ++it) {
     const int m = m0 + it;
     // 2-D: the brick's x range changes every iteration
-    bool activeNext = active;
     if constexpr (!M3) {
       gx0 = m * TX + r0;
       active = gy < (int)a.ny && gx0 < (int)a.nx;
-      activeNext = gy < (int)a.ny && gx0 + TX < (int)a.nx;
       offLo = gx0 == 0 ? 0 : -PITCH;
       offHi = gx0 + RPT >= (int)a.nx ? (RPT - 1) * PITCH : RPT * PITCH;
     }
-    // register prefetch of the next plane's c0 / s2
-    double c0nxt[RPT][S], s2nxt[RPT][S];
+    // register prefetch of c0 / s2, AH iterations ahead
 #pragma unroll
     for (int k = 0; k < RPT; ++k) {
 #pragma unroll
       for (int s = 0; s < S; ++s) {
-        c0nxt[k][s] = 0.0;
-        s2nxt[k][s] = 0.0;
+        c0q[AH][k][s] = 0.0;
+        s2q[AH][k][s] = 0.0;
       }
     }
-    if (it + 1 < nIter && activeNext) {
+    if (it + AH < nIter && activeAt(it + AH)) {
 #pragma unroll
       for (int k = 0; k < RPT; ++k) {
         if constexpr (USE_C0) {
-          smeb_load_voxel<S>(a.c0, g + marchStride + k * rowStride, c0nxt[k]);
+          smeb_load_voxel<S>(a.c0, g + AH * marchStride + k * rowStride,
+                             c0q[AH][k]);
         }
         if constexpr (USE_S2IN) {
-          smeb_load_voxel<S>(a.s2in, g + marchStride + k * rowStride,
-                             s2nxt[k]);
+          smeb_load_voxel<S>(a.s2in, g + AH * marchStride + k * rowStride,
+                             s2q[AH][k]);
         }
       }
     }
@@ -994,20 +1021,23 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
           }
           continue;
         }
-        smeb_update<R, F>(a, col[k + 1], f, c0cur[k], s2cur[k], out, eabs,
+        smeb_update<R, F>(a, col[k + 1], f, c0q[0][k], s2q[0][k], out, eabs,
                           erel);
         if constexpr ((F & SMEB_F_WRITE_S2) != 0 && !ON_DEMAND) {
-          smeb_store_voxel<S>(a.s2out, g + k * rowStride, s2cur[k]);
+          smeb_store_voxel<S>(a.s2out, g + k * rowStride, s2q[0][k]);
         }
         smeb_store_voxel<S>(a.cout, g + k * rowStride, out);
       }
     }
 #pragma unroll
-    for (int k = 0; k < RPT; ++k) {
+    for (int q = 0; q < AH; ++q) {
 #pragma unroll
-      for (int s = 0; s < S; ++s) {
-        c0cur[k][s] = c0nxt[k][s];
-        s2cur[k][s] = s2nxt[k][s];
+      for (int k = 0; k < RPT; ++k) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+          c0q[q][k][s] = c0q[q + 1][k][s];
+          s2q[q][k][s] = s2q[q + 1][k][s];
+        }
       }
     }
     g += marchStride;

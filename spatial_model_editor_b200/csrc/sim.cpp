@@ -134,6 +134,10 @@ void Sim::generateSource(const smeb200_problem &p) {
   src << "#define SMEB_NCOMP " << std::max<uint32_t>(p.n_compartments, 1)
       << "\n";
   src << "#define SMEB_NPARAMS " << p.n_params << "\n";
+  if (const char *env = std::getenv("SMEB200_C0_AHEAD");
+      env != nullptr && env[0] >= '0' && env[0] <= '3') {
+    src << "#define SMEB_C0_AHEAD " << env[0] << "\n"; // A/B measurements
+  }
   src << kDeviceKernelSource << "\n";
   for (uint32_t c = 0; c < p.n_compartments; ++c) {
     const auto &comp = p.compartments[c];
