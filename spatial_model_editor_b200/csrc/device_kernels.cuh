@@ -58,6 +58,9 @@ typedef unsigned int smeb_u32;
 // costs 16 more registers and the kernels get slower)
 #define SMEB_C0_AHEAD 0
 #endif
+#ifndef SMEB_NN_CODE_AHEAD
+#define SMEB_NN_CODE_AHEAD 1 // voxel-list kernel: neighbour code fetched one iteration early
+#endif
 #ifndef SMEB_TILE_MIN_CTAS
 #define SMEB_TILE_MIN_CTAS 2 // resident CTAs per SM the tile kernel is built for
 #endif
@@ -520,11 +523,12 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
 // L1/L2: 4 B of index traffic per voxel instead of 24.  Voxels flagged
 // SMEB_MEMB_FLAG are left to smeb_stage_memb.
 #define SMEB_RUN_BITS 25
+// `code` = nn[i] of the run-compressed layout, loaded by the caller (the stage
+// kernel fetches it one iteration early; ignored for the plain table)
 __device__ __forceinline__ bool
 smeb_neighbours(const smeb_u32 *__restrict__ nn, const int *__restrict__ runs,
-                smeb_u32 i, smeb_u32 *nb) {
+                smeb_u32 i, smeb_u32 code, smeb_u32 *nb) {
   if (runs != nullptr) {
-    const smeb_u32 code = nn[i];
     const int4 d = reinterpret_cast<const int4 *>(
         runs)[code & ((1u << SMEB_RUN_BITS) - 1u)];
     const smeb_u32 fl = code >> SMEB_RUN_BITS;
@@ -553,10 +557,22 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   constexpr int S = R::S;
   double eabs = 0.0, erel = 0.0;
   double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
-  for (smeb_u32 i = a.v0 + blockIdx.x * SMEB_BLOCK + threadIdx.x; i < a.n;
-       i += gridDim.x * SMEB_BLOCK) {
+  // neighbour code -> run deltas -> gathers is a chain of dependent loads: the
+  // code of the next voxel of this thread is fetched one iteration early
+  const smeb_u32 stride = gridDim.x * SMEB_BLOCK;
+  const bool coded = a.runs != nullptr;
+  smeb_u32 i = a.v0 + blockIdx.x * SMEB_BLOCK + threadIdx.x;
+  smeb_u32 codeNext = coded && i < a.n ? a.nn[i] : 0u;
+  for (; i < a.n; i += stride) {
+    const smeb_u32 code =
+        SMEB_NN_CODE_AHEAD != 0 ? codeNext : (coded ? a.nn[i] : 0u);
+    if constexpr (SMEB_NN_CODE_AHEAD != 0) {
+      if (coded && stride < a.n - i) {
+        codeNext = a.nn[i + stride];
+      }
+    }
     smeb_u32 nb[6];
-    if (smeb_neighbours(a.nn, a.runs, i, nb)) {
+    if (smeb_neighbours(a.nn, a.runs, i, code, nb)) {
       continue;
     }
     double c[S], f[S];
@@ -693,7 +709,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
        k += gridDim.x * SMEB_BLOCK) {
     const smeb_u32 i = m.mvox[k];
     smeb_u32 nb[6];
-    smeb_neighbours(a.nn, a.runs, i, nb);
+    smeb_neighbours(a.nn, a.runs, i, a.runs != nullptr ? a.nn[i] : 0u, nb);
     double c[S], f[S];
     smeb_rhs_gather<R>(a, i, nb, c, f);
     const smeb_u32 e1 = m.mstart[k + 1];
