@@ -59,7 +59,7 @@ typedef unsigned int smeb_u32;
 #define SMEB_C0_AHEAD 0
 #endif
 #ifndef SMEB_NN_CODE_AHEAD
-#define SMEB_NN_CODE_AHEAD 1 // voxel-list kernel: neighbour code fetched one iteration early
+#define SMEB_NN_CODE_AHEAD 2 // voxel-list kernel: what is fetched one iteration early (see smeb_stage_nn)
 #endif
 #ifndef SMEB_TILE_MIN_CTAS
 #define SMEB_TILE_MIN_CTAS 2 // resident CTAs per SM the tile kernel is built for
@@ -357,10 +357,12 @@ smeb_update(const SmebStageArgs<R::S> &a, const double *c, const double *fin,
 
 // complete per-voxel epilogue for the direct kernels: loads of c0 / s2,
 // update, stores
+// c0pre: the voxel's c0 if the caller already holds it (nullptr: loaded here)
 template <class R, unsigned F>
 __device__ __forceinline__ void
 smeb_finish_voxel(const SmebStageArgs<R::S> &a, size_t i, const double *c,
-                  const double *f, double &eabs, double &erel, double *nsacc) {
+                  const double *f, double &eabs, double &erel, double *nsacc,
+                  const double *c0pre = nullptr) {
   constexpr int S = R::S;
   if constexpr ((F & SMEB_F_SUM_NS) != 0) {
     // pre-pass: only the sums of dc/dt of the non-spatial species are wanted
@@ -380,7 +382,14 @@ smeb_finish_voxel(const SmebStageArgs<R::S> &a, size_t i, const double *c,
   }
   if constexpr ((F & SMEB_F_OUT_DCDT) == 0) {
     if constexpr ((F & SMEB_F_USE_C0) != 0) {
-      smeb_load_voxel<S>(a.c0, i, c0v);
+      if (c0pre != nullptr) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+          c0v[s] = c0pre[s];
+        }
+      } else {
+        smeb_load_voxel<S>(a.c0, i, c0v);
+      }
     }
     if constexpr ((F & SMEB_F_USE_S2IN) != 0) {
       smeb_load_voxel<S>(a.s2in, i, s2v);
@@ -444,13 +453,15 @@ smeb_diffusion_array(const double *h2, const double *d, const double *dxp_,
 // coefficient of a neighbour is a function of that neighbour's state, which is
 // already in registers, so it is re-evaluated instead of being stored per voxel
 // as the CPU solver does (pixelsim_impl.cpp:494-504,545-589).
-template <class R>
+template <class R, bool HAVE_C = false>
 __device__ __forceinline__ void
 smeb_rhs_gather(const SmebStageArgs<R::S> &a, smeb_u32 i, const smeb_u32 *nb,
                 double *c, double *f) {
   constexpr int S = R::S;
   double xp[S], xm[S], yp[S], ym[S], zp[S], zm[S];
-  smeb_load_voxel<S>(a.cin, i, c);
+  if constexpr (!HAVE_C) { // else the caller loaded the voxel itself
+    smeb_load_voxel<S>(a.cin, i, c);
+  }
   smeb_load_voxel<S>(a.cin, nb[0], xp);
   smeb_load_voxel<S>(a.cin, nb[1], xm);
   smeb_load_voxel<S>(a.cin, nb[2], yp);
@@ -559,25 +570,57 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
   // neighbour code -> run deltas -> gathers is a chain of dependent loads: the
   // code of the next voxel of this thread is fetched one iteration early
+  // (SMEB_NN_CODE_AHEAD >= 1), and so are its own state and c0 (>= 2): with six
+  // resident CTAs the loads of one iteration alone do not keep enough bytes in
+  // flight to cover the DRAM latency
   const smeb_u32 stride = gridDim.x * SMEB_BLOCK;
   const bool coded = a.runs != nullptr;
+  constexpr bool PRE = SMEB_NN_CODE_AHEAD >= 2;
+  constexpr bool PRE_C0 = PRE && (F & SMEB_F_USE_C0) != 0 &&
+                          (F & (SMEB_F_OUT_DCDT | SMEB_F_SUM_NS)) == 0;
   smeb_u32 i = a.v0 + blockIdx.x * SMEB_BLOCK + threadIdx.x;
   smeb_u32 codeNext = coded && i < a.n ? a.nn[i] : 0u;
+  double cNext[S], c0Next[S];
+#pragma unroll
+  for (int s = 0; s < S; ++s) {
+    cNext[s] = 0.0;
+    c0Next[s] = 0.0;
+  }
+  if (PRE && i < a.n) {
+    smeb_load_voxel<S>(a.cin, i, cNext);
+    if constexpr (PRE_C0) {
+      smeb_load_voxel<S>(a.c0, i, c0Next);
+    }
+  }
   for (; i < a.n; i += stride) {
     const smeb_u32 code =
         SMEB_NN_CODE_AHEAD != 0 ? codeNext : (coded ? a.nn[i] : 0u);
-    if constexpr (SMEB_NN_CODE_AHEAD != 0) {
-      if (coded && stride < a.n - i) {
-        codeNext = a.nn[i + stride];
+    double c[S], c0v[S], f[S];
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+      c[s] = cNext[s];
+      c0v[s] = c0Next[s];
+    }
+    if (stride < a.n - i) {
+      if constexpr (SMEB_NN_CODE_AHEAD != 0) {
+        if (coded) {
+          codeNext = a.nn[i + stride];
+        }
+      }
+      if constexpr (PRE) {
+        smeb_load_voxel<S>(a.cin, i + stride, cNext);
+      }
+      if constexpr (PRE_C0) {
+        smeb_load_voxel<S>(a.c0, i + stride, c0Next);
       }
     }
     smeb_u32 nb[6];
     if (smeb_neighbours(a.nn, a.runs, i, code, nb)) {
       continue;
     }
-    double c[S], f[S];
-    smeb_rhs_gather<R>(a, i, nb, c, f);
-    smeb_finish_voxel<R, F>(a, i, c, f, eabs, erel, nsacc);
+    smeb_rhs_gather<R, PRE>(a, i, nb, c, f);
+    smeb_finish_voxel<R, F>(a, i, c, f, eabs, erel, nsacc,
+                            PRE_C0 ? c0v : nullptr);
   }
   if constexpr ((F & SMEB_F_SUM_NS) != 0) {
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);

@@ -138,8 +138,9 @@ void Sim::generateSource(const smeb200_problem &p) {
       env != nullptr && env[0] >= '0' && env[0] <= '3') {
     src << "#define SMEB_C0_AHEAD " << env[0] << "\n"; // A/B measurements
   }
-  if (envFlagOff("SMEB200_NN_PREFETCH")) {
-    src << "#define SMEB_NN_CODE_AHEAD 0\n"; // A/B measurements
+  if (const char *env = std::getenv("SMEB200_NN_PREFETCH");
+      env != nullptr && env[0] >= '0' && env[0] <= '2') {
+    src << "#define SMEB_NN_CODE_AHEAD " << env[0] << "\n"; // A/B measurements
   }
   src << kDeviceKernelSource << "\n";
   for (uint32_t c = 0; c < p.n_compartments; ++c) {
