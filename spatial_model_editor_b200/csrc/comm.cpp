@@ -120,6 +120,28 @@ void ShmComm::barrier() {
             "the other ranks at a barrier");
 }
 
+// in-place sum over ranks of n <= 4 doubles, added in rank order starting from
+// zero on every rank: all ranks get the same bits
+void ShmComm::allreduceSumOrdered(double *vals, int n) {
+  n = std::min(n, 4);
+  ++reduceEpoch_;
+  auto &mine = seg_->slot[rank_];
+  std::memcpy(mine.reduceVals[reduceEpoch_ & 1], vals, n * sizeof(double));
+  mine.reduceSeq.store(reduceEpoch_, std::memory_order_release);
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+  for (int r = 0; r < nRanks_; ++r) {
+    if (r != rank_) {
+      waitUntil(seg_->slot[r].reduceSeq, reduceEpoch_,
+                "the other ranks' partial sums");
+    }
+    const double *v = seg_->slot[r].reduceVals[reduceEpoch_ & 1];
+    for (int i = 0; i < n; ++i) {
+      acc[i] += v[i];
+    }
+  }
+  std::memcpy(vals, acc, n * sizeof(double));
+}
+
 void ShmComm::allreduceMax(double *vals, int n) {
   n = std::min(n, 4);
   ++reduceEpoch_;

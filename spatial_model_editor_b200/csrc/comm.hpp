@@ -68,6 +68,8 @@ public:
   void barrier();
   // in-place max over ranks of n <= 4 doubles (NaN never wins, like std::max)
   void allreduceMax(double *vals, int n);
+  // in-place sum of n <= 4 doubles, added in rank order (same bits on all ranks)
+  void allreduceSumOrdered(double *vals, int n);
   // pointer + length of the page(s) holding the halo flags (for
   // cudaHostRegister)
   void *flagPages() { return &seg_->haloFlag[0][0][0]; }

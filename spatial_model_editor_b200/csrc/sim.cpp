@@ -994,8 +994,11 @@ void Sim::build(const smeb200_problem &p) {
       c.nonSpatial.push_back(pc.non_spatial[k]);
     }
     if (!c.nonSpatial.empty() && p.n_ranks > 1) {
-      throw Error("smeb200: non-spatial species are not supported in a "
-                  "z-slab decomposed simulation");
+      if (c.nonSpatial.size() > 64) {
+        throw Error("smeb200: too many non-spatial species for a z-slab "
+                    "decomposed simulation");
+      }
+      nsInSlabs = true; // the spatial mean is summed over the ranks per stage
     }
     if (pc.inv_storage != nullptr) {
       c.invStorage.assign(pc.inv_storage, pc.inv_storage + c.S);
@@ -1320,6 +1323,19 @@ void Sim::build(const smeb200_problem &p) {
     slabsConnected = true;
     syncMaxStableTimestep(); // per-voxel diffusion constants differ per slab
   }
+  if (nsInSlabs) {
+    if (!comm) {
+      throw Error("smeb200: non-spatial species in a z-slab decomposed "
+                  "simulation need the shared-memory communicator (comm_name)");
+    }
+    check(cudaMallocHost(reinterpret_cast<void **>(&hNs), 64 * sizeof(double)),
+          "allocate pinned non-spatial sums");
+    for (auto &c : comps) { // every rank walks the compartments in the same order
+      double v = static_cast<double>(c.ownedEnd() - c.ownedBegin());
+      comm->allreduceSumOrdered(&v, 1);
+      c.nGlobal = v;
+    }
+  }
 }
 
 // ---- z-slab decomposition -----------------------------------------------------
@@ -1595,6 +1611,7 @@ Sim::~Sim() {
   cudaFree(dErr);
   cudaFreeHost(hErr);
   cudaFreeHost(hErrRing);
+  cudaFreeHost(hNs);
   for (auto e : errEvents) {
     if (e != nullptr) {
       cudaEventDestroy(e);
@@ -1679,6 +1696,11 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     check(cudaStreamWaitEvent(haloStream, stageInputReady, 0), "halo stream wait");
     if (haloSeq > 0) {
       haloWait(haloStream);
+      if (nsInSlabs) {
+        // the pre-pass of the spatial mean runs on the main stream and
+        // evaluates dc/dt of the boundary voxels too: it reads ghosts
+        haloWait(stream);
+      }
     }
   }
   for (std::size_t ci = 0; ci < comps.size(); ++ci) {
@@ -1750,6 +1772,12 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
       // SimCompartment::spatiallyAverageDcdt (pixelsim_impl.cpp:150-163): the
       // averages need dc/dt of every voxel before any voxel can be updated
       launchCompartment(ci, a, c.kSumNs, c.role[sd.cin], true);
+      if (overlapHalo) {
+        // the boundary and membrane kernels on the halo stream use the mean too
+        check(cudaEventRecord(stageInputReady, stream), "mean ready event");
+        check(cudaStreamWaitEvent(haloStream, stageInputReady, 0),
+              "halo stream wait");
+      }
     }
     if (overlapHalo) {
       // z-slab: the owned boundary planes (what the neighbours need) and the
@@ -2067,13 +2095,33 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     }
     const double *partial = c.dNsPartial;
     uint32_t nns = static_cast<uint32_t>(c.nonSpatial.size());
-    double nVox = static_cast<double>(c.n);
+    // z-slabs: this rank's sum over its owned voxels (divided by 1), completed
+    // below; else the mean over the compartment
+    double nVox = nsInSlabs ? 1.0 : static_cast<double>(c.n);
     double *av = c.dNsAv;
     void *fparams[] = {&partial, &nsBlocks, &nns, &nVox, &av};
     check(drv.LaunchKernel(mainModule.fn.at(kNsFinishKernel), 1, 1, 1, BLOCK, 1,
                            1, 0, sMain, fparams, nullptr),
           "launch non-spatial average kernel");
     ++launchCount;
+    if (nsInSlabs) {
+      // sum of the ranks' sums in rank order (the same bits on every rank),
+      // divided by the compartment's voxel count: one small round trip per
+      // stage — the stage kernels cannot start before the mean is known anyway
+      check(cudaMemcpyAsync(hNs, c.dNsAv, nns * sizeof(double),
+                            cudaMemcpyDeviceToHost, sMain),
+            "download non-spatial sums");
+      check(cudaStreamSynchronize(sMain), "cudaStreamSynchronize");
+      for (uint32_t j = 0; j < nns; j += 4) {
+        comm->allreduceSumOrdered(hNs + j, static_cast<int>(std::min(4u, nns - j)));
+      }
+      for (uint32_t j = 0; j < nns; ++j) {
+        hNs[j] = hNs[j] / c.nGlobal;
+      }
+      check(cudaMemcpyAsync(c.dNsAv, hNs, nns * sizeof(double),
+                            cudaMemcpyHostToDevice, sMain),
+            "upload non-spatial averages");
+    }
   }
 }
 

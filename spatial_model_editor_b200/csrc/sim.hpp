@@ -113,6 +113,7 @@ struct CompartmentState {
   std::vector<uint32_t> nonSpatial;  // species whose dc/dt is averaged
   std::vector<double> invStorage;    // [S], empty = unit storage
   double *dNsAv{nullptr};            // [nonSpatial.size()]
+  double nGlobal{0.0};               // voxels of the compartment over all z-slabs
   double *dNsPartial{nullptr};       // block sums of the pre-pass
   uint32_t nsPartialBlocks{0};       // capacity of dNsPartial in blocks
   StageKernels kSumNs;               // pre-pass kernels (F_SUM_NS)
@@ -302,6 +303,9 @@ private:
   struct PendingError {
     double dt, dtMax;
   };
+  // z-slabs with non-spatial species: the spatial mean is summed over the ranks
+  bool nsInSlabs{false};
+  double *hNs{nullptr}; // pinned, 64 doubles
   bool laggedError{false};
   unsigned long long *hErrRing{nullptr}; // pinned, 2 x kErrRing
   cudaEvent_t errEvents[kErrRing]{};

@@ -245,3 +245,84 @@ def test_diffusion_features_in_slabs_match_single_gpu(feature, integ, geom):
         assert r[3] == dt0 and r[4] == ref.maxStableTimestep
     assert np.array_equal(np.concatenate([r[5] for r in res]), c_ref)
     assert np.array_equal(np.concatenate([r[6] for r in res]), d_ref)
+
+
+# ---- non-spatial species in slabs: the spatial mean is summed over the ranks -------
+def _non_spatial_problem(geom, integ):
+    """geom "box": gray-scott with V non-spatial; "cell": the two-compartment cell with
+    the membrane, Y non-spatial in both compartments (SimCompartment::
+    spatiallyAverageDcdt, pixelsim_impl.cpp:150-163)"""
+    if geom == "box":
+        p = M.box_problem(M.GRAY_SCOTT, 24, 20, 13, integrator=integ,
+                          voxel_size=(1.0, 1.5, 2.0))
+        p.compartments[0].non_spatial = [1]
+    else:
+        p = _listed_problem("cell", integ, False)
+        for c in p.compartments:
+            c.non_spatial = [1]
+    p.max_err_abs = p.max_err_rel = smeb.DBL_MAX
+    p.max_timestep = 0.01
+    return p
+
+
+def _non_spatial_worker(rank, world, name, geom, integ, t_end, q):
+    sys.path.insert(0, ROOT)
+    from spatial_model_editor_b200.multigpu import SlabPixelSim
+    try:
+        p = _non_spatial_problem(geom, integ)
+        p.device = rank
+        sim = SlabPixelSim(p, rank, world, comm_name=name)
+        err0 = sim.errorMessage()
+        n = sim.run(t_end / 2) + sim.run(t_end / 2)
+        nc = len(p.compartments)
+        q.put((rank, err0 + sim.errorMessage(), n,
+               [sim.getConcentrations(i).copy() for i in range(nc)],
+               [sim.getDcdt(i).copy() for i in range(nc)]))
+        sim.close()
+    except Exception as e:  # noqa: BLE001
+        q.put((rank, f"exception: {e!r}", 0, None, None))
+
+
+@pytest.mark.parametrize("geom", ["box", "cell"])
+@pytest.mark.parametrize("integ", [smeb.RK101, smeb.RK212, smeb.RK435])
+def test_non_spatial_species_in_slabs(geom, integ):
+    """each rank sums dc/dt of the non-spatial species over its own voxels; the sums
+    are added in rank order and divided by the compartment's voxel count.  The
+    association differs from the single-GPU tree, so the bar is rounding (1e-10
+    relative), not bit identity; the non-spatial species stays uniform over all
+    slabs"""
+    world = min(smeb.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs >= 2 GPUs")
+    import torch.multiprocessing as mp
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from util import assert_parity
+    t_end = 0.1
+    p = _non_spatial_problem(geom, integ)
+    p.device = 0
+    ref = smeb.PixelSim(p)
+    assert ref.errorMessage() == ""
+    n_ref = ref.run(t_end / 2) + ref.run(t_end / 2)
+    nc = len(p.compartments)
+    c_ref = [ref.getConcentrations(i).copy() for i in range(nc)]
+    d_ref = [ref.getDcdt(i).copy() for i in range(nc)]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    name = f"smeb200_nstest_{os.getpid()}_{geom}_{integ}"
+    procs = [ctx.Process(target=_non_spatial_worker, args=(r, world, name, geom, integ, t_end, q))
+             for r in range(world)]
+    for pr in procs:
+        pr.start()
+    res = sorted((q.get(timeout=300) for _ in range(world)), key=lambda r: r[0])
+    for pr in procs:
+        pr.join(timeout=60)
+    for r in res:
+        assert r[1] == "", r[1]
+        assert r[2] == n_ref
+    for i in range(nc):
+        c = np.concatenate([r[3][i] for r in res])
+        d = np.concatenate([r[4][i] for r in res])
+        assert_parity(c, c_ref[i], rel=1e-10, what=f"{geom} conc[{i}]")
+        assert_parity(d, d_ref[i], rel=1e-10, what=f"{geom} dcdt[{i}]")
+        # one value of dc/dt for the non-spatial species across all slabs
+        assert np.ptp(d[:, 1]) == 0.0
