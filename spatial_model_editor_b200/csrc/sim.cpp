@@ -2517,6 +2517,8 @@ std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
     double tNow = 0;
     discardedSteps = 0;
     constexpr double relativeTolerance = 1e-12;
+    errHead = errTail; // nothing is in flight between runs (a run that threw may
+                       // have left slots behind: they are void)
     laggedError = integrator != SMEB200_RK101 && !useGraphs && !anyZeroStorage &&
                   errMaxAbs == std::numeric_limits<double>::max() &&
                   errMaxRel == std::numeric_limits<double>::max() &&
