@@ -562,8 +562,16 @@ smeb_neighbours(const smeb_u32 *__restrict__ nn, const int *__restrict__ runs,
   return (n0.x & SMEB_MEMB_FLAG) != 0;
 }
 
+#ifndef SMEB_NN_MIN_CTAS
+#define SMEB_NN_MIN_CTAS 0 // resident CTAs per SM the register allocation aims at (0: compiler's choice)
+#endif
+#if SMEB_NN_MIN_CTAS > 0
+#define SMEB_NN_BOUNDS __launch_bounds__(SMEB_BLOCK, SMEB_NN_MIN_CTAS)
+#else
+#define SMEB_NN_BOUNDS __launch_bounds__(SMEB_BLOCK)
+#endif
 template <class R, unsigned F>
-__global__ void __launch_bounds__(SMEB_BLOCK)
+__global__ void SMEB_NN_BOUNDS
     smeb_stage_nn(const __grid_constant__ SmebStageArgs<R::S> a) {
   constexpr int S = R::S;
   double eabs = 0.0, erel = 0.0;
