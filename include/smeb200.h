@@ -348,6 +348,11 @@ typedef struct smeb200_comm smeb200_comm;
 int smeb200_comm_create(const char *name, int rank, int n_ranks,
                         smeb200_comm **out);
 int smeb200_comm_allreduce_max(smeb200_comm *comm, double *values, int n);
+/* in-place sum over the ranks of n <= 4 doubles, added in rank order on every
+ * rank (all ranks get the same bits): the spatial mean of non-spatial species in
+ * a z-slab decomposed simulation (SimCompartment::spatiallyAverageDcdt,
+ * pixelsim_impl.cpp:150-163, across slabs) */
+int smeb200_comm_allreduce_sum(smeb200_comm *comm, double *values, int n);
 int smeb200_comm_barrier(smeb200_comm *comm);
 void smeb200_comm_destroy(smeb200_comm *comm);
 /* halo exchanges performed since construction (0 on a single GPU) */

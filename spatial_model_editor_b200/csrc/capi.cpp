@@ -290,6 +290,19 @@ int smeb200_comm_create(const char *name, int rank, int n_ranks,
   return 0;
 }
 
+int smeb200_comm_allreduce_sum(smeb200_comm *comm, double *values, int n) {
+  if (comm == nullptr || values == nullptr) {
+    return -1;
+  }
+  try {
+    comm->impl.allreduceSumOrdered(values, n);
+  } catch (const std::exception &e) {
+    comm->error = e.what();
+    return 1;
+  }
+  return 0;
+}
+
 int smeb200_comm_allreduce_max(smeb200_comm *comm, double *values, int n) {
   if (comm == nullptr || values == nullptr) {
     return -1;

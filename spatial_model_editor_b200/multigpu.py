@@ -204,6 +204,15 @@ class Comm:
             raise RuntimeError("smeb200_comm_allreduce_max failed")
         return a
 
+    def allreduce_sum(self, values: np.ndarray) -> np.ndarray:
+        """sum over the ranks, added in rank order (the same bits on every rank)"""
+        a = np.ascontiguousarray(values, dtype=np.float64).copy()
+        rc = self._lib.smeb200_comm_allreduce_sum(
+            self._h, a.ctypes.data_as(C.POINTER(C.c_double)), a.size)
+        if rc != 0:
+            raise RuntimeError("smeb200_comm_allreduce_sum failed")
+        return a
+
     def barrier(self) -> None:
         if self._lib.smeb200_comm_barrier(self._h) != 0:
             raise RuntimeError("smeb200_comm_barrier failed")

@@ -81,6 +81,7 @@ def _bind(lib, prefix: str):
     fn("set_params", C.c_int, [vp, C.POINTER(C.c_double), C.c_size_t], optional=True)
     fn("comm_create", C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(vp)], optional=True)
     fn("comm_allreduce_max", C.c_int, [vp, C.POINTER(C.c_double), C.c_int], optional=True)
+    fn("comm_allreduce_sum", C.c_int, [vp, C.POINTER(C.c_double), C.c_int], optional=True)
     fn("comm_barrier", C.c_int, [vp], optional=True)
     fn("comm_destroy", None, [vp], optional=True)
     # oracle-only

@@ -176,6 +176,14 @@ def _worker(rank, world, port, q):
             t = torch.from_numpy(v.copy())
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ok = ok and np.array_equal(mine, t.numpy())
+            # ordered sum: every rank gets the bits of "rank 0 + rank 1 + ..."
+            w = rng.uniform(-1, 1, size=3) * 10.0 ** rng.integers(-8, 8)
+            gathered = [torch.zeros(3, dtype=torch.float64) for _ in range(world)]
+            dist.all_gather(gathered, torch.from_numpy(w.copy()))
+            expect = np.zeros(3)
+            for g in gathered:
+                expect = expect + g.numpy()
+            ok = ok and np.array_equal(comm.allreduce_sum(w), expect)
             if it % 50 == 0:
                 comm.barrier()
         comm.barrier()
