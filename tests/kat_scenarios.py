@@ -279,3 +279,27 @@ def example_3d_models_tiny_step(make, names=("gray-scott-3d", "single-compartmen
             assert np.all(np.isfinite(sim.getConcentrations(ci))), name
         sims.append(sim)
     return sims
+
+
+def membrane_parallel_matches_serial(make_serial, make_parallel):
+    """K6, simulate_t.cpp:382-439: very-simple-model, RK101, maxErr = DBL_MAX,
+    maxTimestep 0.01, one interval of 1: the parallel execution takes the same
+    steps as the serial one and agrees in every concentration and dc/dt to 1e-13
+    (Catch::Approx margin 1e-13, epsilon 1e-13)"""
+    sims = []
+    for make in (make_serial, make_parallel):
+        p, _, _ = load_golden("very-simple-model", integrator=smeb.RK101)
+        p.max_err_abs = p.max_err_rel = DBL_MAX
+        p.max_timestep = 0.01
+        sim = make(p)
+        assert sim.errorMessage() == ""
+        sims.append((p, sim, sim.run(1.0)))
+    (p, serial, n_serial), (_, parallel, n_parallel) = sims
+    assert n_serial == n_parallel >= 100
+    tol = 1e-13
+    for ci in range(len(p.compartments)):
+        for get in ("getConcentrations", "getDcdt"):
+            a, b = getattr(serial, get)(ci), getattr(parallel, get)(ci)
+            assert a.shape == b.shape
+            assert np.all(np.abs(a - b) <= tol + tol * np.abs(a)), (ci, get)
+    return sims

@@ -15,3 +15,9 @@ SCENARIOS = [K.uniform_steady_state, K.zero_storage_uniform, K.varying_diffusion
 @pytest.mark.parametrize("scenario", SCENARIOS, ids=lambda f: f.__name__)
 def test_oracle(scenario):
     scenario(OraclePixelSim)
+
+
+def test_k6_membranes_parallel_matches_serial():
+    """the oracle with 1 thread (the reference default) against 2 OpenMP threads"""
+    K.membrane_parallel_matches_serial(lambda p: OraclePixelSim(p, threads=1),
+                                       lambda p: OraclePixelSim(p, threads=2))

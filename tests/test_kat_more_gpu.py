@@ -94,3 +94,13 @@ def test_cuda_path(case):
 
     scenario(tracked)
     assert made and all(m.launches > 0 for m in made)
+
+
+def test_k6_membranes_cuda_matches_serial_cpu():
+    """K6 with the CUDA path in the role of the multi-threaded solver: one thread per
+    membrane voxel, fluxes accumulated in the reference's order without atomics"""
+    def cuda(p):
+        p.device = 0
+        return smeb.PixelSim(p)
+
+    K.membrane_parallel_matches_serial(lambda p: OraclePixelSim(p, threads=1), cuda)
