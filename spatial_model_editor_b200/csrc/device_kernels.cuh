@@ -58,6 +58,9 @@ typedef unsigned int smeb_u32;
 // costs 16 more registers and the kernels get slower)
 #define SMEB_C0_AHEAD 0
 #endif
+#ifndef SMEB_C0_SPLIT
+#define SMEB_C0_SPLIT 0 // 1: c0 two planes ahead also in stages that stream s2 (A/B)
+#endif
 #ifndef SMEB_NN_CODE_AHEAD
 #define SMEB_NN_CODE_AHEAD 2 // voxel-list kernel: what is fetched one iteration early (see smeb_stage_nn)
 #endif
@@ -962,19 +965,24 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   size_t g = M3 ? ((size_t)m0 * a.nx + gx0) * a.ny + gy
                 : ((size_t)m0 * TX + r0) * a.ny + gy;
 
-  // register prefetch queue of c0 / s2: entry q holds the values of iteration
-  // it + q; entry 0 is consumed, entry AH is loaded AH iterations early
-  constexpr int AH = SMEB_C0_AHEAD > 0 ? SMEB_C0_AHEAD
-                     : (USE_C0 && !USE_S2IN) ? 2
-                                             : 1;
-  double c0q[AH + 1][RPT][S], s2q[AH + 1][RPT][S];
+  // register prefetch queues of c0 / s2: entry q holds the values of iteration
+  // it + q; entry 0 is consumed, the last entry is loaded that many iterations
+  // early.  AHC / AHS: depth of the c0 / s2 queue
+  constexpr int AHC = SMEB_C0_AHEAD > 0 ? SMEB_C0_AHEAD
+                      : (USE_C0 && (!USE_S2IN || SMEB_C0_SPLIT != 0)) ? 2
+                                                                      : 1;
+  constexpr int AHS = SMEB_C0_AHEAD > 0 ? SMEB_C0_AHEAD : 1;
+  double c0q[AHC + 1][RPT][S], s2q[AHS + 1][RPT][S];
 #pragma unroll
-  for (int q = 0; q <= AH; ++q) {
+  for (int k = 0; k < RPT; ++k) {
 #pragma unroll
-    for (int k = 0; k < RPT; ++k) {
+    for (int s = 0; s < S; ++s) {
 #pragma unroll
-      for (int s = 0; s < S; ++s) {
+      for (int q = 0; q <= AHC; ++q) {
         c0q[q][k][s] = 0.0;
+      }
+#pragma unroll
+      for (int q = 0; q <= AHS; ++q) {
         s2q[q][k][s] = 0.0;
       }
     }
@@ -991,17 +999,21 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
     }
   };
 #pragma unroll
-  for (int q = 0; q < AH; ++q) {
+  for (int q = 0; q < (AHC > AHS ? AHC : AHS); ++q) {
     if (q < nIter && activeAt(q)) {
 #pragma unroll
       for (int k = 0; k < RPT; ++k) {
         if constexpr (USE_C0) {
-          smeb_load_voxel<S>(a.c0, g + q * marchStride + k * rowStride,
-                             c0q[q][k]);
+          if (q < AHC) {
+            smeb_load_voxel<S>(a.c0, g + q * marchStride + k * rowStride,
+                               c0q[q][k]);
+          }
         }
         if constexpr (USE_S2IN) {
-          smeb_load_voxel<S>(a.s2in, g + q * marchStride + k * rowStride,
-                             s2q[q][k]);
+          if (q < AHS) {
+            smeb_load_voxel<S>(a.s2in, g + q * marchStride + k * rowStride,
+                               s2q[q][k]);
+          }
         }
       }
     }
@@ -1026,25 +1038,30 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
       offLo = gx0 == 0 ? 0 : -PITCH;
       offHi = gx0 + RPT >= (int)a.nx ? (RPT - 1) * PITCH : RPT * PITCH;
     }
-    // register prefetch of c0 / s2, AH iterations ahead
+    // register prefetch of c0 / s2, AHC / AHS iterations ahead
 #pragma unroll
     for (int k = 0; k < RPT; ++k) {
 #pragma unroll
       for (int s = 0; s < S; ++s) {
-        c0q[AH][k][s] = 0.0;
-        s2q[AH][k][s] = 0.0;
+        c0q[AHC][k][s] = 0.0;
+        s2q[AHS][k][s] = 0.0;
       }
     }
-    if (it + AH < nIter && activeAt(it + AH)) {
+    if constexpr (USE_C0) {
+      if (it + AHC < nIter && activeAt(it + AHC)) {
 #pragma unroll
-      for (int k = 0; k < RPT; ++k) {
-        if constexpr (USE_C0) {
-          smeb_load_voxel<S>(a.c0, g + AH * marchStride + k * rowStride,
-                             c0q[AH][k]);
+        for (int k = 0; k < RPT; ++k) {
+          smeb_load_voxel<S>(a.c0, g + AHC * marchStride + k * rowStride,
+                             c0q[AHC][k]);
         }
-        if constexpr (USE_S2IN) {
-          smeb_load_voxel<S>(a.s2in, g + AH * marchStride + k * rowStride,
-                             s2q[AH][k]);
+      }
+    }
+    if constexpr (USE_S2IN) {
+      if (it + AHS < nIter && activeAt(it + AHS)) {
+#pragma unroll
+        for (int k = 0; k < RPT; ++k) {
+          smeb_load_voxel<S>(a.s2in, g + AHS * marchStride + k * rowStride,
+                             s2q[AHS][k]);
         }
       }
     }
@@ -1097,12 +1114,15 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
       }
     }
 #pragma unroll
-    for (int q = 0; q < AH; ++q) {
+    for (int k = 0; k < RPT; ++k) {
 #pragma unroll
-      for (int k = 0; k < RPT; ++k) {
+      for (int s = 0; s < S; ++s) {
 #pragma unroll
-        for (int s = 0; s < S; ++s) {
+        for (int q = 0; q < AHC; ++q) {
           c0q[q][k][s] = c0q[q + 1][k][s];
+        }
+#pragma unroll
+        for (int q = 0; q < AHS; ++q) {
           s2q[q][k][s] = s2q[q + 1][k][s];
         }
       }

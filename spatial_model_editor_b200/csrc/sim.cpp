@@ -138,6 +138,10 @@ void Sim::generateSource(const smeb200_problem &p) {
       env != nullptr && env[0] >= '0' && env[0] <= '3') {
     src << "#define SMEB_C0_AHEAD " << env[0] << "\n"; // A/B measurements
   }
+  if (const char *env = std::getenv("SMEB200_C0_SPLIT");
+      env != nullptr && (env[0] == '0' || env[0] == '1')) {
+    src << "#define SMEB_C0_SPLIT " << env[0] << "\n"; // A/B measurements
+  }
   if (const char *env = std::getenv("SMEB200_NN_MIN_CTAS");
       env != nullptr && env[0] >= '0' && env[0] <= '8') {
     src << "#define SMEB_NN_MIN_CTAS " << env[0] << "\n"; // A/B measurements
