@@ -40,7 +40,7 @@ MODELS = {
     "small-single-compartment-diffusion":
         "test/resources/models/small-single-compartment-diffusion.xml",
     # the rest of the reference's example models (cudapixelsim_t.cpp:542-575 sweeps
-    # all of them); NFkappaB.xml does not parse here (unbound XML prefix)
+    # all of them; NFkappaB.xml, a non-spatial L2 file without geometry, is not one)
     "CalciumWavePropagation3D": "core/resources/models/CalciumWavePropagation3D.xml",
     "FitzhughNagumo3D": "core/resources/models/FitzhughNagumo3D.xml",
     "SelKov3D": "core/resources/models/SelKov3D.xml",

@@ -13,8 +13,7 @@ pytestmark = pytest.mark.gpu
 
 MODELS = ["single-pixel-chain", "very-simple-model", "ABtoC", "gray-scott", "gray-scott-3d",
           "brusselator-model", "liver-simplified", "single-compartment-diffusion",
-          # the rest of allExampleModels (cudapixelsim_t.cpp:50-64); NFkappaB.xml does not
-          # parse with the loader here
+          # the rest of allExampleModels (cudapixelsim_t.cpp:50-64): all 14 are here
           "single-compartment-diffusion-3d", "circadian-clock", "liver-cells",
           "very-simple-model-3d", "FitzhughNagumo3D", "SelKov3D", "CalciumWavePropagation3D"]
 INTEGRATORS = [smeb.RK101, smeb.RK212, smeb.RK323, smeb.RK435]
