@@ -2563,6 +2563,16 @@ std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
       if (stopCb != nullptr && stopCb(user) != 0) {
         stopRequested.store(true);
       }
+      if (comm && slabsConnected && (timeoutMs >= 0.0 || stopCb != nullptr)) {
+        // z-slabs: deadline and callback are evaluated per rank, the decision
+        // must be common (every rank gets here after every step, with the same
+        // arguments): one more value through the shared-memory segment
+        double stop = stopRequested.load() ? 1.0 : 0.0;
+        comm->allreduceMax(&stop, 1);
+        if (stop > 0.0) {
+          stopRequested.store(true);
+        }
+      }
       if (stopRequested.load()) {
         errorMessage = "Simulation stopped early";
         break;
