@@ -226,6 +226,11 @@ class SbmlModel:
     field_params: Dict[str, np.ndarray]             # parameter id -> [nz, ny, nx] (y top)
     vol_over_l3: float
     pixel_options: Dict[str, float] = field(default_factory=dict)
+    # SBML events of the form "time >= t: variable = value" (model_events.cpp:197-221,
+    # 290-299): (id, time, variable, value).  Simulation applies a parameter event
+    # by re-creating the simulator with the new value substituted
+    # (simulate.cpp:183-270, 404-445).
+    events: List[Tuple[str, float, str, float]] = field(default_factory=list)
 
     def species_of(self, comp: str) -> List[SbmlSpecies]:
         return [s for s in self.species if s.compartment == comp]
@@ -420,6 +425,21 @@ def _load_rest(path, model, length, volume, labels, label_of, origin, voxel_size
     for ia in (list(loi) if loi is not None else []):
         initial_assignments[ia.attrib["symbol"]] = mathml_to_node(_child(ia, "math"))
 
+    # events: trigger "time >= t" (or "t <= time"), one assignment of a number
+    # (ModelEvents::getTime / getVariable / getValue, model_events.cpp:168-221,290-299)
+    events = []
+    loe = _child(model, "listOfEvents")
+    for ev in (list(loe) if loe is not None else []):
+        trig, asg = _child(ev, "trigger"), _find_all(ev, "eventAssignment")
+        if trig is None or not asg:
+            continue
+        cns = _find_all(trig, "cn")
+        maths = _find_all(asg[0], "cn")
+        if not cns or not maths:
+            continue
+        events.append((ev.attrib.get("id", ""), float((cns[0].text or "0").strip()),
+                       asg[0].attrib["variable"], float((maths[0].text or "0").strip())))
+
     # annotation: storage values and pixel options
     storage, pixel_options = {}, {}
     ann = _child(model, "annotation")
@@ -496,7 +516,8 @@ def _load_rest(path, model, length, volume, labels, label_of, origin, voxel_size
                      labels=labels, label_of=label_of, membranes=membranes, origin=origin,
                      voxel_size=voxel_size, coord_params=coord_params,
                      field_params=field_params,
-                     vol_over_l3=_vol_over_l3(length, volume), pixel_options=pixel_options)
+                     vol_over_l3=_vol_over_l3(length, volume), pixel_options=pixel_options,
+                     events=events)
 
 
 # ---- SbmlModel -> Problem --------------------------------------------------------

@@ -50,6 +50,28 @@ MODELS = {
 }
 
 
+def event_stages(m, **kw):
+    """Parameter events in time order with the expressions the re-created simulator
+    uses from each event time on (Simulation::applyNextEvent -> initSimulator with
+    eventSubstitutions, simulate.cpp:227-270; events at one time are applied
+    together, :196-208)."""
+    out, subs = [], {}
+    params = set(m.parameters) | {v for _, _, v, _ in m.events}
+    for t in sorted({t for _, t, _, _ in m.events}):
+        ids = []
+        for eid, et, var, val in m.events:
+            if et == t and var in params:
+                subs[var] = val
+                ids.append(eid)
+        if not ids:
+            continue
+        p = sbml.to_problem(m, substitutions=dict(subs), **kw)
+        out.append(dict(time=t, ids=ids, substitutions=dict(subs),
+                        expressions=[c.expressions for c in p.compartments],
+                        membrane_expressions=[mb.expressions for mb in p.membranes]))
+    return out
+
+
 def dump(name, m, problem):
     if int(m.labels.max()) > 255:  # raw ARGB sample values: store small labels
         values = sorted(set(m.labels.ravel().tolist()))
@@ -62,6 +84,7 @@ def dump(name, m, problem):
         integrator=problem.integrator, max_err_abs=problem.max_err_abs,
         max_err_rel=problem.max_err_rel, max_timestep=problem.max_timestep,
         unsupported=problem.unsupported, params=list(problem.params),
+        events=event_stages(m) if not problem.params else [],
         compartments=[dict(id=c.id, species=c.species, expressions=c.expressions,
                            diffusion_constants=[s.diffusion for s in m.species
                                                 if s.id in c.species]

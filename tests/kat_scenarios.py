@@ -281,6 +281,68 @@ def example_3d_models_tiny_step(make, names=("gray-scott-3d", "single-compartmen
     return sims
 
 
+def do_timesteps(make, name, time, integrator=None, tolerances=None):
+    """Simulation::doTimesteps(time) for one interval on a fixture with SBML events
+    (simulate.cpp:397-445 and 227-270): an event inside the interval ends a sub-step
+    at its time, the state is read back, the simulator is destroyed and re-created
+    with the event's value substituted into the reaction expressions — so its
+    controller starts again from nextTimestep = 1e-7 (pixelsim_base.hpp:45) — and
+    restarted from that state (pixelsim.cpp:399-406); then the rest of the interval.
+    Returns (final state per compartment, list of simulators used)."""
+    def problem(stage):
+        p, meta, _ = load_golden(name, integrator=integrator)
+        if tolerances is not None:
+            p.max_err_abs, p.max_err_rel = tolerances
+        if stage is not None:
+            for c, ex in zip(p.compartments, stage["expressions"]):
+                c.expressions = list(ex)
+            for m, ex in zip(p.membranes, stage["membrane_expressions"]):
+                m.expressions = list(ex)
+        return p, meta
+
+    p, meta = problem(None)
+    sims = [make(p)]
+    t = 0.0
+    for stage in meta["events"]:
+        # events at (to 1e-12 of the interval) the current time are applied before
+        # stepping; events after the end of the interval stay queued
+        if (t + (time - t) - stage["time"]) / time <= 0.1e-12:
+            break
+        if stage["time"] > t:
+            assert sims[-1].run(stage["time"] - t) >= 1
+            assert sims[-1].errorMessage() == ""
+            t = stage["time"]
+        state = [np.array(sims[-1].getConcentrations(i))
+                 for i in range(len(p.compartments))]
+        p, _ = problem(stage)
+        for c, s in zip(p.compartments, state):
+            c.conc0 = s
+        sims.append(make(p))
+    if time > t:
+        assert sims[-1].run(time - t) >= 1
+        assert sims[-1].errorMessage() == ""
+    return [np.array(sims[-1].getConcentrations(i)) for i in range(len(p.compartments))], sims
+
+
+def brusselator_rk_orders_agree(make, make_accurate=None):
+    """K5, simulate_t.cpp:1596-1647: on the brusselator example RK212, RK323 and RK435
+    at maxErr = {DBL_MAX, 0.01} end within 1 % (signed, like the reference's
+    assertion) of RK435 at 1e-6 after Simulation::doTimesteps(30).  The model file
+    carries the event "time >= 25: k2 = 4" (brusselator-model.xml, listOfEvents), so
+    the interval is a sub-step of 25, a re-created simulator with k2 = 4, and 5 more."""
+    tol = (DBL_MAX, 1e-6)
+    (c4,), _ = do_timesteps(make_accurate or make, "brusselator-model", 30.0,
+                            integrator=smeb.RK435, tolerances=tol)
+    worst = {}
+    for integ in (smeb.RK212, smeb.RK323, smeb.RK435):
+        (c,), sims = do_timesteps(make, "brusselator-model", 30.0, integrator=integ,
+                                  tolerances=(DBL_MAX, 0.01))
+        assert len(sims) == 2  # the event at t = 25 re-created the simulator once
+        worst[integ] = float(np.max((c[:, 0] - c4[:, 0]) / (c4[:, 0] + 1e-20)))
+        assert worst[integ] < 0.01, (integ, worst)
+    return worst
+
+
 def membrane_parallel_matches_serial(make_serial, make_parallel):
     """K6, simulate_t.cpp:382-439: very-simple-model, RK101, maxErr = DBL_MAX,
     maxTimestep 0.01, one interval of 1: the parallel execution takes the same

@@ -75,6 +75,8 @@ CASES = [
     (K.timeout, WALL_CLOCK),
     (K.stop_then_continue, ADAPTIVE),
     (K.example_3d_models_tiny_step, ADAPTIVE),
+    # K5 with the model's event at t = 25 (simulator re-created with k2 = 4)
+    (K.brusselator_rk_orders_agree, ADAPTIVE),
 ]
 
 
