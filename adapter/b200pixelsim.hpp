@@ -50,6 +50,7 @@ private:
   std::size_t nExtraVars{0}; // time, x, y, z components behind the species
   // BaseSim returns references: host mirrors owned here
   mutable std::vector<std::vector<double>> conc;
+  bool mirrored{true}; // conc[i] is the library's host mirror of compartment i
   mutable std::vector<std::vector<double>> dcdt;
 
   static std::vector<std::string> cudaExpressions(
@@ -470,6 +471,21 @@ public:
       }
       currentErrorMessage = smeb200_error(sim.get());
       maxStableTimestep = smeb200_get_max_stable_timestep(sim.get());
+      if (currentErrorMessage.empty()) {
+        // the vectors BaseSim::getConcentrations hands out are the library's host
+        // mirrors (page-locked in place): one D2H, no second host copy; and the
+        // download starts at the end of run() like the reference GPU backend's
+        // (cudapixelsim.cpp:1486-1516) — Simulation reads the state after every
+        // run (simulate.cpp:313-314)
+        for (std::size_t ci = 0; ci < conc.size(); ++ci) {
+          if (!conc[ci].empty()) {
+            mirrored = smeb200_set_host_mirror(sim.get(), ci, conc[ci].data(),
+                                               conc[ci].size()) == 0 &&
+                       mirrored;
+          }
+        }
+        smeb200_set_async_download(sim.get(), 1);
+      }
     } catch (const std::exception &e) {
       // like the reference constructors: never throw (pixelsim.cpp:415-418)
       currentErrorMessage = e.what();
@@ -508,8 +524,11 @@ public:
     if (sim) {
       const double *data{nullptr};
       std::size_t n{0};
+      // waits for the download run() started; `data` is conc's own storage
+      // when the mirror could be page-locked in place
       if (smeb200_get_concentrations(sim.get(), compartmentIndex, &data, &n) ==
-          0) {
+              0 &&
+          data != conc[compartmentIndex].data()) {
         conc[compartmentIndex].assign(data, data + n);
       }
     }

@@ -7,6 +7,10 @@ over a full-box compartment, driven through the product's public call
 fixed-step configuration (benchmark/benchmark.cpp:214-216: maxErr = DBL_MAX,
 maxTimestep = dt): the controller still reads the fused error norm every step.
 
+With --gpus N (torchrun, one rank per GPU) the SAME global box (512^3 by
+default: BASELINE config 4) is cut into N z-slabs — strong scaling; --weak keeps
+--nz planes per GPU instead (the box grows with N).
+
   python bench.py --gpus N --steps K --warmup W            (own arm)
   python bench.py --impl reference --gpus N --steps K ...  (CPU reference arm)
 """
@@ -138,6 +142,15 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def host_threads():
+    """the host cores this process may use; torchrun exports OMP_NUM_THREADS=1 to
+    its workers, which must not decide how many threads the CPU arm gets"""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_sample_problem(args, integrator, nz):
     """a slab of the bench workload for the CPU arm: same kinetics, same x-y
     extent (capped at 512), nz planes"""
@@ -175,7 +188,7 @@ def cpu_baseline(args, integrator, threads, budget_s=12.0):
         while time.perf_counter() - t0 < budget_s:
             steps += sim.run(args.dt)
         el = time.perf_counter() - t0
-        ncores = OraclePixelSim.maxThreads() if threads == 0 else threads
+        ncores = threads
         return {"value": p.evals_per_step() * steps / el, "unit": UNIT, "cores": ncores,
                 "kind": "port", "sample": f"{text}, {args.integrator.upper()} fixed step, "
                                           f"{steps} steps, {el:.1f} s, OpenMP threads={ncores}"}
@@ -184,7 +197,7 @@ def cpu_baseline(args, integrator, threads, budget_s=12.0):
     sim.nextTimestep = DT  # skip the controller's 1e-7 start-up step
     sim.run(DT)    # warm-up
     value, steps, el = time_oracle(sim, p.evals_per_step(), budget_s, 100000)
-    ncores = OraclePixelSim.maxThreads() if threads == 0 else threads
+    ncores = threads
     return {"value": value, "unit": UNIT, "cores": ncores,
             "kind": "port",
             "sample": f"gray-scott-3d {args.integrator.upper()} fixed step, {nx}x{ny}x{nz} "
@@ -203,7 +216,8 @@ def run_reference(args, rank, world):
     from oracle.oracle_sim import OraclePixelSim
     integrator = INTEGRATOR_NAMES[args.integrator]
     p, (nx, ny, nz) = cpu_sample_problem(args, integrator, 32)
-    sim = OraclePixelSim(p, threads=0)
+    cores = host_threads()
+    sim = OraclePixelSim(p, threads=cores)
     sim.nextTimestep = DT
     for _ in range(max(args.warmup, 1)):
         sim.run(DT)
@@ -215,14 +229,14 @@ def run_reference(args, rank, world):
             break
     el = time.perf_counter() - t0
     value = p.evals_per_step() * steps / el
-    cores = OraclePixelSim.maxThreads()
     sample = (f"{nx}x{ny}x{nz} slab of the gray-scott-3d workload per step "
               f"({nx * ny * nz} voxels x 2 species), OpenMP threads={cores}")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
         "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * el / max(steps, 1), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "scaling": "weak" if args.weak else "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
         "config": {"workload": f"gray-scott-3d {args.integrator.upper()} fixed-step dt={DT}, "
                                f"{sample}"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
@@ -314,6 +328,79 @@ def run_ensemble(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def slab_planes(nz_total, rank, world):
+    from spatial_model_editor_b200.multigpu import slab_range
+    z0, z1 = slab_range(nz_total, rank, world)
+    return z1 - z0
+
+
+def parity_vs_oracle(args, integrator, local_rank, steps=3):
+    """the CUDA path and the CPU oracle on the slab the CPU arm is timed on
+    (512 x 512 x 32 of the headline workload, all host threads): max relative
+    difference after `steps` fixed steps"""
+    import spatial_model_editor_b200 as smeb
+    from oracle.oracle_sim import OraclePixelSim
+    p, (nx, ny, nz) = cpu_sample_problem(args, integrator, 32)
+    p.device = local_rank
+    gpu = smeb.PixelSim(p)
+    cpu = OraclePixelSim(p, threads=host_threads())
+    gpu.nextTimestep = cpu.nextTimestep = DT
+    ng, nc = gpu.run(steps * DT), cpu.run(steps * DT)
+    a, b = gpu.getConcentrations(0), cpu.getConcentrations(0)
+    rel = float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)))
+    gpu.close()
+    return {"max_rel": rel, "steps": int(ng), "oracle_steps": int(nc),
+            "box": f"{nx}x{ny}x{nz}", "tolerance": 1e-12}
+
+
+def parity_slabs_vs_one_gpu(integrator, rank, world, local_rank, dist, torch, steps=4):
+    """a reduced box cut into `world` z-slabs against ONE GPU on the same box: the
+    gathered slabs must be bit-identical (max |difference| = 0)"""
+    import spatial_model_editor_b200 as smeb
+    from spatial_model_editor_b200.multigpu import SlabPixelSim, default_comm_name
+    nx, ny, nz = 128, 64, 16 * world
+    pg = make_problem(nx, ny, nz, integrator, device=local_rank)
+    sim = SlabPixelSim(pg, rank, world, comm_name=default_comm_name("parity"))
+    if sim.errorMessage():
+        raise SystemExit("bench parity: " + sim.errorMessage())
+    sim.nextTimestep = DT
+    n = sim.run(steps * DT)
+    mine = torch.from_numpy(np.ascontiguousarray(sim.getConcentrations(0))).cuda()
+    parts = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(parts, mine)
+    out = None
+    if rank == 0:
+        one = smeb.PixelSim(make_problem(nx, ny, nz, integrator, device=local_rank))
+        one.nextTimestep = DT
+        n1 = one.run(steps * DT)
+        ref = one.getConcentrations(0)
+        got = torch.cat(parts).cpu().numpy()
+        out = {"max_abs": float(np.max(np.abs(got - ref))), "steps": int(n),
+               "one_gpu_steps": int(n1), "box": f"{nx}x{ny}x{nz}", "slabs": world,
+               "halo_exchanges": sim.haloExchanges()}
+        one.close()
+    dist.barrier()
+    sim.close()
+    return out
+
+
+def refcuda_baseline(args, nx, ny, nz, steps=8):
+    """"the kernel to beat" beside the product, same box, same process: the
+    reference GPU backend's unfused kernel sequence restated
+    (baselines/refcuda_port.cu; cudapixelsim.cpp:164-349, 1549-1555, 1584-1616)"""
+    from baselines.refcuda_port import RefCudaPort
+    sim = RefCudaPort(nx, ny, nz, gray_scott_3d_state(nx, ny, nz, 0))
+    sim.steps(args.dt, 3)
+    sampler = ClockSampler(0)
+    sampler.start()
+    ms, _ = sim.steps(args.dt, steps)
+    clocks = sampler.stop()
+    evals = 2 * nx * ny * nz * 2
+    return {"ms_per_step": ms / steps, "value": evals * steps / (ms * 1e-3), "unit": UNIT,
+            "steps": steps, "kind": "port", "source": "baselines/refcuda_port.cu",
+            "clocks": clocks}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -321,9 +408,16 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--size", type=int, default=512, help="box edge (voxels)")
-    ap.add_argument("--nz", type=int, default=0, help="planes per GPU (default: size)")
+    ap.add_argument("--nz", type=int, default=0,
+                    help="planes of the global box (default: size); with --weak: per GPU")
+    ap.add_argument("--weak", action="store_true",
+                    help="N GPUs: --nz planes PER GPU (the box grows with N) instead of "
+                         "one global box cut N ways")
     ap.add_argument("--integrator", default="rk212")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the parity checks, the e2e interval sweep and the "
+                         "reference-GPU-kernel baseline (A/B runs)")
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--workload", default="c4",
                     help="c4 (headline) | c2disc | c3 | ensemble")
@@ -363,45 +457,60 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def allmax(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     nx = ny = args.size
-    nz = args.nz or args.size
+    nz_arg = args.nz or args.size
+    # strong scaling (default): one global box; weak: nz_arg planes per GPU
+    nz_total = nz_arg * world if args.weak else nz_arg
     W, K = max(args.warmup, 3), args.steps
     listed = args.workload in ("c2disc", "c3")
     DTs = args.dt
     if listed:
-        if world > 1:
-            raise SystemExit("bench: voxel-list workloads run on one GPU")
+        from spatial_model_editor_b200.multigpu import SlabPixelSim
         p, workload_text = make_listed_problem(args, integrator, local_rank)
         p.kernel_variant = args.variant
-        sim = smeb.PixelSim(p)
         evals_per_step = p.evals_per_step()
         dom = max(p.compartments, key=lambda c: c.n_voxels * c.n_species)
-        values_per_rank = dom.n_voxels * dom.n_species
         dom_index = p.compartments.index(dom)
+        if world > 1:  # voxel lists cut at plane boundaries (2-D images: along x? no:
+            # the slab axis is z, so a 2-D workload is stacked nz = world planes deep)
+            raise SystemExit("bench: voxel-list workloads are 2-D images here; run them "
+                             "on one GPU (z-slabs need planes to cut)")
+        sim = smeb.PixelSim(p)
+        values_per_rank = dom.n_voxels * dom.n_species
         nn_bytes = sim.neighbourBytesPerVoxel(dom_index) * dom.n_voxels
         workload_text += (f"; neighbour data {sim.neighbourBytesPerVoxel(dom_index)} B/voxel"
                           f" ({sim.neighbourRuns(dom_index)} runs)")
+        nz_local = 1
     elif world > 1:
         from spatial_model_editor_b200.multigpu import SlabPixelSim
         # the global box is only described (no global array is ever built);
         # every rank generates its own planes, ghosts included
         p = make_problem(nx, ny, 1, integrator, device=local_rank)
-        p.compartments[0].box = (nx, ny, nz * world)
+        p.compartments[0].box = (nx, ny, nz_total)
         sim = SlabPixelSim(p, rank, world, make_slab=lambda z0, z1: gray_scott_3d_state(
             nx, ny, z1 - z0, z0), variant=args.variant)
-        evals_per_step = STAGES[integrator] * nx * ny * nz * world * 2
+        evals_per_step = STAGES[integrator] * nx * ny * nz_total * 2
+        nz_local = slab_planes(nz_total, rank, world)
     else:
-        p = make_problem(nx, ny, nz, integrator, device=local_rank)
+        p = make_problem(nx, ny, nz_total, integrator, device=local_rank)
         p.kernel_variant = args.variant
         sim = smeb.PixelSim(p)
         evals_per_step = p.evals_per_step()
+        nz_local = nz_total
     if sim.errorMessage():
         raise SystemExit("bench: " + sim.errorMessage())
     if not listed:
-        values_per_rank = nx * ny * nz * 2
+        values_per_rank = nx * ny * nz_local * 2
         nn_bytes = 0
-        workload_text = (f"gray-scott-3d kinetics, {nx}x{ny}x{nz * world} full-box "
-                         f"compartment ({nz} planes per GPU), S=2")
+        workload_text = (f"gray-scott-3d kinetics, {nx}x{ny}x{nz_total} full-box "
+                         f"compartment ({nz_local} planes on rank 0), S=2")
 
     # warm-up: W steps of DT (the controller's 1e-7 start-up step is skipped by
     # seeding nextTimestep, which run() otherwise raises to DT after one step)
@@ -413,11 +522,10 @@ def main():
         assert sim.run(W * DTs) == W
     launches0 = sim.launchCount()
     disc0 = sim.discardedSteps
-    # dominant-kernel durations by CUDA events inside the timed region: on every
-    # step when a step is long, on every 4th step when the two event records per
-    # launch (a few microseconds of stream time) would show in the step time
-    warm_ms_per_step = sim.lastRunMs() / max(W, 1)
-    timing_stride = 1 if warm_ms_per_step > 1.0 or K < 8 else 4
+    # dominant-kernel durations by CUDA events inside the timed region, on every
+    # 4th step: the two event records per launch cost a few microseconds of stream
+    # time and keep that launch from overlapping its predecessor's tail
+    timing_stride = 1 if K < 8 else 4
     sim.setKernelTiming(timing_stride)
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -435,40 +543,50 @@ def main():
     else:
         assert steps == K, (steps, K, sim.errorMessage())
     if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+        ms = allmax(ms)
         tl = torch.tensor([launches], dtype=torch.float64, device="cuda")
         dist.all_reduce(tl, op=dist.ReduceOp.SUM)
         launches = int(tl.item())
     value = evals_per_step * K / (ms * 1e-3)
 
-    # end to end through the public call with HOST buffers: one image interval =
-    # upload of the state from pinned host memory, K steps, download of the result
-    # pinned mirror (the local slab incl. ghost planes when decomposed)
+    # End to end through the public call with HOST buffers, the way Simulation
+    # drives a simulator (simulate.cpp:397-462): the state is uploaded once from
+    # pinned host memory (a restart: setConcentrations), then image intervals of Ke
+    # steps, each followed by the download of the whole state (getConcentrations).
+    # The headline e2e uses Ke = --steps; the sweep shows the share of the copies.
     ncomp = len(p.compartments)
     hosts = [sim.getConcentrationsWithGhosts(0)] if world > 1 else [
         np.array(sim.getConcentrations(i)) if ncomp > 1 else sim.getConcentrations(i)
         for i in range(ncomp)]
-    h2d = d2h = sum(h.nbytes for h in hosts)
-    barrier()
-    t0 = time.perf_counter()
-    for i, h in enumerate(hosts):
-        sim.setConcentrations(i, h)
-    steps2 = sim.run(args.steps * DTs)
-    if adaptive:
-        steps2 = K
-    checksum = 0.0
-    for i in range(ncomp):
-        out = sim.getConcentrations(i)
-        checksum += float(out[::4097, -1].sum())
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e = evals_per_step * steps2 / e2e_s
+    state_bytes = sum(h.nbytes for h in hosts)
+
+    def e2e_run(ke, intervals):
+        barrier()
+        t0 = time.perf_counter()
+        for i, h in enumerate(hosts):
+            sim.setConcentrations(i, h)
+        done = 0
+        checksum = 0.0
+        for _ in range(intervals):
+            n = sim.run(ke * DTs)
+            done += ke if adaptive else n
+            for i in range(ncomp):
+                out = sim.getConcentrations(i)
+                checksum += float(out[::4097, -1].sum())
+        barrier()
+        el = allmax(time.perf_counter() - t0)
+        return {"value": evals_per_step * done / el, "steps": done, "intervals": intervals,
+                "steps_per_interval": ke, "seconds": el,
+                "h2d_bytes_per_step": state_bytes / max(done, 1),
+                "d2h_bytes_per_step": state_bytes * intervals / max(done, 1),
+                "checksum": checksum}
+
+    head = e2e_run(args.steps, 2)
+    e2e_sweep = None
+    if not args.no_extras and not adaptive:
+        e2e_sweep = {str(ke): {k: v for k, v in e2e_run(ke, n).items()
+                               if k in ("value", "seconds", "intervals")}
+                     for ke, n in ((1, 4), (20, 2), (200, 1))}
 
     # roofline of the dominant kernel (the fused stage kernel): algorithmic bytes
     # per launch = 8 B x values x (reads + writes of whole arrays) averaged over
@@ -477,54 +595,77 @@ def main():
     alg_bytes_per_launch = (bytes_per_value_step * values_per_rank / STAGES[integrator]
                             + nn_bytes)
     launch_scope = "whole compartment"
-    if world > 1 and os.environ.get("SMEB200_HALO_OVERLAP", "1") != "0":
-        # z-slabs: the boundary planes are launched first (their halos travel while
-        # the interior is computed); the timed launch is the interior of the slab
-        ghosts = (1 if rank > 0 else 0) + (1 if rank + 1 < world else 0)
-        alg_bytes_per_launch *= (nz - ghosts) / nz
-        launch_scope = f"slab interior ({nz - ghosts} of {nz} planes)"
+    if world > 1:
+        timed = sim.timedLaunchPlanes()
+        alg_bytes_per_launch *= timed / nz_local
+        launch_scope = f"rank 0: {timed} of its {nz_local} owned planes"
     peak, peak_src = measured_peak()
-    traffic = None
-    try:  # ncu dram__bytes of the same kernel on the headline config (profiles/)
-        with open(os.path.join(ROOT, "profiles", "r1_v4_traffic.json")) as f:
-            tj = json.load(f)
-        if (nx, ny, nz, args.integrator) == (512, 512, 512, "rk212") and not listed:
-            traffic = tj["dram_bytes_per_launch"]["mean"]
-    except Exception:
-        traffic = None
+    traffic = traffic_src = None
+    if (nx, ny, nz_total, args.integrator, world) == (512, 512, 512, "rk212", 1) and not listed:
+        for name in ("r2_traffic.json", "r1_v4_traffic.json"):
+            try:  # ncu dram__bytes of the same kernel on this config (builder-run)
+                with open(os.path.join(ROOT, "profiles", name)) as f:
+                    traffic = json.load(f)["dram_bytes_per_launch"]["mean"]
+                traffic_src = f"profiles/{name} (ncu --set full, builder-run; not measured by this run)"
+                break
+            except Exception:
+                continue
     roofline = None
     if klaunches:
         achieved = alg_bytes_per_launch / (kms / klaunches * 1e-3) / 1e9
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                    "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                    "peak_source": peak_src,
                     "kernel": sim.dominantKernel(), "launches_timed": klaunches,
                     "avg_launch_ms": kms / klaunches,
                     "algorithmic_bytes_per_launch": alg_bytes_per_launch,
                     "launch_scope": launch_scope,
                     "timed_steps": f"every {timing_stride}" if timing_stride > 1 else "all"}
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline(args, integrator, threads=0)
+    sim.close()
+    del hosts
+
+    parity = {}
+    extras = not args.no_extras and not listed
+    if extras and world > 1:
+        parity["slabs_vs_one_gpu"] = parity_slabs_vs_one_gpu(integrator, rank, world,
+                                                             local_rank, dist, torch)
+    if extras and rank == 0:
+        parity["vs_oracle"] = parity_vs_oracle(args, integrator, local_rank)
+    cpu = refcuda = None
+    if rank == 0 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(args, integrator, threads=host_threads())
+    if extras and rank == 0 and world == 1 and args.integrator == "rk212":
+        try:
+            refcuda = refcuda_baseline(args, nx, ny, nz_total)
+            refcuda["product_over_refcuda"] = (ms / K) and refcuda["ms_per_step"] / (ms / K)
+        except Exception as e:  # e.g. not enough memory beside another process
+            refcuda = {"unavailable": str(e)}
     if rank == 0:
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "scaling": "weak" if args.weak else "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
             "config": {
                 "workload": workload_text + f", {args.integrator.upper()} " + (
                     "adaptive relTol=0.005 (a step = one attempted step)" if adaptive else
                     f"fixed step dt={DTs} (maxErr=DBL_MAX like benchmark.cpp:214-216)"),
-                "l2": "inputs larger than L2 (state array %.2f GiB per GPU)" % (
+                "l2": "inputs larger than L2 (state array %.2f GiB on rank 0)" % (
                     values_per_rank * 8 / 2 ** 30),
-                "parallelism": f"z-slabs x{world}" if world > 1 else "single GPU",
+                "parallelism": (f"z-slabs x{world}, " + ("weak: box grows with N" if args.weak
+                                else "strong: one global box")) if world > 1 else "single GPU",
                 "kernel_variant": args.variant},
-            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d / max(steps2, 1),
-                    "d2h_bytes_per_step": d2h / max(steps2, 1),
-                    "note": "one image interval: pinned H2D of the state, K steps, D2H "
-                            "of the result; bytes are per interval / K",
-                    "checksum": checksum},
+            "e2e": {"value": head["value"], "unit": UNIT,
+                    "h2d_bytes_per_step": head["h2d_bytes_per_step"],
+                    "d2h_bytes_per_step": head["d2h_bytes_per_step"],
+                    "note": "Simulation's usage (simulate.cpp:397-462): one pinned H2D of the "
+                            "state (restart), then image intervals of --steps steps, each "
+                            "followed by the D2H of the whole state; bytes are totals / steps",
+                    "intervals": head["intervals"], "steps_per_interval": head["steps_per_interval"],
+                    "seconds": head["seconds"], "checksum": head["checksum"],
+                    "by_steps_per_interval": e2e_sweep},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
-            "cpu_baseline": cpu}))
+            "parity": parity or None, "cpu_baseline": cpu, "refcuda_baseline": refcuda}))
     if world > 1:
         dist.destroy_process_group()
 

@@ -285,6 +285,23 @@ size_t smeb200_get_concentration_padding(const smeb200_sim *sim);
 int smeb200_set_concentrations(smeb200_sim *sim, size_t compartment,
                                const double *data, size_t n);
 
+/* Asynchronous state download, as the reference GPU backend does it
+ * (cudapixelsim.cpp:1486-1516,1657,1665-1669): with enable != 0 every
+ * smeb200_run ends by queueing the device-to-host copy of every compartment's
+ * state on a transfer stream and returns; smeb200_get_concentrations waits for
+ * that copy instead of starting one.  A following run / set_concentrations is
+ * ordered after the copy on the device.  Off by default (a caller that never
+ * reads the state should not pay for the copy); the SME adapter switches it on,
+ * Simulation::updateConcentrations reads the state after every run. */
+void smeb200_set_async_download(smeb200_sim *sim, int enable);
+/* The caller's buffer (n = n_voxels * n_species doubles, alive until
+ * smeb200_destroy or the next call for this compartment) becomes the host
+ * mirror of the compartment: the library page-locks it, downloads into it and
+ * smeb200_get_concentrations returns it — the adapter's std::vector behind
+ * BaseSim::getConcentrations is filled without a second host copy. */
+int smeb200_set_host_mirror(smeb200_sim *sim, size_t compartment, double *buffer,
+                            size_t n);
+
 /* new values for the runtime model parameters (takes effect at the next run) */
 int smeb200_set_params(smeb200_sim *sim, const double *values, size_t n);
 
@@ -334,10 +351,17 @@ const char *smeb200_dominant_kernel(const smeb200_sim *sim);
 /* ---- multi-GPU ---------------------------------------------------------- */
 /* z-slab decomposition (no counterpart in the reference, which has no
  * distributed layer): with n_ranks > 1 every rank's simulator
- *  - updates only its owned planes; after every Runge-Kutta stage it copies its
- *    two boundary planes into the neighbours' ghost planes over NVLink
- *    (CUDA IPC peer memory) and hand-shakes with stream-ordered 32-bit flags
- *    (cuStreamWriteValue32 / cuStreamWaitValue32) — no host involvement;
+ *  - updates only its owned planes; in every Runge-Kutta stage its two boundary
+ *    planes also go into the neighbours' ghost planes over NVLink (CUDA IPC peer
+ *    memory).  Box compartments on the TMA tile path do that inside the stage
+ *    kernel: the CTAs of a boundary plane store their results a second time
+ *    through the peer mapping and the last of them releases a sequence number
+ *    into a flag word in the neighbour's memory, which the neighbour's CTAs
+ *    acquire before they load the ghost plane — one kernel per stage, no copy
+ *    engine, no stream waits.  Voxel-list compartments and membranes: peer
+ *    copies and stream-ordered 32-bit flags (cuStreamWriteValue32 /
+ *    cuStreamWaitValue32) on a high-priority stream beside the slab interior.
+ *    No host involvement either way;
  *  - max-reduces the two error norms over ranks once per adaptive step through
  *    the shared-memory communicator, so that all ranks take identical
  *    step-size decisions.
@@ -348,13 +372,20 @@ typedef struct smeb200_comm smeb200_comm;
 int smeb200_comm_create(const char *name, int rank, int n_ranks,
                         smeb200_comm **out);
 int smeb200_comm_allreduce_max(smeb200_comm *comm, double *values, int n);
-/* in-place sum over the ranks of n <= 4 doubles, added in rank order on every
+/* in-place sum over the ranks of n doubles, added in rank order on every
  * rank (all ranks get the same bits): the spatial mean of non-spatial species in
  * a z-slab decomposed simulation (SimCompartment::spatiallyAverageDcdt,
  * pixelsim_impl.cpp:150-163, across slabs) */
 int smeb200_comm_allreduce_sum(smeb200_comm *comm, double *values, int n);
 int smeb200_comm_barrier(smeb200_comm *comm);
+/* this rank gives up (its run failed): every wait of the other ranks — barrier,
+ * reductions — returns an error from now on instead of spinning to its timeout */
+void smeb200_comm_abort(smeb200_comm *comm);
 void smeb200_comm_destroy(smeb200_comm *comm);
+/* z planes of the largest (box) compartment that the launch timed by
+ * smeb200_set_kernel_timing covers: all owned planes, or the slab interior when
+ * the boundary planes are launched apart (bench.py: roofline of a slab) */
+size_t smeb200_timed_launch_planes(const smeb200_sim *sim);
 /* halo exchanges performed since construction (0 on a single GPU) */
 uint64_t smeb200_halo_exchanges(const smeb200_sim *sim);
 

@@ -170,6 +170,26 @@ int smeb200_set_concentrations(smeb200_sim *sim, size_t compartment,
                  [&] { sim->impl.setConcentrations(compartment, data, n); });
 }
 
+void smeb200_set_async_download(smeb200_sim *sim, int enable) {
+  if (sim != nullptr) {
+    sim->impl.setAsyncDownload(enable != 0);
+  }
+}
+
+int smeb200_set_host_mirror(smeb200_sim *sim, size_t compartment, double *buffer,
+                            size_t n) {
+  if (sim == nullptr) {
+    return -1;
+  }
+  try {
+    sim->impl.setHostMirror(compartment, buffer, n);
+  } catch (const std::exception &e) {
+    sim->impl.errorMessage = e.what();
+    return 1;
+  }
+  return 0;
+}
+
 int smeb200_set_params(smeb200_sim *sim, const double *values, size_t n) {
   return guarded(sim, [&] { sim->impl.setParams(values, n); });
 }
@@ -316,6 +336,12 @@ int smeb200_comm_allreduce_max(smeb200_comm *comm, double *values, int n) {
   return 0;
 }
 
+void smeb200_comm_abort(smeb200_comm *comm) {
+  if (comm != nullptr) {
+    comm->impl.abort();
+  }
+}
+
 int smeb200_comm_barrier(smeb200_comm *comm) {
   if (comm == nullptr) {
     return -1;
@@ -330,6 +356,14 @@ int smeb200_comm_barrier(smeb200_comm *comm) {
 }
 
 void smeb200_comm_destroy(smeb200_comm *comm) { delete comm; }
+
+size_t smeb200_timed_launch_planes(const smeb200_sim *sim) {
+  try {
+    return sim != nullptr ? sim->impl.timedLaunchPlanes() : 0;
+  } catch (...) {
+    return 0;
+  }
+}
 
 uint64_t smeb200_halo_exchanges(const smeb200_sim *sim) {
   return sim != nullptr ? sim->impl.haloExchanges : 0;

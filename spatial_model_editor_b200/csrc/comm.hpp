@@ -36,7 +36,10 @@ struct CommRankSlot {
   uint64_t ghostHiOff[kCommMaxCompartments];
   uint64_t ghostLoCnt[kCommMaxCompartments];
   uint64_t ghostHiCnt[kCommMaxCompartments];
-  int pad_[3];
+  // CUDA IPC handle of the rank's in-kernel halo flag words (fused halo path)
+  unsigned char flagHandle[64];
+  int fusedHalo; // the rank exchanges halos inside its stage kernels
+  int pad_[2];
 };
 
 struct CommSegment {
@@ -44,7 +47,10 @@ struct CommSegment {
   std::atomic<uint64_t> attached;    // ranks that mapped the segment
   std::atomic<uint64_t> barrierCount;
   uint32_t nRanks;
-  uint32_t pad_[9];
+  // set by a rank whose run failed: every wait of the other ranks throws instead
+  // of spinning until its timeout
+  std::atomic<uint32_t> abort;
+  uint32_t pad_[8];
   // halo flags: flag[r][0] = sequence of the last halo pushed into rank r's
   // LOW ghost plane (by rank r-1), flag[r][1] = into its HIGH ghost (by r+1).
   // Own 4 KiB page(s): registered with CUDA by every process.
@@ -66,10 +72,14 @@ public:
   int size() const { return nRanks_; }
   CommSegment *segment() { return seg_; }
   void barrier();
-  // in-place max over ranks of n <= 4 doubles (NaN never wins, like std::max)
+  // in-place max over ranks of n doubles; a NaN never wins against a number on
+  // any rank (fmax), so every rank leaves with the same bits
   void allreduceMax(double *vals, int n);
-  // in-place sum of n <= 4 doubles, added in rank order (same bits on all ranks)
+  // in-place sum of n doubles, added in rank order (same bits on all ranks)
   void allreduceSumOrdered(double *vals, int n);
+  // a rank gives up (its run threw): the waits of all ranks throw from now on
+  void abort();
+  bool aborted() const;
   // pointer + length of the page(s) holding the halo flags (for
   // cudaHostRegister)
   void *flagPages() { return &seg_->haloFlag[0][0][0]; }
@@ -79,6 +89,7 @@ public:
   }
 
 private:
+  void reduce4(double *vals, int n, bool sum);
   void waitUntil(const std::atomic<uint64_t> &v, uint64_t target,
                  const char *what) const;
   std::string name_;

@@ -51,6 +51,7 @@ const DriverApi &DriverApi::get() {
       resolve("cuModuleUnload", api.ModuleUnload);
       resolve("cuModuleGetFunction", api.ModuleGetFunction);
       resolve("cuLaunchKernel", api.LaunchKernel);
+      resolve("cuLaunchKernelEx", api.LaunchKernelEx);
       resolve("cuFuncSetAttribute", api.FuncSetAttribute);
       resolve("cuOccupancyMaxActiveBlocksPerMultiprocessor",
               api.OccupancyMaxActiveBlocksPerMultiprocessor);

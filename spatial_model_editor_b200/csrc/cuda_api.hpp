@@ -24,6 +24,8 @@ struct DriverApi {
   CUresult (*LaunchKernel)(CUfunction, unsigned, unsigned, unsigned, unsigned,
                            unsigned, unsigned, unsigned, CUstream, void **,
                            void **) = nullptr;
+  CUresult (*LaunchKernelEx)(const CUlaunchConfig *, CUfunction, void **,
+                             void **) = nullptr;
   CUresult (*FuncSetAttribute)(CUfunction, CUfunction_attribute, int) = nullptr;
   CUresult (*OccupancyMaxActiveBlocksPerMultiprocessor)(int *, CUfunction, int,
                                                         size_t) = nullptr;

@@ -118,6 +118,15 @@ template __global__ void
 smeb_stage_tile<Reac0, F3, 16, 64, 5, true>(const __grid_constant__ SmebStageArgs<2>,
                                             const __grid_constant__ SmebTensorMap,
                                             const smeb_u32);
+// z-slab variants: halo exchange inside the kernel
+template __global__ void
+smeb_stage_tile<Reac0, F1 | SMEB_F_HALO, 16, 64, 5, true>(
+    const __grid_constant__ SmebStageArgs<2>, const __grid_constant__ SmebTensorMap,
+    const smeb_u32);
+template __global__ void
+smeb_stage_tile<Reac0, F2 | SMEB_F_HALO, 16, 64, 5, true>(
+    const __grid_constant__ SmebStageArgs<2>, const __grid_constant__ SmebTensorMap,
+    const smeb_u32);
 template __global__ void
 smeb_stage_tile<Reac0, F2, 16, 64, 3, false>(const __grid_constant__ SmebStageArgs<2>,
                                              const __grid_constant__ SmebTensorMap,

@@ -44,6 +44,7 @@ typedef unsigned int smeb_u32;
 #define SMEB_F_RELAX_A 4096u     // zero-storage relaxation, first half: residual
                                  // norms, out = c + dt f for those species
 #define SMEB_F_RELAX_B 8192u     // second half: out = c0/2 + c/2 + dt/2 f, error
+#define SMEB_F_HALO 16384u       // z-slabs, tile kernel: halo exchange in the kernel
 
 #define SMEB_MEMB_FLAG 0x80000000u
 #define SMEB_BLOCK 256
@@ -77,7 +78,9 @@ template <int S> struct SmebStageArgs {
   const smeb_u32 *nn;  // voxel-list geometry: [6 n] neighbour indices, or (runs
                        // != 0) [n] run-compressed neighbour codes
   const int *runs;     // [4 n_runs] index deltas of the +x, -x, +z, -z neighbours
-  smeb_u64 *err;       // [2] bit patterns of max abs / max rel error
+  smeb_u64 *err;       // error slot: [0], [1] bit patterns of max abs / max rel
+                       // error, then two u32: CTAs arrived, steps published
+  smeb_u64 *errHost;   // pinned host ring the last CTA of a step publishes into
   const double *nsAv;  // [R::NNS] spatial averages of dc/dt (non-spatial species)
   double *nsPartial;   // [blocks][R::NNS] block sums written by the pre-pass
   const double *darr;  // [n][S] per-voxel diffusion constants (R::NUD)
@@ -87,6 +90,20 @@ template <int S> struct SmebStageArgs {
   smeb_u32 v0;         // voxel list: first voxel updated (z-slab ghosts before it)
   smeb_u32 nx, ny, nz; // box dims; voxel = (z*nx + x)*ny + y
   smeb_u32 z_begin, z_end; // planes updated by this launch (ghosts excluded)
+  smeb_u32 errExpected;    // CTAs of all error-norm launches of this step (0: the
+                           // norms stay in the slot, nothing is published)
+  // z-slabs, tile kernel: halo exchange inside the stage kernel (see
+  // smeb_stage_tile).  haloMode bit 0 / 1: there is a rank below / above.
+  smeb_u32 haloMode;
+  double *peerLo;          // rank below: its HIGH ghost plane of the output buffer
+  double *peerHi;          // rank above: its LOW ghost plane of the output buffer
+  smeb_u32 *halo;          // own words: [0] / [1] sequence number of the last plane
+                           // that arrived from below / above, [2] / [3] CTAs of the
+                           // low / high boundary plane done, [4] error
+  smeb_u32 *peerFlagLo;    // rank below: its halo[1]
+  smeb_u32 *peerFlagHi;    // rank above: its halo[0]
+  smeb_u32 haloSeq;        // sequence number of this stage (inputs carry haloSeq - 1)
+  smeb_u32 pad0_;
   double g1, g2, g3, bdt, delta; // stage coefficients (bdt = beta*dt)
   // CUDA-graph replay of a step: the step size lives in device memory (a
   // captured launch cannot carry a new bdt); bdt = beta * *dtp when dtp != 0
@@ -156,12 +173,55 @@ __device__ __forceinline__ void smeb_store_voxel(double *__restrict__ p,
   }
 }
 
+// Programmatic dependent launch (sm_90+): a kernel lets the next kernel of the
+// stream become resident as soon as all of its own CTAs have started, and touches
+// global memory only after the kernel before it has completed and flushed.  Both
+// are no-ops for launches without the stream-serialization attribute.
+__device__ __forceinline__ void smeb_pdl_trigger() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void smeb_pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+#define SMEB_ERR_RING 8 // entries of the pinned host ring (sim.hpp kErrRing)
+
+// One CTA of an error-norm launch is done.  The CTA that completes the step's
+// count takes the two maxima out of the slot (leaving it zeroed for the next
+// step) and publishes them with the step's sequence number into the pinned host
+// ring: the host polls 32 bytes of its own memory instead of queueing a copy, a
+// memset and an event behind every step (which also kept two kernels from
+// overlapping their tails).  Called by one thread per CTA, after its atomicMax.
+__device__ __forceinline__ void smeb_err_arrive(smeb_u64 *err, smeb_u64 *errHost,
+                                                smeb_u32 expected) {
+  if (expected == 0u) {
+    return;
+  }
+  unsigned int *cnt = reinterpret_cast<unsigned int *>(err + 2);
+  __threadfence();
+  const unsigned int prev = atomicAdd(cnt, 1u);
+  if (prev + 1u == expected) {
+    __threadfence();
+    const smeb_u64 a = atomicExch(err, 0ull);
+    const smeb_u64 r = atomicExch(err + 1, 0ull);
+    atomicExch(cnt, 0u);
+    const unsigned int seq = atomicAdd(cnt + 1, 1u) + 1u;
+    volatile smeb_u64 *h = errHost + 4u * (seq % SMEB_ERR_RING);
+    h[0] = a;
+    h[1] = r;
+    __threadfence_system();
+    h[2] = (smeb_u64)seq;
+    __threadfence_system();
+  }
+}
+
 // max-reduction of the two error norms over the block, then one atomicMax per
 // block on the ordered bit patterns (values are >= 0 and never NaN, because
 // like std::max in pixelsim_impl.cpp:783-788 a NaN or negative candidate is
 // never taken).  Called once per thread at the end of a kernel.
 __device__ __forceinline__ void smeb_block_max2(double eabs, double erel,
-                                                smeb_u64 *err) {
+                                                smeb_u64 *err, smeb_u64 *errHost,
+                                                smeb_u32 expected) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     double a = __shfl_xor_sync(0xffffffffu, eabs, o);
@@ -194,6 +254,7 @@ __device__ __forceinline__ void smeb_block_max2(double eabs, double erel,
       if (erel > 0.0) {
         atomicMax(err + 1, (smeb_u64)__double_as_longlong(erel));
       }
+      smeb_err_arrive(err, errHost, expected);
     }
   }
 }
@@ -584,12 +645,14 @@ __global__ void SMEB_NN_BOUNDS
   // (SMEB_NN_CODE_AHEAD >= 1), and so are its own state and c0 (>= 2): with six
   // resident CTAs the loads of one iteration alone do not keep enough bytes in
   // flight to cover the DRAM latency
+  smeb_pdl_trigger();
   const smeb_u32 stride = gridDim.x * SMEB_BLOCK;
   const bool coded = a.runs != nullptr;
   constexpr bool PRE = SMEB_NN_CODE_AHEAD >= 2;
   constexpr bool PRE_C0 = PRE && (F & SMEB_F_USE_C0) != 0 &&
                           (F & (SMEB_F_OUT_DCDT | SMEB_F_SUM_NS)) == 0;
   smeb_u32 i = a.v0 + blockIdx.x * SMEB_BLOCK + threadIdx.x;
+  smeb_pdl_wait();
   smeb_u32 codeNext = coded && i < a.n ? a.nn[i] : 0u;
   double cNext[S], c0Next[S];
 #pragma unroll
@@ -637,7 +700,7 @@ __global__ void SMEB_NN_BOUNDS
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
   } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
                        (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
-    smeb_block_max2(eabs, erel, a.err);
+    smeb_block_max2(eabs, erel, a.err, a.errHost, a.errExpected);
   }
 }
 
@@ -651,8 +714,10 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   constexpr int S = R::S;
   double eabs = 0.0, erel = 0.0;
   double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
+  smeb_pdl_trigger();
   const smeb_u32 sx = a.ny, sz = a.nx * a.ny;
   const smeb_u32 iEnd = a.z_end * sz;
+  smeb_pdl_wait();
   for (smeb_u32 i = a.z_begin * sz + blockIdx.x * SMEB_BLOCK + threadIdx.x;
        i < iEnd; i += gridDim.x * SMEB_BLOCK) {
     const smeb_u32 y = i % a.ny;
@@ -674,7 +739,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
   } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
                        (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
-    smeb_block_max2(eabs, erel, a.err);
+    smeb_block_max2(eabs, erel, a.err, a.errHost, a.errExpected);
   }
 }
 
@@ -759,6 +824,8 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   constexpr int S = R::S;
   double eabs = 0.0, erel = 0.0;
   double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
+  smeb_pdl_trigger();
+  smeb_pdl_wait();
   for (smeb_u32 k = blockIdx.x * SMEB_BLOCK + threadIdx.x; k < m.n_mvox;
        k += gridDim.x * SMEB_BLOCK) {
     const smeb_u32 i = m.mvox[k];
@@ -777,7 +844,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
   } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
                        (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
-    smeb_block_max2(eabs, erel, a.err);
+    smeb_block_max2(eabs, erel, a.err, a.errHost, a.errExpected);
   }
 }
 
@@ -860,6 +927,55 @@ __device__ __forceinline__ void smeb_lds(const double *p, double *v) {
 
 extern __shared__ __align__(128) unsigned char smeb_dyn_smem[];
 
+// ---- halo exchange inside the stage kernel (z-slabs over NVLink) ---------------
+// A rank's boundary planes are written twice: into its own output buffer and,
+// with plain stores through the peer mapping, into the neighbour's ghost plane of
+// the same buffer.  When the last CTA of a boundary plane is done it releases
+// the stage's sequence number into a flag word in the NEIGHBOUR's memory; the
+// neighbour's CTAs that read that ghost plane in the next stage acquire it
+// before their TMA load.  No copy engine, no extra launches, no stream waits:
+// one kernel per stage, and the stages of a step chain with programmatic
+// dependent launch.  The wait is bounded: after about 10 s it raises halo[4]
+// and goes on (the host reports it), it never hangs the GPU.
+__device__ __forceinline__ smeb_u32 smeb_ld_acquire_sys(const smeb_u32 *p) {
+  smeb_u32 v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void smeb_st_release_sys(smeb_u32 *p, smeb_u32 v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void smeb_halo_acquire(smeb_u32 *halo, int side,
+                                                  smeb_u32 want) {
+  long long t0 = 0;
+  unsigned spins = 0;
+  while ((int)(smeb_ld_acquire_sys(halo + side) - want) < 0) {
+    if (++spins == 64u) {
+      t0 = clock64();
+    } else if (spins > 64u && (spins & 1023u) == 0u &&
+               clock64() - t0 > 20000000000ll) {
+      atomicExch(halo + 4, 1u + (smeb_u32)side);
+      break;
+    }
+  }
+  // the plane was written through the generic proxy (by the neighbour's SMs);
+  // the TMA load that follows reads it through the async proxy
+  asm volatile("fence.proxy.async.global;" ::: "memory");
+}
+
+// waits (one thread) until the planes of stage `seq` have arrived from both
+// neighbours: the end of run(), before getters read ghost planes
+__global__ void smeb_halo_quiesce(smeb_u32 *halo, smeb_u32 mode, smeb_u32 seq) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    if (mode & 1u) {
+      smeb_halo_acquire(halo, 0, seq);
+    }
+    if (mode & 2u) {
+      smeb_halo_acquire(halo, 1, seq);
+    }
+  }
+}
+
 template <class R, unsigned F, int TX, int TY, int NST, bool M3>
 __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
     smeb_stage_tile(const __grid_constant__ SmebStageArgs<R::S> a,
@@ -884,6 +1000,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   static_assert(SMEB_BLOCK % TY == 0 && TX % G == 0, "tile shape");
   static_assert(NST >= LOOK + 2, "ring too short");
 
+  smeb_pdl_trigger();
   __shared__ smeb_u64 fullBar[NST];
   unsigned char *ring = smeb_dyn_smem;
   {
@@ -902,7 +1019,15 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   int m0, m1, x0;
   if constexpr (M3) {
     x0 = blockIdx.y * TX;
-    m0 = a.z_begin + blockIdx.z * chunk;
+    // z-slabs: the chunks that hold the boundary planes are scheduled first
+    // (bottom chunk, top chunk, then the interior), so the halos leave early
+    int zc = blockIdx.z;
+    if constexpr ((F & SMEB_F_HALO) != 0) {
+      if (gridDim.z > 1u) {
+        zc = zc == 1 ? (int)gridDim.z - 1 : (zc > 1 ? zc - 1 : 0);
+      }
+    }
+    m0 = a.z_begin + zc * chunk;
     m1 = min(m0 + (int)chunk, (int)a.z_end);
   } else {
     x0 = 0;
@@ -911,6 +1036,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   }
   const int nIter = m1 - m0;
   if (nIter <= 0) {
+    smeb_pdl_wait();
     if constexpr ((F & SMEB_F_SUM_NS) != 0) {
       const size_t blk =
           ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x +
@@ -918,10 +1044,26 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
       if (threadIdx.x < R::NNS) {
         a.nsPartial[blk * R::NNS + threadIdx.x] = 0.0;
       }
+    } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
+                         (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
+      if (threadIdx.x == 0) { // an empty CTA still counts towards the step's norms
+        smeb_err_arrive(a.err, a.errHost, a.errExpected);
+      }
     }
     return;
   }
   const int nLoads = nIter + LOOK;
+  // halo exchange in the kernel: does this CTA read a ghost plane / own a
+  // boundary plane?
+  constexpr bool HALO = M3 && (F & SMEB_F_HALO) != 0 &&
+                        (F & (SMEB_F_OUT_DCDT | SMEB_F_OUT_LOWER |
+                              SMEB_F_OUT_CNEW | SMEB_F_SUM_NS | SMEB_F_RELAX_A |
+                              SMEB_F_RELAX_B)) == 0;
+  bool haloLo = false, haloHi = false;
+  if constexpr (HALO) {
+    haloLo = (a.haloMode & 1u) != 0u && m0 == (int)a.z_begin;
+    haloHi = (a.haloMode & 2u) != 0u && m1 == (int)a.z_end;
+  }
   // load j fetches plane m0 - 1 + j (M3) / brick m0 + j (2-D)
   auto issue = [&](int j, int slot) {
     const smeb_u32 bar = barAddr + 8u * slot;
@@ -944,6 +1086,23 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  // everything above is independent of the kernels before this one
+  smeb_pdl_wait();
+  if constexpr (HALO) {
+    // a boundary chunk reads a ghost plane (its first / last load): the
+    // neighbour's plane of the previous stage must have arrived.  Both waits sit
+    // here, outside the march loop, which stays the single-GPU loop
+    if (tid == 0) {
+      if (haloLo) {
+        smeb_halo_acquire(a.halo, 0, a.haloSeq - 1u);
+      }
+      if (haloHi) {
+        smeb_halo_acquire(a.halo, 1, a.haloSeq - 1u);
+      }
+    }
+  }
+  if (tid == 0) {
     for (int j = 0; j < NST && j < nLoads; ++j) {
       issue(j, j);
     }
@@ -1141,13 +1300,53 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
       parW ^= 1;
     }
   }
+  if constexpr (HALO) {
+    // The boundary planes of this rank go into the neighbours' ghost planes: every
+    // thread reads back the voxels it stored (own writes, L2 hits) and stores them
+    // a second time through the peer mapping; then the CTA counts itself done and
+    // the last CTA of the plane releases the stage's number to the neighbour.
+    if (haloLo || haloHi) {
+      if (active) {
+        const size_t inPlane = (size_t)gx0 * a.ny + gy;
+        const size_t planeVox = (size_t)a.nx * a.ny;
+#pragma unroll
+        for (int k = 0; k < RPT; ++k) {
+          double v[S];
+          if (haloLo) {
+            smeb_load_voxel<S>(a.cout, (size_t)m0 * planeVox + inPlane + k * rowStride, v);
+            smeb_store_voxel<S>(a.peerLo, inPlane + k * rowStride, v);
+          }
+          if (haloHi) {
+            smeb_load_voxel<S>(a.cout,
+                               (size_t)(m1 - 1) * planeVox + inPlane + k * rowStride, v);
+            smeb_store_voxel<S>(a.peerHi, inPlane + k * rowStride, v);
+          }
+        }
+      }
+      __threadfence_system(); // this thread's peer stores, before the barrier
+      __syncthreads();
+      if (tid == 0) {
+        const smeb_u32 tiles = gridDim.x * gridDim.y;
+        if (haloLo && atomicAdd(a.halo + 2, 1u) + 1u == tiles) {
+          atomicExch(a.halo + 2, 0u);
+          __threadfence_system();
+          smeb_st_release_sys(a.peerFlagLo, a.haloSeq);
+        }
+        if (haloHi && atomicAdd(a.halo + 3, 1u) + 1u == tiles) {
+          atomicExch(a.halo + 3, 0u);
+          __threadfence_system();
+          smeb_st_release_sys(a.peerFlagHi, a.haloSeq);
+        }
+      }
+    }
+  }
   if constexpr ((F & SMEB_F_SUM_NS) != 0) {
     const size_t blk =
         ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + blk * R::NNS);
   } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
                        (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
-    smeb_block_max2(eabs, erel, a.err);
+    smeb_block_max2(eabs, erel, a.err, a.errHost, a.errExpected);
   }
 }
 

@@ -601,6 +601,10 @@ void Sim::chooseGeometry(int variant) {
     // with the least (wave rounding x halo re-read) cost among those that give
     // at least two waves.
     const unsigned wave = static_cast<unsigned>(smCount) * SMEB_TILE_CTAS_PER_SM;
+    // z-slabs: at least four chunks, so that the chunks holding the boundary
+    // planes (scheduled first) are a small part of the launch and the halos
+    // leave early
+    const unsigned minChunks = nRanks > 1 ? 4u : 1u;
     auto pickChunks = [&](unsigned units, unsigned tiles, double haloUnits) {
       unsigned best = 1;
       double bestCost = 1e300;
@@ -609,7 +613,8 @@ void Sim::chooseGeometry(int variant) {
         // too small to fill the GPU whatever the split: chunks of ~8 units
         return std::max(1u, units / 8u);
       }
-      for (unsigned chunks = 1; chunks <= maxChunks; ++chunks) {
+      for (unsigned chunks = std::min(minChunks, maxChunks); chunks <= maxChunks;
+           ++chunks) {
         const unsigned chunk = (units + chunks - 1) / chunks;
         const unsigned used = (units + chunk - 1) / chunk; // non-empty chunks
         if (used != chunks) {
@@ -879,6 +884,7 @@ Sim::Sim(const smeb200_problem &p, bool compileOnlyMode)
     // (pixelsim.cpp:415-418, cudapixelsim.cpp:1156-1167)
     errorMessage = e.what();
     ctorFailed = true;
+    abortSlabs(); // z-slabs: the other ranks' constructors are waiting
   }
 }
 
@@ -1125,6 +1131,20 @@ void Sim::build(const smeb200_problem &p) {
     setupMembranes(p, nnHost);
   }
   chooseGeometry(p.kernel_variant);
+  // z-slabs of box compartments on the TMA tile path exchange their halos inside
+  // the stage kernels (device_kernels.cuh: "halo exchange inside the stage
+  // kernel"); every other combination keeps the stream-ordered exchange
+  if (nRanks > 1 && !envFlagOff("SMEB200_FUSED_HALO") && !nsInSlabs) {
+    bool any = false, all = true;
+    for (const auto &c : comps) {
+      if (c.S == 0 || c.n == 0) {
+        continue;
+      }
+      any = true;
+      all = all && c.geom == Geom::TILE && c.tile.m3;
+    }
+    fusedHalo = any && all;
+  }
 
   // the model module: one kernel per compartment and distinct stage
   generateSource(p);
@@ -1139,9 +1159,9 @@ void Sim::build(const smeb200_problem &p) {
       continue;
     }
     for (const auto &sd : plan) {
-      addName(kernelName(ci, sd.flags(), false));
+      addName(kernelName(ci, stageFlags(sd), false));
       if (comps[ci].nMvox > 0) {
-        addName(kernelName(ci, sd.flags(), true));
+        addName(kernelName(ci, stageFlags(sd), true));
       }
     }
     if (!comps[ci].nonSpatial.empty()) {
@@ -1164,13 +1184,19 @@ void Sim::build(const smeb200_problem &p) {
       }
     }
   }
+  if (fusedHalo) {
+    names.push_back("smeb_halo_quiesce");
+  }
   mainModule = compile(names);
   if (compileOnly) {
     return;
   }
+  if (fusedHalo) {
+    kHaloQuiesce = mainModule.fn.at("smeb_halo_quiesce");
+  }
   dominantKernelName = comps.empty() || comps[dominantComp].S == 0
                            ? std::string{}
-                           : kernelName(dominantComp, plan.back().flags(), false);
+                           : kernelName(dominantComp, stageFlags(plan.back()), false);
 
   for (uint32_t ci = 0; ci < p.n_compartments; ++ci) {
     auto &c = comps[ci];
@@ -1202,7 +1228,7 @@ void Sim::build(const smeb200_problem &p) {
       encodeTensorMaps(c);
     }
     for (const auto &sd : plan) {
-      c.kStage.push_back(lookup(mainModule, ci, sd.flags()));
+      c.kStage.push_back(lookup(mainModule, ci, stageFlags(sd)));
       // occupancy queries up front: none while a step is being captured
       if (c.geom != Geom::TILE && c.kStage.back().main != nullptr) {
         persistentGrid(c.kStage.back().main);
@@ -1273,16 +1299,22 @@ void Sim::build(const smeb200_problem &p) {
     c.hostDcdt.assign(nv, 0.0);
     c.dcdtStale = false;
   }
-  dErr = devAlloc<unsigned long long>(4, "allocate error accumulators");
-  dErrScratch = dErr + 2;
-  check(cudaMemsetAsync(dErr, 0, 32, stream), "clear error accumulators");
-  check(cudaMallocHost(reinterpret_cast<void **>(&hErr), 16),
-        "allocate pinned error mirror");
-  check(cudaMallocHost(reinterpret_cast<void **>(&hErrRing), 16 * kErrRing),
+  // error slot {abs, rel, (arrived, published)} + one scratch slot for on-demand
+  // launches; the pinned ring the publishing CTA writes (smeb_err_arrive)
+  dErr = devAlloc<unsigned long long>(8, "allocate error accumulators");
+  dErrScratch = dErr + 4;
+  check(cudaMemsetAsync(dErr, 0, 64, stream), "clear error accumulators");
+  check(cudaHostAlloc(reinterpret_cast<void **>(&hErrRing), 32 * kErrRing,
+                      cudaHostAllocMapped | cudaHostAllocPortable),
         "allocate pinned error ring");
-  for (auto &e : errEvents) {
-    check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate");
+  std::memset(hErrRing, 0, 32 * kErrRing);
+  {
+    void *dev = nullptr;
+    check(cudaHostGetDevicePointer(&dev, hErrRing, 0),
+          "cudaHostGetDevicePointer(error ring)");
+    dErrRing = static_cast<unsigned long long *>(dev);
   }
+  usePdl = !envFlagOff("SMEB200_PDL");
   check(cudaMallocHost(reinterpret_cast<void **>(&hDt), sizeof(double)),
         "allocate pinned step size");
   dDt = devAlloc<double>(1, "allocate step size");
@@ -1412,12 +1444,32 @@ void Sim::connectSlabs() {
       std::memcpy(mine.memHandle[ci][b], &h, sizeof(h));
     }
   }
+  mine.fusedHalo = fusedHalo ? 1 : 0;
+  if (fusedHalo) {
+    dHalo = devAlloc<uint32_t>(16, "allocate halo flags");
+    check(cudaMemset(dHalo, 0, 16 * sizeof(uint32_t)), "clear halo flags");
+    cudaIpcMemHandle_t h{};
+    check(cudaIpcGetMemHandle(&h, dHalo), "cudaIpcGetMemHandle");
+    std::memcpy(mine.flagHandle, &h, sizeof(h));
+  }
   mine.published.store(1, std::memory_order_release);
   comm->barrier();
   for (int side = 0; side < 2; ++side) {
     const int nb = side == 0 ? rank - 1 : rank + 1;
     if (nb < 0 || nb >= nRanks) {
       continue;
+    }
+    if ((seg->slot[nb].fusedHalo != 0) != fusedHalo) {
+      throw Error("smeb200: neighbouring ranks disagree about the halo exchange "
+                  "path");
+    }
+    if (fusedHalo) {
+      cudaIpcMemHandle_t h{};
+      std::memcpy(&h, seg->slot[nb].flagHandle, sizeof(h));
+      void *ptr = nullptr;
+      check(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess),
+            "cudaIpcOpenMemHandle(halo flags)");
+      peerHalo[side] = static_cast<uint32_t *>(ptr);
     }
     for (std::size_t ci = 0; ci < comps.size(); ++ci) {
       auto &c = comps[ci];
@@ -1458,7 +1510,7 @@ void Sim::connectSlabs() {
   // halos are pushed on their own stream while the interior of the slab is
   // computed (SMEB200_HALO_OVERLAP=0: everything on the main stream)
   const char *ov = std::getenv("SMEB200_HALO_OVERLAP");
-  if (ov == nullptr || std::string(ov) != "0") {
+  if (!fusedHalo && (ov == nullptr || std::string(ov) != "0")) {
     int prLow = 0, prHigh = 0; // boundary CTAs are scheduled ahead of interior ones
     check(cudaDeviceGetStreamPriorityRange(&prLow, &prHigh), "stream priorities");
     check(cudaStreamCreateWithPriority(&haloStream, cudaStreamNonBlocking, prHigh),
@@ -1557,10 +1609,73 @@ void Sim::haloQuiesce() {
   if (!haloPending) {
     return;
   }
+  if (fusedHalo) {
+    // one thread waits for the neighbours' planes of the last stage
+    uint32_t mode = (rank > 0 ? 1u : 0u) | (rank + 1 < nRanks ? 2u : 0u);
+    uint32_t seq = haloSeq;
+    uint32_t *flags = dHalo;
+    void *params[] = {&flags, &mode, &seq};
+    check(DriverApi::get().LaunchKernel(kHaloQuiesce, 1, 1, 1, 32, 1, 1, 0, stream,
+                                        params, nullptr),
+          "launch halo wait kernel");
+    haloPending = false;
+    return;
+  }
+  if (haloStream == nullptr) {
+    haloPending = false;
+    return;
+  }
   check(cudaEventRecord(haloPushed, haloStream), "halo event");
   haloWait(stream);
   check(cudaStreamWaitEvent(stream, haloPushed, 0), "halo pushed wait");
   haloPending = false;
+}
+
+// a bounded in-kernel wait that ran out raised halo[4] (the stream is idle)
+void Sim::checkHaloError() {
+  if (!fusedHalo) {
+    return;
+  }
+  uint32_t flag = 0;
+  check(cudaMemcpy(&flag, dHalo + 4, sizeof(flag), cudaMemcpyDeviceToHost),
+        "read halo status");
+  if (flag != 0) {
+    check(cudaMemset(dHalo + 4, 0, sizeof(flag)), "clear halo status");
+    throw Error("smeb200: timed out waiting for the halo planes of the rank " +
+                std::string(flag == 1 ? "below" : "above"));
+  }
+}
+
+void Sim::abortSlabs() noexcept {
+  if (!comm) {
+    return;
+  }
+  try {
+    comm->abort();
+    if (!slabsConnected) {
+      return;
+    }
+    // the waits compare cyclically: a sequence number far ahead satisfies every
+    // wait the neighbours can still have queued
+    const uint32_t far = haloSeq + 0x40000000u;
+    if (fusedHalo) {
+      if (rank > 0 && peerHalo[0] != nullptr) {
+        cudaMemcpy(peerHalo[0] + 1, &far, sizeof(far), cudaMemcpyHostToDevice);
+      }
+      if (rank + 1 < nRanks && peerHalo[1] != nullptr) {
+        cudaMemcpy(peerHalo[1], &far, sizeof(far), cudaMemcpyHostToDevice);
+      }
+      cudaGetLastError();
+    } else {
+      if (rank > 0) {
+        __atomic_store_n(comm->haloFlag(rank - 1, 1), far, __ATOMIC_RELEASE);
+      }
+      if (rank + 1 < nRanks) {
+        __atomic_store_n(comm->haloFlag(rank + 1, 0), far, __ATOMIC_RELEASE);
+      }
+    }
+  } catch (...) {
+  }
 }
 
 Sim::~Sim() {
@@ -1581,7 +1696,9 @@ Sim::~Sim() {
   if (comm) {
     // nobody may still be pushing halos into this rank's buffers
     try {
-      comm->barrier();
+      if (!comm->aborted()) {
+        comm->barrier();
+      }
     } catch (...) {
     }
     for (auto &side : peerBuf) {
@@ -1593,9 +1710,20 @@ Sim::~Sim() {
         }
       }
     }
+    for (auto *ptr : peerHalo) {
+      if (ptr != nullptr) {
+        cudaIpcCloseMemHandle(ptr);
+      }
+    }
     if (flagsRegistered) {
       cudaHostUnregister(comm->flagPages());
     }
+  }
+  cudaFree(dHalo);
+  if (xferStream != nullptr) {
+    cudaStreamSynchronize(xferStream);
+    cudaStreamDestroy(xferStream);
+    cudaEventDestroy(downloadDone);
   }
   for (auto &c : comps) {
     for (void *b : c.stateAllocs) {
@@ -1613,18 +1741,16 @@ Sim::~Sim() {
     cudaFree(c.dDarr);
     cudaFree(c.dXdMax);
     cudaFree(c.dNsPartial);
-    cudaFreeHost(c.hostConc);
+    if (c.userMirror) {
+      cudaHostUnregister(c.hostConc);
+    } else {
+      cudaFreeHost(c.hostConc);
+    }
   }
   cudaFree(dFluxLen);
   cudaFree(dErr);
-  cudaFreeHost(hErr);
   cudaFreeHost(hErrRing);
   cudaFreeHost(hNs);
-  for (auto e : errEvents) {
-    if (e != nullptr) {
-      cudaEventDestroy(e);
-    }
-  }
   cudaFreeHost(hXdMax);
   cudaFreeHost(hDt);
   cudaFree(dDt);
@@ -1692,37 +1818,34 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
   }
   const bool fork = capturing && !forkStreams.empty();
   const bool overlapHalo = comm != nullptr && haloStream != nullptr;
-  std::vector<std::pair<std::size_t, StageArgsHost>> interior;
-  std::size_t forksUsed = 0;
-  if (fork) {
-    check(cudaEventRecord(forkEvent, stream), "fork event");
-  }
-  if (overlapHalo) {
-    // halo stream: the stage input is complete once the main stream got here
-    // and the neighbours' halos of the previous stage have arrived
-    check(cudaEventRecord(stageInputReady, stream), "stage input event");
-    check(cudaStreamWaitEvent(haloStream, stageInputReady, 0), "halo stream wait");
-    if (haloSeq > 0) {
-      haloWait(haloStream);
-      if (nsInSlabs) {
-        // the pre-pass of the spatial mean runs on the main stream and
-        // evaluates dc/dt of the boundary voxels too: it reads ghosts
-        haloWait(stream);
-      }
-    }
+  // pass 1 (host only): the arguments of every compartment's launches.  In a
+  // z-slab run with the halo stream a compartment is launched in parts: the owned
+  // boundary planes (lo, hi), the membrane voxels, the interior (mid).
+  struct Item {
+    std::size_t ci;
+    StageArgsHost a, lo, hi, mid;
+    bool hasLo{false}, hasHi{false}, hasMid{false};
+  };
+  std::vector<Item> items;
+  if (fusedHalo) {
+    ++haloSeq; // the planes this stage sends carry this number
   }
   for (std::size_t ci = 0; ci < comps.size(); ++ci) {
     auto &c = comps[ci];
     if (c.S == 0 || c.n == 0) {
       continue;
     }
-    StageArgsHost a{};
+    Item item;
+    item.ci = ci;
+    StageArgsHost &a = item.a;
+    a = StageArgsHost{};
     a.cin = c.buf[c.role[sd.cin]];
     a.cout = c.buf[c.role[sd.cout]];
     a.c0 = c.buf[c.role[CUR]];
     a.nn = c.dNn;
     a.runs = c.dRuns;
     a.err = dErr;
+    a.errHost = dErrRing;
     a.n = static_cast<uint32_t>(c.n - c.vGhostHi);
     a.v0 = c.vGhostLo;
     a.nx = c.nx;
@@ -1730,12 +1853,10 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     a.nz = c.nz;
     a.z_begin = c.zLoGhost;
     a.z_end = c.nz - c.zHiGhost;
-    tmapOverride = nullptr;
     if (c.haveOverride && stageIndex == 0) {
       // RK323 / RK435: the stage works on the relaxed copy, the pre-step state
       // c0 stays what doRKInit saved before the relaxation (pixelsim.cpp:166-171)
       a.cin = c.stageInOverride.p;
-      tmapOverride = &c.stageInOverride.t;
     }
     if (sd.s2mode == 2) {
       // s2 after stage 0 is exactly its input (0 + 1 * c): the relaxed copy if
@@ -1760,6 +1881,101 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     a.eps = epsilon;
     std::copy(c.D.begin(), c.D.end(), a.D);
     std::copy(params.begin(), params.end(), a.D + 3 * c.S);
+    a.nsAv = c.dNsAv;
+    a.nsPartial = c.dNsPartial;
+    a.darr = c.dDarr;
+    a.xdMax = c.dXdMax;
+    std::copy(h2, h2 + 3, a.h2);
+    if (fusedHalo) {
+      const int coutBuf = c.role[sd.cout];
+      a.haloMode = (rank > 0 ? 1u : 0u) | (rank + 1 < nRanks ? 2u : 0u);
+      a.halo = dHalo;
+      a.haloSeq = haloSeq;
+      if (rank > 0) {
+        a.peerLo = peerBuf[0][ci][coutBuf] + comm->segment()->slot[rank - 1].ghostHiOff[ci];
+        a.peerFlagLo = peerHalo[0] + 1;
+      }
+      if (rank + 1 < nRanks) {
+        a.peerHi = peerBuf[1][ci][coutBuf];
+        a.peerFlagHi = peerHalo[1];
+      }
+    }
+    if (overlapHalo) {
+      item.lo = item.hi = item.mid = a;
+      if (c.box) {
+        const uint32_t zb = a.z_begin, ze = a.z_end;
+        const uint32_t loEnd = rank > 0 ? std::min(zb + 1, ze) : zb;
+        const uint32_t hiBegin = rank + 1 < nRanks ? std::max(ze - 1, loEnd) : ze;
+        item.lo.z_end = loEnd;
+        item.hi.z_begin = hiBegin;
+        item.mid.z_begin = loEnd;
+        item.mid.z_end = hiBegin;
+      } else {
+        const uint32_t v0 = a.v0, v1 = a.n;
+        const uint32_t loEnd = rank > 0 ? v0 + c.vFirstPlane : v0;
+        const uint32_t hiBegin =
+            rank + 1 < nRanks ? std::max(v1 - c.vLastPlane, loEnd) : v1;
+        item.lo.n = loEnd;
+        item.hi.v0 = hiBegin;
+        item.mid.v0 = loEnd;
+        item.mid.n = hiBegin;
+      }
+      const auto nonEmpty = [&](const StageArgsHost &r) {
+        return c.box ? r.z_begin < r.z_end : r.v0 < r.n;
+      };
+      item.hasLo = nonEmpty(item.lo);
+      item.hasHi = nonEmpty(item.hi);
+      item.hasMid = nonEmpty(item.mid);
+    }
+    items.push_back(item);
+  }
+  // the CTAs that will report error norms in this stage: the one that completes
+  // the count publishes the step's norms (smeb_err_arrive)
+  errExpected = 0;
+  if (sd.final) {
+    for (const auto &it : items) {
+      const auto &k = comps[it.ci].kStage[stageIndex];
+      if (overlapHalo) {
+        errExpected += it.hasLo ? mainGrid(it.ci, it.lo, k.main) : 0u;
+        errExpected += it.hasHi ? mainGrid(it.ci, it.hi, k.main) : 0u;
+        errExpected += it.hasMid ? mainGrid(it.ci, it.mid, k.main) : 0u;
+      } else {
+        errExpected += mainGrid(it.ci, it.a, k.main);
+      }
+      errExpected += membGrid(it.ci, k.memb);
+    }
+    for (auto &it : items) {
+      it.a.errExpected = it.lo.errExpected = it.hi.errExpected =
+          it.mid.errExpected = errExpected;
+    }
+  }
+  std::vector<std::pair<std::size_t, StageArgsHost>> interior;
+  std::size_t forksUsed = 0;
+  if (fork) {
+    check(cudaEventRecord(forkEvent, stream), "fork event");
+  }
+  if (overlapHalo) {
+    // halo stream: the stage input is complete once the main stream got here
+    // and the neighbours' halos of the previous stage have arrived
+    check(cudaEventRecord(stageInputReady, stream), "stage input event");
+    check(cudaStreamWaitEvent(haloStream, stageInputReady, 0), "halo stream wait");
+    if (haloSeq > 0) {
+      haloWait(haloStream);
+      if (nsInSlabs) {
+        // the pre-pass of the spatial mean runs on the main stream and
+        // evaluates dc/dt of the boundary voxels too: it reads ghosts
+        haloWait(stream);
+      }
+    }
+  }
+  for (auto &item : items) {
+    const std::size_t ci = item.ci;
+    auto &c = comps[ci];
+    StageArgsHost &a = item.a;
+    tmapOverride = nullptr;
+    if (c.haveOverride && stageIndex == 0) {
+      tmapOverride = &c.stageInOverride.t;
+    }
     if (fork && forksUsed + 2 <= forkStreams.size()) {
       forkMain = forkStreams[forksUsed];
       // with a pre-pass the membrane kernels stay ordered with the main ones
@@ -1771,15 +1987,12 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
       }
       forksUsed += 2;
     }
-    a.nsAv = c.dNsAv;
-    a.nsPartial = c.dNsPartial;
-    a.darr = c.dDarr;
-    a.xdMax = c.dXdMax;
-    std::copy(h2, h2 + 3, a.h2);
     if (!c.nonSpatial.empty()) {
       // SimCompartment::spatiallyAverageDcdt (pixelsim_impl.cpp:150-163): the
       // averages need dc/dt of every voxel before any voxel can be updated
-      launchCompartment(ci, a, c.kSumNs, c.role[sd.cin], true);
+      StageArgsHost pre = a;
+      pre.errExpected = 0;
+      launchCompartment(ci, pre, c.kSumNs, c.role[sd.cin], true);
       if (overlapHalo) {
         // the boundary and membrane kernels on the halo stream use the mean too
         check(cudaEventRecord(stageInputReady, stream), "mean ready event");
@@ -1792,41 +2005,19 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
       // membrane kernels go to the high-priority halo stream, which pushes the
       // halos as soon as they are done; the interior runs beside them on the
       // main stream (below)
-      StageArgsHost lo = a, hi = a, mid = a;
-      if (c.box) {
-        const uint32_t zb = a.z_begin, ze = a.z_end;
-        const uint32_t loEnd = rank > 0 ? std::min(zb + 1, ze) : zb;
-        const uint32_t hiBegin = rank + 1 < nRanks ? std::max(ze - 1, loEnd) : ze;
-        lo.z_end = loEnd;
-        hi.z_begin = hiBegin;
-        mid.z_begin = loEnd;
-        mid.z_end = hiBegin;
-      } else {
-        const uint32_t v0 = a.v0, v1 = a.n;
-        const uint32_t loEnd = rank > 0 ? v0 + c.vFirstPlane : v0;
-        const uint32_t hiBegin =
-            rank + 1 < nRanks ? std::max(v1 - c.vLastPlane, loEnd) : v1;
-        lo.n = loEnd;
-        hi.v0 = hiBegin;
-        mid.v0 = loEnd;
-        mid.n = hiBegin;
-      }
-      const auto empty = [&](const StageArgsHost &r) {
-        return c.box ? r.z_begin >= r.z_end : r.v0 >= r.n;
-      };
       suppressTiming = true;
       forkMain = forkMemb = haloStream; // concurrent with the interior launch
-      if (!empty(lo)) {
-        launchCompartment(ci, lo, c.kStage[stageIndex], c.role[sd.cin], false, 1);
+      if (item.hasLo) {
+        launchCompartment(ci, item.lo, c.kStage[stageIndex], c.role[sd.cin], false, 1);
       }
-      if (!empty(hi)) {
-        launchCompartment(ci, hi, c.kStage[stageIndex], c.role[sd.cin], false, 1);
+      if (item.hasHi) {
+        launchCompartment(ci, item.hi, c.kStage[stageIndex], c.role[sd.cin], false, 1);
       }
       launchCompartment(ci, a, c.kStage[stageIndex], c.role[sd.cin], false, 2);
       forkMain = forkMemb = nullptr;
       suppressTiming = false;
-      if (!empty(mid)) {
-        interior.emplace_back(ci, mid);
+      if (item.hasMid) {
+        interior.emplace_back(ci, item.mid);
       }
     } else {
       launchCompartment(ci, a, c.kStage[stageIndex], c.role[sd.cin]);
@@ -1844,13 +2035,18 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     }
     if (last) {
       c.last = a;
+      c.last.errExpected = 0;
+      c.last.haloMode = 0;
       c.lastCinBuf = c.role[sd.cin];
       c.lastFlags = sd.flags();
       c.haveLast = true;
     }
   }
   membCinOverride.clear();
-  if (comm && !comps.empty()) {
+  if (fusedHalo) {
+    haloPending = true; // the stage kernels exchanged the planes themselves
+    ++haloExchanges;
+  } else if (comm && !comps.empty()) {
     const int coutBuf = comps[0].role[sd.cout];
     if (overlapHalo) {
       // the halos travel (and the neighbours' arrive) while the interior is
@@ -1870,6 +2066,10 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
       haloPush(coutBuf, stream);
       haloWait(stream);
     }
+  }
+  if (sd.final && errExpected > 0 && !capturing) {
+    ++errSeq; // this step's norms will appear under this number (replays of a
+              // captured step are counted by graphStep)
   }
 }
 
@@ -1909,11 +2109,19 @@ void Sim::solveZeroStorageConstraints(std::size_t stageIndex) {
   }
   auto launchHalf = [&](bool second, double dt) {
     std::vector<const double *> cins(comps.size(), nullptr);
+    uint32_t expected = 0; // CTAs that report residual / error norms
     for (std::size_t ci = 0; ci < comps.size(); ++ci) {
       const auto &c = comps[ci];
       // second half: the compartments with zero-storage species are at c1
       cins[ci] = second && !c.zeroStorage.empty() && c.n > 0 ? c.pool[0].p
                                                               : in[ci].p;
+      if (!c.zeroStorage.empty() && c.n > 0) {
+        StageArgsHost r{};
+        r.n = static_cast<uint32_t>(c.n);
+        r.z_end = c.nz;
+        const auto &k = second ? c.kRelaxB : c.kRelaxA;
+        expected += mainGrid(ci, r, k.main) + membGrid(ci, k.memb);
+      }
     }
     for (std::size_t ci = 0; ci < comps.size(); ++ci) {
       auto &c = comps[ci];
@@ -1927,6 +2135,8 @@ void Sim::solveZeroStorageConstraints(std::size_t stageIndex) {
       a.nn = c.dNn;
       a.runs = c.dRuns;
       a.err = dErr;
+      a.errHost = dErrRing;
+      a.errExpected = expected;
       a.n = static_cast<uint32_t>(c.n);
       a.v0 = 0;
       a.nx = c.nx;
@@ -1946,12 +2156,17 @@ void Sim::solveZeroStorageConstraints(std::size_t stageIndex) {
       membCinOverride = cins;
       tmapOverride = second ? &c.pool[0].t : &in[ci].t;
       if (!c.nonSpatial.empty()) {
-        launchCompartment(ci, a, c.kSumNs, 0, true);
+        StageArgsHost pre = a;
+        pre.errExpected = 0;
+        launchCompartment(ci, pre, c.kSumNs, 0, true);
       }
       launchCompartment(ci, a, second ? c.kRelaxB : c.kRelaxA, 0);
     }
     membCinOverride.clear();
     tmapOverride = nullptr;
+    if (expected > 0) {
+      ++errSeq;
+    }
   };
   relaxing = true;
   try {
@@ -2028,8 +2243,6 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     check(cudaEventRecord(timerEvents[timerUsed].first, stream),
           "cudaEventRecord");
   }
-  const unsigned persistent =
-      c.geom == Geom::TILE || !doMain ? 0u : persistentGrid(k.main);
   if (!doMain) {
     // membrane kernel only
   } else if (c.geom == Geom::TILE) {
@@ -2040,22 +2253,13 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     }
     const CUtensorMap *tm = tmapOverride != nullptr ? tmapOverride : &c.tmap[cinBuf];
     void *params[] = {&a, const_cast<CUtensorMap *>(tm), &chunk};
-    check(drv.LaunchKernel(k.main, c.tile.grid[0], c.tile.grid[1],
-                           c.tile.m3 ? gridZ : c.tile.grid[2], BLOCK, 1, 1,
-                           c.tile.dynSmem, sMain, params, nullptr),
-          "launch tile stage kernel");
+    launchKernel(k.main, c.tile.grid[0], c.tile.grid[1],
+                 c.tile.m3 ? gridZ : c.tile.grid[2], c.tile.dynSmem, sMain, params);
     nsBlocks = c.tile.grid[0] * c.tile.grid[1] * c.tile.grid[2];
   } else {
-    uint64_t work = a.n > a.v0 ? a.n - a.v0 : 0;
-    if (c.geom == Geom::BOX) {
-      work = static_cast<uint64_t>(a.z_end - a.z_begin) * c.nx * c.ny;
-    }
-    const unsigned grid = static_cast<unsigned>(std::max<uint64_t>(
-        1, std::min<uint64_t>((work + BLOCK - 1) / BLOCK, persistent)));
+    const unsigned grid = mainGrid(ci, a, k.main);
     void *params[] = {&a};
-    check(drv.LaunchKernel(k.main, grid, 1, 1, BLOCK, 1, 1, 0, sMain, params,
-                           nullptr),
-          "launch stage kernel");
+    launchKernel(k.main, grid, 1, 1, 0, sMain, params);
     nsBlocks = grid;
   }
   if (doMain) {
@@ -2084,17 +2288,14 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
       blob[4 + j] = reinterpret_cast<unsigned long long>(pj);
     }
     blob[4 + comps.size()] = static_cast<unsigned long long>(c.nMvox);
-    const unsigned mgrid =
-        std::min((c.nMvox + BLOCK - 1) / BLOCK, persistentGrid(k.memb));
+    const unsigned mgrid = membGrid(ci, k.memb);
     StageArgsHost am = a;
     if (nsPrepass) { // the membrane voxels' partial sums follow the main ones
       am.nsPartial = a.nsPartial + nsBlocks * c.nonSpatial.size();
       nsBlocks += mgrid;
     }
     void *mparams[] = {&am, blob.data()};
-    check(drv.LaunchKernel(k.memb, mgrid, 1, 1, BLOCK, 1, 1, 0, sMemb,
-                           mparams, nullptr),
-          "launch membrane stage kernel");
+    launchKernel(k.memb, mgrid, 1, 1, 0, sMemb, mparams);
     ++launchCount;
   }
   if (nsPrepass) {
@@ -2131,6 +2332,61 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
             "upload non-spatial averages");
     }
   }
+}
+
+// grid of the main kernel of one launch: the tiles of the launch's planes, or
+// one resident wave at most for the grid-stride kernels
+unsigned Sim::mainGrid(std::size_t ci, const StageArgsHost &a, CUfunction f) {
+  const auto &c = comps[ci];
+  if (f == nullptr) {
+    return 0;
+  }
+  if (c.geom == Geom::TILE) {
+    unsigned gridZ = c.tile.grid[2];
+    if (c.tile.m3) {
+      gridZ = std::max(1u, (a.z_end - a.z_begin + c.tile.chunk - 1) / c.tile.chunk);
+    }
+    return c.tile.grid[0] * c.tile.grid[1] * gridZ;
+  }
+  uint64_t work = a.n > a.v0 ? a.n - a.v0 : 0;
+  if (c.geom == Geom::BOX) {
+    work = static_cast<uint64_t>(a.z_end - a.z_begin) * c.nx * c.ny;
+  }
+  return static_cast<unsigned>(std::max<uint64_t>(
+      1, std::min<uint64_t>((work + BLOCK - 1) / BLOCK, persistentGrid(f))));
+}
+
+unsigned Sim::membGrid(std::size_t ci, CUfunction f) {
+  const auto &c = comps[ci];
+  if (c.nMvox == 0 || f == nullptr) {
+    return 0;
+  }
+  return std::min((c.nMvox + BLOCK - 1) / BLOCK, persistentGrid(f));
+}
+
+void Sim::launchKernel(CUfunction f, unsigned gx, unsigned gy, unsigned gz,
+                       unsigned smem, cudaStream_t s, void **params) {
+  const auto &drv = DriverApi::get();
+  if (!usePdl || capturing) {
+    check(drv.LaunchKernel(f, gx, gy, gz, BLOCK, 1, 1, smem, s, params, nullptr),
+          "launch stage kernel");
+    return;
+  }
+  CUlaunchAttribute attr{};
+  attr.id = CU_LAUNCH_ATTRIBUTE_PROGRAMMATIC_STREAM_SERIALIZATION;
+  attr.value.programmaticStreamSerializationAllowed = 1;
+  CUlaunchConfig cfg{};
+  cfg.gridDimX = gx;
+  cfg.gridDimY = gy;
+  cfg.gridDimZ = gz;
+  cfg.blockDimX = BLOCK;
+  cfg.blockDimY = 1;
+  cfg.blockDimZ = 1;
+  cfg.sharedMemBytes = smem;
+  cfg.hStream = s;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
+  check(drv.LaunchKernelEx(&cfg, f, params, nullptr), "launch stage kernel");
 }
 
 // Grid-stride kernels are launched as exactly one wave of resident CTAs: with
@@ -2216,11 +2472,6 @@ void Sim::graphStep(double dt) {
                             stream),
             "capture step size upload");
       launchAllStages(dt);
-      if (integrator != SMEB200_RK101) {
-        check(cudaMemcpyAsync(hErr, dErr, 16, cudaMemcpyDeviceToHost, stream),
-              "capture error norm download");
-        check(cudaMemsetAsync(dErr, 0, 16, stream), "capture error norm clear");
-      }
     } catch (...) {
       capturing = false;
       cudaStreamEndCapture(stream, &graph);
@@ -2251,7 +2502,9 @@ void Sim::graphStep(double dt) {
   }
   check(cudaGraphLaunch(it->second.exec, stream), "cudaGraphLaunch");
   launchCount += it->second.launches;
-  errCopyInGraph = integrator != SMEB200_RK101;
+  if (integrator != SMEB200_RK101) {
+    ++errSeq; // the replayed step publishes its norms like a launched one
+  }
   for (std::size_t ci = 0; ci < comps.size(); ++ci) {
     auto &c = comps[ci];
     if (c.S == 0 || c.n == 0) {
@@ -2271,6 +2524,7 @@ void Sim::doStep(double dt) {
     launchAllStages(dt);
   }
   ++timingStep;
+  ++stateVersion;
   for (auto &c : comps) {
     c.dcdtStale = true;
     c.lowerStale = true;
@@ -2290,17 +2544,64 @@ void Sim::rotateAfterAccept() {
   }
 }
 
-void Sim::readError(double &eabs, double &erel) {
-  if (errCopyInGraph) {
-    errCopyInGraph = false; // the replayed graph ends with these two nodes
-  } else {
-    check(cudaMemcpyAsync(hErr, dErr, 16, cudaMemcpyDeviceToHost, stream),
-          "download error norms");
-    check(cudaMemsetAsync(dErr, 0, 16, stream), "clear error accumulators");
+// Waits until the step with sequence number `seq` has published its error norms
+// in the pinned ring.  A kernel that failed never publishes: the streams are
+// looked at every few hundred polls.
+void Sim::waitError(uint32_t seq, double v[2]) {
+  volatile unsigned long long *h = hErrRing + 4 * (seq % kErrRing);
+  const auto t0 = std::chrono::steady_clock::now();
+  for (unsigned spins = 1;; ++spins) {
+    if (static_cast<uint32_t>(h[2]) == seq) {
+      break;
+    }
+    if ((spins & 0x3ffu) == 0) {
+      bool idle = true;
+      for (cudaStream_t st : {stream, haloStream}) {
+        if (st == nullptr) {
+          continue;
+        }
+        const cudaError_t e = cudaStreamQuery(st);
+        if (e == cudaErrorNotReady) {
+          idle = false;
+        } else {
+          check(e, "a stage kernel failed");
+        }
+      }
+      if (idle && static_cast<uint32_t>(h[2]) != seq) {
+        errDesync = true;
+        throw Error("smeb200: internal error (the error norms of a step were "
+                    "not published)");
+      }
+      if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0)
+              .count() > 300.0) {
+        errDesync = true;
+        throw Error("smeb200: timed out waiting for the error norms of a step");
+      }
+    }
   }
+  std::atomic_thread_fence(std::memory_order_acquire);
+  unsigned long long bits[2] = {h[0], h[1]};
+  std::memcpy(v, bits, 16);
+}
+
+// after a failed launch sequence: drain the device, zero the slot (norms, CTA
+// count, published count) and the ring, start numbering from zero again
+void Sim::resyncErrorSeq() {
   check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+  if (haloStream != nullptr) {
+    check(cudaStreamSynchronize(haloStream), "cudaStreamSynchronize");
+  }
+  check(cudaMemsetAsync(dErr, 0, 64, stream), "clear error accumulators");
+  check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+  std::memset(hErrRing, 0, 32 * kErrRing);
+  errSeq = 0;
+  errHead = errTail = 0;
+  errDesync = false;
+}
+
+void Sim::readError(double &eabs, double &erel) {
   double v[2];
-  std::memcpy(v, hErr, 16);
+  waitError(errSeq, v);
   if (allreduceMax != nullptr) {
     allreduceMax(v, 2, allreduceUser);
   } else if (comm) {
@@ -2400,16 +2701,10 @@ double Sim::doRK101(double dt) {
   return dt;
 }
 
-// The error norms of a step, queued behind it: 16 bytes into the next ring slot
-// and an event; nobody waits here.
+// The error norms of the step just launched will be published under errSeq;
+// nothing is queued behind the step and nobody waits here.
 void Sim::enqueueErrorRead(double dt, double dtMax) {
-  const std::size_t slot = errTail % kErrRing;
-  check(cudaMemcpyAsync(hErrRing + 2 * slot, dErr, 16, cudaMemcpyDeviceToHost,
-                        stream),
-        "download error norms");
-  check(cudaMemsetAsync(dErr, 0, 16, stream), "clear error accumulators");
-  check(cudaEventRecord(errEvents[slot], stream), "cudaEventRecord");
-  errPending[slot] = {dt, dtMax};
+  errPending[errTail % kErrRing] = {dt, dtMax, errSeq};
   ++errTail;
 }
 
@@ -2425,26 +2720,21 @@ bool Sim::drainErrors(std::size_t keep) {
                                                         : 1.0 / 2.0;
   while (errTail - errHead > keep) {
     const std::size_t slot = errHead % kErrRing;
-    check(cudaEventSynchronize(errEvents[slot]), "cudaEventSynchronize");
     double v[2];
-    std::memcpy(v, hErrRing + 2 * slot, 16);
+    waitError(errPending[slot].seq, v);
     ++errHead;
     if (allreduceMax != nullptr) {
       allreduceMax(v, 2, allreduceUser);
     } else if (comm) {
       comm->allreduceMax(v, 2);
     }
-    const auto [dt, dtMax] = errPending[slot];
+    const double dt = errPending[slot].dt, dtMax = errPending[slot].dtMax;
     double errFactor = std::min(errMaxAbs / v[0], errMaxRel / v[1]);
     errFactor = std::pow(errFactor, errPower);
     const double next = std::min(0.95 * dt * errFactor, dtMax);
     if (next != dtMax || v[0] > errMaxAbs || v[1] > errMaxRel) {
-      // keep the ranks of a decomposed run in step: everybody reads every slot
-      while (errTail > errHead) {
-        check(cudaEventSynchronize(errEvents[errHead % kErrRing]),
-              "cudaEventSynchronize");
-        ++errHead;
-      }
+      // the steps launched behind the failed one are void
+      errHead = errTail;
       check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
       nextTimestep = next;
       std::string problemSpecies{"unknown"};
@@ -2520,13 +2810,21 @@ std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
       check(cudaEventCreate(&runEv0), "cudaEventCreate");
       check(cudaEventCreate(&runEv1), "cudaEventCreate");
     }
+    if (comm && slabsConnected) {
+      // no rank sends halos of a new run before every rank has left the reads
+      // of the last one (getters and on-demand kernels read ghost planes)
+      comm->barrier();
+    }
+    awaitDownloadOnStream();
     check(cudaEventRecord(runEv0, stream), "cudaEventRecord");
     const auto t0 = std::chrono::steady_clock::now();
     double tNow = 0;
     discardedSteps = 0;
     constexpr double relativeTolerance = 1e-12;
-    errHead = errTail; // nothing is in flight between runs (a run that threw may
-                       // have left slots behind: they are void)
+    errHead = errTail; // nothing is in flight between runs
+    if (errDesync) {
+      resyncErrorSeq();
+    }
     laggedError = integrator != SMEB200_RK101 && !useGraphs && !anyZeroStorage &&
                   errMaxAbs == std::numeric_limits<double>::max() &&
                   errMaxRel == std::numeric_limits<double>::max() &&
@@ -2563,10 +2861,12 @@ std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
       if (stopCb != nullptr && stopCb(user) != 0) {
         stopRequested.store(true);
       }
-      if (comm && slabsConnected && (timeoutMs >= 0.0 || stopCb != nullptr)) {
-        // z-slabs: deadline and callback are evaluated per rank, the decision
-        // must be common (every rank gets here after every step, with the same
-        // arguments): one more value through the shared-memory segment
+      if (comm && slabsConnected) {
+        // z-slabs: deadline, callback and setStopRequested (another thread, one
+        // rank) are per-rank events, the decision must be common — a rank that
+        // stops alone leaves its neighbours waiting for halos that never come.
+        // Every rank gets here after every step: one value through the
+        // shared-memory segment
         double stop = stopRequested.load() ? 1.0 : 0.0;
         comm->allreduceMax(&stop, 1);
         if (stop > 0.0) {
@@ -2590,8 +2890,14 @@ std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
     float ms = 0;
     check(cudaEventElapsedTime(&ms, runEv0, runEv1), "cudaEventElapsedTime");
     lastRunMs = ms;
+    checkHaloError();
+    if (asyncDownload && steps > 0) {
+      startDownload();
+    }
   } catch (const std::exception &e) {
     errorMessage = e.what();
+    errDesync = true; // launches of an unfinished step may be missing
+    abortSlabs();     // the other ranks must not wait for this one
   }
   return steps;
 }
@@ -2610,9 +2916,6 @@ double Sim::benchSteps(double dt, std::size_t nSteps) {
     for (std::size_t i = 0; i < nSteps; ++i) {
       doStep(integrator == SMEB200_RK101 ? std::min(dt, maxStableTimestep)
                                          : dt);
-      if (integrator != SMEB200_RK101) {
-        check(cudaMemsetAsync(dErr, 0, 16, stream), "clear error accumulators");
-      }
       rotateAfterAccept();
     }
     haloQuiesce();
@@ -2640,6 +2943,9 @@ const double *Sim::getConcentrations(std::size_t comp, std::size_t *n) {
   if (n != nullptr) {
     *n = nv;
   }
+  if (c.downloadPending) {
+    finishDownload(); // run() started this copy on the transfer stream
+  }
   if (c.hostStale && nv > 0 && !ctorFailed) {
     bindDevice();
     check(cudaMemcpyAsync(c.hostConc, c.buf[c.role[CUR]], nv * sizeof(double),
@@ -2649,6 +2955,85 @@ const double *Sim::getConcentrations(std::size_t comp, std::size_t *n) {
     c.hostStale = false;
   }
   return c.hostConc;
+}
+
+void Sim::finishDownload() {
+  check(cudaEventSynchronize(downloadDone), "download concentrations");
+  for (auto &o : comps) {
+    if (o.downloadPending) {
+      o.downloadPending = false;
+      // the mirror is current unless steps were taken since the copy started
+      o.hostStale = o.hostStale && downloadVersion != stateVersion;
+    }
+  }
+}
+
+// the state of every compartment starts its way to the host mirrors; the compute
+// stream is idle (run() has just synchronised it)
+void Sim::startDownload() {
+  if (xferStream == nullptr) {
+    check(cudaStreamCreateWithFlags(&xferStream, cudaStreamNonBlocking),
+          "Failed to create the transfer stream");
+    check(cudaEventCreateWithFlags(&downloadDone, cudaEventDisableTiming),
+          "cudaEventCreate");
+  }
+  bool any = false;
+  for (auto &c : comps) {
+    const std::size_t nv = c.n * c.S;
+    if (nv == 0 || !c.hostStale) {
+      continue;
+    }
+    check(cudaMemcpyAsync(c.hostConc, c.buf[c.role[CUR]], nv * sizeof(double),
+                          cudaMemcpyDeviceToHost, xferStream),
+          "download concentrations");
+    c.downloadPending = true;
+    any = true;
+  }
+  if (any) {
+    check(cudaEventRecord(downloadDone, xferStream), "cudaEventRecord");
+    downloadVersion = stateVersion;
+  }
+}
+
+// a download still in flight reads the current state buffer: whatever is queued
+// next on the compute stream (a new run, an upload) starts after it
+void Sim::awaitDownloadOnStream() {
+  bool pending = false;
+  for (const auto &c : comps) {
+    pending = pending || c.downloadPending;
+  }
+  if (pending) {
+    check(cudaStreamWaitEvent(stream, downloadDone, 0), "download wait");
+  }
+}
+
+void Sim::setHostMirror(std::size_t comp, double *buffer, std::size_t n) {
+  if (comp >= comps.size()) {
+    throw Error("compartment index out of range");
+  }
+  auto &c = comps[comp];
+  if (n != c.n * c.S || (buffer == nullptr && n > 0)) {
+    throw Error("setHostMirror: wrong number of values");
+  }
+  if (ctorFailed || n == 0) {
+    return;
+  }
+  bindDevice();
+  if (c.downloadPending) {
+    finishDownload();
+  }
+  check(cudaHostRegister(buffer, n * sizeof(double), cudaHostRegisterPortable),
+        "cudaHostRegister(host mirror)");
+  if (!c.hostStale) {
+    std::memcpy(buffer, c.hostConc, n * sizeof(double));
+  }
+  if (c.userMirror) {
+    cudaHostUnregister(c.hostConc);
+  } else {
+    cudaFreeHost(c.hostConc);
+  }
+  c.hostConc = buffer;
+  c.userMirror = true;
 }
 
 void Sim::setConcentrations(std::size_t comp, const double *data,
@@ -2664,6 +3049,10 @@ void Sim::setConcentrations(std::size_t comp, const double *data,
     return;
   }
   bindDevice();
+  if (c.downloadPending) { // the mirror is the destination of a copy in flight
+    finishDownload();
+  }
+  ++stateVersion;
   // data may be the pinned mirror itself (filled in place by the caller):
   // then the upload is a single pinned H2D copy
   if (data != c.hostConc) {
@@ -2686,6 +3075,7 @@ void Sim::runOnDemand(std::size_t ci, uint32_t flags, double *out) {
   a.cout = out;
   a.s2out = nullptr;
   a.err = dErrScratch;
+  a.errExpected = 0; // the norms of an on-demand launch go nowhere
   const bool timing = kernelTiming;
   kernelTiming = false;
   launchCompartment(ci, a, k, c.lastCinBuf);

@@ -25,7 +25,7 @@ constexpr uint32_t F_USE_C0 = 1u, F_USE_S2 = 2u, F_USE_S2IN = 4u,
                    F_WRITE_S2 = 8u, F_FINAL = 16u, F_LOWER_IS_CIN = 32u,
                    F_CLAMP_OUT = 64u, F_GENERIC = 128u, F_OUT_DCDT = 256u,
                    F_OUT_LOWER = 512u, F_OUT_CNEW = 1024u, F_SUM_NS = 2048u,
-                   F_RELAX_A = 4096u, F_RELAX_B = 8192u;
+                   F_RELAX_A = 4096u, F_RELAX_B = 8192u, F_HALO = 16384u;
 
 // host mirror of the device-side SmebStageArgs<S> (device_kernels.cuh); the
 // D[3*S] table is the tail.
@@ -38,6 +38,7 @@ struct StageArgsHost {
   const uint32_t *nn;
   const int *runs;
   unsigned long long *err;
+  unsigned long long *errHost;
   const double *nsAv;
   double *nsPartial;
   const double *darr;
@@ -47,6 +48,15 @@ struct StageArgsHost {
   uint32_t v0;
   uint32_t nx, ny, nz;
   uint32_t z_begin, z_end;
+  uint32_t errExpected;
+  uint32_t haloMode;
+  double *peerLo;
+  double *peerHi;
+  uint32_t *halo;
+  uint32_t *peerFlagLo;
+  uint32_t *peerFlagHi;
+  uint32_t haloSeq;
+  uint32_t pad0_;
   double g1, g2, g3, bdt, delta;
   double beta;
   const double *dtp;
@@ -153,8 +163,10 @@ struct CompartmentState {
   MembEntryHost *dEnt{nullptr};
   std::vector<StageKernels> kStage; // per plan stage
   // host mirrors
-  double *hostConc{nullptr}; // pinned
+  double *hostConc{nullptr}; // pinned; owned unless userMirror
+  bool userMirror{false};    // hostConc is the caller's buffer, page-locked here
   bool hostStale{true};
+  bool downloadPending{false}; // a D2H of the state is in flight (xferStream)
   std::vector<double> hostDcdt;
   std::vector<double> hostLower;
   bool dcdtStale{true}, lowerStale{true};
@@ -185,6 +197,13 @@ public:
   const double *getDcdt(std::size_t comp, std::size_t *n);
   double getLowerOrder(std::size_t comp, std::size_t species, std::size_t pixel);
   void setConcentrations(std::size_t comp, const double *data, std::size_t n);
+  // asynchronous state download: run() ends by queueing the D2H of every
+  // compartment's state on a transfer stream; getConcentrations waits for it
+  // (cudapixelsim.cpp:1486-1516,1657,1665-1669)
+  void setAsyncDownload(bool enable) { asyncDownload = enable; }
+  // the caller's buffer becomes the host mirror of a compartment (page-locked by
+  // the library): getConcentrations returns it, no second copy on the caller's side
+  void setHostMirror(std::size_t comp, double *buffer, std::size_t n);
   void getAvgMinMax(std::size_t comp, double *out, std::size_t nOut);
   const double *getSpeciesDecimated(std::size_t comp, std::size_t species,
                                     const uint32_t stride[3], std::size_t dims[3]);
@@ -229,6 +248,16 @@ public:
     return c.box ? 0 : (c.dRuns != nullptr ? 4 : 24);
   }
   std::size_t neighbourRuns(std::size_t comp) const { return comps.at(comp).nRuns; }
+  // planes of the dominant (box) compartment the timed launch covers: all owned
+  // planes, or the slab interior when the boundary planes are launched apart
+  std::size_t timedLaunchPlanes() const {
+    const auto &c = comps.at(dominantComp);
+    std::size_t owned = c.nz - c.zLoGhost - c.zHiGhost;
+    if (comm && haloStream != nullptr && !fusedHalo) {
+      owned -= std::min<std::size_t>(owned, c.zLoGhost + c.zHiGhost);
+    }
+    return owned;
+  }
   std::size_t concentrationPadding() const {
     std::size_t pad = 0;
     for (const auto &c : comps) {
@@ -279,7 +308,6 @@ private:
   std::map<uint32_t, StepGraph> stepGraphs;
   bool useGraphs{false};
   bool capturing{false};
-  bool errCopyInGraph{false}; // the replayed step already queued the download
   double *hDt{nullptr};       // pinned
   double *dDt{nullptr};
   double graphDt{-1.0};
@@ -293,22 +321,40 @@ private:
   void launchCompartment(std::size_t ci, StageArgsHost &a,
                          const StageKernels &k, int cinBuf,
                          bool nsPrepass = false, unsigned parts = 3);
+  // grid of the main / membrane kernel of one launch (host-side, no side effects)
+  unsigned mainGrid(std::size_t ci, const StageArgsHost &a, CUfunction f);
+  unsigned membGrid(std::size_t ci, CUfunction f);
+  // kernel launch with the programmatic-stream-serialization attribute: the
+  // kernel may become resident while its predecessor in the stream drains (the
+  // stage kernels wait with griddepcontrol.wait before touching memory)
+  void launchKernel(CUfunction f, unsigned gx, unsigned gy, unsigned gz,
+                    unsigned smem, cudaStream_t s, void **params);
+  bool usePdl{true};
   void rotateAfterAccept();
   void readError(double &eabs, double &erel);
   // unbounded tolerances (maxErr = {DBL_MAX, DBL_MAX}, the reference benchmark's
   // fixed-step configuration): the controller's decision does not depend on a
   // finite error norm, so the norms are checked kErrLag steps late instead of
   // stalling the stream after every step
-  static constexpr std::size_t kErrLag = 2, kErrRing = 4;
+  static constexpr std::size_t kErrLag = 2, kErrRing = 8; // SMEB_ERR_RING
   struct PendingError {
     double dt, dtMax;
+    uint32_t seq;
   };
   // z-slabs with non-spatial species: the spatial mean is summed over the ranks
   bool nsInSlabs{false};
   double *hNs{nullptr}; // pinned, 64 doubles
   bool laggedError{false};
-  unsigned long long *hErrRing{nullptr}; // pinned, 2 x kErrRing
-  cudaEvent_t errEvents[kErrRing]{};
+  // Error norms of a step: the last CTA of the step's final-stage kernels writes
+  // {abs, rel, sequence number} into this pinned, device-mapped ring
+  // (device_kernels.cuh: smeb_err_arrive); nothing is queued behind the kernels
+  unsigned long long *hErrRing{nullptr}; // 4 x kErrRing
+  unsigned long long *dErrRing{nullptr}; // device address of hErrRing
+  uint32_t errSeq{0};      // sequence number of the last publishing step launched
+  bool errDesync{false};   // a failed launch sequence left the device counter behind
+  uint32_t errExpected{0}; // CTAs of the error-norm launches of the current step
+  void waitError(uint32_t seq, double v[2]);
+  void resyncErrorSeq();
   PendingError errPending[kErrRing]{};
   std::size_t errHead{0}, errTail{0}; // slots [errHead, errTail) are in flight
   void enqueueErrorRead(double dt, double dtMax);
@@ -327,6 +373,21 @@ private:
   void syncMaxStableTimestep();
   bool slabsConnected{false};
   bool haloPending{false};
+  // halo exchange inside the tile kernel (all compartments box / TMA tile path):
+  // own flag words in device memory, the neighbours' through CUDA IPC
+  bool fusedHalo{false};
+  uint32_t *dHalo{nullptr};
+  uint32_t *peerHalo[2]{nullptr, nullptr};
+  CUfunction kHaloQuiesce{nullptr};
+  void checkHaloError();
+  // this rank gives up: the other ranks' host waits throw and their device-side
+  // halo waits are released
+  void abortSlabs() noexcept;
+  // template flags of a plan stage's kernels (on-demand variants never carry
+  // F_HALO)
+  uint32_t stageFlags(const StageDesc &sd) const {
+    return sd.flags() | (fusedHalo ? F_HALO : 0u);
+  }
   cudaStream_t haloStream{nullptr};
   cudaEvent_t stageInputReady{nullptr}, haloPushed{nullptr}, boundaryDone{nullptr};
   bool suppressTiming{false};
@@ -357,6 +418,13 @@ private:
   CUdeviceptr flagBaseDev{0};
   uint32_t haloSeq{0};
 
+  bool asyncDownload{false};
+  cudaStream_t xferStream{nullptr};
+  cudaEvent_t downloadDone{nullptr};
+  uint64_t stateVersion{0}, downloadVersion{0}; // steps taken / state in flight
+  void finishDownload();     // wait for the copy in flight
+  void startDownload();      // end of run()
+  void awaitDownloadOnStream(); // before anything overwrites a state buffer
   int device{0};
   cudaStream_t stream{nullptr};
   Module mainModule;
@@ -371,7 +439,6 @@ private:
   uint32_t nMembranes{0};
   unsigned long long *dErr{nullptr};
   unsigned long long *dErrScratch{nullptr};
-  unsigned long long *hErr{nullptr}; // pinned
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timerEvents;
   std::size_t timerUsed{0};
   int imageNx{0}, imageNy{0}, imageNz{0};

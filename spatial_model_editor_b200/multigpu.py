@@ -43,10 +43,18 @@ def ghost_range(nz: int, rank: int, world: int) -> Tuple[int, int, int, int]:
     return z0 - lo, z1 + hi, lo, hi
 
 
+_comm_generation = 0
+
+
 def default_comm_name(tag: str = "") -> str:
-    """a name all ranks of one torchrun job agree on without communicating"""
+    """a name all ranks of one torchrun job agree on without communicating: the
+    job's identity plus a counter of the communicators this process has named (all
+    ranks create their decomposed simulators in the same order), so back-to-back
+    simulators never meet on one segment"""
+    global _comm_generation
+    _comm_generation += 1
     job = os.environ.get("TORCHELASTIC_RUN_ID", "") + os.environ.get("MASTER_PORT", "")
-    return f"smeb200_{os.getuid()}_{job}_{tag}"
+    return f"smeb200_{os.getuid()}_{job}_{tag}_{_comm_generation}"
 
 
 def list_slab(voxels: np.ndarray, nz: int, rank: int, world: int
@@ -185,6 +193,10 @@ class SlabPixelSim(PixelSim):
     def haloExchanges(self) -> int:
         return int(self._lib.smeb200_halo_exchanges(self._h))
 
+    def timedLaunchPlanes(self) -> int:
+        """planes of the largest compartment the timed stage launch covers"""
+        return int(self._lib.smeb200_timed_launch_planes(self._h))
+
 
 class Comm:
     """the node-local communicator on its own (CPU-usable; tests)"""
@@ -216,6 +228,10 @@ class Comm:
     def barrier(self) -> None:
         if self._lib.smeb200_comm_barrier(self._h) != 0:
             raise RuntimeError("smeb200_comm_barrier failed")
+
+    def abort(self) -> None:
+        """this rank gives up: every wait of the other ranks raises from now on"""
+        self._lib.smeb200_comm_abort(self._h)
 
     def close(self) -> None:
         if self._h:

@@ -78,11 +78,16 @@ def _bind(lib, prefix: str):
     fn("dominant_kernel", C.c_char_p, [vp], optional=True)
     fn("set_allreduce_max", None, [vp, _ALLREDUCE_CB, vp], optional=True)
     fn("halo_exchanges", C.c_uint64, [vp], optional=True)
+    fn("timed_launch_planes", C.c_size_t, [vp], optional=True)
     fn("set_params", C.c_int, [vp, C.POINTER(C.c_double), C.c_size_t], optional=True)
+    fn("set_async_download", None, [vp, C.c_int], optional=True)
+    fn("set_host_mirror", C.c_int, [vp, C.c_size_t, C.POINTER(C.c_double), C.c_size_t],
+       optional=True)
     fn("comm_create", C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(vp)], optional=True)
     fn("comm_allreduce_max", C.c_int, [vp, C.POINTER(C.c_double), C.c_int], optional=True)
     fn("comm_allreduce_sum", C.c_int, [vp, C.POINTER(C.c_double), C.c_int], optional=True)
     fn("comm_barrier", C.c_int, [vp], optional=True)
+    fn("comm_abort", None, [vp], optional=True)
     fn("comm_destroy", None, [vp], optional=True)
     # oracle-only
     fn("set_threads", None, [vp, C.c_int], optional=True)
@@ -295,6 +300,23 @@ class PixelSim(CSim):
             return np.zeros((0,), dtype=np.float64)
         a = np.ctypeslib.as_array(data, shape=(n,)).copy()
         return a.reshape(mz, mx, my) if (my > 1 or mz > 1) else a
+
+    def setAsyncDownload(self, enable: bool) -> None:
+        """run() ends by starting the D2H of the state on a transfer stream;
+        getConcentrations waits for it (cudapixelsim.cpp:1486-1516)"""
+        self._f("set_async_download")(self._h, 1 if enable else 0)
+
+    def setHostMirror(self, compartmentIndex: int, buffer: np.ndarray) -> None:
+        """``buffer`` (float64, C-contiguous, [N, S]) becomes the host mirror that
+        getConcentrations returns; it must outlive the simulator"""
+        assert buffer.dtype == np.float64 and buffer.flags.c_contiguous
+        rc = self._f("set_host_mirror")(self._h, compartmentIndex,
+                                        buffer.ctypes.data_as(C.POINTER(C.c_double)),
+                                        buffer.size)
+        if rc != 0:
+            raise RuntimeError(self.errorMessage())
+        self._mirrors = getattr(self, "_mirrors", {})
+        self._mirrors[compartmentIndex] = buffer
 
     def neighbourBytesPerVoxel(self, compartmentIndex: int) -> int:
         """0 (box), 4 (run-compressed neighbour codes) or 24 (plain table)"""

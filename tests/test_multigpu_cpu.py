@@ -206,3 +206,62 @@ def test_communicator_allreduce_max_matches_gloo(world):
     for pr in procs:
         pr.join(timeout=60)
     assert sorted(results) == [(r, True) for r in range(world)]
+
+
+def _worker_robust(rank, world, name, q):
+    """reductions of more than 4 values, a NaN on one rank only,
+    back-to-back communicators on ONE name, and a rank that gives up"""
+    sys.path.insert(0, ROOT)
+    try:
+        ok = True
+        for generation in range(3):  # same name three times in a row
+            comm = MG.Comm(name, rank, world)
+            v = np.arange(11, dtype=np.float64) * (1.0 if rank == 0 else -1.0) + rank
+            mx = comm.allreduce_max(v)
+            expect = np.maximum.reduce([np.arange(11) * (1.0 if r == 0 else -1.0) + r
+                                        for r in range(world)])
+            ok = ok and np.array_equal(mx, expect)
+            sm = comm.allreduce_sum(np.full(9, 0.1 * (rank + 1)))
+            acc = np.zeros(9)
+            for r in range(world):
+                acc = acc + np.full(9, 0.1 * (r + 1))
+            ok = ok and np.array_equal(sm, acc)
+            # a NaN on one rank never wins, and every rank gets the same bits
+            w = np.array([np.nan if rank == generation % world else 1.0 + rank, 2.0])
+            got = comm.allreduce_max(w)
+            others = [1.0 + r for r in range(world) if r != generation % world]
+            ok = ok and got[0] == max(others) and got[1] == 2.0
+            comm.barrier()
+            comm.close()
+        # a rank that gives up releases the others' waits with a common error
+        comm = MG.Comm(name + "_abort", rank, world)
+        comm.barrier()
+        if rank == world - 1:
+            comm.abort()
+            failed = True
+        else:
+            try:
+                comm.barrier()  # the last rank never comes
+                failed = False
+            except RuntimeError:
+                failed = True
+        comm.close()
+        q.put((rank, ok and failed))
+    except Exception as e:  # noqa: BLE001
+        q.put((rank, f"exception: {e!r}"))
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_communicator_generations_wide_reductions_and_abort(world):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    name = f"smeb200_robust_{os.getpid()}_{world}"
+    procs = [ctx.Process(target=_worker_robust, args=(r, world, name, q))
+             for r in range(world)]
+    for pr in procs:
+        pr.start()
+    results = [q.get(timeout=180) for _ in range(world)]
+    for pr in procs:
+        pr.join(timeout=60)
+    assert sorted(results) == [(r, True) for r in range(world)]

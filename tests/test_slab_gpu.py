@@ -326,3 +326,81 @@ def test_non_spatial_species_in_slabs(geom, integ):
         assert_parity(d, d_ref[i], rel=1e-10, what=f"{geom} dcdt[{i}]")
         # one value of dc/dt for the non-spatial species across all slabs
         assert np.ptp(d[:, 1]) == 0.0
+
+
+# ---- a stop decided on ONE rank is a decision of all ranks ------------------------
+def _stop_worker(rank, world, name, mode, q):
+    """mode "timeout": every rank passes a deadline (the clocks differ);
+    "callback": only the last rank's callback asks to stop, after 5 steps;
+    "flag": only rank 0 gets setStopRequested, from another thread, mid-run"""
+    sys.path.insert(0, ROOT)
+    import threading
+    import time
+    from spatial_model_editor_b200.multigpu import SlabPixelSim
+    try:
+        p = _problem(smeb.RK212, False, (64, 64, 16 * world))
+        p.device = rank
+        sim = SlabPixelSim(p, rank, world, comm_name=name)
+        err0 = sim.errorMessage()
+        sim.nextTimestep = 0.01
+        t0 = time.perf_counter()
+        if mode == "timeout":
+            n = sim.run(1000.0, 300.0)
+        elif mode == "callback":
+            calls = [0]
+
+            def cb():
+                calls[0] += 1
+                return rank == world - 1 and calls[0] >= 5
+
+            n = sim.run(1000.0, -1.0, cb)
+        else:
+            if rank == 0:
+                threading.Timer(0.3, lambda: sim.setStopRequested(True)).start()
+            n = sim.run(1000.0)
+        el = time.perf_counter() - t0
+        msg = sim.errorMessage()
+        # the ranks are still in step: the states of the slabs fit together
+        c = sim.getConcentrations(0).copy()
+        q.put((rank, err0, msg, n, el, c))
+        sim.close()
+    except Exception as e:  # noqa: BLE001
+        q.put((rank, f"exception: {e!r}", "", 0, 0.0, None))
+
+
+@pytest.mark.parametrize("mode", ["timeout", "callback", "flag"])
+def test_stop_is_collective_in_slabs(mode):
+    world = min(smeb.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs >= 2 GPUs")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    name = f"smeb200_stoptest_{os.getpid()}_{mode}"
+    procs = [ctx.Process(target=_stop_worker, args=(r, world, name, mode, q))
+             for r in range(world)]
+    for pr in procs:
+        pr.start()
+    res = sorted((q.get(timeout=300) for _ in range(world)), key=lambda r: r[0])
+    for pr in procs:
+        pr.join(timeout=60)
+    for r in res:
+        assert r[1] == "", r[1]
+        assert r[2] == "Simulation stopped early"
+        assert r[4] < 60.0  # nobody waited for a neighbour that had stopped
+    steps = {r[3] for r in res}
+    assert len(steps) == 1 and steps.pop() >= (5 if mode == "callback" else 1)
+    # the same number of steps on one GPU gives the same state
+    p = _problem(smeb.RK212, False, (64, 64, 16 * world))
+    p.device = 0
+    ref = smeb.PixelSim(p)
+    ref.nextTimestep = 0.01
+    n = res[0][3]
+    calls = [0]
+
+    def after_n():
+        calls[0] += 1
+        return calls[0] >= n
+
+    assert ref.run(1000.0, -1.0, after_n) == n  # the same sequence of step sizes
+    assert np.array_equal(np.concatenate([r[5] for r in res]), ref.getConcentrations(0))
