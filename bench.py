@@ -296,9 +296,22 @@ def run_ensemble(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     p, _, _ = load_golden("liver-simplified-scan")
     vals = EN.scan_values(p.params[0], args.members)
-    ens = EN.Ensemble(p, vals, rank=rank, world=world, device=local_rank,
-                      concurrency=args.concurrency)
-    ens.run(args.sim_time / 10)  # warm-up: module compile, allocator, clocks
+    if args.ensemble_impl == "batched":
+        # members as gridDim.y of one launch per stage (smeb200_ensemble_*)
+        ens = EN.BatchedEnsemble(p, vals, rank=rank, world=world, device=local_rank)
+        impl_text = "member-batched launches (smeb200_ensemble_run)"
+    else:
+        ens = EN.Ensemble(p, vals, rank=rank, world=world, device=local_rank,
+                          concurrency=args.concurrency)
+        impl_text = f"{args.concurrency} concurrent single simulations per GPU"
+    if args.ensemble_impl == "batched":
+        # warm-up on a throw-away ensemble: run() continues from the members' states
+        warm = EN.BatchedEnsemble(p, vals[:max(world, 1) * 2], rank=rank, world=world,
+                                  device=local_rank)
+        warm.run(args.sim_time / 10)
+        warm.close()
+    else:
+        ens.run(args.sim_time / 10)  # warm-up: module compile, allocator, clocks
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -321,7 +334,7 @@ def run_ensemble(args, rank, world, local_rank):
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"liver-simplified parameter scan, {args.members} members x "
                                    f"t={args.sim_time}, RK212 adaptive (model settings), "
-                                   f"{args.concurrency} concurrent members per GPU",
+                                   f"{impl_text}",
                        "parallelism": f"one simulation per GPU slot x{world}"},
             "wall_s": el, "errors": sorted({r.error for r in res if r.error})}))
     if world > 1:
@@ -426,6 +439,8 @@ def main():
     ap.add_argument("--dt", type=float, default=DT)
     ap.add_argument("--members", type=int, default=64)
     ap.add_argument("--concurrency", type=int, default=8)
+    ap.add_argument("--ensemble-impl", default="batched",
+                    help="ensemble workload: batched (members = gridDim.y) | threads")
     ap.add_argument("--sim-time", type=float, default=1.0)
     args = ap.parse_args()
 

@@ -188,7 +188,10 @@ typedef struct smeb200_problem {
    * where the shape allows it), 1 = direct-gather kernels only, 2 = require
    * the TMA tile kernel for box compartments (error if it cannot be used),
    * 3 = keep the plain six-index neighbour table of voxel-list compartments
-   * (default: run-compressed to one 32-bit code per voxel where possible) */
+   * (default: run-compressed to one 32-bit code per voxel where possible),
+   * 4 = voxel-list compartments use the segment-staged kernel where their runs
+   * allow it (pieces of runs staged in shared memory by bulk copies; measured
+   * level with the direct kernel, kept for comparison) */
   int32_t kernel_variant;
   /* runtime model parameters: expressions may refer to sme_param_0 ..
    * sme_param_{n_params-1}; their values are kernel arguments, so simulators
@@ -395,6 +398,58 @@ uint64_t smeb200_halo_exchanges(const smeb200_sim *sim);
 typedef void (*smeb200_allreduce_max_fn)(double *values, int n, void *user);
 void smeb200_set_allreduce_max(smeb200_sim *sim, smeb200_allreduce_max_fn fn,
                                void *user);
+
+/* ---- member-batched ensembles -------------------------------------------------
+ * A parameter scan / a population of optimizer candidates: n_members simulations
+ * of ONE model that differ only in the values of the runtime parameters
+ * (smeb200_problem::n_params).  The reference has no counterpart — a scan is a
+ * loop that sets a parameter and simulates again (sme_model.cpp:541-617), the
+ * optimizer evaluates its candidates one simulation at a time
+ * (optimize_impl.cpp:150-186) — and every member re-compiles the reactions
+ * because parameter values are inlined into the expression text
+ * (pde.cpp:65-77).  Here the members share geometry tables and one compiled
+ * module, the state is [member][voxel][species], a Runge-Kutta stage of all
+ * members of a compartment is ONE kernel launch (members = gridDim.y), and every
+ * member has its own step-size controller (PixelSim::run / doRKAdaptive per
+ * member, evaluated after each batched step), so a member takes exactly the
+ * steps it would take alone.  member_params: [n_members][n_params], row m = the
+ * values of member m (p->params is ignored).  Not available with z-slab
+ * decomposition (an ensemble lives on one GPU; shard members over GPUs by
+ * creating one ensemble per rank), zero-storage / non-spatial species or
+ * cross-diffusion.  Error conventions as for smeb200_create. */
+typedef struct smeb200_ensemble smeb200_ensemble;
+int smeb200_ensemble_create(const smeb200_problem *p, uint32_t n_members,
+                            const double *member_params, smeb200_ensemble **out);
+void smeb200_ensemble_destroy(smeb200_ensemble *ens);
+/* every member integrates [0, time] (BaseSim::run per member); returns the sum of
+ * the members' accepted steps.  timeout / stop_cb are polled once per batched
+ * step and stop all members ("Simulation stopped early"). */
+size_t smeb200_ensemble_run(smeb200_ensemble *ens, double time, double timeout_ms,
+                            int (*stop_cb)(void *user), void *user);
+/* BaseSim::getConcentrations of one member (pinned mirror, valid until the next
+ * run) and the restart path (SimCompartment::setConcentrations) */
+int smeb200_ensemble_get_concentrations(smeb200_ensemble *ens, uint32_t member,
+                                        size_t compartment, const double **data,
+                                        size_t *n);
+int smeb200_ensemble_set_concentrations(smeb200_ensemble *ens, uint32_t member,
+                                        size_t compartment, const double *data,
+                                        size_t n);
+/* per member: accepted / discarded steps of the last run, controller state */
+size_t smeb200_ensemble_get_steps(const smeb200_ensemble *ens, uint32_t member);
+size_t smeb200_ensemble_get_discarded_steps(const smeb200_ensemble *ens,
+                                            uint32_t member);
+double smeb200_ensemble_get_next_timestep(const smeb200_ensemble *ens,
+                                          uint32_t member);
+void smeb200_ensemble_set_next_timestep(smeb200_ensemble *ens, uint32_t member,
+                                        double dt);
+/* member >= 0: that member's error (adaptive failure), empty = OK; member < 0: the
+ * ensemble's own error (construction, stop, device failure) */
+const char *smeb200_ensemble_error(const smeb200_ensemble *ens, int member);
+void smeb200_ensemble_set_stop_requested(smeb200_ensemble *ens, int stop);
+/* measurement hooks */
+uint64_t smeb200_ensemble_launch_count(const smeb200_ensemble *ens);
+uint64_t smeb200_ensemble_batched_steps(const smeb200_ensemble *ens);
+double smeb200_ensemble_last_run_ms(const smeb200_ensemble *ens);
 
 #ifdef __cplusplus
 }

@@ -1,6 +1,7 @@
 // extern "C" surface of libsmeb200.so — see include/smeb200.h for the contract
 // and the reference interface each entry point stands in for.
 #include "comm.hpp"
+#include "ensemble.hpp"
 #include "sim.hpp"
 #include <cstring>
 
@@ -375,6 +376,128 @@ void smeb200_set_allreduce_max(smeb200_sim *sim, smeb200_allreduce_max_fn fn,
     sim->impl.allreduceMax = fn;
     sim->impl.allreduceUser = user;
   }
+}
+
+
+/* ---- member-batched ensembles ---------------------------------------------- */
+struct smeb200_ensemble {
+  smeb200::EnsembleSim impl;
+  smeb200_ensemble(const smeb200_problem &p, uint32_t n, const double *params)
+      : impl(p, n, params) {}
+};
+
+int smeb200_ensemble_create(const smeb200_problem *p, uint32_t n_members,
+                            const double *member_params, smeb200_ensemble **out) {
+  if (out == nullptr) {
+    return -1;
+  }
+  *out = nullptr;
+  if (p == nullptr) {
+    return -1;
+  }
+  try {
+    *out = new smeb200_ensemble(*p, n_members, member_params);
+  } catch (...) {
+    return -1;
+  }
+  return (*out)->impl.errorMessage.empty() ? 0 : 1;
+}
+
+void smeb200_ensemble_destroy(smeb200_ensemble *ens) { delete ens; }
+
+size_t smeb200_ensemble_run(smeb200_ensemble *ens, double time, double timeout_ms,
+                            int (*stop_cb)(void *user), void *user) {
+  if (ens == nullptr) {
+    return 0;
+  }
+  return ens->impl.run(time, timeout_ms, stop_cb, user);
+}
+
+int smeb200_ensemble_get_concentrations(smeb200_ensemble *ens, uint32_t member,
+                                        size_t compartment, const double **data,
+                                        size_t *n) {
+  if (ens == nullptr) {
+    return -1;
+  }
+  try {
+    const double *p = ens->impl.getConcentrations(member, compartment, n);
+    if (data != nullptr) {
+      *data = p;
+    }
+  } catch (const std::exception &e) {
+    ens->impl.errorMessage = e.what();
+    return 1;
+  }
+  return 0;
+}
+
+int smeb200_ensemble_set_concentrations(smeb200_ensemble *ens, uint32_t member,
+                                        size_t compartment, const double *data,
+                                        size_t n) {
+  if (ens == nullptr) {
+    return -1;
+  }
+  try {
+    ens->impl.setConcentrations(member, compartment, data, n);
+  } catch (const std::exception &e) {
+    ens->impl.errorMessage = e.what();
+    return 1;
+  }
+  return 0;
+}
+
+size_t smeb200_ensemble_get_steps(const smeb200_ensemble *ens, uint32_t member) {
+  return ens != nullptr && member < ens->impl.nMembers() ? ens->impl.steps[member]
+                                                         : 0;
+}
+
+size_t smeb200_ensemble_get_discarded_steps(const smeb200_ensemble *ens,
+                                            uint32_t member) {
+  return ens != nullptr && member < ens->impl.nMembers()
+             ? ens->impl.discarded[member]
+             : 0;
+}
+
+double smeb200_ensemble_get_next_timestep(const smeb200_ensemble *ens,
+                                          uint32_t member) {
+  return ens != nullptr && member < ens->impl.nMembers()
+             ? ens->impl.nextTimestep[member]
+             : 0.0;
+}
+
+void smeb200_ensemble_set_next_timestep(smeb200_ensemble *ens, uint32_t member,
+                                        double dt) {
+  if (ens != nullptr && member < ens->impl.nMembers()) {
+    ens->impl.nextTimestep[member] = dt;
+  }
+}
+
+const char *smeb200_ensemble_error(const smeb200_ensemble *ens, int member) {
+  if (ens == nullptr) {
+    return "";
+  }
+  if (member < 0 || static_cast<uint32_t>(member) >= ens->impl.nMembers()) {
+    return ens->impl.errorMessage.c_str();
+  }
+  return ens->impl.memberError[member].c_str();
+}
+
+void smeb200_ensemble_set_stop_requested(smeb200_ensemble *ens, int stop) {
+  if (ens != nullptr) {
+    ens->impl.stopRequested.store(stop != 0);
+  }
+}
+
+uint64_t smeb200_ensemble_launch_count(const smeb200_ensemble *ens) {
+  return ens != nullptr ? ens->impl.launchCount : 0;
+}
+
+uint64_t smeb200_ensemble_batched_steps(const smeb200_ensemble *ens) {
+  return ens != nullptr ? ens->impl.batchedSteps : 0;
+}
+
+double smeb200_ensemble_last_run_ms(const smeb200_ensemble *ens) {
+  return ens != nullptr ? ens->impl.lastRunMs : 0.0;
 }
 
 } // extern "C"

@@ -118,6 +118,22 @@ template __global__ void
 smeb_stage_tile<Reac0, F3, 16, 64, 5, true>(const __grid_constant__ SmebStageArgs<2>,
                                             const __grid_constant__ SmebTensorMap,
                                             const smeb_u32);
+// voxel lists staged in shared memory piece by piece (2-D and 3-D)
+template __global__ void
+smeb_stage_seg<Reac0, F1, 512, 2, false>(const __grid_constant__ SmebStageArgs<2>);
+template __global__ void
+smeb_stage_seg<Reac0, F2, 512, 2, false>(const __grid_constant__ SmebStageArgs<2>);
+template __global__ void
+smeb_stage_seg<Reac0, F2, 256, 2, true>(const __grid_constant__ SmebStageArgs<2>);
+// member-batched ensemble variants (gridDim.y = members)
+template __global__ void
+smeb_stage_nn<Reac0, F2 | SMEB_F_MEMBERS>(const __grid_constant__ SmebStageArgs<2>);
+template __global__ void
+smeb_stage_memb<Reac0, F2 | SMEB_F_MEMBERS>(const __grid_constant__ SmebStageArgs<2>,
+                                            const __grid_constant__ SmebMembArgs);
+template __global__ void
+smeb_stage_seg<Reac0, F2 | SMEB_F_MEMBERS, 512, 2, false>(
+    const __grid_constant__ SmebStageArgs<2>);
 // z-slab variants: halo exchange inside the kernel
 template __global__ void
 smeb_stage_tile<Reac0, F1 | SMEB_F_HALO, 16, 64, 5, true>(

@@ -45,6 +45,7 @@ typedef unsigned int smeb_u32;
                                  // norms, out = c + dt f for those species
 #define SMEB_F_RELAX_B 8192u     // second half: out = c0/2 + c/2 + dt/2 f, error
 #define SMEB_F_HALO 16384u       // z-slabs, tile kernel: halo exchange in the kernel
+#define SMEB_F_MEMBERS 32768u    // member-batched ensemble: gridDim.y = members
 
 #define SMEB_MEMB_FLAG 0x80000000u
 #define SMEB_BLOCK 256
@@ -78,9 +79,17 @@ template <int S> struct SmebStageArgs {
   const smeb_u32 *nn;  // voxel-list geometry: [6 n] neighbour indices, or (runs
                        // != 0) [n] run-compressed neighbour codes
   const int *runs;     // [4 n_runs] index deltas of the +x, -x, +z, -z neighbours
-  smeb_u64 *err;       // error slot: [0], [1] bit patterns of max abs / max rel
-                       // error, then two u32: CTAs arrived, steps published
+  const smeb_u32 *seg; // segment-staged voxel-list kernel: [2 nSeg] (first voxel,
+                       // length) of pieces of runs, at most SEG voxels each
+  smeb_u64 *err;       // [2] bit patterns of max abs / max rel error of this
+                       // simulation (ensembles: of this member, errBase + 2 m)
+  smeb_u64 *errBase;   // error slot: errPairs pairs, then two u32: CTAs arrived,
+                       // steps published
   smeb_u64 *errHost;   // pinned host ring the last CTA of a step publishes into
+  // member-batched ensembles (SMEB_F_MEMBERS): gridDim.y = members; a member's
+  // buffers, step size and parameter values come from these tables
+  const struct SmebMember *members; // [nMembers] of this compartment
+  const double *memberParams;       // [nMembers][SMEB_NPARAMS]
   const double *nsAv;  // [R::NNS] spatial averages of dc/dt (non-spatial species)
   double *nsPartial;   // [blocks][R::NNS] block sums written by the pre-pass
   const double *darr;  // [n][S] per-voxel diffusion constants (R::NUD)
@@ -97,13 +106,18 @@ template <int S> struct SmebStageArgs {
   smeb_u32 haloMode;
   double *peerLo;          // rank below: its HIGH ghost plane of the output buffer
   double *peerHi;          // rank above: its LOW ghost plane of the output buffer
-  smeb_u32 *halo;          // own words: [0] / [1] sequence number of the last plane
-                           // that arrived from below / above, [2] / [3] CTAs of the
-                           // low / high boundary plane done, [4] error
+  smeb_u32 *halo;          // own words: [0] / [1] count of boundary-plane tiles that
+                           // have arrived from below / above since the start (every
+                           // stage adds one per tile of the plane)
   smeb_u32 *peerFlagLo;    // rank below: its halo[1]
   smeb_u32 *peerFlagHi;    // rank above: its halo[0]
-  smeb_u32 haloSeq;        // sequence number of this stage (inputs carry haloSeq - 1)
-  smeb_u32 pad0_;
+  smeb_u32 *haloErr;       // own word: raised when a bounded wait ran out
+  smeb_u32 haloSeq;        // number of this stage: its inputs are complete when the
+                           // counts have reached (haloSeq - 1) * tiles
+  smeb_u32 nSeg;           // segments in `seg`
+  smeb_u32 errPairs;       // pairs in the error slot: 1, or the members of an ensemble
+  smeb_u32 roles;          // ensembles: buffer roles (CUR, RA, RB, RS = 0..3; 15 =
+                           // none) of cin | cout << 4 | s2in << 8 | s2out << 12
   double g1, g2, g3, bdt, delta; // stage coefficients (bdt = beta*dt)
   // CUDA-graph replay of a step: the step size lives in device memory (a
   // captured launch cannot carry a new bdt); bdt = beta * *dtp when dtp != 0
@@ -114,6 +128,15 @@ template <int S> struct SmebStageArgs {
   // (values of sme_param_k: scanned parameters of an ensemble stay symbolic so
   // that one compiled module serves every member)
   double D[3 * S + SMEB_NPARAMS];
+};
+
+// one member of an ensemble, per compartment; rewritten by the host before every
+// step (the roles of a member's buffers rotate when ITS step is accepted)
+struct SmebMember {
+  double *buf[4];  // concentration buffers by role: CUR, RA, RB, RS
+  double dt;       // step size of this attempt
+  smeb_u32 active; // 0: the member has reached the end time (its CTAs only report in)
+  smeb_u32 pad_;
 };
 
 struct SmebMembEntry {
@@ -131,6 +154,7 @@ struct SmebMembArgs {
   const SmebMembEntry *ent;   // faces in reference order (membrane, direction)
   const double *flux_len;     // [n_membranes*6]
   const double *comp_cin[SMEB_NCOMP]; // stage input of every compartment
+  const SmebMember *comp_members[SMEB_NCOMP]; // ensembles: member tables
   smeb_u32 n_mvox;
   smeb_u32 pad_;
 };
@@ -173,10 +197,14 @@ __device__ __forceinline__ void smeb_store_voxel(double *__restrict__ p,
   }
 }
 
-// Programmatic dependent launch (sm_90+): a kernel lets the next kernel of the
-// stream become resident as soon as all of its own CTAs have started, and touches
-// global memory only after the kernel before it has completed and flushed.  Both
-// are no-ops for launches without the stream-serialization attribute.
+// Programmatic dependent launch (sm_90+).  Every stage kernel first waits until
+// the kernel in front of it in the stream has completed and flushed
+// (griddepcontrol.wait) and only then lets the kernel behind it become resident
+// (griddepcontrol.launch_dependents): a kernel's prologue therefore overlaps the
+// tail of its immediate predecessor and nothing older, and what it does before
+// the wait (barrier setup, index arithmetic, loads of data that the predecessor
+// does not write — the pre-step state c0) is safe.  Both are no-ops for launches
+// without the stream-serialization attribute.
 __device__ __forceinline__ void smeb_pdl_trigger() {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
@@ -187,30 +215,33 @@ __device__ __forceinline__ void smeb_pdl_wait() {
 #define SMEB_ERR_RING 8 // entries of the pinned host ring (sim.hpp kErrRing)
 
 // One CTA of an error-norm launch is done.  The CTA that completes the step's
-// count takes the two maxima out of the slot (leaving it zeroed for the next
-// step) and publishes them with the step's sequence number into the pinned host
-// ring: the host polls 32 bytes of its own memory instead of queueing a copy, a
-// memset and an event behind every step (which also kept two kernels from
-// overlapping their tails).  Called by one thread per CTA, after its atomicMax.
-__device__ __forceinline__ void smeb_err_arrive(smeb_u64 *err, smeb_u64 *errHost,
+// count takes the maxima out of the slot (leaving it zeroed for the next step)
+// and publishes them with the step's sequence number into the pinned host ring:
+// the host polls its own memory instead of queueing a copy, a memset and an event
+// behind every step (which also kept two kernels from overlapping their tails).
+// `pairs` pairs of maxima (ensembles: one per member); a ring entry is 2 pairs + 2
+// words, the sequence number at [2 pairs].  Called by one thread per CTA, after
+// its atomicMax.
+__device__ __forceinline__ void smeb_err_arrive(smeb_u64 *errBase, smeb_u32 pairs,
+                                                smeb_u64 *errHost,
                                                 smeb_u32 expected) {
   if (expected == 0u) {
     return;
   }
-  unsigned int *cnt = reinterpret_cast<unsigned int *>(err + 2);
+  unsigned int *cnt = reinterpret_cast<unsigned int *>(errBase + 2u * pairs);
   __threadfence();
   const unsigned int prev = atomicAdd(cnt, 1u);
   if (prev + 1u == expected) {
     __threadfence();
-    const smeb_u64 a = atomicExch(err, 0ull);
-    const smeb_u64 r = atomicExch(err + 1, 0ull);
-    atomicExch(cnt, 0u);
     const unsigned int seq = atomicAdd(cnt + 1, 1u) + 1u;
-    volatile smeb_u64 *h = errHost + 4u * (seq % SMEB_ERR_RING);
-    h[0] = a;
-    h[1] = r;
+    volatile smeb_u64 *h =
+        errHost + (size_t)(2u * pairs + 2u) * (seq % SMEB_ERR_RING);
+    for (smeb_u32 k = 0; k < 2u * pairs; ++k) {
+      h[k] = atomicExch(errBase + k, 0ull);
+    }
+    atomicExch(cnt, 0u);
     __threadfence_system();
-    h[2] = (smeb_u64)seq;
+    h[2u * pairs] = (smeb_u64)seq;
     __threadfence_system();
   }
 }
@@ -220,7 +251,8 @@ __device__ __forceinline__ void smeb_err_arrive(smeb_u64 *err, smeb_u64 *errHost
 // like std::max in pixelsim_impl.cpp:783-788 a NaN or negative candidate is
 // never taken).  Called once per thread at the end of a kernel.
 __device__ __forceinline__ void smeb_block_max2(double eabs, double erel,
-                                                smeb_u64 *err, smeb_u64 *errHost,
+                                                smeb_u64 *err, smeb_u64 *errBase,
+                                                smeb_u32 pairs, smeb_u64 *errHost,
                                                 smeb_u32 expected) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -254,7 +286,7 @@ __device__ __forceinline__ void smeb_block_max2(double eabs, double erel,
       if (erel > 0.0) {
         atomicMax(err + 1, (smeb_u64)__double_as_longlong(erel));
       }
-      smeb_err_arrive(err, errHost, expected);
+      smeb_err_arrive(errBase, pairs, errHost, expected);
     }
   }
 }
@@ -586,6 +618,49 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
   }
 }
 
+// ---- member-batched ensembles (SMEB_F_MEMBERS) -----------------------------------
+// A parameter scan is many simulations of one model that differ in the values of
+// runtime parameters (BASELINE config 5: 64 x liver-simplified).  Each of them is
+// launch bound on its own; batched, the members are gridDim.y of ONE launch per
+// stage and compartment.  Geometry tables, coefficients and stage constants are
+// shared (the kernel arguments); what differs per member comes from a table the
+// host rewrites before every step: the member's buffers by role (a member whose
+// step was rejected keeps its roles, the others rotate), its step size and
+// whether it is still running, and its parameter values.  The kernel patches a
+// private copy of its arguments and runs the ordinary body.
+template <class R, unsigned F>
+__device__ __forceinline__ bool smeb_member_select(SmebStageArgs<R::S> &a) {
+  constexpr int S = R::S;
+  const smeb_u32 mIdx = blockIdx.y;
+  const SmebMember mb = a.members[mIdx];
+  const smeb_u32 rCin = a.roles & 15u, rCout = (a.roles >> 4) & 15u,
+                 rS2in = (a.roles >> 8) & 15u, rS2out = (a.roles >> 12) & 15u;
+  a.cin = mb.buf[rCin];
+  a.cout = mb.buf[rCout];
+  a.c0 = mb.buf[0];
+  a.s2in = rS2in < 4u ? mb.buf[rS2in] : nullptr;
+  a.s2out = rS2out < 4u ? mb.buf[rS2out] : nullptr;
+  a.bdt = a.beta * mb.dt; // the product the host forms for a single simulation
+  a.dtp = nullptr;
+  a.err = a.errBase + 2u * mIdx;
+#pragma unroll
+  for (int k = 0; k < SMEB_NPARAMS; ++k) {
+    a.D[3 * S + k] = a.memberParams[(size_t)mIdx * SMEB_NPARAMS + k];
+  }
+  if (mb.active == 0u) {
+    // a finished member: its CTAs still count towards the step's error norms
+    smeb_pdl_wait();
+    smeb_pdl_trigger();
+    if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0)) {
+      if (threadIdx.x == 0) {
+        smeb_err_arrive(a.errBase, a.errPairs, a.errHost, a.errExpected);
+      }
+    }
+    return false;
+  }
+  return true;
+}
+
 // ---- direct-gather stage kernels: grid-stride loop, one voxel at a time -----
 // voxel-list geometry.  The neighbour table of the reference (six indices per
 // voxel, geometry.cpp:98-110; 24 B per voxel as uint32) is stored run-compressed
@@ -635,8 +710,7 @@ smeb_neighbours(const smeb_u32 *__restrict__ nn, const int *__restrict__ runs,
 #define SMEB_NN_BOUNDS __launch_bounds__(SMEB_BLOCK)
 #endif
 template <class R, unsigned F>
-__global__ void SMEB_NN_BOUNDS
-    smeb_stage_nn(const __grid_constant__ SmebStageArgs<R::S> a) {
+__device__ __forceinline__ void smeb_stage_nn_body(const SmebStageArgs<R::S> &a) {
   constexpr int S = R::S;
   double eabs = 0.0, erel = 0.0;
   double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
@@ -645,7 +719,6 @@ __global__ void SMEB_NN_BOUNDS
   // (SMEB_NN_CODE_AHEAD >= 1), and so are its own state and c0 (>= 2): with six
   // resident CTAs the loads of one iteration alone do not keep enough bytes in
   // flight to cover the DRAM latency
-  smeb_pdl_trigger();
   const smeb_u32 stride = gridDim.x * SMEB_BLOCK;
   const bool coded = a.runs != nullptr;
   constexpr bool PRE = SMEB_NN_CODE_AHEAD >= 2;
@@ -653,6 +726,7 @@ __global__ void SMEB_NN_BOUNDS
                           (F & (SMEB_F_OUT_DCDT | SMEB_F_SUM_NS)) == 0;
   smeb_u32 i = a.v0 + blockIdx.x * SMEB_BLOCK + threadIdx.x;
   smeb_pdl_wait();
+  smeb_pdl_trigger();
   smeb_u32 codeNext = coded && i < a.n ? a.nn[i] : 0u;
   double cNext[S], c0Next[S];
 #pragma unroll
@@ -700,7 +774,21 @@ __global__ void SMEB_NN_BOUNDS
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
   } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
                        (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
-    smeb_block_max2(eabs, erel, a.err, a.errHost, a.errExpected);
+    smeb_block_max2(eabs, erel, a.err, a.errBase, a.errPairs, a.errHost,
+                    a.errExpected);
+  }
+}
+
+template <class R, unsigned F>
+__global__ void SMEB_NN_BOUNDS
+    smeb_stage_nn(const __grid_constant__ SmebStageArgs<R::S> ain) {
+  if constexpr ((F & SMEB_F_MEMBERS) != 0) {
+    SmebStageArgs<R::S> a = ain;
+    if (smeb_member_select<R, F>(a)) {
+      smeb_stage_nn_body<R, F>(a);
+    }
+  } else {
+    smeb_stage_nn_body<R, F>(ain);
   }
 }
 
@@ -709,15 +797,14 @@ __global__ void SMEB_NN_BOUNDS
 // neighbour = own index, geometry.cpp:98-110); only planes
 // [z_begin, z_end) are updated (the others are z-slab ghost planes).
 template <class R, unsigned F>
-__global__ void __launch_bounds__(SMEB_BLOCK)
-    smeb_stage_box(const __grid_constant__ SmebStageArgs<R::S> a) {
+__device__ __forceinline__ void smeb_stage_box_body(const SmebStageArgs<R::S> &a) {
   constexpr int S = R::S;
   double eabs = 0.0, erel = 0.0;
   double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
-  smeb_pdl_trigger();
   const smeb_u32 sx = a.ny, sz = a.nx * a.ny;
   const smeb_u32 iEnd = a.z_end * sz;
   smeb_pdl_wait();
+  smeb_pdl_trigger();
   for (smeb_u32 i = a.z_begin * sz + blockIdx.x * SMEB_BLOCK + threadIdx.x;
        i < iEnd; i += gridDim.x * SMEB_BLOCK) {
     const smeb_u32 y = i % a.ny;
@@ -739,7 +826,21 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
   } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
                        (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
-    smeb_block_max2(eabs, erel, a.err, a.errHost, a.errExpected);
+    smeb_block_max2(eabs, erel, a.err, a.errBase, a.errPairs, a.errHost,
+                    a.errExpected);
+  }
+}
+
+template <class R, unsigned F>
+__global__ void __launch_bounds__(SMEB_BLOCK)
+    smeb_stage_box(const __grid_constant__ SmebStageArgs<R::S> ain) {
+  if constexpr ((F & SMEB_F_MEMBERS) != 0) {
+    SmebStageArgs<R::S> a = ain;
+    if (smeb_member_select<R, F>(a)) {
+      smeb_stage_box_body<R, F>(a);
+    }
+  } else {
+    smeb_stage_box_body<R, F>(ain);
   }
 }
 
@@ -818,14 +919,13 @@ smeb_memb_dispatch(smeb_u32 info, smeb_u32 partner, const double *cown,
                    const SmebMembArgs &m, const double *params, double *f);
 
 template <class R, unsigned F>
-__global__ void __launch_bounds__(SMEB_BLOCK)
-    smeb_stage_memb(const __grid_constant__ SmebStageArgs<R::S> a,
-                    const __grid_constant__ SmebMembArgs m) {
+__device__ __forceinline__ void smeb_stage_memb_body(const SmebStageArgs<R::S> &a,
+                                                     const SmebMembArgs &m) {
   constexpr int S = R::S;
   double eabs = 0.0, erel = 0.0;
   double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
-  smeb_pdl_trigger();
   smeb_pdl_wait();
+  smeb_pdl_trigger();
   for (smeb_u32 k = blockIdx.x * SMEB_BLOCK + threadIdx.x; k < m.n_mvox;
        k += gridDim.x * SMEB_BLOCK) {
     const smeb_u32 i = m.mvox[k];
@@ -844,7 +944,30 @@ __global__ void __launch_bounds__(SMEB_BLOCK)
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
   } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
                        (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
-    smeb_block_max2(eabs, erel, a.err, a.errHost, a.errExpected);
+    smeb_block_max2(eabs, erel, a.err, a.errBase, a.errPairs, a.errHost,
+                    a.errExpected);
+  }
+}
+
+template <class R, unsigned F>
+__global__ void __launch_bounds__(SMEB_BLOCK)
+    smeb_stage_memb(const __grid_constant__ SmebStageArgs<R::S> ain,
+                    const __grid_constant__ SmebMembArgs min) {
+  if constexpr ((F & SMEB_F_MEMBERS) != 0) {
+    SmebStageArgs<R::S> a = ain;
+    SmebMembArgs m = min;
+    // the partner voxels are read from the same member's stage input
+#pragma unroll
+    for (int j = 0; j < SMEB_NCOMP; ++j) {
+      if (m.comp_members[j] != nullptr) {
+        m.comp_cin[j] = m.comp_members[j][blockIdx.y].buf[a.roles & 15u];
+      }
+    }
+    if (smeb_member_select<R, F>(a)) {
+      smeb_stage_memb_body<R, F>(a, m);
+    }
+  } else {
+    smeb_stage_memb_body<R, F>(ain, min);
   }
 }
 
@@ -930,23 +1053,25 @@ extern __shared__ __align__(128) unsigned char smeb_dyn_smem[];
 // ---- halo exchange inside the stage kernel (z-slabs over NVLink) ---------------
 // A rank's boundary planes are written twice: into its own output buffer and,
 // with plain stores through the peer mapping, into the neighbour's ghost plane of
-// the same buffer.  When the last CTA of a boundary plane is done it releases
-// the stage's sequence number into a flag word in the NEIGHBOUR's memory; the
-// neighbour's CTAs that read that ghost plane in the next stage acquire it
-// before their TMA load.  No copy engine, no extra launches, no stream waits:
-// one kernel per stage, and the stages of a step chain with programmatic
-// dependent launch.  The wait is bounded: after about 10 s it raises halo[4]
-// and goes on (the host reports it), it never hangs the GPU.
+// the same buffer.  A CTA that has stored its tile of a boundary plane adds one,
+// with release semantics at system scope, to a counter word in the NEIGHBOUR's
+// memory (fire and forget: nothing comes back, nobody on this side waits for the
+// other tiles); the neighbour's CTAs that read that ghost plane in the next stage
+// acquire the counter before their TMA loads: (stage - 1) x tiles means every
+// tile of every earlier stage has landed.  No copy engine, no extra launches, no
+// stream waits: one kernel per stage, and the stages chain with programmatic
+// dependent launch.  The wait is bounded: after about 10 s it raises haloErr and
+// goes on (the host reports it), it never hangs the GPU.
 __device__ __forceinline__ smeb_u32 smeb_ld_acquire_sys(const smeb_u32 *p) {
   smeb_u32 v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void smeb_st_release_sys(smeb_u32 *p, smeb_u32 v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void smeb_red_release_sys(smeb_u32 *p, smeb_u32 v) {
+  asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ void smeb_halo_acquire(smeb_u32 *halo, int side,
-                                                  smeb_u32 want) {
+                                                  smeb_u32 want, smeb_u32 *err) {
   long long t0 = 0;
   unsigned spins = 0;
   while ((int)(smeb_ld_acquire_sys(halo + side) - want) < 0) {
@@ -954,7 +1079,7 @@ __device__ __forceinline__ void smeb_halo_acquire(smeb_u32 *halo, int side,
       t0 = clock64();
     } else if (spins > 64u && (spins & 1023u) == 0u &&
                clock64() - t0 > 20000000000ll) {
-      atomicExch(halo + 4, 1u + (smeb_u32)side);
+      atomicExch(err, 1u + (smeb_u32)side);
       break;
     }
   }
@@ -965,13 +1090,15 @@ __device__ __forceinline__ void smeb_halo_acquire(smeb_u32 *halo, int side,
 
 // waits (one thread) until the planes of stage `seq` have arrived from both
 // neighbours: the end of run(), before getters read ghost planes
-__global__ void smeb_halo_quiesce(smeb_u32 *halo, smeb_u32 mode, smeb_u32 seq) {
+__global__ void smeb_halo_quiesce(smeb_u32 *halo, smeb_u32 mode, smeb_u32 want,
+                                  smeb_u32 *err) {
+  // want: the count the words must have reached (stages x tiles of a plane)
   if (threadIdx.x == 0 && blockIdx.x == 0) {
     if (mode & 1u) {
-      smeb_halo_acquire(halo, 0, seq);
+      smeb_halo_acquire(halo, 0, want, err);
     }
     if (mode & 2u) {
-      smeb_halo_acquire(halo, 1, seq);
+      smeb_halo_acquire(halo, 1, want, err);
     }
   }
 }
@@ -1000,7 +1127,6 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   static_assert(SMEB_BLOCK % TY == 0 && TX % G == 0, "tile shape");
   static_assert(NST >= LOOK + 2, "ring too short");
 
-  smeb_pdl_trigger();
   __shared__ smeb_u64 fullBar[NST];
   unsigned char *ring = smeb_dyn_smem;
   {
@@ -1037,6 +1163,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   const int nIter = m1 - m0;
   if (nIter <= 0) {
     smeb_pdl_wait();
+    smeb_pdl_trigger();
     if constexpr ((F & SMEB_F_SUM_NS) != 0) {
       const size_t blk =
           ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x +
@@ -1047,7 +1174,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
     } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
                          (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
       if (threadIdx.x == 0) { // an empty CTA still counts towards the step's norms
-        smeb_err_arrive(a.err, a.errHost, a.errExpected);
+        smeb_err_arrive(a.errBase, a.errPairs, a.errHost, a.errExpected);
       }
     }
     return;
@@ -1079,36 +1206,6 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
                        (y0 - 1) * S - PAD, (m0 + j) * TX - 1, 0, bar);
     }
   };
-  if (tid == 0) {
-#pragma unroll
-    for (int s = 0; s < NST; ++s) {
-      smeb_mbar_init(barAddr + 8u * s, 1);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-  }
-  // everything above is independent of the kernels before this one
-  smeb_pdl_wait();
-  if constexpr (HALO) {
-    // a boundary chunk reads a ghost plane (its first / last load): the
-    // neighbour's plane of the previous stage must have arrived.  Both waits sit
-    // here, outside the march loop, which stays the single-GPU loop
-    if (tid == 0) {
-      if (haloLo) {
-        smeb_halo_acquire(a.halo, 0, a.haloSeq - 1u);
-      }
-      if (haloHi) {
-        smeb_halo_acquire(a.halo, 1, a.haloSeq - 1u);
-      }
-    }
-  }
-  if (tid == 0) {
-    for (int j = 0; j < NST && j < nLoads; ++j) {
-      issue(j, j);
-    }
-  }
-  __syncthreads();
-
   // per-thread geometry: Neumann faces as address selects
   const int offYm = gy == 0 ? 0 : -S;
   const int offYp = gy + 1 >= (int)a.ny ? 0 : S;
@@ -1157,22 +1254,62 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
       return gy < (int)a.ny && (m0 + it) * TX + r0 < (int)a.nx;
     }
   };
+  // The pre-step state c0 is not written by any kernel of this step, so its first
+  // planes are requested before the wait for the kernel in front of this one:
+  // they travel while that kernel drains.
 #pragma unroll
-  for (int q = 0; q < (AHC > AHS ? AHC : AHS); ++q) {
-    if (q < nIter && activeAt(q)) {
+  for (int q = 0; q < AHC; ++q) {
+    if constexpr (USE_C0) {
+      if (q < nIter && activeAt(q)) {
 #pragma unroll
-      for (int k = 0; k < RPT; ++k) {
-        if constexpr (USE_C0) {
-          if (q < AHC) {
-            smeb_load_voxel<S>(a.c0, g + q * marchStride + k * rowStride,
-                               c0q[q][k]);
-          }
+        for (int k = 0; k < RPT; ++k) {
+          smeb_load_voxel<S>(a.c0, g + q * marchStride + k * rowStride,
+                             c0q[q][k]);
         }
-        if constexpr (USE_S2IN) {
-          if (q < AHS) {
-            smeb_load_voxel<S>(a.s2in, g + q * marchStride + k * rowStride,
-                               s2q[q][k]);
-          }
+      }
+    }
+  }
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NST; ++s) {
+      smeb_mbar_init(barAddr + 8u * s, 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  // everything above is independent of the kernels before this one
+  smeb_pdl_wait();
+  smeb_pdl_trigger();
+  if constexpr (HALO) {
+    // a boundary chunk reads a ghost plane (its first / last load): the
+    // neighbour's plane of the previous stage must have arrived.  Both waits sit
+    // here, outside the march loop, which stays the single-GPU loop
+    if (tid == 0) {
+      const smeb_u32 want = (a.haloSeq - 1u) * (gridDim.x * gridDim.y);
+      if (haloLo) {
+        smeb_halo_acquire(a.halo, 0, want, a.haloErr);
+      }
+      if (haloHi) {
+        smeb_halo_acquire(a.halo, 1, want, a.haloErr);
+      }
+    }
+  }
+  if (tid == 0) {
+    for (int j = 0; j < NST && j < nLoads; ++j) {
+      issue(j, j);
+    }
+  }
+  __syncthreads();
+
+  // the running sum was written by the stage before this one: after the wait
+#pragma unroll
+  for (int q = 0; q < AHS; ++q) {
+    if constexpr (USE_S2IN) {
+      if (q < nIter && activeAt(q)) {
+#pragma unroll
+        for (int k = 0; k < RPT; ++k) {
+          smeb_load_voxel<S>(a.s2in, g + q * marchStride + k * rowStride,
+                             s2q[q][k]);
         }
       }
     }
@@ -1270,6 +1407,19 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
           smeb_store_voxel<S>(a.s2out, g + k * rowStride, s2q[0][k]);
         }
         smeb_store_voxel<S>(a.cout, g + k * rowStride, out);
+        if constexpr (HALO) {
+          // a boundary plane also goes into the neighbour's ghost plane: plain
+          // stores through the peer mapping, they drain while the march goes on
+          if ((haloLo && it == 0) || (haloHi && it == nIter - 1)) {
+            const size_t inPlane = (size_t)(gx0 + k) * a.ny + gy;
+            if (haloLo && it == 0) {
+              smeb_store_voxel<S>(a.peerLo, inPlane, out);
+            }
+            if (haloHi && it == nIter - 1) {
+              smeb_store_voxel<S>(a.peerHi, inPlane, out);
+            }
+          }
+        }
       }
     }
 #pragma unroll
@@ -1301,42 +1451,15 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
     }
   }
   if constexpr (HALO) {
-    // The boundary planes of this rank go into the neighbours' ghost planes: every
-    // thread reads back the voxels it stored (own writes, L2 hits) and stores them
-    // a second time through the peer mapping; then the CTA counts itself done and
-    // the last CTA of the plane releases the stage's number to the neighbour.
-    if (haloLo || haloHi) {
-      if (active) {
-        const size_t inPlane = (size_t)gx0 * a.ny + gy;
-        const size_t planeVox = (size_t)a.nx * a.ny;
-#pragma unroll
-        for (int k = 0; k < RPT; ++k) {
-          double v[S];
-          if (haloLo) {
-            smeb_load_voxel<S>(a.cout, (size_t)m0 * planeVox + inPlane + k * rowStride, v);
-            smeb_store_voxel<S>(a.peerLo, inPlane + k * rowStride, v);
-          }
-          if (haloHi) {
-            smeb_load_voxel<S>(a.cout,
-                               (size_t)(m1 - 1) * planeVox + inPlane + k * rowStride, v);
-            smeb_store_voxel<S>(a.peerHi, inPlane + k * rowStride, v);
-          }
-        }
+    // this CTA's tile of a boundary plane is in the neighbour's ghost plane (all
+    // threads are past the barrier that ended the last iteration): count it,
+    // with release semantics, in the neighbour's memory
+    if (tid == 0) {
+      if (haloLo) {
+        smeb_red_release_sys(a.peerFlagLo, 1u);
       }
-      __threadfence_system(); // this thread's peer stores, before the barrier
-      __syncthreads();
-      if (tid == 0) {
-        const smeb_u32 tiles = gridDim.x * gridDim.y;
-        if (haloLo && atomicAdd(a.halo + 2, 1u) + 1u == tiles) {
-          atomicExch(a.halo + 2, 0u);
-          __threadfence_system();
-          smeb_st_release_sys(a.peerFlagLo, a.haloSeq);
-        }
-        if (haloHi && atomicAdd(a.halo + 3, 1u) + 1u == tiles) {
-          atomicExch(a.halo + 3, 0u);
-          __threadfence_system();
-          smeb_st_release_sys(a.peerFlagHi, a.haloSeq);
-        }
+      if (haloHi) {
+        smeb_red_release_sys(a.peerFlagHi, 1u);
       }
     }
   }
@@ -1346,7 +1469,268 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
     smeb_block_sum<R::NNS>(nsacc, a.nsPartial + blk * R::NNS);
   } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
                        (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
-    smeb_block_max2(eabs, erel, a.err, a.errHost, a.errExpected);
+    smeb_block_max2(eabs, erel, a.err, a.errBase, a.errPairs, a.errHost,
+                    a.errExpected);
+  }
+}
+
+// ---- segment-staged stage kernel for voxel-list compartments -------------------
+// The voxel list is z-major with y fastest (geometry.cpp:55-72), so along a piece
+// of a run (consecutive voxels with constant index distances to the neighbouring
+// columns / planes, see smeb_neighbours) the -y / +y neighbours are the voxels
+// before / after, and the +x, -x (+z, -z) neighbours of the piece are CONTIGUOUS
+// ranges of the state array: [i0 + d, i0 + d + L).  A CTA therefore stages, per
+// segment, three (3-D: five) rows of the stage input in shared memory with 1-D
+// bulk copies (cp.async.bulk + mbarrier complete_tx), NST segments deep, and all
+// seven stencil operands come from shared memory.  The bytes in flight no longer
+// depend on how many gathers a thread can have outstanding: the direct kernel
+// (smeb_stage_nn) waited on its code -> run deltas -> gather chain with 55-70 %
+// long-scoreboard stalls at 5 resident CTAs.  Segments are handed out round robin
+// (segment = block + j * grid), so the CTAs that run together work on a
+// contiguous window of the list and the rows they share meet in L2.  A voxel
+// whose neighbour does not exist (code bit off) uses its own value; the rows are
+// clamped to the array, so such a voxel's slot may hold anything and is never
+// read.  Voxels flagged SMEB_MEMB_FLAG are left to smeb_stage_memb.
+__device__ __forceinline__ void smeb_bulk_load(smeb_u32 dst, const void *src,
+                                               smeb_u32 bytes, smeb_u32 bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes "
+               "[%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+
+#ifndef SMEB_SEG_MIN_CTAS
+#define SMEB_SEG_MIN_CTAS 4 // resident CTAs per SM the register allocation aims at
+#endif
+template <class R, unsigned F, int SEG, int NST, bool Z>
+__device__ __forceinline__ void smeb_stage_seg_body(const SmebStageArgs<R::S> &a) {
+  constexpr int S = R::S;
+  static_assert(S % 2 == 0, "bulk copies need 16-byte voxels");
+  static_assert(SEG % SMEB_BLOCK == 0, "segment length");
+  constexpr int VPT = SEG / SMEB_BLOCK; // voxels per thread and segment
+  constexpr int NROW = Z ? 5 : 3;       // own (+ halo), +x, -x (, +z, -z)
+  constexpr smeb_u32 VB = S * 8;        // bytes per voxel
+  constexpr smeb_u32 OWN_BYTES = (SEG + 2) * VB;
+  constexpr smeb_u32 ROW_BYTES = SEG * VB;
+  constexpr smeb_u32 STAGE_BYTES =
+      (OWN_BYTES + (NROW - 1) * ROW_BYTES + 127u) & ~127u;
+  constexpr bool USE_C0 = (F & SMEB_F_USE_C0) != 0 &&
+                          (F & (SMEB_F_OUT_DCDT | SMEB_F_SUM_NS)) == 0;
+  __shared__ smeb_u64 fullBar[NST];
+  unsigned char *ring = smeb_dyn_smem;
+  {
+    const smeb_u32 mis = smeb_smem_addr(ring) & 127u;
+    ring += (128u - mis) & 127u;
+  }
+  const smeb_u32 ringAddr = smeb_smem_addr(ring);
+  const smeb_u32 barAddr = smeb_smem_addr(fullBar);
+  const int tid = threadIdx.x;
+  const smeb_u32 G = gridDim.x;
+  const int nMine =
+      blockIdx.x < a.nSeg ? (int)((a.nSeg - 1u - blockIdx.x) / G) + 1 : 0;
+  const uint2 *segs = reinterpret_cast<const uint2 *>(a.seg);
+  const int4 *runs = reinterpret_cast<const int4 *>(a.runs);
+
+  // thread 0: bulk copies of segment j of this CTA into ring slot j % NST
+  auto issue = [&](int j) {
+    const uint2 sd = segs[blockIdx.x + (smeb_u32)j * G];
+    const long long i0 = sd.x, L = sd.y, n = a.n;
+    const int4 d = runs[a.nn[sd.x] & ((1u << SMEB_RUN_BITS) - 1u)];
+    const int slot = j % NST;
+    const smeb_u32 base = ringAddr + slot * STAGE_BYTES;
+    const smeb_u32 bar = barAddr + 8u * slot;
+    long long src[NROW], cnt[NROW];
+    smeb_u32 dst[NROW];
+    // own row with one voxel of halo on each side, clamped to the array
+    {
+      const long long lo = i0 > 0 ? i0 - 1 : i0;
+      const long long hi = i0 + L + 1 < n ? i0 + L + 1 : n;
+      src[0] = lo;
+      cnt[0] = hi - lo;
+      dst[0] = base + (smeb_u32)(lo - (i0 - 1)) * VB;
+    }
+    const int delta[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+    for (int r = 1; r < NROW; ++r) {
+      const long long s0 = i0 + delta[r - 1];
+      const long long lo = s0 > 0 ? s0 : 0;
+      const long long hi = s0 + L < n ? s0 + L : n;
+      // delta 0: no voxel of the run has a neighbour in this direction
+      const bool used = delta[r - 1] != 0 && hi > lo;
+      src[r] = lo;
+      cnt[r] = used ? hi - lo : 0;
+      dst[r] = base + OWN_BYTES + (smeb_u32)(r - 1) * ROW_BYTES +
+               (smeb_u32)(lo - s0) * VB;
+    }
+    smeb_u32 total = 0;
+#pragma unroll
+    for (int r = 0; r < NROW; ++r) {
+      total += (smeb_u32)cnt[r] * VB;
+    }
+    smeb_mbar_expect_tx(bar, total);
+#pragma unroll
+    for (int r = 0; r < NROW; ++r) {
+      if (cnt[r] > 0) {
+        smeb_bulk_load(dst[r], a.cin + src[r] * S, (smeb_u32)cnt[r] * VB, bar);
+      }
+    }
+  };
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < NST; ++s) {
+      smeb_mbar_init(barAddr + 8u * s, 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  smeb_pdl_wait();
+  smeb_pdl_trigger();
+  if (tid == 0) {
+    for (int j = 0; j < NST && j < nMine; ++j) {
+      issue(j);
+    }
+  }
+  __syncthreads();
+
+  double eabs = 0.0, erel = 0.0;
+  double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
+  // neighbour codes and the pre-step state of a thread's voxels are fetched one
+  // segment early with plain coalesced loads
+  smeb_u32 codeN[VPT];
+  double c0N[VPT][S];
+  auto prefetch = [&](int j) {
+#pragma unroll
+    for (int v = 0; v < VPT; ++v) {
+      codeN[v] = 0u;
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        c0N[v][s] = 0.0;
+      }
+    }
+    if (j < nMine) {
+      const uint2 sd = segs[blockIdx.x + (smeb_u32)j * G];
+#pragma unroll
+      for (int v = 0; v < VPT; ++v) {
+        const smeb_u32 t = tid + v * SMEB_BLOCK;
+        if (t < sd.y) {
+          codeN[v] = a.nn[sd.x + t];
+          if constexpr (USE_C0) {
+            smeb_load_voxel<S>(a.c0, sd.x + t, c0N[v]);
+          }
+        }
+      }
+    }
+  };
+  prefetch(0);
+  for (int j = 0; j < nMine; ++j) {
+    const uint2 sd = segs[blockIdx.x + (smeb_u32)j * G];
+    smeb_u32 code[VPT];
+    double c0v[VPT][S];
+#pragma unroll
+    for (int v = 0; v < VPT; ++v) {
+      code[v] = codeN[v];
+#pragma unroll
+      for (int s = 0; s < S; ++s) {
+        c0v[v][s] = c0N[v][s];
+      }
+    }
+    prefetch(j + 1);
+    const int slot = j % NST;
+    smeb_mbar_wait(barAddr + 8u * slot, (smeb_u32)(j / NST) & 1u);
+    const double *own =
+        reinterpret_cast<const double *>(ring + slot * STAGE_BYTES);
+    const double *rows = own + (SEG + 2) * S;
+    // The VPT voxels of a thread are independent: the stencil and reaction
+    // arithmetic of all of them is written without branches so that the compiler
+    // interleaves their fp64 dependency chains; only the global loads and stores
+    // are predicated (a slot beyond a short segment holds stale data that is
+    // computed on and dropped).
+    bool valid[VPT];
+    double c[VPT][S], f[VPT][S];
+#pragma unroll
+    for (int v = 0; v < VPT; ++v) {
+      const smeb_u32 t = tid + v * SMEB_BLOCK;
+      valid[v] = t < sd.y && (code[v] & SMEB_MEMB_FLAG) == 0u;
+      const smeb_u32 fl = code[v] >> SMEB_RUN_BITS;
+      const double *o = own + (t + 1) * S;
+      double xp[S], xm[S], yp[S], ym[S], zp[S], zm[S];
+      smeb_lds<S>(o, c[v]);
+      smeb_lds<S>((fl & 1u) ? rows + t * S : o, xp);
+      smeb_lds<S>((fl & 2u) ? rows + (SEG + t) * S : o, xm);
+      smeb_lds<S>((fl & 4u) ? o + S : o, yp);
+      smeb_lds<S>((fl & 8u) ? o - S : o, ym);
+      if constexpr (Z) {
+        smeb_lds<S>((fl & 16u) ? rows + (2 * SEG + t) * S : o, zp);
+        smeb_lds<S>((fl & 32u) ? rows + (3 * SEG + t) * S : o, zm);
+      } else {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+          zp[s] = c[v][s];
+          zm[s] = c[v][s];
+        }
+      }
+      smeb_rhs_values<R>(a, c[v], xp, xm, yp, ym, zp, zm, f[v]);
+    }
+#pragma unroll
+    for (int v = 0; v < VPT; ++v) {
+      const size_t i = (size_t)sd.x + tid + v * SMEB_BLOCK;
+      if constexpr ((F & SMEB_F_SUM_NS) != 0) {
+        double pick[R::NNS > 0 ? R::NNS : 1];
+        R::nonSpatialPick(f[v], pick);
+#pragma unroll
+        for (int q = 0; q < R::NNS; ++q) {
+          nsacc[q] += valid[v] ? pick[q] : 0.0;
+        }
+      } else {
+        constexpr bool onDemand =
+            (F & (SMEB_F_OUT_DCDT | SMEB_F_OUT_LOWER | SMEB_F_OUT_CNEW)) != 0;
+        double s2v[S], out[S];
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+          s2v[s] = 0.0;
+        }
+        if constexpr ((F & SMEB_F_USE_S2IN) != 0 && (F & SMEB_F_OUT_DCDT) == 0) {
+          if (valid[v]) {
+            smeb_load_voxel<S>(a.s2in, i, s2v);
+          }
+        }
+        double ea = eabs, er = erel;
+        smeb_update<R, F>(a, c[v], f[v], c0v[v], s2v, out, ea, er);
+        if (valid[v]) {
+          eabs = ea;
+          erel = er;
+          if constexpr ((F & SMEB_F_WRITE_S2) != 0 && !onDemand) {
+            smeb_store_voxel<S>(a.s2out, i, s2v);
+          }
+          smeb_store_voxel<S>(a.cout, i, out);
+        }
+      }
+    }
+    __syncthreads(); // every thread is done with this slot
+    if (tid == 0 && j + NST < nMine) {
+      issue(j + NST);
+    }
+  }
+  if constexpr ((F & SMEB_F_SUM_NS) != 0) {
+    smeb_block_sum<R::NNS>(nsacc, a.nsPartial + (size_t)blockIdx.x * R::NNS);
+  } else if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0) ||
+                       (F & (SMEB_F_RELAX_A | SMEB_F_RELAX_B)) != 0) {
+    smeb_block_max2(eabs, erel, a.err, a.errBase, a.errPairs, a.errHost,
+                    a.errExpected);
+  }
+}
+
+template <class R, unsigned F, int SEG, int NST, bool Z>
+__global__ void __launch_bounds__(SMEB_BLOCK, SMEB_SEG_MIN_CTAS)
+    smeb_stage_seg(const __grid_constant__ SmebStageArgs<R::S> ain) {
+  if constexpr ((F & SMEB_F_MEMBERS) != 0) {
+    SmebStageArgs<R::S> a = ain;
+    if (smeb_member_select<R, F>(a)) {
+      smeb_stage_seg_body<R, F, SEG, NST, Z>(a);
+    }
+  } else {
+    smeb_stage_seg_body<R, F, SEG, NST, Z>(ain);
   }
 }
 

@@ -145,6 +145,22 @@ void Sim::generateSource(const smeb200_problem &p) {
   if (const char *env = std::getenv("SMEB200_NN_MIN_CTAS");
       env != nullptr && env[0] >= '0' && env[0] <= '8') {
     src << "#define SMEB_NN_MIN_CTAS " << env[0] << "\n"; // A/B measurements
+  } else {
+    // small models (<= 2 species, uniform diffusion): the voxel-list kernel is
+    // held to 48 registers, five resident CTAs per SM; larger ones would spill
+    bool small = p.n_compartments > 0;
+    for (uint32_t c = 0; c < p.n_compartments; ++c) {
+      const auto &pc = p.compartments[c];
+      small = small && pc.n_species <= 2 && pc.diffusion_array == nullptr &&
+              pc.n_cross_diffusion == 0;
+    }
+    if (small) {
+      src << "#define SMEB_NN_MIN_CTAS 5\n";
+    }
+  }
+  if (const char *env = std::getenv("SMEB200_SEG_MIN_CTAS");
+      env != nullptr && env[0] >= '1' && env[0] <= '8') {
+    src << "#define SMEB_SEG_MIN_CTAS " << env[0] << "\n"; // A/B measurements
   }
   if (const char *env = std::getenv("SMEB200_NN_PREFETCH");
       env != nullptr && env[0] >= '0' && env[0] <= '2') {
@@ -313,6 +329,9 @@ std::string Sim::kernelName(std::size_t ci, uint32_t flags, bool memb) const {
       << (c.tile.m3 ? "true" : "false") << ">";
   } else if (c.geom == Geom::BOX) {
     s << "smeb_stage_box<Reac" << ci << ", " << flags << "u>";
+  } else if (c.geom == Geom::SEG) {
+    s << "smeb_stage_seg<Reac" << ci << ", " << flags << "u, " << c.segLen << ", "
+      << c.segNst << ", " << (c.segZ ? "true" : "false") << ">";
   } else {
     s << "smeb_stage_nn<Reac" << ci << ", " << flags << "u>";
   }
@@ -409,10 +428,12 @@ StageKernels Sim::lookup(const Module &m, std::size_t ci,
   auto it = m.fn.find(kernelName(ci, flags, false));
   if (it != m.fn.end()) {
     k.main = it->second;
-    if (comps[ci].geom == Geom::TILE) {
+    if (comps[ci].geom == Geom::TILE || comps[ci].geom == Geom::SEG) {
       check(drv.FuncSetAttribute(
                 k.main, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES,
-                static_cast<int>(comps[ci].tile.dynSmem)),
+                static_cast<int>(comps[ci].geom == Geom::TILE
+                                     ? comps[ci].tile.dynSmem
+                                     : comps[ci].segSmem)),
             "cuFuncSetAttribute(max dynamic shared memory)");
     }
   }
@@ -526,6 +547,97 @@ bool compressNeighbourTable(const uint32_t *nn, uint64_t n,
                             runs);
 }
 
+// ---- segment-staged voxel-list kernel (device_kernels.cuh: smeb_stage_seg) -------
+// Decides per voxel-list compartment whether its stage kernels stage pieces of
+// runs in shared memory, and cuts the list into those pieces.  Conditions: the
+// run-compressed neighbour codes exist, voxels are 16-byte multiples (even
+// species count: the bulk copies), uniform diffusion without cross terms (the
+// staged operands are the seven states), one GPU (a z-slab updates a sub-range),
+// and runs long enough that a piece fills most of a CTA.  variant 1 / 3 keep the
+// direct kernel, SMEB200_SEG=0 does too (A/B).
+void Sim::chooseSegments(int variant,
+                         std::vector<std::vector<uint32_t>> &nnHost) {
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    auto &c = comps[ci];
+    if (c.box || c.S == 0 || c.n == 0 || compileOnly || nnHost[ci].empty() ||
+        variant == 3) {
+      continue;
+    }
+    if (!compressNeighbours(nnHost[ci], c.n, c.hostCodes, c.hostRuns)) {
+      c.hostCodes.clear();
+      c.hostRuns.clear();
+      continue;
+    }
+    // Measured on B200 (profiles/r2_seg_ab.md): 8192^2 two-compartment brusselator
+    // RK323 0.469 ms per stage launch against 0.470 ms of the direct kernel, the
+    // 4096^2 disc 0.062 against 0.054 ms — both kernels sit at the same 76 % of the
+    // HBM rate, limited by instruction issue and fp64 latency per voxel, not by
+    // loads in flight.  The staged kernel therefore stays opt-in (kernel_variant 4
+    // or SMEB200_SEG=1).
+    const char *segEnv = std::getenv("SMEB200_SEG");
+    const bool wanted = variant == 4 || (segEnv != nullptr && segEnv[0] == '1');
+    if (!wanted || nRanks > 1 || c.S % 2 != 0 || c.nonUniform ||
+        !c.crossTarget.empty()) {
+      continue;
+    }
+    bool z = false;
+    for (std::size_t r = 0; r < c.hostRuns.size() / 4; ++r) {
+      z = z || c.hostRuns[4 * r + 2] != 0 || c.hostRuns[4 * r + 3] != 0;
+    }
+    // piece length: 512 voxels where four stages of (own + halo, +x, -x [, +z,
+    // -z]) rows fit beside a second CTA, else 256
+    const unsigned rows = z ? 5u : 3u;
+    int seg = 0, nst = 2; // two stages of 512 voxels: four CTAs per SM
+    int forcedLen = 0;
+    if (const char *env = std::getenv("SMEB200_SEG_NST"); env != nullptr) {
+      nst = std::max(2, std::min(8, std::atoi(env))); // A/B measurements
+    }
+    if (const char *env = std::getenv("SMEB200_SEG_LEN"); env != nullptr) {
+      forcedLen = std::atoi(env);
+    }
+    for (int cand : {1024, 512, 256}) {
+      if (cand == 1024 && forcedLen != 1024) {
+        continue; // four voxels per thread: A/B measurements only
+      }
+      const unsigned stage =
+          ((static_cast<unsigned>(cand) * rows + 2u) * c.S * 8u + 127u) & ~127u;
+      if ((forcedLen == 0 || forcedLen == cand) &&
+          stage * static_cast<unsigned>(nst) + 128u <= 200u * 1024u) {
+        seg = cand;
+        c.segSmem = stage * static_cast<unsigned>(nst) + 128u;
+        break;
+      }
+    }
+    if (seg == 0) {
+      continue;
+    }
+    constexpr uint32_t runMask = (1u << 25) - 1u;
+    std::vector<uint32_t> segs;
+    uint64_t i = 0;
+    while (i < c.n) {
+      const uint32_t run = c.hostCodes[i] & runMask;
+      uint64_t e = i + 1;
+      while (e < c.n && e - i < static_cast<uint64_t>(seg) &&
+             (c.hostCodes[e] & runMask) == run) {
+        ++e;
+      }
+      segs.push_back(static_cast<uint32_t>(i));
+      segs.push_back(static_cast<uint32_t>(e - i));
+      i = e;
+    }
+    const double avg = static_cast<double>(c.n) / (segs.size() / 2);
+    if (avg < 0.4 * seg) {
+      continue; // short runs (cell outlines): the direct kernel
+    }
+    c.geom = Geom::SEG;
+    c.segLen = seg;
+    c.segNst = nst;
+    c.segZ = z;
+    c.nSeg = static_cast<uint32_t>(segs.size() / 2);
+    c.hostSeg = std::move(segs);
+  }
+}
+
 constexpr unsigned SMEB_TILE_CTAS_PER_SM = 2; // device_kernels.cuh SMEB_TILE_MIN_CTAS
 
 // ---- geometry path per compartment -------------------------------------------
@@ -536,8 +648,7 @@ constexpr unsigned SMEB_TILE_CTAS_PER_SM = 2; // device_kernels.cuh SMEB_TILE_MI
 void Sim::chooseGeometry(int variant) {
   for (auto &c : comps) {
     if (!c.box) {
-      c.geom = Geom::NN;
-      continue;
+      continue; // Geom::NN, or Geom::SEG chosen by chooseSegments
     }
     c.geom = Geom::BOX;
     // per-voxel diffusion constants and cross-diffusion live in the direct
@@ -1129,12 +1240,19 @@ void Sim::build(const smeb200_problem &p) {
     }
   } else {
     setupMembranes(p, nnHost);
+    chooseSegments(p.kernel_variant, nnHost);
   }
   chooseGeometry(p.kernel_variant);
   // z-slabs of box compartments on the TMA tile path exchange their halos inside
   // the stage kernels (device_kernels.cuh: "halo exchange inside the stage
   // kernel"); every other combination keeps the stream-ordered exchange
-  if (nRanks > 1 && !envFlagOff("SMEB200_FUSED_HALO") && !nsInSlabs) {
+  // Measured on 2 B200s (profiles/r2_halo_ab.md), 64 planes per rank: 0.264 ms per
+  // step against 0.243 ms with boundary-plane launches and copy-engine pushes on
+  // the halo stream — the kernel variant alone costs 4 us per step and the
+  // stores through the peer mapping 10 more — so the in-kernel exchange is opt-in
+  // (SMEB200_FUSED_HALO=1).
+  const char *fusedEnv = std::getenv("SMEB200_FUSED_HALO");
+  if (nRanks > 1 && fusedEnv != nullptr && fusedEnv[0] == '1' && !nsInSlabs) {
     bool any = false, all = true;
     for (const auto &c : comps) {
       if (c.S == 0 || c.n == 0) {
@@ -1213,13 +1331,17 @@ void Sim::build(const smeb200_problem &p) {
                           nv * sizeof(double), cudaMemcpyHostToDevice, stream),
           "upload initial concentrations");
     if (!c.box) {
-      std::vector<uint32_t> codes;
-      std::vector<int> runs;
-      if (p.kernel_variant != 3 && compressNeighbours(nnHost[ci], c.n, codes, runs)) {
-        c.nRuns = static_cast<uint32_t>(runs.size() / 4);
-        c.dNn = devUpload(codes, stream, "upload neighbour codes");
-        c.dRuns = devUpload(runs, stream, "upload neighbour runs");
+      if (!c.hostCodes.empty()) {
+        c.nRuns = static_cast<uint32_t>(c.hostRuns.size() / 4);
+        c.dNn = devUpload(c.hostCodes, stream, "upload neighbour codes");
+        c.dRuns = devUpload(c.hostRuns, stream, "upload neighbour runs");
+        if (c.geom == Geom::SEG) {
+          c.dSeg = devUpload(c.hostSeg, stream, "upload segment table");
+        }
         check(cudaStreamSynchronize(stream), "upload neighbour codes");
+        c.hostCodes = {};
+        c.hostRuns = {};
+        c.hostSeg = {};
       } else {
         c.dNn = devUpload(nnHost[ci], stream, "upload neighbour list");
       }
@@ -1231,7 +1353,7 @@ void Sim::build(const smeb200_problem &p) {
       c.kStage.push_back(lookup(mainModule, ci, stageFlags(sd)));
       // occupancy queries up front: none while a step is being captured
       if (c.geom != Geom::TILE && c.kStage.back().main != nullptr) {
-        persistentGrid(c.kStage.back().main);
+        persistentGrid(c.kStage.back().main, c.geom == Geom::SEG ? c.segSmem : 0u);
       }
       if (c.kStage.back().memb != nullptr) {
         persistentGrid(c.kStage.back().memb);
@@ -1249,7 +1371,7 @@ void Sim::build(const smeb200_problem &p) {
       c.kRelaxB = lookup(mainModule, ci, F_RELAX_B | F_USE_C0);
       for (const auto &k : {c.kRelaxA, c.kRelaxB}) {
         if (c.geom != Geom::TILE && k.main != nullptr) {
-          persistentGrid(k.main);
+          persistentGrid(k.main, c.geom == Geom::SEG ? c.segSmem : 0u);
         }
         if (k.memb != nullptr) {
           persistentGrid(k.memb);
@@ -1273,7 +1395,7 @@ void Sim::build(const smeb200_problem &p) {
     if (!c.nonSpatial.empty()) {
       c.kSumNs = lookup(mainModule, ci, F_SUM_NS);
       if (c.geom != Geom::TILE && c.kSumNs.main != nullptr) {
-        persistentGrid(c.kSumNs.main);
+        persistentGrid(c.kSumNs.main, c.geom == Geom::SEG ? c.segSmem : 0u);
       }
       if (c.kSumNs.memb != nullptr) {
         persistentGrid(c.kSumNs.memb);
@@ -1446,8 +1568,9 @@ void Sim::connectSlabs() {
   }
   mine.fusedHalo = fusedHalo ? 1 : 0;
   if (fusedHalo) {
-    dHalo = devAlloc<uint32_t>(16, "allocate halo flags");
-    check(cudaMemset(dHalo, 0, 16 * sizeof(uint32_t)), "clear halo flags");
+    static_assert(2 * kCommMaxCompartments < kHaloErrWord, "halo words");
+    dHalo = devAlloc<uint32_t>(kHaloWords, "allocate halo flags");
+    check(cudaMemset(dHalo, 0, kHaloWords * sizeof(uint32_t)), "clear halo flags");
     cudaIpcMemHandle_t h{};
     check(cudaIpcGetMemHandle(&h, dHalo), "cudaIpcGetMemHandle");
     std::memcpy(mine.flagHandle, &h, sizeof(h));
@@ -1609,15 +1732,27 @@ void Sim::haloQuiesce() {
   if (!haloPending) {
     return;
   }
+  if (fusedHalo && std::getenv("SMEB200_HALO_DEBUG") != nullptr) {
+    haloPending = false; // timing experiments: nothing was exchanged
+    return;
+  }
   if (fusedHalo) {
-    // one thread waits for the neighbours' planes of the last stage
+    // one thread per compartment waits for the neighbours' planes of the last
+    // stage: every stage adds one count per tile of a boundary plane
     uint32_t mode = (rank > 0 ? 1u : 0u) | (rank + 1 < nRanks ? 2u : 0u);
-    uint32_t seq = haloSeq;
-    uint32_t *flags = dHalo;
-    void *params[] = {&flags, &mode, &seq};
-    check(DriverApi::get().LaunchKernel(kHaloQuiesce, 1, 1, 1, 32, 1, 1, 0, stream,
-                                        params, nullptr),
-          "launch halo wait kernel");
+    for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+      const auto &c = comps[ci];
+      if (c.S == 0 || c.n == 0) {
+        continue;
+      }
+      uint32_t want = haloSeq * (c.tile.grid[0] * c.tile.grid[1]);
+      uint32_t *words = dHalo + 2 * ci;
+      uint32_t *err = dHalo + kHaloErrWord;
+      void *params[] = {&words, &mode, &want, &err};
+      check(DriverApi::get().LaunchKernel(kHaloQuiesce, 1, 1, 1, 32, 1, 1, 0,
+                                          stream, params, nullptr),
+            "launch halo wait kernel");
+    }
     haloPending = false;
     return;
   }
@@ -1637,10 +1772,11 @@ void Sim::checkHaloError() {
     return;
   }
   uint32_t flag = 0;
-  check(cudaMemcpy(&flag, dHalo + 4, sizeof(flag), cudaMemcpyDeviceToHost),
+  check(cudaMemcpy(&flag, dHalo + kHaloErrWord, sizeof(flag),
+                   cudaMemcpyDeviceToHost),
         "read halo status");
   if (flag != 0) {
-    check(cudaMemset(dHalo + 4, 0, sizeof(flag)), "clear halo status");
+    check(cudaMemset(dHalo + kHaloErrWord, 0, sizeof(flag)), "clear halo status");
     throw Error("smeb200: timed out waiting for the halo planes of the rank " +
                 std::string(flag == 1 ? "below" : "above"));
   }
@@ -1659,11 +1795,17 @@ void Sim::abortSlabs() noexcept {
     // wait the neighbours can still have queued
     const uint32_t far = haloSeq + 0x40000000u;
     if (fusedHalo) {
-      if (rank > 0 && peerHalo[0] != nullptr) {
-        cudaMemcpy(peerHalo[0] + 1, &far, sizeof(far), cudaMemcpyHostToDevice);
-      }
-      if (rank + 1 < nRanks && peerHalo[1] != nullptr) {
-        cudaMemcpy(peerHalo[1], &far, sizeof(far), cudaMemcpyHostToDevice);
+      for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+        const uint32_t farCount =
+            haloSeq * (comps[ci].tile.grid[0] * comps[ci].tile.grid[1]) + 0x40000000u;
+        if (rank > 0 && peerHalo[0] != nullptr) {
+          cudaMemcpy(peerHalo[0] + 2 * ci + 1, &farCount, sizeof(farCount),
+                     cudaMemcpyHostToDevice);
+        }
+        if (rank + 1 < nRanks && peerHalo[1] != nullptr) {
+          cudaMemcpy(peerHalo[1] + 2 * ci, &farCount, sizeof(farCount),
+                     cudaMemcpyHostToDevice);
+        }
       }
       cudaGetLastError();
     } else {
@@ -1731,6 +1873,7 @@ Sim::~Sim() {
     }
     cudaFree(c.dNn);
     cudaFree(c.dRuns);
+    cudaFree(c.dSeg);
     cudaFree(c.dMvox);
     cudaFree(c.dMstart);
     cudaFree(c.dEnt);
@@ -1791,6 +1934,45 @@ Sim::~Sim() {
   cudaStreamDestroy(stream);
 }
 
+StageArgsHost Sim::stageArgsTemplate(std::size_t ci,
+                                     std::size_t stageIndex) const {
+  const StageDesc &sd = plan[stageIndex];
+  const auto &c = comps[ci];
+  StageArgsHost a{};
+  a.nn = c.dNn;
+  a.runs = c.dRuns;
+  a.seg = c.dSeg;
+  a.nSeg = c.nSeg;
+  a.err = dErr;
+  a.errBase = dErr;
+  a.errPairs = 1;
+  a.errHost = dErrRing;
+  a.n = static_cast<uint32_t>(c.n - c.vGhostHi);
+  a.v0 = c.vGhostLo;
+  a.nx = c.nx;
+  a.ny = c.ny;
+  a.nz = c.nz;
+  a.z_begin = c.zLoGhost;
+  a.z_end = c.nz - c.zHiGhost;
+  a.g1 = sd.g1;
+  a.g2 = sd.g2;
+  a.g3 = sd.g3;
+  a.beta = sd.beta;
+  a.delta = sd.delta;
+  a.cF = sd.cF;
+  a.s2F = sd.s2F;
+  a.s3F = sd.s3F;
+  a.eps = epsilon;
+  std::copy(c.D.begin(), c.D.end(), a.D);
+  std::copy(params.begin(), params.end(), a.D + 3 * c.S);
+  a.nsAv = c.dNsAv;
+  a.nsPartial = c.dNsPartial;
+  a.darr = c.dDarr;
+  a.xdMax = c.dXdMax;
+  std::copy(h2, h2 + 3, a.h2);
+  return a;
+}
+
 // ---- one fused stage over all compartments ----------------------------------
 // replaces calculateDcdt() + the RK substep (+ error norm, + clamp) of
 // pixelsim.cpp:92-120,194-205
@@ -1838,21 +2020,10 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     Item item;
     item.ci = ci;
     StageArgsHost &a = item.a;
-    a = StageArgsHost{};
+    a = stageArgsTemplate(ci, stageIndex);
     a.cin = c.buf[c.role[sd.cin]];
     a.cout = c.buf[c.role[sd.cout]];
     a.c0 = c.buf[c.role[CUR]];
-    a.nn = c.dNn;
-    a.runs = c.dRuns;
-    a.err = dErr;
-    a.errHost = dErrRing;
-    a.n = static_cast<uint32_t>(c.n - c.vGhostHi);
-    a.v0 = c.vGhostLo;
-    a.nx = c.nx;
-    a.ny = c.ny;
-    a.nz = c.nz;
-    a.z_begin = c.zLoGhost;
-    a.z_end = c.nz - c.zHiGhost;
     if (c.haveOverride && stageIndex == 0) {
       // RK323 / RK435: the stage works on the relaxed copy, the pre-step state
       // c0 stays what doRKInit saved before the relaxation (pixelsim.cpp:166-171)
@@ -1868,36 +2039,37 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
     if (sd.writeS2) {
       a.s2out = c.buf[c.role[RS]];
     }
-    a.g1 = sd.g1;
-    a.g2 = sd.g2;
-    a.g3 = sd.g3;
     a.bdt = sd.beta * dt;
-    a.beta = sd.beta;
     a.dtp = capturing ? dDt : nullptr;
-    a.delta = sd.delta;
-    a.cF = sd.cF;
-    a.s2F = sd.s2F;
-    a.s3F = sd.s3F;
-    a.eps = epsilon;
-    std::copy(c.D.begin(), c.D.end(), a.D);
-    std::copy(params.begin(), params.end(), a.D + 3 * c.S);
-    a.nsAv = c.dNsAv;
-    a.nsPartial = c.dNsPartial;
-    a.darr = c.dDarr;
-    a.xdMax = c.dXdMax;
-    std::copy(h2, h2 + 3, a.h2);
     if (fusedHalo) {
       const int coutBuf = c.role[sd.cout];
       a.haloMode = (rank > 0 ? 1u : 0u) | (rank + 1 < nRanks ? 2u : 0u);
-      a.halo = dHalo;
+      a.halo = dHalo + 2 * ci;
+      a.haloErr = dHalo + kHaloErrWord;
       a.haloSeq = haloSeq;
       if (rank > 0) {
         a.peerLo = peerBuf[0][ci][coutBuf] + comm->segment()->slot[rank - 1].ghostHiOff[ci];
-        a.peerFlagLo = peerHalo[0] + 1;
+        a.peerFlagLo = peerHalo[0] + 2 * ci + 1;
       }
       if (rank + 1 < nRanks) {
         a.peerHi = peerBuf[1][ci][coutBuf];
-        a.peerFlagHi = peerHalo[1];
+        a.peerFlagHi = peerHalo[1] + 2 * ci;
+      }
+      // timing experiments only (results are wrong): 1 = the boundary planes are
+      // stored into local scratch memory instead of the neighbour's, nobody
+      // waits; 2 = no boundary work at all in the halo-variant kernel
+      static const int dbg = std::getenv("SMEB200_HALO_DEBUG") != nullptr
+                                 ? std::atoi(std::getenv("SMEB200_HALO_DEBUG"))
+                                 : 0;
+      if (dbg == 1) {
+        if (c.scratch == nullptr) {
+          c.scratch = devAlloc<double>(c.n * c.S, "allocate scratch buffer");
+        }
+        a.peerLo = a.peerHi = c.scratch;
+        a.peerFlagLo = a.peerFlagHi = dHalo + 12;
+        a.haloSeq = 1;
+      } else if (dbg == 2) {
+        a.haloMode = 0;
       }
     }
     if (overlapHalo) {
@@ -2134,7 +2306,13 @@ void Sim::solveZeroStorageConstraints(std::size_t stageIndex) {
       a.cout = second ? c.pool[1].p : c.pool[0].p;
       a.nn = c.dNn;
       a.runs = c.dRuns;
+      a.seg = c.dSeg;
+      a.nSeg = c.nSeg;
       a.err = dErr;
+      a.errBase = dErr;
+      a.errPairs = 1;
+    a.errBase = dErr;
+    a.errPairs = 1;
       a.errHost = dErrRing;
       a.errExpected = expected;
       a.n = static_cast<uint32_t>(c.n);
@@ -2259,7 +2437,8 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
   } else {
     const unsigned grid = mainGrid(ci, a, k.main);
     void *params[] = {&a};
-    launchKernel(k.main, grid, 1, 1, 0, sMain, params);
+    launchKernel(k.main, grid, 1, 1, c.geom == Geom::SEG ? c.segSmem : 0u, sMain,
+                 params);
     nsBlocks = grid;
   }
   if (doMain) {
@@ -2274,8 +2453,9 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     }
   }
   if (c.nMvox > 0 && doMemb) {
-    // SmebMembArgs: 4 pointers, SMEB_NCOMP pointers, 2 x u32
-    std::vector<unsigned long long> blob(4 + comps.size() + 1);
+    // SmebMembArgs: 4 pointers, SMEB_NCOMP stage inputs, SMEB_NCOMP member
+    // tables (ensembles only), 2 x u32
+    std::vector<unsigned long long> blob(4 + 2 * comps.size() + 1, 0ull);
     blob[0] = reinterpret_cast<unsigned long long>(c.dMvox);
     blob[1] = reinterpret_cast<unsigned long long>(c.dMstart);
     blob[2] = reinterpret_cast<unsigned long long>(c.dEnt);
@@ -2287,7 +2467,7 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
       }
       blob[4 + j] = reinterpret_cast<unsigned long long>(pj);
     }
-    blob[4 + comps.size()] = static_cast<unsigned long long>(c.nMvox);
+    blob[4 + 2 * comps.size()] = static_cast<unsigned long long>(c.nMvox);
     const unsigned mgrid = membGrid(ci, k.memb);
     StageArgsHost am = a;
     if (nsPrepass) { // the membrane voxels' partial sums follow the main ones
@@ -2348,6 +2528,9 @@ unsigned Sim::mainGrid(std::size_t ci, const StageArgsHost &a, CUfunction f) {
     }
     return c.tile.grid[0] * c.tile.grid[1] * gridZ;
   }
+  if (c.geom == Geom::SEG) {
+    return std::max(1u, std::min(c.nSeg, persistentGrid(f, c.segSmem)));
+  }
   uint64_t work = a.n > a.v0 ? a.n - a.v0 : 0;
   if (c.geom == Geom::BOX) {
     work = static_cast<uint64_t>(a.z_end - a.z_begin) * c.nx * c.ny;
@@ -2393,14 +2576,14 @@ void Sim::launchKernel(CUfunction f, unsigned gx, unsigned gy, unsigned gz,
 // more CTAs than fit (e.g. 8 per SM when 6 are resident) the second, partial
 // wave runs at a fraction of the occupancy while holding a full share of the
 // work (ncu: 53 % achieved warps on smeb_stage_nn before this).
-unsigned Sim::persistentGrid(CUfunction f) {
+unsigned Sim::persistentGrid(CUfunction f, unsigned dynSmem) {
   if (auto it = persistentGridOf.find(f); it != persistentGridOf.end()) {
     return it->second;
   }
   int perSm = 0;
   const auto &drv = DriverApi::get();
   if (drv.OccupancyMaxActiveBlocksPerMultiprocessor(
-          &perSm, f, static_cast<int>(BLOCK), 0) != CUDA_SUCCESS ||
+          &perSm, f, static_cast<int>(BLOCK), dynSmem) != CUDA_SUCCESS ||
       perSm <= 0) {
     perSm = 4;
   }
@@ -3075,6 +3258,8 @@ void Sim::runOnDemand(std::size_t ci, uint32_t flags, double *out) {
   a.cout = out;
   a.s2out = nullptr;
   a.err = dErrScratch;
+  a.errBase = dErrScratch;
+  a.errPairs = 1;
   a.errExpected = 0; // the norms of an on-demand launch go nowhere
   const bool timing = kernelTiming;
   kernelTiming = false;

@@ -25,7 +25,8 @@ constexpr uint32_t F_USE_C0 = 1u, F_USE_S2 = 2u, F_USE_S2IN = 4u,
                    F_WRITE_S2 = 8u, F_FINAL = 16u, F_LOWER_IS_CIN = 32u,
                    F_CLAMP_OUT = 64u, F_GENERIC = 128u, F_OUT_DCDT = 256u,
                    F_OUT_LOWER = 512u, F_OUT_CNEW = 1024u, F_SUM_NS = 2048u,
-                   F_RELAX_A = 4096u, F_RELAX_B = 8192u, F_HALO = 16384u;
+                   F_RELAX_A = 4096u, F_RELAX_B = 8192u, F_HALO = 16384u,
+                   F_MEMBERS = 32768u;
 
 // host mirror of the device-side SmebStageArgs<S> (device_kernels.cuh); the
 // D[3*S] table is the tail.
@@ -37,8 +38,12 @@ struct StageArgsHost {
   double *cout;
   const uint32_t *nn;
   const int *runs;
+  const uint32_t *seg;
   unsigned long long *err;
+  unsigned long long *errBase;
   unsigned long long *errHost;
+  const void *members;
+  const double *memberParams;
   const double *nsAv;
   double *nsPartial;
   const double *darr;
@@ -55,8 +60,11 @@ struct StageArgsHost {
   uint32_t *halo;
   uint32_t *peerFlagLo;
   uint32_t *peerFlagHi;
+  uint32_t *haloErr;
   uint32_t haloSeq;
-  uint32_t pad0_;
+  uint32_t nSeg;
+  uint32_t errPairs;
+  uint32_t roles;
   double g1, g2, g3, bdt, delta;
   double beta;
   const double *dtp;
@@ -83,7 +91,7 @@ struct StageDesc {
   uint32_t flags() const;
 };
 
-enum class Geom { NN, BOX, TILE };
+enum class Geom { NN, BOX, TILE, SEG };
 
 // kernel pair for one compartment and one set of stage flags
 struct StageKernels {
@@ -116,6 +124,15 @@ struct CompartmentState {
     return box ? uint64_t{nz - zHiGhost} * nx * ny : n - vGhostHi;
   }
   TileConfig tile;
+  // segment-staged voxel-list kernel (Geom::SEG): pieces of runs of at most
+  // segLen voxels, staged in shared memory by 1-D bulk copies
+  int segLen{0}, segNst{0};
+  bool segZ{false};
+  unsigned segSmem{0};
+  uint32_t nSeg{0};
+  uint32_t *dSeg{nullptr};
+  std::vector<uint32_t> hostSeg, hostCodes; // until the upload
+  std::vector<int> hostRuns;
   std::vector<std::string> speciesNames;
   std::vector<double> D;
   // CPU-solver semantics beyond the reference GPU backend (smeb200.h)
@@ -184,7 +201,11 @@ bool compressNeighbourTable(const uint32_t *nn, uint64_t n,
                             std::vector<uint32_t> &codes,
                             std::vector<int> &runs);
 
+class EnsembleSim;
+
 class Sim {
+  friend class EnsembleSim;
+
 public:
   explicit Sim(const smeb200_problem &p, bool compileOnlyMode = false);
   ~Sim();
@@ -283,6 +304,7 @@ private:
   StageKernels lookup(const Module &m, std::size_t ci, uint32_t flags) const;
   StageKernels onDemandKernels(std::size_t ci, uint32_t flags);
   void chooseGeometry(int variant);
+  void chooseSegments(int variant, std::vector<std::vector<uint32_t>> &nnHost);
   void encodeTensorMaps(CompartmentState &c);
   void setupMembranes(const smeb200_problem &p,
                       std::vector<std::vector<uint32_t>> &nnHost);
@@ -316,6 +338,9 @@ private:
   cudaEvent_t forkEvent{nullptr};
   cudaStream_t forkMain{nullptr}, forkMemb{nullptr};
   void launchStage(std::size_t stageIndex, double dt);
+  // the arguments of compartment ci's kernels in plan stage `stageIndex` that do
+  // not depend on the step: geometry tables, stage coefficients, constants
+  StageArgsHost stageArgsTemplate(std::size_t ci, std::size_t stageIndex) const;
   // parts: 1 = main kernel over the range in `a` (z_begin..z_end / v0..n),
   // 2 = membrane kernel, 3 = both
   void launchCompartment(std::size_t ci, StageArgsHost &a,
@@ -376,6 +401,9 @@ private:
   // halo exchange inside the tile kernel (all compartments box / TMA tile path):
   // own flag words in device memory, the neighbours' through CUDA IPC
   bool fusedHalo{false};
+  // [2 ci + side] counts of boundary-plane tiles arrived from below / above per
+  // compartment; [kHaloErrWord] raised by a wait that ran out
+  static constexpr int kHaloWords = 16, kHaloErrWord = 15;
   uint32_t *dHalo{nullptr};
   uint32_t *peerHalo[2]{nullptr, nullptr};
   CUfunction kHaloQuiesce{nullptr};
@@ -403,7 +431,7 @@ private:
   std::vector<const double *> membCinOverride;
   // one full wave of resident CTAs for a grid-stride kernel: SMs x the CTAs of
   // this kernel that fit on one SM (cached per function)
-  unsigned persistentGrid(CUfunction f);
+  unsigned persistentGrid(CUfunction f, unsigned dynSmem = 0);
   std::map<CUfunction, unsigned> persistentGridOf;
   double h2[3]{1.0, 1.0, 1.0}; // voxel width^2, height^2, depth^2
   bool anyCross{false};

@@ -20,7 +20,9 @@ from typing import List, Optional, Sequence
 
 import numpy as np
 
-from .pixelsim import PixelSim
+import ctypes as C
+
+from .pixelsim import PixelSim, _STOP_CB, load_library
 from .problem import Problem
 
 
@@ -97,3 +99,90 @@ class Ensemble:
         with ThreadPoolExecutor(max_workers=min(self.concurrency, len(rest))) as pool:
             others = list(pool.map(lambda m: self._run_member(m, time), rest))
         return [first] + others
+
+
+class BatchedEnsemble:
+    """All members of this rank in ONE simulator object behind the C-ABI
+    (``smeb200_ensemble_*``): the state is [member][voxel][species], a Runge-Kutta
+    stage of all members of a compartment is one kernel launch (members =
+    gridDim.y), every member keeps its own step-size controller.  Same constructor
+    and ``run`` result as ``Ensemble``; replaces its thread pool of launch-bound
+    single simulations (40 us per step and member)."""
+
+    def __init__(self, problem: Problem, values: Sequence[Sequence[float]],
+                 rank: int = 0, world: int = 1, device: int = 0):
+        self.problem = problem
+        self.values = np.atleast_2d(np.asarray(values, dtype=np.float64))
+        if self.values.shape[0] == 1 and len(problem.params) == 1 and \
+                np.asarray(values).ndim == 1:
+            self.values = self.values.T
+        assert self.values.shape[1] == len(problem.params)
+        self.members = members_of_rank(self.values.shape[0], rank, world)
+        self._lib = load_library()
+        self._h = C.c_void_p()
+        p = copy.copy(problem)
+        p.device = device
+        cproblem, keep = p.to_c()
+        mine = np.ascontiguousarray(self.values[self.members])
+        self._lib.smeb200_ensemble_create(
+            C.byref(cproblem), len(self.members),
+            mine.ctypes.data_as(C.POINTER(C.c_double)), C.byref(self._h))
+        del keep
+        if not self._h:
+            raise RuntimeError("ensemble construction failed")
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.smeb200_ensemble_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def errorMessage(self, member: int = -1) -> str:
+        return self._lib.smeb200_ensemble_error(self._h, member).decode()
+
+    def setNextTimestep(self, dt: float) -> None:
+        for k in range(len(self.members)):
+            self._lib.smeb200_ensemble_set_next_timestep(self._h, k, dt)
+
+    def launchCount(self) -> int:
+        return int(self._lib.smeb200_ensemble_launch_count(self._h))
+
+    def batchedSteps(self) -> int:
+        return int(self._lib.smeb200_ensemble_batched_steps(self._h))
+
+    def lastRunMs(self) -> float:
+        return float(self._lib.smeb200_ensemble_last_run_ms(self._h))
+
+    def getConcentrations(self, k: int, compartmentIndex: int) -> np.ndarray:
+        p = C.POINTER(C.c_double)()
+        n = C.c_size_t()
+        rc = self._lib.smeb200_ensemble_get_concentrations(
+            self._h, k, compartmentIndex, C.byref(p), C.byref(n))
+        if rc != 0:
+            raise RuntimeError(self.errorMessage())
+        S = max(self.problem.compartments[compartmentIndex].n_species, 1)
+        if n.value == 0:
+            return np.zeros((0, S))
+        return np.ctypeslib.as_array(p, shape=(n.value,)).reshape(-1, S)
+
+    def run(self, time: float, timeout_ms: float = -1.0) -> List[MemberResult]:
+        if self.errorMessage():
+            raise RuntimeError(self.errorMessage())
+        self._lib.smeb200_ensemble_run(self._h, time, timeout_ms, _STOP_CB(), None)
+        ncomp = len(self.problem.compartments)
+        out = []
+        for k, m in enumerate(self.members):
+            out.append(MemberResult(
+                member=m, params=self.values[m].copy(),
+                steps=int(self._lib.smeb200_ensemble_get_steps(self._h, k)),
+                discarded=int(self._lib.smeb200_ensemble_get_discarded_steps(self._h, k)),
+                error=self.errorMessage(k) or self.errorMessage(),
+                concentrations=[self.getConcentrations(k, ci).copy()
+                                for ci in range(ncomp)],
+                device_ms=self.lastRunMs()))
+        return out

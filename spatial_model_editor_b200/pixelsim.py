@@ -89,6 +89,24 @@ def _bind(lib, prefix: str):
     fn("comm_barrier", C.c_int, [vp], optional=True)
     fn("comm_abort", None, [vp], optional=True)
     fn("comm_destroy", None, [vp], optional=True)
+    # member-batched ensembles
+    u32 = C.c_uint32
+    fn("ensemble_create", C.c_int,
+       [C.POINTER(CProblem), u32, C.POINTER(C.c_double), C.POINTER(vp)], optional=True)
+    fn("ensemble_destroy", None, [vp], optional=True)
+    fn("ensemble_run", C.c_size_t, [vp, C.c_double, C.c_double, _STOP_CB, vp], optional=True)
+    fn("ensemble_get_concentrations", C.c_int, [vp, u32, C.c_size_t, dpp, szp], optional=True)
+    fn("ensemble_set_concentrations", C.c_int,
+       [vp, u32, C.c_size_t, C.POINTER(C.c_double), C.c_size_t], optional=True)
+    fn("ensemble_get_steps", C.c_size_t, [vp, u32], optional=True)
+    fn("ensemble_get_discarded_steps", C.c_size_t, [vp, u32], optional=True)
+    fn("ensemble_get_next_timestep", C.c_double, [vp, u32], optional=True)
+    fn("ensemble_set_next_timestep", None, [vp, u32, C.c_double], optional=True)
+    fn("ensemble_error", C.c_char_p, [vp, C.c_int], optional=True)
+    fn("ensemble_set_stop_requested", None, [vp, C.c_int], optional=True)
+    fn("ensemble_launch_count", C.c_uint64, [vp], optional=True)
+    fn("ensemble_batched_steps", C.c_uint64, [vp], optional=True)
+    fn("ensemble_last_run_ms", C.c_double, [vp], optional=True)
     # oracle-only
     fn("set_threads", None, [vp, C.c_int], optional=True)
     fn("max_threads", C.c_int, [], optional=True)

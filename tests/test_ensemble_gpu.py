@@ -69,3 +69,82 @@ def test_module_cache_makes_members_cheap():
     smeb.PixelSim(p).close()
     second = time.perf_counter() - t0
     assert second < 0.5 * first or second < 0.05
+
+
+def _scan_problem(integrator=None):
+    p, _, _ = load_golden("liver-simplified-scan", integrator=integrator)
+    p.device = 0
+    return p
+
+
+@pytest.mark.parametrize("integ", [smeb.RK101, smeb.RK212, smeb.RK323, smeb.RK435])
+def test_batched_members_match_oracle_fixed_step(integ):
+    """smeb200_ensemble_*: members as gridDim.y of one launch per stage; every
+    member equals the CPU oracle run with its parameter value (<= 1e-12)"""
+    p = _scan_problem(integ)
+    p.max_err_abs = p.max_err_rel = smeb.DBL_MAX
+    probe = smeb.PixelSim(copy.copy(p))
+    p.max_timestep = 0.5 * probe.maxStableTimestep
+    probe.close()
+    vals = EN.scan_values(p.params[0], 6)
+    t_end = 25 * p.max_timestep
+    ens = EN.BatchedEnsemble(p, vals, device=0)
+    assert ens.errorMessage() == ""
+    res = ens.run(t_end)
+    assert ens.launchCount() > 0
+    for r in res:
+        assert r.error == "" and r.steps >= 25
+        q = copy.copy(p)
+        q.params = list(r.params)
+        cpu = OraclePixelSim(q)
+        assert cpu.run(t_end) == r.steps
+        for ci in range(2):
+            assert_parity(r.concentrations[ci], cpu.getConcentrations(ci),
+                          what=f"member {r.member} comp {ci}")
+    ens.close()
+
+
+def test_batched_members_adaptive_take_their_own_steps():
+    """adaptive RK212 (the model's settings): every member has its own controller —
+    the same accepted / discarded steps and the same state as that member simulated
+    alone through smeb200_run (bit-identical: same kernels' arithmetic, same
+    controller formulas), members finishing at different times"""
+    p = _scan_problem(smeb.RK212)
+    vals = EN.scan_values(p.params[0], 8)
+    t_end = 0.05
+    ens = EN.BatchedEnsemble(p, vals, device=0)
+    res = ens.run(t_end)
+    counts = set()
+    for r in res:
+        q = copy.copy(p)
+        q.params = list(r.params)
+        one = smeb.PixelSim(q)
+        n = one.run(t_end)
+        assert (n, one.discardedSteps) == (r.steps, r.discarded)
+        counts.add((n, one.discardedSteps))
+        for ci in range(2):
+            assert np.array_equal(r.concentrations[ci], one.getConcentrations(ci))
+        one.close()
+    assert ens.batchedSteps() >= max(c[0] + c[1] for c in counts)
+    # far fewer launches than members x steps x kernels
+    assert ens.launchCount() <= 8 * ens.batchedSteps()
+    ens.close()
+
+
+def test_batched_ensemble_continues_and_restarts():
+    """a second run continues from the members' states and step sizes; a member can
+    be restarted from a given state"""
+    p = _scan_problem(smeb.RK212)
+    vals = EN.scan_values(p.params[0], 3)
+    ens = EN.BatchedEnsemble(p, vals, device=0)
+    a = ens.run(0.01)
+    b = ens.run(0.01)
+    for k, (ra, rb) in enumerate(zip(a, b)):
+        q = copy.copy(p)
+        q.params = list(ra.params)
+        one = smeb.PixelSim(q)
+        assert one.run(0.01) == ra.steps
+        assert one.run(0.01) == rb.steps
+        assert np.array_equal(rb.concentrations[0], one.getConcentrations(0))
+        one.close()
+    ens.close()
