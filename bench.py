@@ -298,8 +298,10 @@ def run_ensemble(args, rank, world, local_rank):
     vals = EN.scan_values(p.params[0], args.members)
     if args.ensemble_impl == "batched":
         # members as gridDim.y of one launch per stage (smeb200_ensemble_*)
-        ens = EN.BatchedEnsemble(p, vals, rank=rank, world=world, device=local_rank)
-        impl_text = "member-batched launches (smeb200_ensemble_run)"
+        ens = EN.GroupedEnsemble(p, vals, rank=rank, world=world, device=local_rank,
+                                 groups=args.groups)
+        impl_text = (f"member-batched launches (smeb200_ensemble_run), {args.groups} "
+                     f"group(s) per GPU")
     else:
         ens = EN.Ensemble(p, vals, rank=rank, world=world, device=local_rank,
                           concurrency=args.concurrency)
@@ -439,6 +441,9 @@ def main():
     ap.add_argument("--dt", type=float, default=DT)
     ap.add_argument("--members", type=int, default=64)
     ap.add_argument("--concurrency", type=int, default=8)
+    ap.add_argument("--groups", type=int, default=2,
+                    help="ensemble workload: member-batched ensembles per GPU, one "
+                         "host thread each")
     ap.add_argument("--ensemble-impl", default="batched",
                     help="ensemble workload: batched (members = gridDim.y) | threads")
     ap.add_argument("--sim-time", type=float, default=1.0)
@@ -574,6 +579,8 @@ def main():
         np.array(sim.getConcentrations(i)) if ncomp > 1 else sim.getConcentrations(i)
         for i in range(ncomp)]
     state_bytes = sum(h.nbytes for h in hosts)
+
+    sim.setAsyncDownload(True)  # what the SME adapter does: the D2H starts in run()
 
     def e2e_run(ke, intervals):
         barrier()

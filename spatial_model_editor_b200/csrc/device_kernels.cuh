@@ -118,6 +118,11 @@ template <int S> struct SmebStageArgs {
   smeb_u32 errPairs;       // pairs in the error slot: 1, or the members of an ensemble
   smeb_u32 roles;          // ensembles: buffer roles (CUR, RA, RB, RS = 0..3; 15 =
                            // none) of cin | cout << 4 | s2in << 8 | s2out << 12
+  smeb_u32 zig;            // tile kernel, 3-D: grid = (chunks, tiles y, tiles x) and
+                           // the chunks of a tile march in alternating directions
+  smeb_u32 errPublish;     // the first CTA publishes the error slot before it starts:
+                           // the norms of the step BEFORE this kernel, whose final
+                           // stage only left its maxima in the slot (errExpected 0)
   double g1, g2, g3, bdt, delta; // stage coefficients (bdt = beta*dt)
   // CUDA-graph replay of a step: the step size lives in device memory (a
   // captured launch cannot carry a new bdt); bdt = beta * *dtp when dtp != 0
@@ -214,35 +219,61 @@ __device__ __forceinline__ void smeb_pdl_wait() {
 
 #define SMEB_ERR_RING 8 // entries of the pinned host ring (sim.hpp kErrRing)
 
-// One CTA of an error-norm launch is done.  The CTA that completes the step's
-// count takes the maxima out of the slot (leaving it zeroed for the next step)
-// and publishes them with the step's sequence number into the pinned host ring:
-// the host polls its own memory instead of queueing a copy, a memset and an event
-// behind every step (which also kept two kernels from overlapping their tails).
-// `pairs` pairs of maxima (ensembles: one per member); a ring entry is 2 pairs + 2
-// words, the sequence number at [2 pairs].  Called by one thread per CTA, after
-// its atomicMax.
-__device__ __forceinline__ void smeb_err_arrive(smeb_u64 *errBase, smeb_u32 pairs,
-                                                smeb_u64 *errHost,
-                                                smeb_u32 expected) {
+// One CTA of an error-norm launch is done: returns true to the thread of the CTA
+// that completes the step's count.  That CTA takes the maxima out of the slot
+// (leaving it zeroed for the next step) and publishes them with the step's
+// sequence number into the pinned host ring (smeb_err_publish): the host polls
+// its own memory instead of queueing a copy, a memset and an event behind every
+// step (which also kept two kernels from overlapping their tails).  `pairs` pairs
+// of maxima (ensembles: one per member); a ring entry is 2 pairs + 2 words, the
+// sequence number at [2 pairs].  Called by one thread per CTA, after its
+// atomicMax.
+__device__ __forceinline__ bool smeb_err_count(smeb_u64 *errBase, smeb_u32 pairs,
+                                               smeb_u32 expected) {
   if (expected == 0u) {
-    return;
+    return false;
   }
   unsigned int *cnt = reinterpret_cast<unsigned int *>(errBase + 2u * pairs);
   __threadfence();
   const unsigned int prev = atomicAdd(cnt, 1u);
   if (prev + 1u == expected) {
     __threadfence();
-    const unsigned int seq = atomicAdd(cnt + 1, 1u) + 1u;
-    volatile smeb_u64 *h =
-        errHost + (size_t)(2u * pairs + 2u) * (seq % SMEB_ERR_RING);
-    for (smeb_u32 k = 0; k < 2u * pairs; ++k) {
-      h[k] = atomicExch(errBase + k, 0ull);
-    }
+    return true;
+  }
+  return false;
+}
+
+// the publishing CTA: lanes [0, nLanes) of one warp (or one thread, nLanes = 1)
+// move the maxima to the host ring entry of the next sequence number
+__device__ __forceinline__ void smeb_err_publish(smeb_u64 *errBase, smeb_u32 pairs,
+                                                 smeb_u64 *errHost, int lane,
+                                                 int nLanes) {
+  unsigned int *cnt = reinterpret_cast<unsigned int *>(errBase + 2u * pairs);
+  const unsigned int seq = *reinterpret_cast<volatile unsigned int *>(cnt + 1) + 1u;
+  volatile smeb_u64 *h =
+      errHost + (size_t)(2u * pairs + 2u) * (seq % SMEB_ERR_RING);
+  for (smeb_u32 k = lane; k < 2u * pairs; k += nLanes) {
+    h[k] = atomicExch(errBase + k, 0ull);
+  }
+  __threadfence_system();
+  if (nLanes > 1) {
+    __syncwarp();
+  }
+  if (lane == 0) {
     atomicExch(cnt, 0u);
+    atomicExch(cnt + 1, seq);
     __threadfence_system();
     h[2u * pairs] = (smeb_u64)seq;
     __threadfence_system();
+  }
+}
+
+// a CTA that only reports in (an empty tile CTA, a finished ensemble member)
+__device__ __forceinline__ void smeb_err_arrive(smeb_u64 *errBase, smeb_u32 pairs,
+                                                smeb_u64 *errHost,
+                                                smeb_u32 expected) {
+  if (smeb_err_count(errBase, pairs, expected)) {
+    smeb_err_publish(errBase, pairs, errHost, 0, 1);
   }
 }
 
@@ -279,6 +310,7 @@ __device__ __forceinline__ void smeb_block_max2(double eabs, double erel,
       eabs = a > eabs ? a : eabs;
       erel = r > erel ? r : erel;
     }
+    int publisher = 0;
     if (lane == 0) {
       if (eabs > 0.0) {
         atomicMax(err, (smeb_u64)__double_as_longlong(eabs));
@@ -286,8 +318,37 @@ __device__ __forceinline__ void smeb_block_max2(double eabs, double erel,
       if (erel > 0.0) {
         atomicMax(err + 1, (smeb_u64)__double_as_longlong(erel));
       }
-      smeb_err_arrive(errBase, pairs, errHost, expected);
+      publisher = smeb_err_count(errBase, pairs, expected) ? 1 : 0;
     }
+    publisher = __shfl_sync(0xffffffffu, publisher, 0);
+    if (publisher != 0) { // the whole warp moves the (2 x members) maxima
+      smeb_err_publish(errBase, pairs, errHost, lane, 32);
+    }
+  }
+}
+
+// Deferred publication.  Counting the CTAs of a final stage costs every one of
+// them a fence and an atomic round trip at its end, while it still holds its
+// shared memory and registers: with 2048 CTAs on 296 slots that was 14 us per
+// final-stage launch (24 of 151 us on a 64-plane slab; ncu, profiles/r2_*).  Where
+// the host does not wait for a step's norms before it launches the next step
+// (unbounded tolerances: they are checked two steps late), the final stage only
+// leaves its maxima in the slot, and the first CTA of the NEXT kernel — which
+// starts after the final stage has completed (griddepcontrol.wait / stream order)
+// — moves them to the host ring.  smeb_err_flush does the same for the last step
+// of a run, and behind final stages of large grids when the host does wait.
+template <int S>
+__device__ __forceinline__ void smeb_err_publish_previous(const SmebStageArgs<S> &a) {
+  if (a.errPublish != 0u && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 &&
+      threadIdx.x < 32) {
+    smeb_err_publish(a.errBase, a.errPairs, a.errHost, (int)threadIdx.x, 32);
+  }
+}
+
+__global__ void smeb_err_flush(smeb_u64 *errBase, smeb_u32 pairs, smeb_u64 *errHost) {
+  smeb_pdl_wait();
+  if (blockIdx.x == 0 && threadIdx.x < 32) {
+    smeb_err_publish(errBase, pairs, errHost, (int)threadIdx.x, 32);
   }
 }
 
@@ -651,6 +712,7 @@ __device__ __forceinline__ bool smeb_member_select(SmebStageArgs<R::S> &a) {
     // a finished member: its CTAs still count towards the step's error norms
     smeb_pdl_wait();
     smeb_pdl_trigger();
+    smeb_err_publish_previous<R::S>(a);
     if constexpr (((F & SMEB_F_FINAL) != 0 && (F & SMEB_F_OUT_LOWER) == 0)) {
       if (threadIdx.x == 0) {
         smeb_err_arrive(a.errBase, a.errPairs, a.errHost, a.errExpected);
@@ -727,6 +789,7 @@ __device__ __forceinline__ void smeb_stage_nn_body(const SmebStageArgs<R::S> &a)
   smeb_u32 i = a.v0 + blockIdx.x * SMEB_BLOCK + threadIdx.x;
   smeb_pdl_wait();
   smeb_pdl_trigger();
+  smeb_err_publish_previous<R::S>(a);
   smeb_u32 codeNext = coded && i < a.n ? a.nn[i] : 0u;
   double cNext[S], c0Next[S];
 #pragma unroll
@@ -805,6 +868,7 @@ __device__ __forceinline__ void smeb_stage_box_body(const SmebStageArgs<R::S> &a
   const smeb_u32 iEnd = a.z_end * sz;
   smeb_pdl_wait();
   smeb_pdl_trigger();
+  smeb_err_publish_previous<R::S>(a);
   for (smeb_u32 i = a.z_begin * sz + blockIdx.x * SMEB_BLOCK + threadIdx.x;
        i < iEnd; i += gridDim.x * SMEB_BLOCK) {
     const smeb_u32 y = i % a.ny;
@@ -926,6 +990,7 @@ __device__ __forceinline__ void smeb_stage_memb_body(const SmebStageArgs<R::S> &
   double nsacc[R::NNS > 0 ? R::NNS : 1] = {};
   smeb_pdl_wait();
   smeb_pdl_trigger();
+  smeb_err_publish_previous<R::S>(a);
   for (smeb_u32 k = blockIdx.x * SMEB_BLOCK + threadIdx.x; k < m.n_mvox;
        k += gridDim.x * SMEB_BLOCK) {
     const smeb_u32 i = m.mvox[k];
@@ -1139,31 +1204,46 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   const int tid = threadIdx.x;
   const int ty = tid % TY, tg = tid / TY;
   const int r0 = tg * RPT; // first tile row of this thread
-  const int y0 = blockIdx.x * TY;
-  const int gy = y0 + ty;
   // march range [m0, m1): planes (M3) or bricks of TX rows (2-D)
-  int m0, m1, x0;
+  int m0, m1, x0, y0;
+  // Zig-zag (3-D): the chunks of one tile are adjacent in the launch order (chunk
+  // index fastest), so they run together, and they march in alternating
+  // directions — even chunks down from their top plane, odd chunks up from their
+  // bottom plane.  Two neighbouring chunks then start at their common boundary,
+  // or arrive at it, at the same time, and the two halo planes each of them reads
+  // beyond its own range are the planes the other one is reading just then: L2
+  // hits instead of a second trip to HBM ((chunk + 2) / chunk of the stage input
+  // otherwise: 25 % at 8 planes per chunk).
+  bool down = false;
+  smeb_u32 tilesPerPlane = gridDim.x * gridDim.y;
   if constexpr (M3) {
-    x0 = blockIdx.y * TX;
-    // z-slabs: the chunks that hold the boundary planes are scheduled first
-    // (bottom chunk, top chunk, then the interior), so the halos leave early
-    int zc = blockIdx.z;
-    if constexpr ((F & SMEB_F_HALO) != 0) {
-      if (gridDim.z > 1u) {
-        zc = zc == 1 ? (int)gridDim.z - 1 : (zc > 1 ? zc - 1 : 0);
-      }
+    int zc;
+    if (a.zig != 0u) {
+      zc = blockIdx.x;
+      y0 = blockIdx.y * TY;
+      x0 = blockIdx.z * TX;
+      down = (zc & 1) == 0;
+      tilesPerPlane = gridDim.y * gridDim.z;
+    } else {
+      zc = blockIdx.z;
+      y0 = blockIdx.x * TY;
+      x0 = blockIdx.y * TX;
     }
     m0 = a.z_begin + zc * chunk;
     m1 = min(m0 + (int)chunk, (int)a.z_end);
   } else {
+    y0 = blockIdx.x * TY;
     x0 = 0;
     m0 = blockIdx.y * chunk;
     m1 = min(m0 + (int)chunk, (int)((a.nx + TX - 1) / TX));
   }
+  const int gy = y0 + ty;
+  const int dir = down ? -1 : 1;
   const int nIter = m1 - m0;
   if (nIter <= 0) {
     smeb_pdl_wait();
     smeb_pdl_trigger();
+    smeb_err_publish_previous<R::S>(a);
     if constexpr ((F & SMEB_F_SUM_NS) != 0) {
       const size_t blk =
           ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x +
@@ -1191,14 +1271,16 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
     haloLo = (a.haloMode & 1u) != 0u && m0 == (int)a.z_begin;
     haloHi = (a.haloMode & 2u) != 0u && m1 == (int)a.z_end;
   }
-  // load j fetches plane m0 - 1 + j (M3) / brick m0 + j (2-D)
+  // load j fetches plane m0 - 1 + j, or m1 - j marching down (M3) / brick m0 + j
+  // (2-D)
   auto issue = [&](int j, int slot) {
     const smeb_u32 bar = barAddr + 8u * slot;
     smeb_mbar_expect_tx(bar, BOX_BYTES);
     if constexpr (M3) {
       // planes outside the array are never read (Neumann select below);
       // the coordinate is clamped so that every box overlaps the tensor
-      const int plane = max(0, min((int)a.nz - 1, m0 - 1 + j));
+      const int plane =
+          max(0, min((int)a.nz - 1, down ? m1 - j : m0 - 1 + j));
       smeb_tma_load_3d(ringAddr + slot * SLOT_BYTES, &tmap,
                        (y0 - 1) * S - PAD, x0 - 1, plane, bar);
     } else {
@@ -1216,9 +1298,11 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   int offHi = (M3 && gx0 + RPT >= (int)a.nx) ? (RPT - 1) * PITCH
                                               : RPT * PITCH; // row r0 + RPT
   const size_t rowStride = (size_t)a.ny;               // voxels per x row
+  // voxels per iteration (negative marching down; size_t arithmetic wraps)
   const size_t marchStride =
-      M3 ? (size_t)a.nx * a.ny : (size_t)TX * a.ny;    // voxels per iteration
-  size_t g = M3 ? ((size_t)m0 * a.nx + gx0) * a.ny + gy
+      M3 ? (size_t)((long long)dir * (long long)((size_t)a.nx * a.ny))
+         : (size_t)TX * a.ny;
+  size_t g = M3 ? ((size_t)(down ? m1 - 1 : m0) * a.nx + gx0) * a.ny + gy
                 : ((size_t)m0 * TX + r0) * a.ny + gy;
 
   // register prefetch queues of c0 / s2: entry q holds the values of iteration
@@ -1280,12 +1364,13 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   // everything above is independent of the kernels before this one
   smeb_pdl_wait();
   smeb_pdl_trigger();
+  smeb_err_publish_previous<R::S>(a);
   if constexpr (HALO) {
     // a boundary chunk reads a ghost plane (its first / last load): the
     // neighbour's plane of the previous stage must have arrived.  Both waits sit
     // here, outside the march loop, which stays the single-GPU loop
     if (tid == 0) {
-      const smeb_u32 want = (a.haloSeq - 1u) * (gridDim.x * gridDim.y);
+      const smeb_u32 want = (a.haloSeq - 1u) * tilesPerPlane;
       if (haloLo) {
         smeb_halo_acquire(a.halo, 0, want, a.haloErr);
       }
@@ -1326,7 +1411,7 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
     smeb_mbar_wait(barAddr + 8u * (1 % NST), 0);
   }
   for (int it = 0; it < nIter; ++it) {
-    const int m = m0 + it;
+    const int m = down ? m1 - 1 - it : m0 + it;
     // 2-D: the brick's x range changes every iteration
     if constexpr (!M3) {
       gx0 = m * TX + r0;
@@ -1367,12 +1452,15 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
           reinterpret_cast<const double *>(ring + slotC * SLOT_BYTES) + ownOff;
       const double *sm = sc, *sp = sc;
       if constexpr (M3) {
+        // the plane loaded before the current one is z - 1 marching up, z + 1
+        // marching down; the newest plane is the other neighbour
+        const int slotBelow = down ? slotW : slotM, slotAbove = down ? slotM : slotW;
         if (m > 0) {
-          sm = reinterpret_cast<const double *>(ring + slotM * SLOT_BYTES) +
+          sm = reinterpret_cast<const double *>(ring + slotBelow * SLOT_BYTES) +
                ownOff;
         }
         if (m + 1 < (int)a.nz) {
-          sp = reinterpret_cast<const double *>(ring + slotW * SLOT_BYTES) +
+          sp = reinterpret_cast<const double *>(ring + slotAbove * SLOT_BYTES) +
                ownOff;
         }
       }
@@ -1410,12 +1498,12 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
         if constexpr (HALO) {
           // a boundary plane also goes into the neighbour's ghost plane: plain
           // stores through the peer mapping, they drain while the march goes on
-          if ((haloLo && it == 0) || (haloHi && it == nIter - 1)) {
+          if ((haloLo && m == m0) || (haloHi && m == m1 - 1)) {
             const size_t inPlane = (size_t)(gx0 + k) * a.ny + gy;
-            if (haloLo && it == 0) {
+            if (haloLo && m == m0) {
               smeb_store_voxel<S>(a.peerLo, inPlane, out);
             }
-            if (haloHi && it == nIter - 1) {
+            if (haloHi && m == m1 - 1) {
               smeb_store_voxel<S>(a.peerHi, inPlane, out);
             }
           }
@@ -1586,6 +1674,7 @@ __device__ __forceinline__ void smeb_stage_seg_body(const SmebStageArgs<R::S> &a
   }
   smeb_pdl_wait();
   smeb_pdl_trigger();
+  smeb_err_publish_previous<R::S>(a);
   if (tid == 0) {
     for (int j = 0; j < NST && j < nMine; ++j) {
       issue(j);

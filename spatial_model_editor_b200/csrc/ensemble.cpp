@@ -134,6 +134,19 @@ void EnsembleSim::build(const smeb200_problem &p, const double *memberParams) {
   for (auto &e : tableEvents) {
     check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate");
   }
+  if (const char *env = std::getenv("SMEB200_GRAPHS"); env != nullptr) {
+    useGraph = env[0] != '0';
+  }
+  check(cudaEventCreateWithFlags(&forkEvent, cudaEventDisableTiming),
+        "cudaEventCreate");
+  for (std::size_t k = 0; k < 2 * nc; ++k) {
+    cudaStream_t st{};
+    cudaEvent_t e{};
+    check(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking), "cudaStreamCreate");
+    check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate");
+    forkStreams.push_back(st);
+    joinEvents.push_back(e);
+  }
   check(cudaEventCreate(&ev0), "cudaEventCreate");
   check(cudaEventCreate(&ev1), "cudaEventCreate");
   check(cudaStreamSynchronize(stream), "initial upload");
@@ -161,24 +174,30 @@ EnsembleSim::~EnsembleSim() {
       cudaEventDestroy(e);
     }
   }
+  if (stepGraph != nullptr) {
+    cudaGraphExecDestroy(stepGraph);
+  }
+  for (auto st : forkStreams) {
+    cudaStreamDestroy(st);
+  }
+  for (auto e : joinEvents) {
+    cudaEventDestroy(e);
+  }
+  if (forkEvent != nullptr) {
+    cudaEventDestroy(forkEvent);
+  }
   if (ev0 != nullptr) {
     cudaEventDestroy(ev0);
     cudaEventDestroy(ev1);
   }
 }
 
-// one attempted step of every active member: member tables up, then one launch
-// per stage and compartment (plus its membrane launch) with gridDim.y = M
+// one attempted step of every active member: the member tables are rewritten in
+// pinned memory, then the step's launches are replayed (or issued)
 void EnsembleSim::batchedStep(const std::vector<double> &dt,
                               const std::vector<char> &active) {
   Sim &s = *proto;
   cudaStream_t stream = s.stream;
-  const int slot = tableSlot % kTableRing;
-  if (tableSlot >= kTableRing) {
-    // the upload that last read this part of the pinned tables has finished
-    check(cudaEventSynchronize(tableEvents[slot]), "cudaEventSynchronize");
-  }
-  ++tableSlot;
   for (std::size_t ci = 0; ci < cd.size(); ++ci) {
     const auto &c = s.comps[ci];
     auto &d = cd[ci];
@@ -186,7 +205,7 @@ void EnsembleSim::batchedStep(const std::vector<double> &dt,
     if (nv == 0) {
       continue;
     }
-    MemberRec *t = d.hTable + static_cast<std::size_t>(slot) * M;
+    MemberRec *t = d.hTable;
     for (uint32_t m = 0; m < M; ++m) {
       for (int r = 0; r < 4; ++r) {
         const int b = role[m][r];
@@ -199,11 +218,57 @@ void EnsembleSim::batchedStep(const std::vector<double> &dt,
         d.hostStale[m] = 1;
       }
     }
-    check(cudaMemcpyAsync(d.dTable, t, sizeof(MemberRec) * M,
+  }
+  if (useGraph) {
+    if (stepGraph == nullptr) {
+      cudaGraph_t graph{};
+      const uint64_t launches0 = launchCount;
+      const uint32_t seq0 = errSeq;
+      check(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal),
+            "cudaStreamBeginCapture");
+      s.capturing = true;
+      try {
+        enqueueStep(true);
+      } catch (...) {
+        s.capturing = false;
+        cudaStreamEndCapture(stream, &graph);
+        if (graph != nullptr) {
+          cudaGraphDestroy(graph);
+        }
+        throw;
+      }
+      s.capturing = false;
+      check(cudaStreamEndCapture(stream, &graph), "cudaStreamEndCapture");
+      launchesPerStep = launchCount - launches0;
+      launchCount = launches0;
+      errSeq = seq0;
+      const cudaError_t e = cudaGraphInstantiate(&stepGraph, graph, 0);
+      cudaGraphDestroy(graph);
+      check(e, "cudaGraphInstantiate");
+    }
+    check(cudaGraphLaunch(stepGraph, stream), "cudaGraphLaunch");
+    launchCount += launchesPerStep;
+    if (s.integrator != SMEB200_RK101) {
+      ++errSeq;
+    }
+  } else {
+    enqueueStep(false);
+  }
+  ++batchedSteps;
+}
+
+void EnsembleSim::enqueueStep(bool fork) {
+  Sim &s = *proto;
+  cudaStream_t stream = s.stream;
+  for (std::size_t ci = 0; ci < cd.size(); ++ci) {
+    const auto &c = s.comps[ci];
+    if (c.n * c.S == 0) {
+      continue;
+    }
+    check(cudaMemcpyAsync(cd[ci].dTable, cd[ci].hTable, sizeof(MemberRec) * M,
                           cudaMemcpyHostToDevice, stream),
           "upload member table");
   }
-  check(cudaEventRecord(tableEvents[slot], stream), "cudaEventRecord");
   for (std::size_t si = 0; si < s.plan.size(); ++si) {
     const StageDesc &sd = s.plan[si];
     uint32_t expected = 0;
@@ -230,6 +295,13 @@ void EnsembleSim::batchedStep(const std::vector<double> &dt,
         expected += (s.mainGrid(ci, a, k.main) + s.membGrid(ci, k.memb)) * M;
       }
     }
+    // within a stage the kernels of different compartments, and a compartment's
+    // main and membrane kernels, write disjoint voxels and only read the stage
+    // input: parallel branches of the captured step
+    if (fork) {
+      check(cudaEventRecord(forkEvent, stream), "fork event");
+    }
+    std::size_t used = 0;
     for (std::size_t ci = 0; ci < cd.size(); ++ci) {
       const auto &c = s.comps[ci];
       if (c.n * c.S == 0) {
@@ -238,12 +310,22 @@ void EnsembleSim::batchedStep(const std::vector<double> &dt,
       StageArgsHost &a = args[ci];
       a.errExpected = expected;
       const auto &k = cd[ci].kStage[si];
+      cudaStream_t sMain = stream, sMemb = stream;
+      if (fork) {
+        sMain = forkStreams[2 * ci];
+        sMemb = forkStreams[2 * ci + 1];
+        check(cudaStreamWaitEvent(sMain, forkEvent, 0), "fork wait");
+      }
       {
         const unsigned grid = s.mainGrid(ci, a, k.main);
         void *params[] = {&a};
         s.launchKernel(k.main, grid, M, 1, c.geom == Geom::SEG ? c.segSmem : 0u,
-                       stream, params);
+                       sMain, params);
         ++launchCount;
+      }
+      if (fork) {
+        check(cudaEventRecord(joinEvents[2 * ci], sMain), "join event");
+        check(cudaStreamWaitEvent(stream, joinEvents[2 * ci], 0), "join");
       }
       if (c.nMvox > 0 && k.memb != nullptr) {
         // SmebMembArgs (sim.cpp: launchCompartment): the stage inputs of the
@@ -259,15 +341,23 @@ void EnsembleSim::batchedStep(const std::vector<double> &dt,
         }
         blob[4 + 2 * ncomp] = static_cast<unsigned long long>(c.nMvox);
         void *mparams[] = {&a, blob.data()};
-        s.launchKernel(k.memb, s.membGrid(ci, k.memb), M, 1, 0, stream, mparams);
+        if (fork) {
+          check(cudaStreamWaitEvent(sMemb, forkEvent, 0), "fork wait");
+        }
+        s.launchKernel(k.memb, s.membGrid(ci, k.memb), M, 1, 0, sMemb, mparams);
         ++launchCount;
+        if (fork) {
+          check(cudaEventRecord(joinEvents[2 * ci + 1], sMemb), "join event");
+          check(cudaStreamWaitEvent(stream, joinEvents[2 * ci + 1], 0), "join");
+        }
       }
+      ++used;
     }
+    (void)used;
     if (sd.final && expected > 0) {
       ++errSeq;
     }
   }
-  ++batchedSteps;
 }
 
 void EnsembleSim::waitErrors(std::vector<double> &eabs, std::vector<double> &erel) {
@@ -350,6 +440,11 @@ std::size_t EnsembleSim::run(double time, double timeoutMs, int (*stopCb)(void *
       batchedStep(dt, active);
       if (s.integrator != SMEB200_RK101) {
         waitErrors(eabs, erel);
+      } else {
+        // no norms to wait for: the uploads of this step must have read the
+        // pinned tables before the next step rewrites them
+        check(cudaEventRecord(tableEvents[0], s.stream), "cudaEventRecord");
+        check(cudaEventSynchronize(tableEvents[0]), "cudaEventSynchronize");
       }
       for (uint32_t m = 0; m < M; ++m) {
         if (!active[m]) {

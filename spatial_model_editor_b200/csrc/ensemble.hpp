@@ -62,9 +62,20 @@ private:
     std::vector<char> hostStale;
     std::vector<StageKernels> kStage;
   };
-  static constexpr int kTableRing = 4;
+  static constexpr int kTableRing = 1; // refilled only after the step before it has
+                                       // reported in (or the stream was drained)
   void build(const smeb200_problem &p, const double *memberParams);
   void batchedStep(const std::vector<double> &dt, const std::vector<char> &active);
+  // the launches of one batched step: table uploads, then per stage the kernels of
+  // all compartments as parallel branches (captured once into a CUDA graph: a
+  // step is launch-latency bound)
+  void enqueueStep(bool fork);
+  cudaGraphExec_t stepGraph{nullptr};
+  uint64_t launchesPerStep{0};
+  bool useGraph{true};
+  std::vector<cudaStream_t> forkStreams;
+  std::vector<cudaEvent_t> joinEvents;
+  cudaEvent_t forkEvent{nullptr};
   void waitErrors(std::vector<double> &eabs, std::vector<double> &erel);
 
   std::unique_ptr<Sim> proto;

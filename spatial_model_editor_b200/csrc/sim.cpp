@@ -763,6 +763,7 @@ void Sim::chooseGeometry(int variant) {
       t.grid[0] = tilesY;
       t.grid[1] = tilesX;
       t.grid[2] = chunks;
+      t.zig = !envFlagOff("SMEB200_ZIGZAG") && chunks > 1;
     } else {
       const unsigned bricks = (c.nx + t.tx - 1) / t.tx;
       unsigned chunks = forced ? std::min(forced, bricks)
@@ -1305,10 +1306,12 @@ void Sim::build(const smeb200_problem &p) {
   if (fusedHalo) {
     names.push_back("smeb_halo_quiesce");
   }
+  names.push_back("smeb_err_flush");
   mainModule = compile(names);
   if (compileOnly) {
     return;
   }
+  kErrFlush = mainModule.fn.at("smeb_err_flush");
   if (fusedHalo) {
     kHaloQuiesce = mainModule.fn.at("smeb_halo_quiesce");
   }
@@ -2104,6 +2107,7 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
   // the CTAs that will report error norms in this stage: the one that completes
   // the count publishes the step's norms (smeb_err_arrive)
   errExpected = 0;
+  uint32_t finalCtas = 0;
   if (sd.final) {
     for (const auto &it : items) {
       const auto &k = comps[it.ci].kStage[stageIndex];
@@ -2115,6 +2119,14 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
         errExpected += mainGrid(it.ci, it.a, k.main);
       }
       errExpected += membGrid(it.ci, k.memb);
+    }
+    finalCtas = errExpected;
+    // Counting the CTAs costs each of them a fence and an atomic round trip while
+    // it holds its SM slot.  Not needed when the host does not wait for these
+    // norms before the next launch (lagged check), and for large grids a
+    // one-warp flush kernel behind the stage is cheaper than the counting
+    if (!capturing && !relaxing && (deferPublish || errExpected > 1024u)) {
+      errExpected = 0;
     }
     for (auto &it : items) {
       it.a.errExpected = it.lo.errExpected = it.hi.errExpected =
@@ -2239,10 +2251,29 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
       haloWait(stream);
     }
   }
-  if (sd.final && errExpected > 0 && !capturing) {
+  if (sd.final && finalCtas > 0 && !capturing) {
     ++errSeq; // this step's norms will appear under this number (replays of a
               // captured step are counted by graphStep)
+    if (errExpected == 0) {
+      errUnpublished = true; // the next kernel launched, or flushErrors()
+    }
   }
+}
+
+// the maxima of the last final stage leave the slot now (one warp, stream
+// ordered behind that stage)
+void Sim::flushErrors() {
+  if (!errUnpublished) {
+    return;
+  }
+  unsigned long long *base = dErr, *host = dErrRing;
+  uint32_t pairs = 1;
+  void *params[] = {&base, &pairs, &host};
+  const auto &drv = DriverApi::get();
+  check(drv.LaunchKernel(kErrFlush, 1, 1, 1, 32, 1, 1, 0, stream, params, nullptr),
+        "launch error flush kernel");
+  ++launchCount;
+  errUnpublished = false;
 }
 
 // PixelSim::solveZeroStorageConstraints (pixelsim.cpp:23-90) before the stage
@@ -2421,6 +2452,15 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     check(cudaEventRecord(timerEvents[timerUsed].first, stream),
           "cudaEventRecord");
   }
+  // the first kernel launched behind a final stage that did not count its CTAs
+  // publishes that stage's norms before it starts (every kernel of this stage is
+  // stream-ordered behind all kernels of the previous one)
+  const bool publishHere = errUnpublished && !capturing &&
+                           (doMain || (c.nMvox > 0 && doMemb));
+  if (publishHere) {
+    a.errPublish = 1;
+    errUnpublished = false;
+  }
   if (!doMain) {
     // membrane kernel only
   } else if (c.geom == Geom::TILE) {
@@ -2430,9 +2470,15 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
       gridZ = std::max(1u, (a.z_end - a.z_begin + chunk - 1) / chunk);
     }
     const CUtensorMap *tm = tmapOverride != nullptr ? tmapOverride : &c.tmap[cinBuf];
+    a.zig = c.tile.m3 && c.tile.zig ? 1u : 0u;
     void *params[] = {&a, const_cast<CUtensorMap *>(tm), &chunk};
-    launchKernel(k.main, c.tile.grid[0], c.tile.grid[1],
-                 c.tile.m3 ? gridZ : c.tile.grid[2], c.tile.dynSmem, sMain, params);
+    if (a.zig != 0u) { // chunk index fastest: the chunks of a tile run together
+      launchKernel(k.main, gridZ, c.tile.grid[0], c.tile.grid[1], c.tile.dynSmem,
+                   sMain, params);
+    } else {
+      launchKernel(k.main, c.tile.grid[0], c.tile.grid[1],
+                   c.tile.m3 ? gridZ : c.tile.grid[2], c.tile.dynSmem, sMain, params);
+    }
     nsBlocks = c.tile.grid[0] * c.tile.grid[1] * c.tile.grid[2];
   } else {
     const unsigned grid = mainGrid(ci, a, k.main);
@@ -2443,6 +2489,7 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
   }
   if (doMain) {
     ++launchCount;
+    a.errPublish = 0; // published by the main kernel: not again by the membrane one
   }
   if (timed) {
     check(cudaEventRecord(timerEvents[timerUsed].second, stream),
@@ -2477,6 +2524,7 @@ void Sim::launchCompartment(std::size_t ci, StageArgsHost &a,
     void *mparams[] = {&am, blob.data()};
     launchKernel(k.memb, mgrid, 1, 1, 0, sMemb, mparams);
     ++launchCount;
+    a.errPublish = 0;
   }
   if (nsPrepass) {
     if (nsBlocks > c.nsPartialBlocks) {
@@ -2780,10 +2828,12 @@ void Sim::resyncErrorSeq() {
   errSeq = 0;
   errHead = errTail = 0;
   errDesync = false;
+  errUnpublished = false;
 }
 
 void Sim::readError(double &eabs, double &erel) {
   double v[2];
+  flushErrors();
   waitError(errSeq, v);
   if (allreduceMax != nullptr) {
     allreduceMax(v, 2, allreduceUser);
@@ -2904,6 +2954,9 @@ bool Sim::drainErrors(std::size_t keep) {
   while (errTail - errHead > keep) {
     const std::size_t slot = errHead % kErrRing;
     double v[2];
+    if (errPending[slot].seq == errSeq) {
+      flushErrors(); // the newest step: no kernel behind it publishes its norms
+    }
     waitError(errPending[slot].seq, v);
     ++errHead;
     if (allreduceMax != nullptr) {
@@ -3012,6 +3065,7 @@ std::size_t Sim::run(double time, double timeoutMs, int (*stopCb)(void *),
                   errMaxAbs == std::numeric_limits<double>::max() &&
                   errMaxRel == std::numeric_limits<double>::max() &&
                   !envFlagOff("SMEB200_LAGGED_ERROR");
+    deferPublish = laggedError && !envFlagOff("SMEB200_DEFER_PUBLISH");
     while (tNow + time * relativeTolerance < time) {
       const double maxDt = std::min(maxTimestep, time - tNow);
       if (integrator == SMEB200_RK101) {
@@ -3095,12 +3149,14 @@ double Sim::benchSteps(double dt, std::size_t nSteps) {
     check(cudaEventCreate(&e0), "cudaEventCreate");
     check(cudaEventCreate(&e1), "cudaEventCreate");
     check(cudaStreamSynchronize(stream), "cudaStreamSynchronize");
+    deferPublish = !useGraphs;
     check(cudaEventRecord(e0, stream), "cudaEventRecord");
     for (std::size_t i = 0; i < nSteps; ++i) {
       doStep(integrator == SMEB200_RK101 ? std::min(dt, maxStableTimestep)
                                          : dt);
       rotateAfterAccept();
     }
+    flushErrors();
     haloQuiesce();
     check(cudaEventRecord(e1, stream), "cudaEventRecord");
     check(cudaEventSynchronize(e1), "cudaEventSynchronize");

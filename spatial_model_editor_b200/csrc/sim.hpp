@@ -65,6 +65,8 @@ struct StageArgsHost {
   uint32_t nSeg;
   uint32_t errPairs;
   uint32_t roles;
+  uint32_t zig;
+  uint32_t errPublish;
   double g1, g2, g3, bdt, delta;
   double beta;
   const double *dtp;
@@ -103,6 +105,7 @@ constexpr const char *kNsFinishKernel = "smeb_ns_finish";
 struct TileConfig {
   int tx{0}, ty{0}, nst{0};
   bool m3{true};
+  bool zig{false}; // 3-D: chunk index fastest in the grid, alternating directions
   uint32_t chunk{1};
   unsigned grid[3]{1, 1, 1};
   unsigned dynSmem{0};
@@ -378,6 +381,13 @@ private:
   uint32_t errSeq{0};      // sequence number of the last publishing step launched
   bool errDesync{false};   // a failed launch sequence left the device counter behind
   uint32_t errExpected{0}; // CTAs of the error-norm launches of the current step
+  // deferred publication (device_kernels.cuh: smeb_err_publish_previous): the
+  // final stage of a step only leaves its maxima in the slot and the first kernel
+  // launched after it — or smeb_err_flush — publishes them
+  bool deferPublish{false};   // this run's final stages do not count their CTAs
+  bool errUnpublished{false}; // a final stage's maxima wait in the slot
+  CUfunction kErrFlush{nullptr};
+  void flushErrors();
   void waitError(uint32_t seq, double v[2]);
   void resyncErrorSeq();
   PendingError errPending[kErrRing]{};

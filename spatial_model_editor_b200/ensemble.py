@@ -118,6 +118,19 @@ class BatchedEnsemble:
             self.values = self.values.T
         assert self.values.shape[1] == len(problem.params)
         self.members = members_of_rank(self.values.shape[0], rank, world)
+        self._open(device)
+
+    @classmethod
+    def of_members(cls, problem: Problem, values: np.ndarray, members: List[int],
+                   device: int = 0) -> "BatchedEnsemble":
+        """an ensemble of an explicit list of member indices into ``values``"""
+        self = cls.__new__(cls)
+        self.problem, self.values, self.members = problem, values, list(members)
+        self._open(device)
+        return self
+
+    def _open(self, device: int) -> None:
+        problem = self.problem
         self._lib = load_library()
         self._h = C.c_void_p()
         p = copy.copy(problem)
@@ -186,3 +199,45 @@ class BatchedEnsemble:
                                 for ci in range(ncomp)],
                 device_ms=self.lastRunMs()))
         return out
+
+
+class GroupedEnsemble:
+    """This rank's members as ``groups`` member-batched ensembles driven by one
+    host thread each: while one group's step-size controllers look at the error
+    norms of its step, the other group's step is running — the GPU never waits for
+    the host round trip between two batched steps."""
+
+    def __init__(self, problem: Problem, values: Sequence[Sequence[float]],
+                 rank: int = 0, world: int = 1, device: int = 0, groups: int = 2):
+        probe = BatchedEnsemble.__new__(BatchedEnsemble)
+        v = np.atleast_2d(np.asarray(values, dtype=np.float64))
+        if v.shape[0] == 1 and len(problem.params) == 1 and np.asarray(values).ndim == 1:
+            v = v.T
+        self.values = v
+        mine = members_of_rank(v.shape[0], rank, world)
+        groups = max(1, min(groups, len(mine)))
+        self.parts = [BatchedEnsemble.of_members(problem, v, mine[g::groups], device)
+                      for g in range(groups)]
+        del probe
+
+    def errorMessage(self) -> str:
+        return "; ".join(e for e in (p.errorMessage() for p in self.parts) if e)
+
+    def launchCount(self) -> int:
+        return sum(p.launchCount() for p in self.parts)
+
+    def batchedSteps(self) -> int:
+        return sum(p.batchedSteps() for p in self.parts)
+
+    def run(self, time: float) -> List[MemberResult]:
+        if len(self.parts) == 1:
+            res = self.parts[0].run(time)
+        else:
+            with ThreadPoolExecutor(max_workers=len(self.parts)) as pool:
+                res = [r for part in pool.map(lambda p: p.run(time), self.parts)
+                       for r in part]
+        return sorted(res, key=lambda r: r.member)
+
+    def close(self) -> None:
+        for p in self.parts:
+            p.close()

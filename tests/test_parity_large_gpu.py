@@ -105,3 +105,31 @@ def test_c2_disc_4096_voxel_list_matches_oracle():
     args = argparse.Namespace(size=4096, adaptive=False, dt=0.25, workload="c2disc")
     p, _ = bench.make_listed_problem(args, smeb.RK212, 0)
     _compare_fixed(p, 0.25, 3)
+
+
+@pytest.mark.parametrize("workload,size,integ,dt", [("c3", 1024, smeb.RK323, 0.01),
+                                                    ("c2disc", 2048, smeb.RK212, 0.25),
+                                                    ("c3", 1024, smeb.RK435, 0.01)])
+def test_segment_staged_kernel_matches_oracle(workload, size, integ, dt):
+    """kernel_variant = 4: the voxel-list stage kernel that stages pieces of runs in
+    shared memory with bulk copies (smeb_stage_seg) — same bits as the oracle's, and
+    the same bits as the direct kernel's"""
+    import argparse
+    import bench
+    args = argparse.Namespace(size=size, adaptive=False, dt=dt, workload=workload)
+    p, _ = bench.make_listed_problem(args, integ, 0)
+    p.kernel_variant = 4
+    gpu = smeb.PixelSim(p)
+    assert gpu.errorMessage() == ""
+    assert "smeb_stage_seg" in gpu.dominantKernel()
+    gpu.close()
+    _compare_fixed(p, dt, 3)
+    q, _ = bench.make_listed_problem(args, integ, 0)
+    q.device = 0
+    a, b = smeb.PixelSim(p), smeb.PixelSim(q)
+    assert "smeb_stage_nn" in b.dominantKernel()
+    a.nextTimestep = b.nextTimestep = dt
+    assert a.run(4 * dt) == b.run(4 * dt) == 4
+    for i in range(len(p.compartments)):
+        assert np.array_equal(a.getConcentrations(i), b.getConcentrations(i))
+        assert np.array_equal(a.getDcdt(i), b.getDcdt(i))

@@ -24,8 +24,10 @@ def _problem(integ, adaptive, dims):
     return p
 
 
-def _worker(rank, world, name, integ, adaptive, dims, t_end, q):
+def _worker(rank, world, name, integ, adaptive, dims, t_end, q, fused=False):
     sys.path.insert(0, ROOT)
+    if fused:  # halo exchange inside the tile kernel (opt-in)
+        os.environ["SMEB200_FUSED_HALO"] = "1"
     from spatial_model_editor_b200.multigpu import SlabPixelSim
     try:
         p = _problem(integ, adaptive, dims)
@@ -41,11 +43,12 @@ def _worker(rank, world, name, integ, adaptive, dims, t_end, q):
         q.put((rank, f"exception: {e!r}", 0, 0, None, None, 0))
 
 
+@pytest.mark.parametrize("fused", [False, True], ids=["halo-stream", "in-kernel"])
 @pytest.mark.parametrize("integ,adaptive", [(smeb.RK101, False), (smeb.RK212, False),
                                             (smeb.RK212, True), (smeb.RK323, True),
                                             (smeb.RK435, False)])
 @pytest.mark.parametrize("dims", [(40, 70, 37), (64, 48, 1 + 8)])
-def test_slabs_match_single_gpu(integ, adaptive, dims):
+def test_slabs_match_single_gpu(integ, adaptive, dims, fused):
     world = min(smeb.device_count(), 4)
     if world < 2:
         pytest.skip("needs >= 2 GPUs")
@@ -59,8 +62,9 @@ def test_slabs_match_single_gpu(integ, adaptive, dims):
     c_ref, d_ref = ref.getConcentrations(0).copy(), ref.getDcdt(0).copy()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    name = f"smeb200_slabtest_{os.getpid()}_{integ}_{int(adaptive)}_{dims[2]}"
-    procs = [ctx.Process(target=_worker, args=(r, world, name, integ, adaptive, dims, t_end, q))
+    name = f"smeb200_slabtest_{os.getpid()}_{integ}_{int(adaptive)}_{dims[2]}_{int(fused)}"
+    procs = [ctx.Process(target=_worker,
+                         args=(r, world, name, integ, adaptive, dims, t_end, q, fused))
              for r in range(world)]
     for pr in procs:
         pr.start()
