@@ -364,7 +364,11 @@ private:
   // fixed-step configuration): the controller's decision does not depend on a
   // finite error norm, so the norms are checked kErrLag steps late instead of
   // stalling the stream after every step
-  static constexpr std::size_t kErrLag = 2, kErrRing = 8; // SMEB_ERR_RING
+  static constexpr std::size_t kErrRing = 8; // SMEB_ERR_RING
+  // steps the host may run ahead of the norms it has looked at: 2 on one GPU; 4 in
+  // a z-slab run, where a step is a few dozen driver calls on every rank and the
+  // ranks meet in two host reductions per step (SMEB200_ERR_LAG = 1 .. 6)
+  std::size_t errLag{2};
   struct PendingError {
     double dt, dtMax;
     uint32_t seq;

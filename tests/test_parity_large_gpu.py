@@ -56,7 +56,8 @@ def test_c4_512_cubed_rk212_matches_oracle():
     nz = 512 if _available_gib() > 64.0 else 128
     p = bench.make_problem(512, 512, nz, smeb.RK212)
     _, launches = _compare_fixed(p, bench.DT, 3)
-    assert launches == 6
+    assert launches in (6, 7)  # 3 steps x 2 stage kernels (+ the one-warp flush of the
+    # last step's error norms)
 
 
 def test_c2_4096_squared_rk212_matches_oracle():
