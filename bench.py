@@ -642,6 +642,13 @@ def main():
                     "avg_launch_ms": kms / klaunches,
                     "algorithmic_bytes_per_launch": alg_bytes_per_launch,
                     "launch_scope": launch_scope,
+                    # the same bytes over the whole step (launch gaps included, no
+                    # event records around the launches): a lower bound that does
+                    # not carry the few microseconds the timing events add to a
+                    # short launch; single-compartment workloads only
+                    "frac_of_step": (bytes_per_value_step * values_per_rank
+                                     + nn_bytes * STAGES[integrator])
+                    / (ms / K * 1e-3) / 1e9 / peak if (ncomp == 1 and world == 1) else None,
                     "timed_steps": f"every {timing_stride}" if timing_stride > 1 else "all"}
     sim.close()
     del hosts
@@ -654,7 +661,7 @@ def main():
     if extras and rank == 0:
         parity["vs_oracle"] = parity_vs_oracle(args, integrator, local_rank)
     cpu = refcuda = None
-    if rank == 0 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline(args, integrator, threads=host_threads())
     if extras and rank == 0 and world == 1 and args.integrator == "rk212":
         try:

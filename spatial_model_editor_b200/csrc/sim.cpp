@@ -167,6 +167,17 @@ void Sim::generateSource(const smeb200_problem &p) {
     src << "#define SMEB_NN_CODE_AHEAD " << env[0] << "\n"; // A/B measurements
   }
   src << kDeviceKernelSource << "\n";
+  // SymEngine's code printer writes integer powers as pow(x, 2) (Symbolic::cudaCode,
+  // symbolic.cpp:250-254), while the CPU solver's LLVM visitor multiplies
+  // (llvm.powi).  Inside the generated functors pow with an INTEGER literal
+  // exponent is therefore repeated multiplication — the same bits as the CPU
+  // solver and no libdevice pow on the hot path; any other exponent is ::pow.
+  src << "__device__ __forceinline__ double smeb_pow(double x, int n) {\n"
+         "  return n == 2 ? x * x : n == 3 ? (x * x) * x : n == 4 ? (x * x) * (x * x)\n"
+         "       : n == 1 ? x : n == 0 ? 1.0 : ::pow(x, (double)n);\n}\n"
+         "__device__ __forceinline__ double smeb_pow(double x, double y) {\n"
+         "  return ::pow(x, y);\n}\n"
+         "#define pow(x, y) smeb_pow((x), (y))\n";
   for (uint32_t c = 0; c < p.n_compartments; ++c) {
     const auto &comp = p.compartments[c];
     if (comp.n_species == 0) {
@@ -304,6 +315,7 @@ void Sim::generateSource(const smeb200_problem &p) {
     src << functorSource(h.str(), SAP + SBP + NE, mb.expressions, SAP + SBP,
                          p.n_params);
   }
+  src << "#undef pow\n";
   src << "template <int S_OWN>\n__device__ __forceinline__ void\n"
          "smeb_memb_dispatch(smeb_u32 info, smeb_u32 partner, const double "
          "*cown,\n                   const SmebMembArgs &m, const double "
@@ -2192,6 +2204,14 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
       // membrane kernels go to the high-priority halo stream, which pushes the
       // halos as soon as they are done; the interior runs beside them on the
       // main stream (below)
+      // The interior launch is enqueued first: the nine driver calls of the halo
+      // stream must not sit between two interior launches on the host side; on
+      // the device the halo stream's priority still gives the boundary CTAs
+      // the next free SM slots.  (SMEB200_INTERIOR_FIRST=0: after the pushes.)
+      static const bool interiorFirst = !envFlagOff("SMEB200_INTERIOR_FIRST");
+      if (interiorFirst && item.hasMid) {
+        launchCompartment(ci, item.mid, c.kStage[stageIndex], c.role[sd.cin], false, 1);
+      }
       suppressTiming = true;
       forkMain = forkMemb = haloStream; // concurrent with the interior launch
       if (item.hasLo) {
@@ -2203,7 +2223,7 @@ void Sim::launchStage(std::size_t stageIndex, double dt) {
       launchCompartment(ci, a, c.kStage[stageIndex], c.role[sd.cin], false, 2);
       forkMain = forkMemb = nullptr;
       suppressTiming = false;
-      if (item.hasMid) {
+      if (item.hasMid && !interiorFirst) {
         interior.emplace_back(ci, item.mid);
       }
     } else {

@@ -148,3 +148,23 @@ def test_neighbour_codes_refuse_foreign_orderings():
     nn = np.array([[1, 0, 2, 0, 0, 0], [1, 0, 1, 1, 1, 1], [2, 2, 2, 0, 2, 2]], dtype=np.uint32)
     rc, _, _ = _compress(nn)
     assert rc == 1
+
+
+def test_symengine_style_expression_text_compiles():
+    """What Symbolic::cudaCode prints (SymEngine's CUDA code printer: integer powers as
+    pow(x, 2), plain decimal literals, nested parentheses, exp / sqrt / fabs calls)
+    goes through smeb200_create's NVRTC path; integer-literal powers become
+    multiplications (the CPU solver's LLVM visitor uses llvm.powi)"""
+    import spatial_model_editor_b200 as smeb
+    from spatial_model_editor_b200 import models as M
+    p = M.box_problem(M.GRAY_SCOTT, 8, 8, 4)
+    c = p.compartments[0]
+    c.expressions = [
+        "0.0 + -1.0*sme_var_0*pow(sme_var_1, 2) + 0.037000000000000005*(1.0 - sme_var_0)",
+        "0.0 + sme_var_0*pow(sme_var_1, 2) - 0.097*sme_var_1 + 0.0*exp(-pow(sme_var_0, 3))"
+        " + 0.0*sqrt(fabs(sme_var_1)) + 0.0*pow(sme_var_0, 0.5)",
+    ]
+    sim = smeb.PixelSim(p, compile_only=True)
+    assert sim.errorMessage() == ""
+    src = sim.kernelSource()
+    assert "smeb_pow" in src and "pow(sme_var_1, 2)" in src

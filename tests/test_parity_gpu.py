@@ -308,3 +308,24 @@ def test_lagged_error_check_with_stop_and_timeout(monkeypatch):
     compare_state(gpu, cpu, p, "stopped after 5 steps")
     assert gpu.run(1e9, 50.0) >= 1
     assert gpu.errorMessage() == "Simulation stopped early"
+
+
+def test_symengine_pow_text_equals_products():
+    """pow(x, 2) as SymEngine prints it vs x * x as the Python printer writes it: the
+    same bits on the device, and the oracle's (product form) within 1e-12"""
+    import copy
+    p = M.box_problem(M.GRAY_SCOTT, 40, 36, 10, integrator=smeb.RK212,
+                      max_err_rel=smeb.DBL_MAX, max_err_abs=smeb.DBL_MAX, max_timestep=0.05)
+    p.device = 0
+    q = copy.deepcopy(p)
+    c = q.compartments[0]
+    c.expressions = [e.replace("(sme_var_1 * sme_var_1)", "pow(sme_var_1, 2)")
+                     for e in c.expressions]
+    assert all("pow(" in e for e in c.expressions)
+    a, b = smeb.PixelSim(p), smeb.PixelSim(q)
+    assert a.errorMessage() == b.errorMessage() == ""
+    assert a.run(1.0) == b.run(1.0)
+    assert np.array_equal(a.getConcentrations(0), b.getConcentrations(0))
+    cpu = OraclePixelSim(p)
+    cpu.run(1.0)
+    assert_parity(b.getConcentrations(0), cpu.getConcentrations(0), what="pow text")
