@@ -68,7 +68,27 @@ def make_listed_problem(args, integrator, device):
     n = args.size
     tol = dict(max_err_rel=0.005) if args.adaptive else dict(
         max_err_rel=smeb.DBL_MAX, max_err_abs=smeb.DBL_MAX, max_timestep=args.dt)
-    if args.workload == "c2disc":
+    if args.workload == "c4blob":
+        # BASELINE config 4's irregular variant: the blob of the gray-scott-3d example
+        # (11 789 of 50^3 voxels) upscaled to size^3 by nearest neighbour — a 3-D
+        # voxel list that z-slabs can cut
+        from spatial_model_editor_b200 import geometry as G
+        z = np.load(os.path.join(ROOT, "tests", "golden", "gray-scott-3d.npz"))
+        small = z["labels"].astype(np.int32)
+        src = (np.arange(n) * small.shape[0]) // n
+        lab = small[np.ix_(src, (np.arange(n) * small.shape[1]) // n,
+                           (np.arange(n) * small.shape[2]) // n)]
+        label = int(np.bincount(small.ravel())[1:].argmax()) + 1
+        lab = (lab == label).astype(np.int32)
+        vox = G.compartment_voxels(lab, 1)
+        px, py, pz = ((vox[:, k] % 100).astype(np.float64) for k in range(3))
+        conc0 = np.ones((len(vox), 2))
+        conc0[:, 1] = (np.exp(-((px - 33.0) ** 2 + (py - 40.0) ** 2 + (pz - 25.0) ** 2) / 50.0)
+                       + np.exp(-((px - 70.0) ** 2 + (py - 66.0) ** 2 + (pz - 60.0) ** 2) / 50.0))
+        p = M.labelled_problem(lab, [dict(label=1, id="blob", kin=M.GRAY_SCOTT, conc0=conc0)],
+                               voxel_size=(2.0, 2.0, 2.0), integrator=integrator, **tol)
+        text = f"gray-scott kinetics on the gray-scott-3d blob upscaled to {n}^3"
+    elif args.workload == "c2disc":
         lab = M.disc_labels(n, n)
         from spatial_model_editor_b200 import geometry as G
         vox = G.compartment_voxels(lab, 1)
@@ -176,10 +196,10 @@ def cpu_baseline(args, integrator, threads, budget_s=12.0):
     the same workload (a 32-plane slab of the same x-y extent, about 10-20 s of
     CPU work), all host threads"""
     from oracle.oracle_sim import OraclePixelSim
-    if args.workload in ("c2disc", "c3"):
+    if args.workload in ("c2disc", "c3", "c4blob"):
         import copy
         a2 = copy.copy(args)
-        a2.size, a2.adaptive = min(args.size, 2048), False
+        a2.size, a2.adaptive = min(args.size, 192 if args.workload == "c4blob" else 2048), False
         p, text = make_listed_problem(a2, integrator, -1)
         sim = OraclePixelSim(p, threads=threads)
         sim.nextTimestep = args.dt
@@ -435,7 +455,7 @@ def main():
                          "reference-GPU-kernel baseline (A/B runs)")
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--workload", default="c4",
-                    help="c4 (headline) | c2disc | c3 | ensemble")
+                    help="c4 (headline) | c4blob | c2disc | c3 | ensemble")
     ap.add_argument("--adaptive", action="store_true",
                     help="c2disc / c3: adaptive steps at relTol 0.005 instead of fixed dt")
     ap.add_argument("--dt", type=float, default=DT)
@@ -489,7 +509,7 @@ def main():
     # strong scaling (default): one global box; weak: nz_arg planes per GPU
     nz_total = nz_arg * world if args.weak else nz_arg
     W, K = max(args.warmup, 3), args.steps
-    listed = args.workload in ("c2disc", "c3")
+    listed = args.workload in ("c2disc", "c3", "c4blob")
     DTs = args.dt
     if listed:
         from spatial_model_editor_b200.multigpu import SlabPixelSim
@@ -498,12 +518,14 @@ def main():
         evals_per_step = p.evals_per_step()
         dom = max(p.compartments, key=lambda c: c.n_voxels * c.n_species)
         dom_index = p.compartments.index(dom)
-        if world > 1:  # voxel lists cut at plane boundaries (2-D images: along x? no:
-            # the slab axis is z, so a 2-D workload is stacked nz = world planes deep)
-            raise SystemExit("bench: voxel-list workloads are 2-D images here; run them "
-                             "on one GPU (z-slabs need planes to cut)")
-        sim = smeb.PixelSim(p)
-        values_per_rank = dom.n_voxels * dom.n_species
+        if world > 1 and args.workload != "c4blob":
+            raise SystemExit("bench: c2disc / c3 are 2-D images (one z plane): z-slabs have "
+                             "nothing to cut; the 3-D voxel-list workload is c4blob")
+        if world > 1:  # the voxel list and its membranes cut at plane boundaries
+            sim = SlabPixelSim(p, rank, world, variant=args.variant)
+        else:
+            sim = smeb.PixelSim(p)
+        values_per_rank = dom.n_voxels * dom.n_species // world
         nn_bytes = sim.neighbourBytesPerVoxel(dom_index) * dom.n_voxels
         workload_text += (f"; neighbour data {sim.neighbourBytesPerVoxel(dom_index)} B/voxel"
                           f" ({sim.neighbourRuns(dom_index)} runs)")
@@ -617,7 +639,13 @@ def main():
     alg_bytes_per_launch = (bytes_per_value_step * values_per_rank / STAGES[integrator]
                             + nn_bytes)
     launch_scope = "whole compartment"
-    if world > 1:
+    if world > 1 and listed:
+        nn_bytes //= world
+        alg_bytes_per_launch = (bytes_per_value_step * values_per_rank / STAGES[integrator]
+                                + nn_bytes)
+        launch_scope = ("rank 0: its share of the voxel list (the two boundary planes are "
+                        "launched apart: an upper bound of the launch's bytes)")
+    elif world > 1:
         timed = sim.timedLaunchPlanes()
         alg_bytes_per_launch *= timed / nz_local
         launch_scope = f"rank 0: {timed} of its {nz_local} owned planes"

@@ -265,3 +265,25 @@ def test_communicator_generations_wide_reductions_and_abort(world):
     for pr in procs:
         pr.join(timeout=60)
     assert sorted(results) == [(r, True) for r in range(world)]
+
+
+def test_balanced_cuts_deal_voxels_not_planes():
+    """voxel-list slabs: plane cuts by voxel count, every rank at least one plane"""
+    rng = np.random.default_rng(3)
+    nz = 40
+    # an off-centre blob: nothing in the lowest 12 planes, a lot around plane 25
+    z = np.clip(rng.normal(25.0, 4.0, size=20000).round().astype(int), 12, nz - 1)
+    for world in (2, 3, 8):
+        cuts = MG.balanced_cuts([z], nz, world)
+        assert cuts[0] == 0 and cuts[-1] == nz and len(cuts) == world + 1
+        assert all(b > a for a, b in zip(cuts, cuts[1:]))
+        counts = [int(np.count_nonzero((z >= a) & (z < b))) for a, b in zip(cuts, cuts[1:])]
+        assert sum(counts) == len(z)
+        assert max(counts) < 2.2 * len(z) / world  # within a plane's worth of the mean
+        even = [int(np.count_nonzero((z >= MG.slab_range(nz, r, world)[0])
+                                     & (z < MG.slab_range(nz, r, world)[1])))
+                for r in range(world)]
+        assert max(counts) <= max(even)
+    # more ranks than occupied planes still gives everybody a plane
+    cuts = MG.balanced_cuts([np.array([5, 5, 5, 6])], 8, 8)
+    assert cuts == list(range(9))
