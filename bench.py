@@ -697,6 +697,14 @@ def main():
             refcuda["product_over_refcuda"] = (ms / K) and refcuda["ms_per_step"] / (ms / K)
         except Exception as e:  # e.g. not enough memory beside another process
             refcuda = {"unavailable": str(e)}
+    # every stage streams its whole input and output arrays: nothing of a step is
+    # left in L2 for the next one when the rotating buffers together exceed it
+    nbuf = {0: 2, 1: 3, 2: 3, 3: 4}[integrator]
+    working_set = nbuf * values_per_rank * 8
+    l2_text = ("rotating state buffers on rank 0: %d x %.3f GiB %s the 126 MB L2" % (
+        nbuf, values_per_rank * 8 / 2 ** 30,
+        "— larger than" if working_set > 126e6 * 1.5 else
+        "— NOT larger than (L2-resident numbers: no flush between steps)"))
     if rank == 0:
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
@@ -707,8 +715,7 @@ def main():
                 "workload": workload_text + f", {args.integrator.upper()} " + (
                     "adaptive relTol=0.005 (a step = one attempted step)" if adaptive else
                     f"fixed step dt={DTs} (maxErr=DBL_MAX like benchmark.cpp:214-216)"),
-                "l2": "inputs larger than L2 (state array %.2f GiB on rank 0)" % (
-                    values_per_rank * 8 / 2 ** 30),
+                "l2": l2_text,
                 "parallelism": (f"z-slabs x{world}, " + ("weak: box grows with N" if args.weak
                                 else "strong: one global box")) if world > 1 else "single GPU",
                 "kernel_variant": args.variant},
