@@ -106,7 +106,8 @@ typedef struct smeb200_compartment {
    * pseudo-time before every Runge-Kutta stage
    * (PixelSim::solveZeroStorageConstraints, pixelsim.cpp:23-90), its dc/dt is
    * zero and it is left out of the error norm (pixelsim_impl.cpp:778-781).
-   * Not available in a z-slab decomposed simulation. */
+   * In a z-slab decomposed simulation the iterates exchange their boundary
+   * planes and the norms are max-reduced over the ranks. */
   const double *inv_storage;
   /* Non-uniform diffusion (SimCompartment::evaluateDiffusionOperator, array
    * branch, pixelsim_impl.cpp:453-485): [n_voxels*n_species] diffusion

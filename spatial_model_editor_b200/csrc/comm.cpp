@@ -4,6 +4,8 @@
 #include <chrono>
 #include <cmath>
 #include <cstring>
+#include <cerrno>
+#include <csignal>
 #include <fcntl.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
@@ -83,6 +85,7 @@ ShmComm::ShmComm(const std::string &name, int rank, int nRanks,
     if (rank == 0) {
       // a fresh segment is zero-filled; publish it
       seg_->nRanks = static_cast<uint32_t>(nRanks);
+      seg_->creatorPid = static_cast<int32_t>(getpid());
       seg_->magic.store(kMagic, std::memory_order_release);
       seg_->attached.fetch_add(1, std::memory_order_acq_rel);
       break;
@@ -112,6 +115,10 @@ ShmComm::ShmComm(const std::string &name, int rank, int nRanks,
         throw Error("smeb200: timed out waiting for the communicator header");
       }
       std::this_thread::sleep_for(std::chrono::milliseconds(1));
+    }
+    if (!stale && seg_->creatorPid > 0 && kill(seg_->creatorPid, 0) != 0 &&
+        errno == ESRCH) {
+      stale = true; // left behind by a process that no longer exists
     }
     if (!stale && seg_->nRanks != static_cast<uint32_t>(nRanks)) {
       munmap(seg_, sizeof(CommSegment));

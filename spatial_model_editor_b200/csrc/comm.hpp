@@ -21,7 +21,7 @@
 namespace smeb200 {
 
 constexpr int kCommMaxRanks = 16;
-constexpr int kCommMaxBuffers = 4;
+constexpr int kCommMaxBuffers = 8; // 4 rotating state buffers + 3 relaxation buffers
 constexpr int kCommMaxCompartments = 4;
 
 struct CommRankSlot {
@@ -50,7 +50,10 @@ struct CommSegment {
   // set by a rank whose run failed: every wait of the other ranks throws instead
   // of spinning until its timeout
   std::atomic<uint32_t> abort;
-  uint32_t pad_[8];
+  // the process that created the segment: a segment whose creator is gone is a
+  // leftover of a crashed run, whatever its attach count says
+  int32_t creatorPid;
+  uint32_t pad_[7];
   // halo flags: flag[r][0] = sequence of the last halo pushed into rank r's
   // LOW ghost plane (by rank r-1), flag[r][1] = into its HIGH ghost (by r+1).
   // Own 4 KiB page(s): registered with CUDA by every process.

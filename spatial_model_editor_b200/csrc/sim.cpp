@@ -1195,10 +1195,6 @@ void Sim::build(const smeb200_problem &p) {
         // Zero storage: an algebraic species, relaxed in pseudo-time before
         // every stage (pixelsim.cpp:23-90).  Its diffusion bounds the
         // relaxation step, not the time step (pixelsim_impl.cpp:238-247).
-        if (p.n_ranks > 1) {
-          throw Error("smeb200: zero-storage species are not supported in a "
-                      "z-slab decomposed simulation");
-        }
         c.zeroStorage.push_back(s);
         anyZeroStorage = true;
         double dsum = c.D[3 * s] + c.D[3 * s + 1] + c.D[3 * s + 2];
@@ -1268,7 +1264,8 @@ void Sim::build(const smeb200_problem &p) {
   // stores through the peer mapping 10 more — so the in-kernel exchange is opt-in
   // (SMEB200_FUSED_HALO=1).
   const char *fusedEnv = std::getenv("SMEB200_FUSED_HALO");
-  if (nRanks > 1 && fusedEnv != nullptr && fusedEnv[0] == '1' && !nsInSlabs) {
+  if (nRanks > 1 && fusedEnv != nullptr && fusedEnv[0] == '1' && !nsInSlabs &&
+      !anyZeroStorage) {
     bool any = false, all = true;
     for (const auto &c : comps) {
       if (c.S == 0 || c.n == 0) {
@@ -1583,6 +1580,15 @@ void Sim::connectSlabs() {
       static_assert(sizeof(h) == 64, "CUDA IPC handle size");
       std::memcpy(mine.memHandle[ci][b], &h, sizeof(h));
     }
+    // the relaxation buffers of zero-storage species take part in the exchange
+    for (std::size_t k = 0; k < c.pool.size() && c.n > 0 && c.S > 0; ++k) {
+      if (4 + k >= static_cast<std::size_t>(kCommMaxBuffers)) {
+        throw Error("smeb200: internal error (relaxation buffers)");
+      }
+      cudaIpcMemHandle_t h{};
+      check(cudaIpcGetMemHandle(&h, c.pool[k].p), "cudaIpcGetMemHandle");
+      std::memcpy(mine.memHandle[ci][4 + k], &h, sizeof(h));
+    }
   }
   mine.fusedHalo = fusedHalo ? 1 : 0;
   if (fusedHalo) {
@@ -1637,6 +1643,16 @@ void Sim::connectSlabs() {
               "cudaIpcOpenMemHandle (is peer access between the GPUs of this "
               "node available?)");
         peerBuf[side][ci][b] = static_cast<double *>(ptr);
+        ipcOpened.push_back(ptr);
+      }
+      for (std::size_t k = 0; k < c.pool.size(); ++k) {
+        cudaIpcMemHandle_t h{};
+        std::memcpy(&h, seg->slot[nb].memHandle[ci][4 + k], sizeof(h));
+        void *ptr = nullptr;
+        check(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess),
+              "cudaIpcOpenMemHandle(relaxation buffer)");
+        c.pool[k].peer[side] = static_cast<double *>(ptr);
+        ipcOpened.push_back(ptr);
       }
     }
   }
@@ -1674,6 +1690,19 @@ void Sim::connectSlabs() {
 // which this rank writes after the boundary-plane and membrane kernels of its
 // stage k-1 -- the only kernels that read ghost voxels.)
 void Sim::haloPush(int coutBuf, cudaStream_t s) {
+  std::vector<const double *> local(comps.size(), nullptr);
+  std::vector<std::array<double *, 2>> peer(comps.size(),
+                                            std::array<double *, 2>{nullptr, nullptr});
+  for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+    local[ci] = comps[ci].buf[coutBuf];
+    peer[ci] = {peerBuf[0][ci][coutBuf], peerBuf[1][ci][coutBuf]};
+  }
+  haloPushPtrs(local, peer, s);
+}
+
+void Sim::haloPushPtrs(const std::vector<const double *> &local,
+                       const std::vector<std::array<double *, 2>> &peer,
+                       cudaStream_t s) {
   const auto &drv = DriverApi::get();
   auto *seg = comm->segment();
   ++haloSeq;
@@ -1685,7 +1714,7 @@ void Sim::haloPush(int coutBuf, cudaStream_t s) {
   };
   for (std::size_t ci = 0; ci < comps.size(); ++ci) {
     auto &c = comps[ci];
-    if (c.S == 0 || c.n == 0) {
+    if (c.S == 0 || c.n == 0 || local[ci] == nullptr) {
       continue;
     }
     // box: whole planes; voxel list: the voxels of the first / last owned plane
@@ -1698,14 +1727,13 @@ void Sim::haloPush(int coutBuf, cudaStream_t s) {
         c.box ? (c.nz - 1 - c.zHiGhost) * plane
               : (c.n - c.vGhostHi) * c.S - hiCnt;
     if (rank > 0 && loCnt > 0) { // first owned plane -> HIGH ghosts of rank-1
-      check(cudaMemcpyAsync(peerBuf[0][ci][coutBuf] +
-                                seg->slot[rank - 1].ghostHiOff[ci],
-                            c.buf[coutBuf] + loOff, loCnt * sizeof(double),
+      check(cudaMemcpyAsync(peer[ci][0] + seg->slot[rank - 1].ghostHiOff[ci],
+                            local[ci] + loOff, loCnt * sizeof(double),
                             cudaMemcpyDefault, s),
             "halo push (low neighbour)");
     }
     if (rank + 1 < nRanks && hiCnt > 0) { // last owned plane -> LOW ghosts of rank+1
-      check(cudaMemcpyAsync(peerBuf[1][ci][coutBuf], c.buf[coutBuf] + hiOff,
+      check(cudaMemcpyAsync(peer[ci][1], local[ci] + hiOff,
                             hiCnt * sizeof(double), cudaMemcpyDefault, s),
             "halo push (high neighbour)");
     }
@@ -1861,14 +1889,8 @@ Sim::~Sim() {
       }
     } catch (...) {
     }
-    for (auto &side : peerBuf) {
-      for (auto &cb : side) {
-        for (double *ptr : cb) {
-          if (ptr != nullptr) {
-            cudaIpcCloseMemHandle(ptr);
-          }
-        }
-      }
+    for (void *ptr : ipcOpened) {
+      cudaIpcCloseMemHandle(ptr);
     }
     for (auto *ptr : peerHalo) {
       if (ptr != nullptr) {
@@ -2325,6 +2347,8 @@ void Sim::solveZeroStorageConstraints(std::size_t stageIndex) {
     const int idx = c.role[sd.cin];
     in[ci].p = c.buf[idx];
     in[ci].t = c.tmap[idx];
+    in[ci].peer[0] = peerBuf[0][ci][idx];
+    in[ci].peer[1] = peerBuf[1][ci][idx];
     if (protect && !c.zeroStorage.empty() && c.n > 0) {
       // the pre-step state (s3) must keep the un-relaxed values: relax a copy
       check(cudaMemcpyAsync(c.pool[2].p, c.buf[idx], c.n * c.S * sizeof(double),
@@ -2343,8 +2367,10 @@ void Sim::solveZeroStorageConstraints(std::size_t stageIndex) {
                                                               : in[ci].p;
       if (!c.zeroStorage.empty() && c.n > 0) {
         StageArgsHost r{};
-        r.n = static_cast<uint32_t>(c.n);
-        r.z_end = c.nz;
+        r.v0 = c.vGhostLo;
+        r.n = static_cast<uint32_t>(c.n - c.vGhostHi);
+        r.z_begin = c.zLoGhost;
+        r.z_end = c.nz - c.zHiGhost;
         const auto &k = second ? c.kRelaxB : c.kRelaxA;
         expected += mainGrid(ci, r, k.main) + membGrid(ci, k.memb);
       }
@@ -2369,13 +2395,14 @@ void Sim::solveZeroStorageConstraints(std::size_t stageIndex) {
     a.errPairs = 1;
       a.errHost = dErrRing;
       a.errExpected = expected;
-      a.n = static_cast<uint32_t>(c.n);
-      a.v0 = 0;
+      // z-slabs: the owned voxels; the iterate's ghosts come from the neighbours
+      a.n = static_cast<uint32_t>(c.n - c.vGhostHi);
+      a.v0 = c.vGhostLo;
       a.nx = c.nx;
       a.ny = c.ny;
       a.nz = c.nz;
-      a.z_begin = 0;
-      a.z_end = c.nz;
+      a.z_begin = c.zLoGhost;
+      a.z_end = c.nz - c.zHiGhost;
       a.bdt = second ? 0.5 * dt : dt;
       a.eps = epsilon;
       std::copy(c.D.begin(), c.D.end(), a.D);
@@ -2399,7 +2426,30 @@ void Sim::solveZeroStorageConstraints(std::size_t stageIndex) {
     if (expected > 0) {
       ++errSeq;
     }
+    if (comm && slabsConnected) {
+      // z-slabs: the boundary planes of the new iterate go to the neighbours
+      // before anybody reads it (every rank takes the same accept / reject
+      // decisions from max-reduced norms, so the ranks' buffers swap in lock step
+      // and a buffer's peer mapping stays its counterpart)
+      std::vector<const double *> local(comps.size(), nullptr);
+      std::vector<std::array<double *, 2>> peer(
+          comps.size(), std::array<double *, 2>{nullptr, nullptr});
+      for (std::size_t ci = 0; ci < comps.size(); ++ci) {
+        const auto &c = comps[ci];
+        if (c.zeroStorage.empty() || c.n == 0) {
+          continue;
+        }
+        const auto &out = second ? c.pool[1] : c.pool[0];
+        local[ci] = out.p;
+        peer[ci] = {out.peer[0], out.peer[1]};
+      }
+      haloPushPtrs(local, peer, stream);
+      haloWait(stream);
+    }
   };
+  if (comm && slabsConnected) {
+    haloQuiesce(); // the stage input's ghosts have arrived, the halo stream is idle
+  }
   relaxing = true;
   try {
     constexpr std::size_t maxIterations{100};
@@ -2445,6 +2495,8 @@ void Sim::solveZeroStorageConstraints(std::size_t stageIndex) {
       const int idx = c.role[sd.cin];
       c.buf[idx] = in[ci].p;
       c.tmap[idx] = in[ci].t;
+      peerBuf[0][ci][idx] = in[ci].peer[0];
+      peerBuf[1][ci][idx] = in[ci].peer[1];
     }
   }
 }
@@ -2945,6 +2997,11 @@ void Sim::syncMaxStableTimestep() {
   double v = -maxStableTimestep; // exact under negation
   comm->allreduceMax(&v, 1);
   maxStableTimestep = -v;
+  if (anyZeroStorage) { // the pseudo-time step of the relaxation as well
+    double r = -maxRelaxStableTimestep;
+    comm->allreduceMax(&r, 1);
+    maxRelaxStableTimestep = -r;
+  }
 }
 
 double Sim::doRK101(double dt) {

@@ -9,6 +9,7 @@
 #include "comm.hpp"
 #include "cuda_api.hpp"
 #include <algorithm>
+#include <array>
 #include <atomic>
 #include <cstdint>
 #include <limits>
@@ -160,6 +161,9 @@ struct CompartmentState {
   struct PoolBuf {
     double *p{nullptr};
     CUtensorMap t{};
+    // z-slabs: the same buffer of the rank below / above (CUDA IPC mapping); the
+    // ranks swap their buffers in lock step, so the pairing survives the swaps
+    double *peer[2]{nullptr, nullptr};
   };
   std::vector<uint32_t> zeroStorage;
   std::vector<PoolBuf> pool;
@@ -407,6 +411,11 @@ private:
   void setupSlabs(const smeb200_problem &p);
   void connectSlabs();
   void haloPush(int coutBuf, cudaStream_t s);
+  // boundary planes of arbitrary per-compartment buffers (nullptr: skip) into the
+  // neighbours' ghost planes of the paired buffers, then the flags
+  void haloPushPtrs(const std::vector<const double *> &local,
+                    const std::vector<std::array<double *, 2>> &peer,
+                    cudaStream_t s);
   void haloWait(cudaStream_t s);
   void haloQuiesce();
   void syncMaxStableTimestep();
@@ -456,6 +465,7 @@ private:
   int rank{0}, nRanks{1};
   std::unique_ptr<ShmComm> comm;
   double *peerBuf[2][kCommMaxCompartments][kCommMaxBuffers]{};
+  std::vector<void *> ipcOpened; // every mapping opened (closed once, at the end)
   bool flagsRegistered{false};
   CUdeviceptr flagBaseDev{0};
   uint32_t haloSeq{0};

@@ -408,3 +408,77 @@ def test_stop_is_collective_in_slabs(mode):
 
     assert ref.run(1000.0, -1.0, after_n) == n  # the same sequence of step sizes
     assert np.array_equal(np.concatenate([r[5] for r in res]), ref.getConcentrations(0))
+
+
+# ---- zero-storage (algebraic) species: the relaxation's iterates cross the slabs ----
+def _zero_storage_problem(geom, integ):
+    from spatial_model_editor_b200.pde import ReactionDef  # noqa: F401
+    if geom == "box":
+        p = M.box_problem(M.ABTOC, 24, 32, 12, integrator=integ)
+        zs = 2
+    else:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        from util import load_golden
+        p, _, _ = load_golden("single-compartment-diffusion-3d", integrator=integ)
+        zs = 0
+    c = p.compartments[0]
+    inv = np.ones(c.n_species)
+    inv[zs] = 0.0
+    c.inv_storage = inv
+    p.max_err_abs, p.max_err_rel = smeb.DBL_MAX, 0.01  # tolerances of the relaxation
+    p.max_timestep = 1e-3
+    return p
+
+
+def _zero_storage_worker(rank, world, name, geom, integ, q):
+    sys.path.insert(0, ROOT)
+    from spatial_model_editor_b200.multigpu import SlabPixelSim
+    try:
+        p = _zero_storage_problem(geom, integ)
+        p.device = rank
+        sim = SlabPixelSim(p, rank, world, comm_name=name)
+        err0 = sim.errorMessage()
+        if integ != smeb.RK101:
+            sim.nextTimestep = 1e-3
+        n = sim.run(3e-3) + sim.run(2e-3)
+        q.put((rank, err0 + sim.errorMessage(), n, sim.getConcentrations(0).copy(),
+               sim.haloExchanges()))
+        sim.close()
+    except Exception as e:  # noqa: BLE001
+        q.put((rank, f"exception: {e!r}", 0, None, 0))
+
+
+@pytest.mark.parametrize("geom", ["box", "list"])
+@pytest.mark.parametrize("integ", [smeb.RK101, smeb.RK212, smeb.RK323])
+def test_zero_storage_species_in_slabs_match_single_gpu(geom, integ):
+    """PixelSim::solveZeroStorageConstraints (pixelsim.cpp:23-90) across z-slabs: the
+    pseudo-time iterates exchange their boundary planes, the residual and error norms
+    are max-reduced, every rank takes the single-GPU iteration — bit-identical state"""
+    world = min(smeb.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs >= 2 GPUs")
+    import torch.multiprocessing as mp
+    p = _zero_storage_problem(geom, integ)
+    p.device = 0
+    ref = smeb.PixelSim(p)
+    assert ref.errorMessage() == ""
+    if integ != smeb.RK101:
+        ref.nextTimestep = 1e-3
+    n_ref = ref.run(3e-3) + ref.run(2e-3)
+    assert n_ref >= 5 and ref.errorMessage() == ""
+    c_ref = ref.getConcentrations(0).copy()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    name = f"smeb200_zstest_{os.getpid()}_{geom}_{integ}"
+    procs = [ctx.Process(target=_zero_storage_worker, args=(r, world, name, geom, integ, q))
+             for r in range(world)]
+    for pr in procs:
+        pr.start()
+    res = sorted((q.get(timeout=300) for _ in range(world)), key=lambda r: r[0])
+    for pr in procs:
+        pr.join(timeout=60)
+    for r in res:
+        assert r[1] == "", r[1]
+        assert r[2] == n_ref
+        assert r[4] >= 2 * n_ref  # the relaxation exchanged halos of its own
+    assert np.array_equal(np.concatenate([r[3] for r in res]), c_ref)
