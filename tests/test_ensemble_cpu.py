@@ -1,5 +1,6 @@
 """host logic of the parameter-scan ensembles (BASELINE config 5) on CPU"""
 import numpy as np
+import pytest
 
 import spatial_model_editor_b200 as smeb
 from spatial_model_editor_b200 import ensemble as EN
@@ -54,3 +55,28 @@ def test_ensemble_driver_with_the_oracle_as_backend():
     assert np.array_equal(a.getConcentrations(0), b.getConcentrations(0))
     # different parameter values give different trajectories
     assert not np.array_equal(res[0].concentrations[0], res[1].concentrations[0])
+
+
+def test_batched_ensemble_without_a_device_carries_the_error():
+    """smeb200_ensemble_create never throws: without a GPU the object carries the
+    reference-style "no device / driver" message and nothing is computed on the CPU"""
+    import spatial_model_editor_b200 as smeb
+    if smeb.device_count() > 0:
+        pytest.skip("a GPU is present")
+    p, _, _ = load_golden("liver-simplified-scan")
+    ens = EN.BatchedEnsemble(p, EN.scan_values(p.params[0], 4))
+    msg = ens.errorMessage()
+    assert msg.startswith("No CUDA devices were found") or \
+        msg.startswith("Failed to initialize the CUDA driver") or \
+        msg.startswith("Failed to query CUDA devices")
+    with pytest.raises(RuntimeError):
+        ens.run(0.1)
+    assert ens.launchCount() == 0
+    ens.close()
+
+
+def test_members_are_dealt_round_robin_and_groups_cover_them():
+    assert EN.members_of_rank(10, 1, 4) == [1, 5, 9]
+    mine = EN.members_of_rank(64, 3, 8)
+    groups = [mine[g::2] for g in range(2)]
+    assert sorted(groups[0] + groups[1]) == mine and len(mine) == 8
