@@ -46,6 +46,7 @@ typedef unsigned int smeb_u32;
 #define SMEB_F_RELAX_B 8192u     // second half: out = c0/2 + c/2 + dt/2 f, error
 #define SMEB_F_HALO 16384u       // z-slabs, tile kernel: halo exchange in the kernel
 #define SMEB_F_MEMBERS 32768u    // member-batched ensemble: gridDim.y = members
+#define SMEB_F_ZIG 65536u        // tile kernel, 3-D: zig-zag chunk order (opt-in)
 
 #define SMEB_MEMB_FLAG 0x80000000u
 #define SMEB_BLOCK 256
@@ -1216,9 +1217,10 @@ __global__ void __launch_bounds__(SMEB_BLOCK, SMEB_TILE_MIN_CTAS)
   // otherwise: 25 % at 8 planes per chunk).
   bool down = false;
   smeb_u32 tilesPerPlane = gridDim.x * gridDim.y;
+  constexpr bool ZIG = M3 && (F & SMEB_F_ZIG) != 0; // compiled in only on request
   if constexpr (M3) {
     int zc;
-    if (a.zig != 0u) {
+    if (ZIG && a.zig != 0u) {
       zc = blockIdx.x;
       y0 = blockIdx.y * TY;
       x0 = blockIdx.z * TX;

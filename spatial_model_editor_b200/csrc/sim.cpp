@@ -728,6 +728,10 @@ void Sim::chooseGeometry(int variant) {
     // planes (scheduled first) are a small part of the launch and the halos
     // leave early
     const unsigned minChunks = nRanks > 1 ? 4u : 1u;
+    double haloWeight = 0.5;
+    if (const char *env = std::getenv("SMEB200_HALO_WEIGHT"); env != nullptr) {
+      haloWeight = std::atof(env); // A/B measurements (round 1: 1.0)
+    }
     auto pickChunks = [&](unsigned units, unsigned tiles, double haloUnits) {
       unsigned best = 1;
       double bestCost = 1e300;
@@ -748,8 +752,10 @@ void Sim::chooseGeometry(int variant) {
           continue;
         }
         const double waves = std::ceil(total / wave);
+        // the halo units of a chunk are read again, but from L2 (ncu: DRAM reads
+        // stay at 1.01 x the stage input down to 8-plane chunks): half weight
         const double cost =
-            waves * wave / total * (chunk + haloUnits) / chunk;
+            waves * wave / total * (chunk + haloWeight * haloUnits) / chunk;
         if (cost < bestCost - 1e-12) {
           bestCost = cost;
           best = chunks;
@@ -779,6 +785,7 @@ void Sim::chooseGeometry(int variant) {
       // ms/step, 512x512x64 0.2385 vs 0.2348): opt-in only
       const char *zz = std::getenv("SMEB200_ZIGZAG");
       t.zig = zz != nullptr && zz[0] == '1' && chunks > 1;
+      zigzag = zigzag || t.zig;
     } else {
       const unsigned bricks = (c.nx + t.tx - 1) / t.tx;
       unsigned chunks = forced ? std::min(forced, bricks)

@@ -27,7 +27,7 @@ constexpr uint32_t F_USE_C0 = 1u, F_USE_S2 = 2u, F_USE_S2IN = 4u,
                    F_CLAMP_OUT = 64u, F_GENERIC = 128u, F_OUT_DCDT = 256u,
                    F_OUT_LOWER = 512u, F_OUT_CNEW = 1024u, F_SUM_NS = 2048u,
                    F_RELAX_A = 4096u, F_RELAX_B = 8192u, F_HALO = 16384u,
-                   F_MEMBERS = 32768u;
+                   F_MEMBERS = 32768u, F_ZIG = 65536u;
 
 // host mirror of the device-side SmebStageArgs<S> (device_kernels.cuh); the
 // D[3*S] table is the tail.
@@ -424,6 +424,7 @@ private:
   // halo exchange inside the tile kernel (all compartments box / TMA tile path):
   // own flag words in device memory, the neighbours' through CUDA IPC
   bool fusedHalo{false};
+  bool zigzag{false}; // SMEB200_ZIGZAG=1: the tile kernels carry the zig-zag order
   // [2 ci + side] counts of boundary-plane tiles arrived from below / above per
   // compartment; [kHaloErrWord] raised by a wait that ran out
   static constexpr int kHaloWords = 16, kHaloErrWord = 15;
@@ -437,7 +438,7 @@ private:
   // template flags of a plan stage's kernels (on-demand variants never carry
   // F_HALO)
   uint32_t stageFlags(const StageDesc &sd) const {
-    return sd.flags() | (fusedHalo ? F_HALO : 0u);
+    return sd.flags() | (fusedHalo ? F_HALO : 0u) | (zigzag ? F_ZIG : 0u);
   }
   cudaStream_t haloStream{nullptr};
   cudaEvent_t stageInputReady{nullptr}, haloPushed{nullptr}, boundaryDone{nullptr};
