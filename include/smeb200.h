@@ -253,6 +253,36 @@ int smeb200_get_lower_order(smeb200_sim *sim, size_t compartment,
  * species; n_out must be 3 * n_primary_species. */
 int smeb200_get_avg_min_max(smeb200_sim *sim, size_t compartment, double *out,
                             size_t n_out);
+/* The same reduction for callers that cannot allocate (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart
+ * in the reference.
+ *
+ * d_state: DEVICE pointer to n_voxels x values_per_voxel doubles, the layout of
+ * smeb200_get_concentrations (the first n_primary_species values of a voxel are
+ * the model species).  d_out: DEVICE pointer to 3 * n_primary_species doubles,
+ * out[3*s .. 3*s+2] = {average, minimum, maximum} as above, written by two
+ * kernels enqueued on `stream` (a cudaStream_t; NULL = the default stream) of
+ * the CURRENT device; the call does not synchronise.  It calls no cudaMalloc,
+ * cudaFree or allocating library routine: the block partials go into one
+ * file-scope device array of SMEB200_NO_ALLOC_SCRATCH_BYTES that every GPU
+ * loading the library holds until the process exits.  All calls on a device
+ * share that array, which keeps the last call's contents (nothing in it has to
+ * start at zero: a call overwrites every slot it later reads); calls that
+ * overlap on the GPU race, so serialise them (one stream, or events).
+ * The first call on a device resolves the array's address
+ * (cudaGetSymbolAddress); with n_voxels = 0 a call does only that, which is the
+ * way to prepare a device before a stream capture begins.
+ * Returns 0, or 1 with a message in err[0 .. err_len) (may be NULL) when a size
+ * exceeds the limits below, a pointer is NULL or a CUDA call fails. */
+#define SMEB200_NO_ALLOC_MAX_SPECIES 16
+#define SMEB200_NO_ALLOC_MAX_VALUES_PER_VOXEL 64
+#define SMEB200_NO_ALLOC_MAX_VOXELS 2147483648ull /* 32-bit voxel indices */
+#define SMEB200_NO_ALLOC_MAX_BLOCKS 2048
+#define SMEB200_NO_ALLOC_SCRATCH_BYTES 786432 /* 2048 blocks x 16 species x 3 x 8 */
+int smeb200_avg_min_max_no_alloc(const double *d_state, uint64_t n_voxels,
+                                 uint32_t values_per_voxel,
+                                 uint32_t n_primary_species, double *d_out,
+                                 void *stream, char *err, size_t err_len);
 /* One species of every (stride[0], stride[1], stride[2]) = (x, y, z)-th voxel of a
  * compartment's current state, gathered on the device and downloaded into a
  * pinned buffer owned by the simulator (valid until the next call on `sim`):
