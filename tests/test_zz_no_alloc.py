@@ -3,6 +3,8 @@ nothing, checked through the C-ABI against smeb200_get_avg_min_max on two calls 
 a row (they share one file-scope scratch array on the device).  Collected last on
 purpose."""
 import ctypes as C
+import os
+import re
 
 import numpy as np
 import pytest
@@ -37,6 +39,18 @@ def test_sizes_beyond_the_maximum_are_rejected():
         assert word in err.value.decode(), err.value
     # the message buffer is optional
     assert fn(None, 10, 4, MAX_SPECIES + 1, None, None, None, 0) == 1
+
+
+def test_source_calls_no_allocating_routine():
+    """the guarantee is structural: outside comments, csrc/no_alloc.cu names no
+    allocator and resolves its scratch array with cudaGetSymbolAddress"""
+    src = open(os.path.join(os.path.dirname(LIB_PATH), "csrc", "no_alloc.cu")).read()
+    code = re.sub(r"//[^\n]*|/\*.*?\*/", "", src, flags=re.S)
+    for word in ("cudaMalloc", "cudaFree", "cudaHostAlloc", "cuMemAlloc", "malloc(",
+                 "new ", "std::vector", "std::string", "cudaMemset", "cudaMemcpy"):
+        assert word not in code, word
+    assert "static __device__ __align__(256) double g_scratch" in code
+    assert "cudaGetSymbolAddress(&p, g_scratch)" in code
 
 
 @pytest.mark.gpu
